@@ -1,0 +1,127 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes binding of oracle/_ref/libspm_ref.so, the
+unmodified reference compiled by oracle/build_ref.py.  Used as the parity
+checker (tests/, smoke()) and as bench.py's reference arm / cpu_baseline.
+Never imported by the product package."""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "_ref", "libspm_ref.so")
+
+_lib = None
+
+
+def available():
+    return os.path.exists(LIB)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB):
+            from . import build_ref
+            build_ref.build()
+        L = ctypes.CDLL(LIB)
+        L.ref_load.restype = ctypes.c_void_p
+        L.ref_load.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+        L.ref_free.argtypes = [ctypes.c_void_p]
+        L.ref_last_error.restype = ctypes.c_char_p
+        L.ref_set_encode_extra_options.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+        L.ref_set_vocabulary.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int]
+        L.ref_piece_size.argtypes = [ctypes.c_void_p]
+        L.ref_piece_type.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.ref_encode_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                       ctypes.c_int64, ctypes.c_int, ctypes.c_void_p,
+                                       ctypes.c_int64, ctypes.c_void_p]
+        L.ref_encode_count.restype = ctypes.c_int64
+        L.ref_encode_count.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                       ctypes.c_int64, ctypes.c_int]
+        L.ref_normalize.restype = ctypes.c_int64
+        L.ref_normalize.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64,
+                                    ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+        if hasattr(L, "ref_train"):
+            L.ref_train.argtypes = [ctypes.c_char_p]
+        _lib = L
+    return _lib
+
+
+class RefProcessor:
+    """The reference SentencePieceProcessor (Load / Encode(ids) batch loop)."""
+
+    def __init__(self, model_bytes):
+        self.L = lib()
+        self.h = self.L.ref_load(model_bytes, len(model_bytes))
+        if not self.h:
+            raise RuntimeError("reference Load failed: %s" % self.L.ref_last_error().decode())
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_free(self.h)
+            self.h = None
+
+    @classmethod
+    def from_file(cls, path):
+        with open(path, "rb") as f:
+            return cls(f.read())
+
+    def set_encode_extra_options(self, opts):
+        rc = self.L.ref_set_encode_extra_options(self.h, opts.encode())
+        if rc:
+            raise ValueError(self.L.ref_last_error().decode())
+
+    def set_vocabulary(self, pieces):
+        if pieces is None:
+            rc = self.L.ref_set_vocabulary(self.h, None, -1)
+        else:
+            buf = b"".join(p.encode() + b"\0" for p in pieces)
+            rc = self.L.ref_set_vocabulary(self.h, buf, len(pieces))
+        if rc:
+            raise ValueError(self.L.ref_last_error().decode())
+
+    def piece_size(self):
+        return self.L.ref_piece_size(self.h)
+
+    def encode_batch(self, text, off, threads=1):
+        """text uint8[], off int64[n+1] -> (ids int32[], id_off int64[n+1])"""
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        n = len(off) - 1
+        id_off = np.zeros(n + 1, dtype=np.int64)
+        # ids capacity bound: one id per byte + bos/eos
+        cap = int(off[-1] - off[0]) + 2 * n + 16
+        ids = np.empty(cap, dtype=np.int32)
+        rc = self.L.ref_encode_batch(self.h, text.ctypes.data, off.ctypes.data, n, threads,
+                                     ids.ctypes.data, cap, id_off.ctypes.data)
+        if rc:
+            raise RuntimeError("reference Encode status %d" % rc)
+        return ids[: id_off[n]].copy(), id_off
+
+    def encode_count(self, text, off, threads=1):
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        return self.L.ref_encode_count(self.h, text.ctypes.data, off.ctypes.data, len(off) - 1,
+                                       threads)
+
+    def encode(self, s):
+        b = s.encode() if isinstance(s, str) else bytes(s)
+        text = np.frombuffer(b, dtype=np.uint8)
+        ids, _ = self.encode_batch(text, np.array([0, len(b)], dtype=np.int64))
+        return ids.tolist()
+
+    def normalize(self, s):
+        b = s.encode() if isinstance(s, str) else bytes(s)
+        cap = 40 * len(b) + 64
+        out = ctypes.create_string_buffer(cap)
+        n2o = np.zeros(cap + 1, dtype=np.int64)
+        n = self.L.ref_normalize(self.h, b, len(b), out, cap, n2o.ctypes.data)
+        if n < 0:
+            raise RuntimeError("ref_normalize failed")
+        return out.raw[:n], n2o[: n + 1].copy() if n else n2o[:0]
+
+
+def train(args):
+    rc = lib().ref_train(args.encode())
+    if rc:
+        raise RuntimeError("reference spm_train failed: %s" % lib().ref_last_error().decode())

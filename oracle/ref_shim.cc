@@ -1,0 +1,218 @@
+// TEST INFRASTRUCTURE ONLY -- not part of the product path.
+//
+// C-ABI shim around the UNMODIFIED reference SentencePieceProcessor, compiled
+// from the sources where they lie under /root/reference (see build_ref.py).
+// The result, oracle/_ref/libspm_ref.so, is the parity checker and the
+// "reference" CPU baseline.  Only tests/, __graft_entry__.smoke() and
+// bench.py's cpu_baseline / --impl reference legs may load it.
+//
+// Reference interfaces wrapped here:
+//   SentencePieceProcessor::LoadFromSerializedProto  src/sentencepiece_processor.h:203
+//   SentencePieceProcessor::Encode(ids)              src/sentencepiece_processor.h:244
+//   SentencePieceProcessor::SetEncodeExtraOptions    src/sentencepiece_processor.h:210
+//   SentencePieceProcessor::SetVocabulary            src/sentencepiece_processor.h:224
+//   normalizer::Normalizer::Normalize                src/normalizer.h
+//   SentencePieceTrainer::Train(args)                src/sentencepiece_trainer.h:59
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "normalizer.h"
+#include "sentencepiece_model.pb.h"
+#include "sentencepiece_processor.h"
+#ifdef REF_WITH_TRAINER
+#include "sentencepiece_trainer.h"
+#include "unigram_model_trainer.h"
+#endif
+
+namespace {
+struct RefHandle {
+  sentencepiece::SentencePieceProcessor sp;
+  std::unique_ptr<sentencepiece::normalizer::Normalizer> norm;
+};
+thread_local std::string g_err;
+}  // namespace
+
+extern "C" {
+
+const char *ref_last_error() { return g_err.c_str(); }
+
+void *ref_load(const void *model, size_t len) {
+  auto *h = new RefHandle;
+  auto st = h->sp.LoadFromSerializedProto(
+      std::string(static_cast<const char *>(model), len));
+  if (!st.ok()) {
+    g_err = st.ToString();
+    delete h;
+    return nullptr;
+  }
+  h->norm.reset(new sentencepiece::normalizer::Normalizer(
+      h->sp.model_proto().normalizer_spec(), h->sp.model_proto().trainer_spec()));
+  return h;
+}
+
+void ref_free(void *p) { delete static_cast<RefHandle *>(p); }
+
+int ref_set_encode_extra_options(void *p, const char *opts) {
+  auto st = static_cast<RefHandle *>(p)->sp.SetEncodeExtraOptions(opts);
+  if (!st.ok()) g_err = st.ToString();
+  return static_cast<int>(st.code());
+}
+
+// pieces: NUL-separated list of n valid pieces; n < 0 => ResetVocabulary.
+int ref_set_vocabulary(void *p, const char *pieces, int n) {
+  auto *h = static_cast<RefHandle *>(p);
+  sentencepiece::util::Status st;
+  if (n < 0) {
+    st = h->sp.ResetVocabulary();
+  } else {
+    std::vector<std::string> v;
+    const char *q = pieces;
+    for (int i = 0; i < n; ++i) {
+      v.emplace_back(q);
+      q += v.back().size() + 1;
+    }
+    st = h->sp.SetVocabulary(v);
+  }
+  if (!st.ok()) g_err = st.ToString();
+  return static_cast<int>(st.code());
+}
+
+int ref_piece_size(void *p) { return static_cast<RefHandle *>(p)->sp.GetPieceSize(); }
+int ref_piece_type(void *p, int id) {
+  return static_cast<RefHandle *>(p)->sp.model_proto().pieces(id).type();
+}
+
+// Batch encode with `threads` std::threads (Encode is const / re-entrant,
+// src/unigram_model.cc:710).  Two-call protocol: ids == nullptr => only
+// id_offsets is filled (sizes); else ids must hold id_offsets[n] entries.
+// Returns 0, or the first non-OK status code.
+int ref_encode_batch(void *p, const char *text, const int64_t *off, int64_t n,
+                     int threads, int32_t *ids, int64_t cap, int64_t *id_off) {
+  auto *h = static_cast<RefHandle *>(p);
+  if (threads < 1) threads = 1;
+  std::vector<std::vector<int>> out(n);
+  std::vector<int> codes(threads, 0);
+  auto work = [&](int t) {
+    const int64_t lo = n * t / threads, hi = n * (t + 1) / threads;
+    for (int64_t i = lo; i < hi; ++i) {
+      auto st = h->sp.Encode(std::string(text + off[i], off[i + 1] - off[i]), &out[i]);
+      if (!st.ok() && codes[t] == 0) codes[t] = static_cast<int>(st.code());
+    }
+  };
+  if (threads == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; ++t) th.emplace_back(work, t);
+    for (auto &x : th) x.join();
+  }
+  id_off[0] = 0;
+  for (int64_t i = 0; i < n; ++i) id_off[i + 1] = id_off[i] + (int64_t)out[i].size();
+  if (ids != nullptr) {
+    if (id_off[n] > cap) return 8;  // RESOURCE_EXHAUSTED
+    for (int64_t i = 0; i < n; ++i)
+      if (!out[i].empty())
+        std::memcpy(ids + id_off[i], out[i].data(), out[i].size() * sizeof(int));
+  }
+  for (int c : codes)
+    if (c) return c;
+  return 0;
+}
+
+// Timed variant for the CPU baseline: encodes and discards, returns total ids.
+int64_t ref_encode_count(void *p, const char *text, const int64_t *off, int64_t n,
+                         int threads) {
+  auto *h = static_cast<RefHandle *>(p);
+  if (threads < 1) threads = 1;
+  std::vector<int64_t> tot(threads, 0);
+  auto work = [&](int t) {
+    const int64_t lo = n * t / threads, hi = n * (t + 1) / threads;
+    std::vector<int> ids;
+    for (int64_t i = lo; i < hi; ++i) {
+      h->sp.Encode(std::string(text + off[i], off[i + 1] - off[i]), &ids).IgnoreError();
+      tot[t] += (int64_t)ids.size();
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 0; t < threads; ++t) th.emplace_back(work, t);
+  for (auto &x : th) x.join();
+  int64_t s = 0;
+  for (auto v : tot) s += v;
+  return s;
+}
+
+// Normalizer only.  out must hold cap bytes; n2o (may be null) cap+1 entries.
+// Returns the normalized length, or -1 when cap is too small.
+int64_t ref_normalize(void *p, const char *text, int64_t len, char *out, int64_t cap,
+                      int64_t *n2o) {
+  auto *h = static_cast<RefHandle *>(p);
+  std::string norm;
+  std::vector<size_t> map;
+  h->norm->SetPrefixMatcher(nullptr);
+  auto st = h->norm->Normalize(std::string(text, len), &norm, &map);
+  if (!st.ok()) {
+    g_err = st.ToString();
+    return -2;
+  }
+  if ((int64_t)norm.size() > cap) return -1;
+  std::memcpy(out, norm.data(), norm.size());
+  if (n2o)
+    for (size_t i = 0; i < map.size(); ++i) n2o[i] = (int64_t)map[i];
+  return (int64_t)norm.size();
+}
+
+#ifdef REF_WITH_TRAINER
+int ref_train(const char *args) {
+  auto st = sentencepiece::SentencePieceTrainer::Train(args);
+  if (!st.ok()) g_err = st.ToString();
+  return static_cast<int>(st.code());
+}
+
+// Unigram E-step over (word, freq) with the reference TrainerModel
+// (src/unigram_model_trainer.cc:237-287, single thread, stride order).
+// pieces: NUL-separated; scores[V].  words: NUL-separated normalized words.
+// Outputs expected[V] (float, reference accumulation order), logz[n] (per
+// word Z, float), obj, ntokens.
+int ref_estep(const char *pieces, const float *scores, int V, const char *words,
+              const int64_t *freq, int64_t n, float *expected, float *logz,
+              double *obj, int64_t *ntokens) {
+  using namespace sentencepiece;
+  TrainerSpec ts;
+  NormalizerSpec ns;
+  unigram::TrainerModel model(ts, ns);
+  unigram::TrainerModel::SentencePieces sps;
+  const char *q = pieces;
+  for (int i = 0; i < V; ++i) {
+    sps.emplace_back(std::string(q), scores[i]);
+    q += sps.back().first.size() + 1;
+  }
+  model.SetSentencePieces(std::move(sps));
+  std::vector<float> exp(V, 0.0f);
+  int64_t all_freq = 0;
+  for (int64_t i = 0; i < n; ++i) all_freq += freq[i];
+  float o = 0.0f;
+  int64_t nt = 0;
+  unigram::Lattice lattice;
+  const char *w = words;
+  for (int64_t i = 0; i < n; ++i) {
+    const size_t wl = std::strlen(w);
+    lattice.SetSentence(absl::string_view(w, wl));
+    model.PopulateNodes(&lattice);
+    const float Z = lattice.PopulateMarginal(freq[i], &exp);
+    nt += lattice.Viterbi().size();
+    if (logz) logz[i] = Z;
+    o -= Z / all_freq;
+    w += wl + 1;
+  }
+  std::memcpy(expected, exp.data(), V * sizeof(float));
+  *obj = o;
+  *ntokens = nt;
+  return 0;
+}
+#endif
+
+}  // extern "C"
