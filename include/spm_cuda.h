@@ -1,0 +1,95 @@
+/* spm_cuda.h -- C ABI of the B200 batch encoder for SentencePiece models.
+ *
+ * This is the drop-in boundary for the reference's encode path.  The reference
+ * (SentencePiece 0.1.82) has no C ABI or batch entry point of its own; each
+ * function below names the C++ interface it stands in for, so that a
+ * `sentencepiece::SentencePieceProcessor`-shaped facade (see
+ * sentencepiece-comments_b200/csrc/spm_processor.h and INTEGRATION.md) can be
+ * built on top with unchanged signatures.
+ *
+ * Error convention: every int-returning function returns a
+ * sentencepiece::util::error::Code value (src/sentencepiece_processor.h:101-119;
+ * 0 = OK).  spm_cuda_last_error() returns the thread-local message of the
+ * last failure.  Nothing aborts the process.
+ *
+ * There is no CPU fallback: all calls fail with UNAVAILABLE-style INTERNAL
+ * errors when no CUDA device is usable.
+ */
+#ifndef SPM_CUDA_H_
+#define SPM_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct spm_cuda_model spm_cuda_model;
+
+/* memory_space values */
+#define SPM_CUDA_HOST 0   /* text, offsets, ids, id_offsets are host pointers   */
+#define SPM_CUDA_DEVICE 1 /* ... are device pointers on the model's device      */
+
+/* Extra options (SetEncodeExtraOptions "bos:eos:reverse",
+ * src/sentencepiece_processor.cc:945-1023) are a list applied in order; they
+ * are packed two bits per entry, first entry in the low bits, 0 terminates. */
+#define SPM_CUDA_OPT_BOS 1u
+#define SPM_CUDA_OPT_EOS 2u
+#define SPM_CUDA_OPT_REVERSE 3u
+
+/* Replaces SentencePieceProcessor::LoadFromSerializedProto
+ * (src/sentencepiece_processor.h:203, .cc:103-157): parses an unmodified
+ * serialized ModelProto, builds the piece trie / charsmap tables and uploads
+ * them to `device`.  UNIGRAM and BPE models only (WORD/CHAR: UNIMPLEMENTED). */
+int spm_cuda_model_load(const void *serialized_model, size_t len, int device, spm_cuda_model **out);
+
+void spm_cuda_model_free(spm_cuda_model *model);
+
+/* Replaces the effect of SetVocabulary / ResetVocabulary
+ * (src/sentencepiece_processor.h:224-228, .cc:203-231): overwrite the piece
+ * types (ModelProto::SentencePiece::Type values, one byte per piece).  Must
+ * not run concurrently with encode calls on the same model. */
+int spm_cuda_model_set_piece_types(spm_cuda_model *model, const uint8_t *types, int n);
+
+/* Replaces a loop of SentencePieceProcessor::Encode(input, std::vector<int>*)
+ * (src/sentencepiece_processor.h:244, .cc:319-330) over n sentences.
+ *   text, text_offsets[n+1] : sentence i is text[text_offsets[i], text_offsets[i+1])
+ *   extra_options           : packed option list (see above)
+ *   ids[ids_capacity]       : output ids, CSR values
+ *   id_offsets[n+1]         : output CSR offsets; id_offsets[n] = total ids
+ * Returns RESOURCE_EXHAUSTED (8) when ids_capacity is too small (id_offsets is
+ * still complete, so id_offsets[n] is the capacity to retry with), INTERNAL
+ * (13) if some sentence hit the reference's "all normalized characters are not
+ * consumed" error (that sentence gets zero ids, as the reference returns).
+ * cuda_stream is a cudaStream_t (NULL = default stream); the call returns
+ * after the stream work for it has completed. */
+int spm_cuda_encode_batch(const spm_cuda_model *model, const char *text, const int64_t *text_offsets,
+                          int64_t n, uint32_t extra_options, int32_t *ids, int64_t ids_capacity,
+                          int64_t *id_offsets, int memory_space, void *cuda_stream);
+
+/* Model introspection (SentencePieceProcessor::GetPieceSize / IdToPiece /
+ * GetScore / PieceToId / unk_id ..., src/sentencepiece_processor.h:397-432). */
+int spm_cuda_model_piece_size(const spm_cuda_model *model);
+const char *spm_cuda_model_piece(const spm_cuda_model *model, int id, int *len);
+float spm_cuda_model_score(const spm_cuda_model *model, int id);
+int spm_cuda_model_piece_type(const spm_cuda_model *model, int id);
+int spm_cuda_model_piece_to_id(const spm_cuda_model *model, const char *piece, size_t len);
+int spm_cuda_model_type(const spm_cuda_model *model);  /* TrainerSpec::ModelType */
+int spm_cuda_model_unk_id(const spm_cuda_model *model);
+int spm_cuda_model_bos_id(const spm_cuda_model *model);
+int spm_cuda_model_eos_id(const spm_cuda_model *model);
+int spm_cuda_model_pad_id(const spm_cuda_model *model);
+
+/* Statistics of the last encode call on this model (for bench.py / profiling):
+ * stats[0] kernel launches, [1] sentences sent to the exact fallback tier,
+ * [2] device-side milliseconds between first and last launch (CUDA events on
+ * the caller's stream), [3] bytes of workspace currently allocated. */
+int spm_cuda_last_stats(const spm_cuda_model *model, double *stats, int n);
+
+const char *spm_cuda_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPM_CUDA_H_ */

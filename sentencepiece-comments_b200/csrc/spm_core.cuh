@@ -1,0 +1,614 @@
+// spm_core.cuh -- per-sentence algorithms of the B200 batch encoder.
+//
+// Everything here is `__host__ __device__` so that the very same arithmetic
+// that runs inside the CUDA kernels (spm_kernels.cu) can be compiled for the
+// host by the *test suite* (tests/host_core.cc) and compared with the oracle
+// in the GPU-less build container.  The shipped library never runs these on
+// the host.
+//
+// Reformulations relative to the reference (behaviour is bit-identical):
+//   * piece matching walks our own flat double array ("XDA", built by
+//     spm_model.cc) whose units carry has_leaf/has_child bits and whose leaf
+//     table carries (id, type, score) -- replaces Darts commonPrefixSearch +
+//     pieces(id) lookups (third_party/darts_clone/darts.h:467-513,
+//     src/unigram_model.cc:572-595);
+//   * the unigram lattice is never materialised: nodes are pushed into a ring
+//     of pending end positions as the trie walk finds them and Viterbi is
+//     evaluated on the fly with *pruned candidate lists* that provably select
+//     the same predecessor as the reference's strict-'>' scan over
+//     end_nodes_[pos] (src/unigram_model.cc:222-261); see unigram_encode().
+//   * BPE keeps the reference's agenda semantics (max score, then smallest
+//     left index; lazy invalidation by size; src/bpe_model.cc:55-61,143-169)
+//     on a flat binary heap.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define SPM_HD __host__ __device__ __forceinline__
+#define SPM_HDN __host__ __device__
+#else
+#define SPM_HD inline
+#define SPM_HDN inline
+#endif
+
+#if !defined(__CUDACC__)
+struct uint2 { uint32_t x, y; };
+#endif
+
+namespace spmb {
+
+// piece types (src/sentencepiece_model.proto:243-250)
+enum : uint32_t { T_NORMAL = 1, T_UNKNOWN = 2, T_CONTROL = 3, T_USER_DEFINED = 4, T_UNUSED = 5 };
+enum : int32_t { M_UNIGRAM = 1, M_BPE = 2, M_WORD = 3, M_CHAR = 4 };
+
+// per-sentence status bits written by the kernels
+enum : uint32_t {
+  ST_OK = 0,
+  ST_NORM_OVERFLOW = 1,   // normalized text did not fit the tier's capacity
+  ST_IDS_OVERFLOW = 2,    // ids did not fit the tier's staging capacity
+  ST_CAND_OVERFLOW = 4,   // more near-tied Viterbi candidates than the tier keeps
+  ST_TOO_LONG = 8,        // sentence exceeds the tier's length limit
+  ST_INTERNAL = 16,       // reference would return util::error::INTERNAL
+};
+
+// XDA unit: [7:0] label  [8] has_leaf  [9] has_child  [31:10] base.
+// child(node, c) = base(node) ^ c, valid iff label == c and (leaf|child) != 0.
+// Bases are unique per parent, which makes the label test sufficient.
+struct TrieView {
+  const uint32_t *units;
+  const uint2 *leaf;   // parallel to units: .x = id | type << 28, .y = score bits
+  uint32_t n;
+};
+struct ModelView {
+  TrieView pieces;           // NORMAL / USER_DEFINED / UNUSED and reserved pieces
+  TrieView user;             // user-defined symbols (n == 0: none)
+  const uint32_t *cm_units;  // charsmap darts units (model data, uploaded verbatim)
+  const uint8_t *cm_pool;    // NUL-delimited replacement strings
+  const uint32_t *cm_first2; // 65536-bit filter: can a rule start with (b0,b1)?
+  uint32_t cm_n;             // 0: identity normalization
+  uint32_t user_first[8];    // 256-bit filter on the first byte of user symbols
+  int32_t model_type;
+  int32_t unk_id;
+  float unk_score;           // min_score_ - kUnkPenalty (unigram_model.cc:550-551)
+  float max_score;           // max(FLT_MIN, max NORMAL score) (unigram_model.cc:683-689)
+  float smax;                // bound on |score| of any lattice node (for pruning)
+  int32_t ring;              // power of two >= max piece bytes + 5
+  uint8_t add_dummy_prefix, remove_extra_ws, escape_ws, ws_suffix;
+  uint8_t has_unused;        // any UNUSED piece (BPE resegmentation needed)
+  uint8_t pad_[3];
+};
+
+#if defined(__CUDA_ARCH__)
+SPM_HD float __uint_as_float_hd(uint32_t x) { return __uint_as_float(x); }
+#else
+SPM_HD float __uint_as_float_hd(uint32_t x) { union { uint32_t u; float f; } v; v.u = x; return v.f; }
+#endif
+
+// ------------------------------------------------------------------ UTF-8
+// src/util.h:389-391
+SPM_HD int one_char_len(uint8_t b) { return (int)((0x4322111111111111ull >> ((b >> 4) * 4)) & 0xF); }
+SPM_HD bool is_trail(uint8_t x) { return (int8_t)x < -0x40; }  // src/util.h:401
+SPM_HD bool is_valid_cp(uint32_t c) { return c < 0xD800u || (c >= 0xE000u && c <= 0x10FFFFu); }
+
+// src/util.cc:187-221 + src/util.h:459-462: returns true and *mblen when the
+// prefix is one valid char (a literal U+FFFD counts as valid); else *mblen = 1.
+SPM_HD bool valid_decode_utf8(const uint8_t *b, int64_t len, int *mblen) {
+  const uint32_t b0 = b[0];
+  if (b0 < 0x80) { *mblen = 1; return true; }
+  if (len >= 2 && (b0 & 0xE0) == 0xC0) {
+    const uint32_t cp = ((b0 & 0x1F) << 6) | (b[1] & 0x3F);
+    if (is_trail(b[1]) && cp >= 0x80 && is_valid_cp(cp)) { *mblen = 2; return true; }
+  } else if (len >= 3 && (b0 & 0xF0) == 0xE0) {
+    const uint32_t cp = ((b0 & 0x0F) << 12) | ((uint32_t)(b[1] & 0x3F) << 6) | (b[2] & 0x3F);
+    if (is_trail(b[1]) && is_trail(b[2]) && cp >= 0x800 && is_valid_cp(cp)) { *mblen = 3; return true; }
+  } else if (len >= 4 && (b0 & 0xF8) == 0xF0) {
+    const uint32_t cp = ((b0 & 0x07) << 18) | ((uint32_t)(b[1] & 0x3F) << 12) |
+                        ((uint32_t)(b[2] & 0x3F) << 6) | (b[3] & 0x3F);
+    if (is_trail(b[1]) && is_trail(b[2]) && is_trail(b[3]) && cp >= 0x10000 && is_valid_cp(cp)) {
+      *mblen = 4; return true;
+    }
+  }
+  *mblen = 1;
+  return false;
+}
+
+// ------------------------------------------------------------------ tries
+#if defined(__CUDA_ARCH__)
+#define SPM_LDG(p) __ldg(p)
+#else
+#define SPM_LDG(p) (*(p))
+#endif
+
+SPM_HD bool xda_valid(uint32_t u, uint32_t c) { return (u & 0xFF) == c && (u & 0x300) != 0; }
+
+// Longest key of `t` that is a prefix of s[0..n): 0 when none.
+SPM_HD int xda_longest_prefix(const TrieView &t, const uint8_t *s, int64_t n) {
+  uint32_t u = SPM_LDG(t.units);
+  int best = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    if (!(u & 0x200)) break;
+    const uint32_t c = s[i];
+    const uint32_t child = (u >> 10) ^ c;
+    u = SPM_LDG(t.units + child);
+    if (!xda_valid(u, c)) break;
+    if (u & 0x100) best = (int)i + 1;
+  }
+  return best;
+}
+
+// Exact match of s[0..n): leaf word (.x id|type<<28, .y score) or .x = ~0u.
+SPM_HD uint2 xda_exact(const TrieView &t, const uint8_t *s, int64_t n) {
+  uint32_t u = SPM_LDG(t.units);
+  uint32_t pos = 0;
+  uint2 miss; miss.x = 0xFFFFFFFFu; miss.y = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    if (!(u & 0x200)) return miss;
+    const uint32_t c = s[i];
+    pos = (u >> 10) ^ c;
+    u = SPM_LDG(t.units + pos);
+    if (!xda_valid(u, c)) return miss;
+  }
+  if (n == 0 || !(u & 0x100)) return miss;
+  return SPM_LDG(t.leaf + pos);
+}
+
+// darts-clone unit (data format of the model's precompiled charsmap;
+// third_party/darts_clone/darts.h:50-80)
+SPM_HD uint32_t du_offset(uint32_t u) { return (u >> 10) << ((u & (1u << 9)) >> 6); }
+SPM_HD uint32_t du_label(uint32_t u) { return u & ((1u << 31) | 0xFF); }
+
+// Longest charsmap key that prefixes s[0..n): returns its length (0: none) and
+// the pool offset of its replacement (src/normalizer.cc:258-268: the longest
+// result wins; results are unique per length).
+SPM_HD int charsmap_longest(const ModelView &m, const uint8_t *s, int64_t n, uint32_t *value) {
+  const uint32_t *a = m.cm_units;
+  uint32_t pos = 0;
+  uint32_t u = SPM_LDG(a);
+  pos ^= du_offset(u);
+  int best = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const uint32_t c = s[i];
+    pos ^= c;
+    if (pos >= m.cm_n) break;  // malformed blob guard
+    u = SPM_LDG(a + pos);
+    if (du_label(u) != c) break;
+    pos ^= du_offset(u);
+    if ((u >> 8) & 1) {
+      if (pos >= m.cm_n) break;
+      best = (int)i + 1;
+      *value = SPM_LDG(a + pos) & 0x7FFFFFFFu;
+    }
+  }
+  return best;
+}
+
+// normalizer.cc:362-384 restricted to what callers use: longest user-defined
+// symbol prefixing s (0: none).
+SPM_HD int user_prefix_match(const ModelView &m, const uint8_t *s, int64_t n) {
+  if (m.user.n == 0) return 0;
+  const uint32_t b0 = s[0];
+  if (!((m.user_first[b0 >> 5] >> (b0 & 31)) & 1)) return 0;
+  return xda_longest_prefix(m.user, s, n);
+}
+
+// ------------------------------------------------------------------ normalizer
+// One leftmost-longest step (src/normalizer.cc:231-300).  Returns the number of
+// input bytes consumed; the replacement is [*rep, *rep + *rep_len).
+SPM_HD int normalize_prefix(const ModelView &m, const uint8_t *in, int64_t n, const uint8_t **rep,
+                            int *rep_len) {
+  const int ul = user_prefix_match(m, in, n);
+  if (ul > 0) { *rep = in; *rep_len = ul; return ul; }  // raw bytes, un-normalised (:239-243)
+  if (m.cm_n != 0) {
+    const uint32_t b0 = in[0];
+    // filter: bit (b0,b1) set iff some rule is b0 alone or starts with b0 b1
+    const uint32_t key = (b0 << 8) | (n >= 2 ? (uint32_t)in[1] : 0u);
+    bool maybe = true;
+    if (m.cm_first2 != nullptr && n >= 2) maybe = (SPM_LDG(m.cm_first2 + (key >> 5)) >> (key & 31)) & 1;
+    if (maybe) {
+      uint32_t value = 0;
+      const int l = charsmap_longest(m, in, n, &value);
+      if (l > 0) {
+        const uint8_t *r = m.cm_pool + value;
+        int rl = 0;
+        while (SPM_LDG(r + rl) != 0) ++rl;  // NUL-terminated (:293-296)
+        *rep = r; *rep_len = rl;
+        return l;
+      }
+    }
+  }
+  int mblen = 1;
+  if (!valid_decode_utf8(in, n, &mblen)) { *rep = nullptr; *rep_len = 3; return 1; }  // U+FFFD, 1 byte
+  *rep = in; *rep_len = mblen;
+  return mblen;
+}
+
+// Whole-sentence normalisation (src/normalizer.cc:88-211) into out[0..cap).
+// Returns the normalized length, or -1 when it does not fit (tier overflow).
+// norm_to_orig is not produced (ids do not need it).
+SPM_HDN int32_t normalize_sentence(const ModelView &m, const uint8_t *in, int64_t n, uint8_t *out,
+                                   int64_t cap) {
+  if (n == 0) return 0;
+  const uint8_t *rep; int rl;
+  if (m.remove_extra_ws) {  // strip leading spaces (:103-112)
+    while (n > 0) {
+      const int c = normalize_prefix(m, in, n, &rep, &rl);
+      if (!(rl == 1 && rep != nullptr && rep[0] == ' ')) break;
+      in += c; n -= c;
+    }
+  }
+  if (n == 0) return 0;
+  int64_t o = 0;
+  const bool esc = m.escape_ws;
+  if (!m.ws_suffix && m.add_dummy_prefix) {  // add_ws (:132-153)
+    if (esc) { if (o + 3 > cap) return -1; out[o] = 0xE2; out[o + 1] = 0x96; out[o + 2] = 0x81; o += 3; }
+    else { if (o + 1 > cap) return -1; out[o++] = ' '; }
+  }
+  bool is_prev_space = m.remove_extra_ws;
+  while (n > 0) {
+    const int c = normalize_prefix(m, in, n, &rep, &rl);
+    if (rep == nullptr) {  // malformed byte -> U+FFFD
+      if (o + 3 > cap) return -1;
+      out[o] = 0xEF; out[o + 1] = 0xBF; out[o + 2] = 0xBD; o += 3;
+      is_prev_space = false;
+    } else {
+      int k = 0;
+      while (is_prev_space && k < rl && rep[k] == ' ') ++k;  // ConsumePrefix(" ") loop
+      if (k < rl) {
+        for (; k < rl; ++k) {
+          const uint8_t b = rep[k];
+          if (esc && b == ' ') {
+            if (o + 3 > cap) return -1;
+            out[o] = 0xE2; out[o + 1] = 0x96; out[o + 2] = 0x81; o += 3;
+          } else {
+            if (o + 1 > cap) return -1;
+            out[o++] = b;
+          }
+        }
+        is_prev_space = rep[rl - 1] == ' ';
+      }
+    }
+    in += c; n -= c;
+    if (!m.remove_extra_ws) is_prev_space = false;
+  }
+  if (m.remove_extra_ws) {  // strip trailing whitespace symbols (:191-201)
+    if (esc) { while (o >= 3 && out[o - 3] == 0xE2 && out[o - 2] == 0x96 && out[o - 1] == 0x81) o -= 3; }
+    else { while (o >= 1 && out[o - 1] == ' ') o -= 1; }
+  }
+  if (m.ws_suffix && m.add_dummy_prefix) {
+    if (esc) { if (o + 3 > cap) return -1; out[o] = 0xE2; out[o + 1] = 0x96; out[o + 2] = 0x81; o += 3; }
+    else { if (o + 1 > cap) return -1; out[o++] = ' '; }
+  }
+  return (int32_t)o;
+}
+
+// ------------------------------------------------------------------ unigram
+// Scratch of one sentence for unigram_encode<CAPC>.
+struct UniScratch {
+  float *ringM;        // [ring]          max backtrace score pending at an end position
+  uint32_t *ringCnt;   // [ring]          live candidates at that position
+  float *candBt;       // [ring * CAPC]   candidate backtrace scores, in begin order
+  uint64_t *candRec;   // [ring * CAPC]   id | len << 32 | prev slot << 48
+  uint64_t *back;      // [CAPC][stride]  records of visited positions (slot-major)
+  int64_t stride;      // >= n + 1
+};
+SPM_HD int64_t uni_scratch_words(int ring, int capc, int64_t n) {  // in 4-byte words
+  return (int64_t)ring * 2 + (int64_t)ring * capc * 3 + (int64_t)capc * (n + 1) * 2 + 2;
+}
+
+SPM_HD uint64_t pack_rec(uint32_t id, uint32_t len, uint32_t prevslot) {
+  return (uint64_t)id | ((uint64_t)len << 32) | ((uint64_t)prevslot << 48);
+}
+
+// PopulateNodes + Viterbi + backtrace of one normalized sentence
+// (src/unigram_model.cc:535-604, :222-261, :705-720) followed by the unk-run
+// merge of src/sentencepiece_processor.cc:525-529.
+//
+// Positions are byte offsets of character starts (characters delimited by
+// OneCharLen jumps clamped to the sentence, unigram_model.cc:155-161).  For the
+// position p being expanded, every node (p -> e) the reference would insert is
+// scored immediately: bt = fl(bt_l* + score) with l* chosen exactly as the
+// reference's scan over end_nodes_[p] (ascending begin, strict '>').  Instead
+// of the full end list we keep, per pending end position, only candidates that
+// can still be chosen by SOME right node:
+//   - a candidate whose bt is below the running max M by more than
+//     eps = 2^-20 (max(|M|,|bt|) + smax) loses to M for every right score s,
+//     because fl(x1+s) < fl(x2+s) whenever x2-x1 exceeds two float spacings at
+//     magnitude |x|+|s|;
+//   - a candidate whose bt equals an earlier kept candidate's bt yields the
+//     same sum and loses the first-wins tie.
+// Kept candidates stay in begin order, so the scan over them returns the
+// reference's choice.  More than CAPC near-ties set ST_CAND_OVERFLOW (the
+// caller reruns the sentence with a larger CAPC).
+//
+// Writes ids (forward order) to out[0..cap) and returns their count; when they
+// do not fit, sets ST_IDS_OVERFLOW and still returns the count.
+template <int CAPC>
+SPM_HDN int32_t unigram_encode(const ModelView &m, const uint8_t *s, int32_t n, const UniScratch &sc,
+                               int32_t *out, int32_t cap, uint32_t *status) {
+  if (n <= 0) return 0;
+  const uint32_t mask = (uint32_t)m.ring - 1;
+  for (int i = 0; i < m.ring; ++i) sc.ringCnt[i] = 0;
+  sc.ringCnt[0] = 1; sc.ringM[0] = 0.0f; sc.candBt[0] = 0.0f; sc.candRec[0] = pack_rec(0, 0, 0);  // BOS
+  uint32_t st = 0;
+
+  auto push = [&](int32_t e, float bt, uint32_t id, uint32_t len, uint32_t prevslot) {
+    const uint32_t r = (uint32_t)e & mask;
+    const uint32_t cnt = sc.ringCnt[r];
+    const uint64_t rec = pack_rec(id, len, prevslot);
+    if (cnt == 0) {
+      sc.ringM[r] = bt; sc.candBt[r * CAPC] = bt; sc.candRec[r * CAPC] = rec; sc.ringCnt[r] = 1;
+      return;
+    }
+    const float M = sc.ringM[r];
+    const float am = fabsf(M), ab = fabsf(bt);
+    const float eps = ((am > ab ? am : ab) + m.smax) * 9.5367431640625e-07f;
+    if (bt - M > eps) {
+      sc.ringM[r] = bt; sc.candBt[r * CAPC] = bt; sc.candRec[r * CAPC] = rec; sc.ringCnt[r] = 1;
+    } else if (M - bt > eps) {
+      // can never be selected
+    } else {
+      for (uint32_t k = 0; k < cnt; ++k)
+        if (sc.candBt[r * CAPC + k] == bt) return;  // loses the first-wins tie for every s
+      if (cnt == CAPC) { st |= ST_CAND_OVERFLOW; return; }
+      sc.candBt[r * CAPC + cnt] = bt; sc.candRec[r * CAPC + cnt] = rec; sc.ringCnt[r] = cnt + 1;
+      if (bt > M) sc.ringM[r] = bt;
+    }
+  };
+
+  int32_t p = 0;
+  while (p < n) {
+    const uint32_t r = (uint32_t)p & mask;
+    const uint32_t cnt = sc.ringCnt[r];
+    for (uint32_t k = 0; k < cnt; ++k) sc.back[(int64_t)k * sc.stride + p] = sc.candRec[r * CAPC + k];
+    // best predecessor for a right node of score sr (unigram_model.cc:229-246)
+    auto pick = [&](float sr, uint32_t *slot) {
+      float best = sc.candBt[r * CAPC] + sr;
+      uint32_t bs = 0;
+      for (uint32_t k = 1; k < cnt; ++k) {
+        const float v = sc.candBt[r * CAPC + k] + sr;
+        if (v > best) { best = v; bs = k; }
+      }
+      *slot = bs;
+      return best;
+    };
+    int cl = one_char_len(s[p]);
+    if (cl > n - p) cl = n - p;
+    int32_t nb = p + cl;   // end of the character that contains the byte being walked
+    int nchars = 1;
+    bool has_single = false;
+    uint32_t u = SPM_LDG(m.pieces.units);
+    for (int32_t i = p; i < n; ++i) {
+      if (!(u & 0x200)) break;
+      const uint32_t c = s[i];
+      const uint32_t child = (u >> 10) ^ c;
+      u = SPM_LDG(m.pieces.units + child);
+      if (!xda_valid(u, c)) break;
+      if (i == nb) {  // byte i starts the next character
+        int l2 = one_char_len((uint8_t)c);
+        if (l2 > n - i) l2 = n - i;
+        nb = i + l2;
+        ++nchars;
+      }
+      if (u & 0x100) {
+        const uint2 lf = SPM_LDG(m.pieces.leaf + child);
+        const uint32_t type = lf.x >> 28;
+        if (type == T_NORMAL || type == T_USER_DEFINED) {  // UNUSED skipped (:586); reserved not in trie_
+          // user-defined bonus: float product, double add, float store (:590-591)
+          const float sr = type == T_USER_DEFINED ? (float)((double)((float)nchars * m.max_score) + 1.0)
+                                                  : __uint_as_float_hd(lf.y);
+          uint32_t slot;
+          const float bt = pick(sr, &slot);
+          push(nb, bt, lf.x & 0x0FFFFFFFu, (uint32_t)(nb - p), slot);
+          if (nchars == 1) has_single = true;
+        }
+      }
+    }
+    if (!has_single) {  // UNK node of one character (:598-602)
+      uint32_t slot;
+      const float bt = pick(m.unk_score, &slot);
+      push(p + cl, bt, (uint32_t)m.unk_id, (uint32_t)cl, slot);
+    }
+    sc.ringCnt[r] = 0;
+    p += cl;
+  }
+  // EOS (score 0) picks among the candidates ending at n
+  const uint32_t r = (uint32_t)n & mask;
+  const uint32_t cnt = sc.ringCnt[r];
+  for (uint32_t k = 0; k < cnt; ++k) sc.back[(int64_t)k * sc.stride + n] = sc.candRec[r * CAPC + k];
+  uint32_t eos_slot = 0;
+  {
+    float best = sc.candBt[r * CAPC] + 0.0f;
+    for (uint32_t k = 1; k < cnt; ++k) {
+      const float v = sc.candBt[r * CAPC + k] + 0.0f;
+      if (v > best) { best = v; eos_slot = k; }
+    }
+  }
+  // backtrace twice: count (with unk-run merge), then write from the back
+  int32_t total = 0;
+  for (int pass = 0; pass < 2; ++pass) {
+    int32_t pos = n, idx = total;
+    uint32_t slot = eos_slot;
+    int64_t pending = -1;
+    while (pos > 0) {
+      const uint64_t rec = sc.back[(int64_t)slot * sc.stride + pos];
+      const int32_t id = (int32_t)(uint32_t)rec;
+      if (pending >= 0 && !(id == m.unk_id && (int32_t)pending == m.unk_id)) {
+        if (pass == 0) ++total; else out[--idx] = (int32_t)pending;
+      }
+      pending = id;
+      pos -= (int32_t)((rec >> 32) & 0xFFFF);
+      slot = (uint32_t)(rec >> 48) & 0xFF;
+    }
+    if (pending >= 0) { if (pass == 0) ++total; else out[--idx] = (int32_t)pending; }
+    if (pass == 0 && total > cap) { st |= ST_IDS_OVERFLOW; break; }
+  }
+  *status |= st;
+  return total;
+}
+
+// ------------------------------------------------------------------ BPE
+// Scratch of one sentence for bpe_encode (4-byte words): symbols (5 ns), agenda
+// heap (4 cap), UNUSED-merge log (3 cap), with ns <= n symbols and cap = 3 ns + 4.
+SPM_HD int64_t bpe_scratch_words(int64_t n) { return 5 * n + 7 * (3 * n + 4) + 2; }
+
+// src/bpe_model.cc:37-199 followed by the post-processing of
+// src/sentencepiece_processor.cc:488-551 (unk-run merge; a CONTROL id leaves
+// normalized bytes unconsumed => INTERNAL error, no ids).
+// Returns the id count (ids forward in out), or -1 for the INTERNAL case.
+SPM_HDN int32_t bpe_encode(const ModelView &m, const uint8_t *s, int32_t n, int32_t *w, int32_t *out,
+                           int32_t cap, uint32_t *status) {
+  if (n <= 0) return 0;
+  int32_t *begin = w, *size = w + n, *prev = w + 2 * n, *next = w + 3 * n, *freeze = w + 4 * n;
+  const int32_t hcap = 3 * n + 4;
+  float *hscore = (float *)(w + 5 * n);
+  int32_t *hleft = w + 5 * n + hcap, *hright = hleft + hcap, *hsize = hright + hcap;
+  int32_t *lbegin = hsize + hcap, *lsize = lbegin + hcap, *lleft = lsize + hcap;
+  int32_t hn = 0, ln = 0, ns = 0;
+
+  // split into symbols: one char each, or one frozen user-defined symbol (:121-131)
+  for (int32_t p = 0; p < n;) {
+    int mb = user_prefix_match(m, s + p, n - p);
+    const int fr = mb > 0;
+    if (!fr) { mb = one_char_len(s[p]); if (mb > n - p) mb = n - p; }
+    begin[ns] = p; size[ns] = mb; prev[ns] = ns - 1; next[ns] = ns + 1; freeze[ns] = fr;
+    ++ns; p += mb;
+  }
+  next[ns - 1] = -1;
+
+  // agenda order (:55-61): larger score first, then smaller left index
+  auto before = [&](int a, int b) {
+    return hscore[a] > hscore[b] || (hscore[a] == hscore[b] && hleft[a] < hleft[b]);
+  };
+  auto hswap = [&](int a, int b) {
+    float fs = hscore[a]; hscore[a] = hscore[b]; hscore[b] = fs;
+    int32_t t = hleft[a]; hleft[a] = hleft[b]; hleft[b] = t;
+    t = hright[a]; hright[a] = hright[b]; hright[b] = t;
+    t = hsize[a]; hsize[a] = hsize[b]; hsize[b] = t;
+  };
+  // MaybeAddNewSymbolPair (:94-118)
+  auto maybe_add = [&](int32_t l, int32_t r) {
+    if (l < 0 || r < 0 || freeze[l] || freeze[r]) return;
+    const int32_t sz = size[l] + size[r];
+    const uint2 lf = xda_exact(m.pieces, s + begin[l], sz);
+    if (lf.x == 0xFFFFFFFFu) return;
+    const uint32_t type = lf.x >> 28;
+    if (!(type == T_NORMAL || type == T_USER_DEFINED || type == T_UNUSED)) return;  // pieces_ only
+    if (hn >= hcap) { *status |= ST_INTERNAL; return; }
+    int i = hn++;
+    hscore[i] = __uint_as_float_hd(lf.y); hleft[i] = l; hright[i] = r; hsize[i] = sz;
+    while (i > 0) {
+      const int par = (i - 1) >> 1;
+      if (!before(i, par)) break;
+      hswap(i, par); i = par;
+    }
+    if (type == T_UNUSED && ln < hcap) { lbegin[ln] = begin[l]; lsize[ln] = sz; lleft[ln] = size[l]; ++ln; }
+  };
+  for (int32_t i = 1; i < ns; ++i) maybe_add(i - 1, i);
+  while (hn > 0) {  // main loop (:143-169)
+    const int32_t l = hleft[0], r = hright[0], sz = hsize[0];
+    --hn;
+    if (hn > 0) {
+      hswap(0, hn);
+      int i = 0;
+      for (;;) {
+        int a = 2 * i + 1, b = a + 1, best = i;
+        if (a < hn && before(a, best)) best = a;
+        if (b < hn && before(b, best)) best = b;
+        if (best == i) break;
+        hswap(i, best); i = best;
+      }
+    }
+    if (size[l] == 0 || size[r] == 0 || size[l] + size[r] != sz) continue;  // stale (:148-152)
+    size[l] = sz;
+    next[l] = next[r];
+    if (next[r] >= 0) prev[next[r]] = l;
+    size[r] = 0;
+    maybe_add(prev[l], l);
+    maybe_add(l, next[l]);
+  }
+
+  // emit: PieceToId (model_interface.cc:87-97), UNUSED pieces split back through
+  // the last-recorded merge of the same string (rev_merge, :171-189)
+  int32_t total = 0;
+  bool is_prev_unk = false, control_seen = false;
+  auto emit = [&](int32_t id, uint32_t type) {
+    const bool is_unk = type == T_UNKNOWN;
+    if (type == T_CONTROL) {
+      control_seen = true;
+    } else if (!(is_prev_unk && is_unk)) {
+      if (total < cap) out[total] = id;
+      ++total;
+    }
+    is_prev_unk = is_unk;
+  };
+  int32_t *stb = (int32_t *)hscore, *sts = hleft;  // explicit stack reuses the (now empty) agenda
+  for (int32_t k = 0; k != -1; k = next[k]) {
+    int sp = 0;
+    stb[0] = begin[k]; sts[0] = size[k]; sp = 1;
+    while (sp > 0) {
+      --sp;
+      const int32_t b = stb[sp], z = sts[sp];
+      const uint2 lf = xda_exact(m.pieces, s + b, z);
+      int32_t id = m.unk_id;
+      uint32_t type = T_UNKNOWN;
+      if (lf.x != 0xFFFFFFFFu) { id = (int32_t)(lf.x & 0x0FFFFFFFu); type = lf.x >> 28; }
+      int32_t split = -1;
+      if (type == T_UNUSED) {
+        for (int32_t j = ln - 1; j >= 0 && split < 0; --j) {
+          if (lsize[j] != z) continue;
+          bool eq = true;
+          for (int32_t q = 0; q < z && eq; ++q) eq = s[lbegin[j] + q] == s[b + q];
+          if (eq) split = lleft[j];
+        }
+      }
+      if (split < 0) { emit(id, type); continue; }
+      if (sp + 2 > hcap) { *status |= ST_INTERNAL; break; }
+      stb[sp] = b + split; sts[sp] = z - split; ++sp;   // right first, left on top
+      stb[sp] = b; sts[sp] = split; ++sp;
+    }
+  }
+  if (control_seen) { *status |= ST_INTERNAL; return -1; }
+  if (total > cap) *status |= ST_IDS_OVERFLOW;
+  return total;
+}
+
+
+// ------------------------------------------------------------------ extra options
+// ApplyExtraOptions (src/sentencepiece_processor.cc:945-979) folded into one
+// layout: final = pre[0..npre) ++ (flip ? reversed(core) : core) ++ suf[0..nsuf).
+struct ExtraPlan {
+  int32_t npre, nsuf, flip;
+  int32_t pre[16], suf[16];
+};
+SPM_HD ExtraPlan make_extra_plan(uint32_t opts, int32_t bos_id, int32_t eos_id) {
+  ExtraPlan p;
+  p.npre = p.nsuf = p.flip = 0;
+  for (uint32_t o = opts; o & 3u; o >>= 2) {
+    const uint32_t c = o & 3u;
+    if (c == 1u) {  // bos: insert at the front
+      for (int i = p.npre; i > 0; --i) p.pre[i] = p.pre[i - 1];
+      p.pre[0] = bos_id; ++p.npre;
+    } else if (c == 2u) {  // eos: append
+      p.suf[p.nsuf++] = eos_id;
+    } else {  // reverse the whole sequence
+      ExtraPlan q;
+      q.npre = p.nsuf; q.nsuf = p.npre; q.flip = p.flip ^ 1;
+      for (int i = 0; i < p.nsuf; ++i) q.pre[i] = p.suf[p.nsuf - 1 - i];
+      for (int i = 0; i < p.npre; ++i) q.suf[i] = p.pre[p.npre - 1 - i];
+      p = q;
+    }
+  }
+  return p;
+}
+// number of final ids of a sentence whose model output has `core` ids
+// (core < 0: the reference returned an error and no ids at all)
+SPM_HD int32_t final_count(const ExtraPlan &p, int32_t core) { return core < 0 ? 0 : core + p.npre + p.nsuf; }
+SPM_HD int32_t final_id_at(const ExtraPlan &p, const int32_t *core_ids, int32_t core, int32_t j) {
+  if (j < p.npre) return p.pre[j];
+  j -= p.npre;
+  if (j < core) return core_ids[p.flip ? core - 1 - j : j];
+  return p.suf[j - core];
+}
+
+}  // namespace spmb

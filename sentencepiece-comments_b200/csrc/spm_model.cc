@@ -1,0 +1,341 @@
+#include "spm_model.h"
+
+#include <float.h>
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+#include <queue>
+
+namespace spmb {
+namespace {
+
+// ------------------------------------------------------------ proto2 wire reader
+struct Reader {
+  const uint8_t *p, *e;
+  bool ok;
+  Reader(const void *d, size_t n) : p((const uint8_t *)d), e((const uint8_t *)d + n), ok(true) {}
+  bool more() const { return ok && p < e; }
+  uint64_t varint() {
+    uint64_t v = 0;
+    for (int sh = 0; sh < 70 && p < e; sh += 7) {
+      const uint8_t b = *p++;
+      if (sh < 64) v |= (uint64_t)(b & 0x7F) << sh;
+      if (!(b & 0x80)) return v;
+    }
+    ok = false;
+    return 0;
+  }
+  struct Field { int num, wt; uint64_t v; const uint8_t *s; size_t n; };
+  Field next() {
+    Field f = {0, 0, 0, nullptr, 0};
+    const uint64_t key = varint();
+    if (!ok) return f;
+    f.num = (int)(key >> 3);
+    f.wt = (int)(key & 7);
+    if (f.wt == 0) {
+      f.v = varint();
+    } else if (f.wt == 1) {
+      if (e - p < 8) { ok = false; return f; }
+      memcpy(&f.v, p, 8); p += 8;
+    } else if (f.wt == 5) {
+      if (e - p < 4) { ok = false; return f; }
+      uint32_t x; memcpy(&x, p, 4); f.v = x; p += 4;
+    } else if (f.wt == 2) {
+      const uint64_t l = varint();
+      if (!ok || (uint64_t)(e - p) < l) { ok = false; return f; }
+      f.s = p; f.n = (size_t)l; p += l;
+    } else {
+      ok = false;  // groups are not used by sentencepiece_model.proto
+    }
+    return f;
+  }
+};
+
+bool parse_proto(const void *data, size_t len, HostModel *m) {
+  Reader r(data, len);
+  while (r.more()) {
+    const Reader::Field f = r.next();
+    if (!r.ok) return false;
+    if (f.wt != 2) continue;
+    Reader q(f.s, f.n);
+    if (f.num == 1) {  // repeated SentencePiece pieces
+      std::string pc;
+      float sc = 0.0f;
+      uint32_t ty = T_NORMAL;
+      while (q.more()) {
+        const Reader::Field g = q.next();
+        if (!q.ok) return false;
+        if (g.num == 1 && g.wt == 2) pc.assign((const char *)g.s, g.n);
+        else if (g.num == 2 && g.wt == 5) { const uint32_t x = (uint32_t)g.v; memcpy(&sc, &x, 4); }
+        else if (g.num == 3 && g.wt == 0) ty = (uint32_t)g.v;
+      }
+      m->piece.push_back(pc);
+      m->score.push_back(sc);
+      m->type.push_back((uint8_t)ty);
+    } else if (f.num == 2) {  // TrainerSpec
+      while (q.more()) {
+        const Reader::Field g = q.next();
+        if (!q.ok) return false;
+        if (g.num == 3 && g.wt == 0) m->model_type = (int)g.v;
+        else if (g.num == 24 && g.wt == 0) m->ws_suffix = g.v != 0;
+        else if (g.num == 45 && g.wt == 2) m->unk_piece.assign((const char *)g.s, g.n);
+        else if (g.num == 46 && g.wt == 2) m->bos_piece.assign((const char *)g.s, g.n);
+        else if (g.num == 47 && g.wt == 2) m->eos_piece.assign((const char *)g.s, g.n);
+        else if (g.num == 48 && g.wt == 2) m->pad_piece.assign((const char *)g.s, g.n);
+      }
+    } else if (f.num == 3) {  // NormalizerSpec
+      while (q.more()) {
+        const Reader::Field g = q.next();
+        if (!q.ok) return false;
+        if (g.num == 2 && g.wt == 2) m->charsmap.assign((const char *)g.s, g.n);
+        else if (g.num == 3 && g.wt == 0) m->add_dummy_prefix = g.v != 0;
+        else if (g.num == 4 && g.wt == 0) m->remove_extra_ws = g.v != 0;
+        else if (g.num == 5 && g.wt == 0) m->escape_ws = g.v != 0;
+      }
+    }
+  }
+  return r.ok;
+}
+
+// ------------------------------------------------------------ XDA builder
+// Flat double array with unique bases (label test suffices) and hot-first
+// placement: nodes are laid out in order of descending subtree weight, so the
+// units the walks touch most sit at the low indices (one compact, cache- and
+// shared-memory-friendly prefix of the array).
+struct TNode {
+  std::map<uint8_t, int> kids;
+  int value = -1;  // index into the key list
+  double weight = 0;
+};
+
+struct Key { std::string s; uint32_t leaf_x; uint32_t leaf_y; double weight; };
+
+bool build_xda(const std::vector<Key> &keys, HostTrie *out, std::string *err) {
+  out->units.clear();
+  out->leaf.clear();
+  if (keys.empty()) return true;
+  std::vector<TNode> nodes(1);
+  for (size_t k = 0; k < keys.size(); ++k) {
+    int cur = 0;
+    nodes[0].weight += keys[k].weight;
+    for (unsigned char ch : keys[k].s) {
+      auto it = nodes[cur].kids.find(ch);
+      int nx;
+      if (it == nodes[cur].kids.end()) {
+        nx = (int)nodes.size();
+        nodes[cur].kids[ch] = nx;
+        nodes.emplace_back();
+      } else {
+        nx = it->second;
+      }
+      nodes[nx].weight += keys[k].weight;
+      cur = nx;
+    }
+    nodes[cur].value = (int)k;
+  }
+  std::vector<uint32_t> &units = out->units;
+  std::vector<uint2> &leaf = out->leaf;
+  std::vector<uint8_t> used, base_used;
+  std::vector<int> block_free;
+  auto grow = [&]() {
+    units.resize(units.size() + 256, 0);
+    used.resize(units.size(), 0);
+    base_used.resize(units.size(), 0);
+    block_free.push_back(256);
+  };
+  grow();
+  used[0] = 1; block_free[0]--;
+  std::vector<uint32_t> pos_of(nodes.size(), 0);
+  units[0] = 0;
+  typedef std::pair<double, int> QE;
+  std::priority_queue<QE> pq;
+  pq.push(QE(nodes[0].weight, 0));
+  size_t lo_block = 0;
+  while (!pq.empty()) {
+    const int nd = pq.top().second;
+    pq.pop();
+    TNode &N = nodes[nd];
+    if (N.kids.empty()) continue;
+    std::vector<uint8_t> labels;
+    for (auto &kv : N.kids) labels.push_back(kv.first);
+    uint32_t base = 0;
+    bool found = false;
+    for (size_t B = lo_block; !found; ++B) {
+      if (B == block_free.size()) grow();
+      if (block_free[B] < (int)labels.size()) continue;
+      const uint32_t bb = (uint32_t)B << 8;
+      for (uint32_t x = 0; x < 256 && !found; ++x) {
+        const uint32_t b = bb | x;
+        if (base_used[b]) continue;
+        bool fit = true;
+        for (uint8_t c : labels)
+          if (used[b ^ c]) { fit = false; break; }
+        if (fit) { base = b; found = true; }
+      }
+    }
+    while (lo_block + 1 < block_free.size() &&
+           (block_free[lo_block] == 0 || block_free.size() - lo_block > 16)) ++lo_block;
+    if (base >= (1u << 22)) { *err = "piece trie exceeds 4M units"; return false; }
+    base_used[base] = 1;
+    units[pos_of[nd]] |= (base << 10) | 0x200;
+    for (auto &kv : N.kids) {
+      const uint32_t cp = base ^ kv.first;
+      used[cp] = 1;
+      block_free[cp >> 8]--;
+      pos_of[kv.second] = cp;
+      units[cp] = kv.first | (nodes[kv.second].value >= 0 ? 0x100u : 0u);
+      pq.push(QE(nodes[kv.second].weight, kv.second));
+    }
+  }
+  leaf.assign(units.size(), uint2{0xFFFFFFFFu, 0});
+  for (size_t i = 1; i < nodes.size(); ++i)
+    if (nodes[i].value >= 0) {
+      leaf[pos_of[i]].x = keys[nodes[i].value].leaf_x;
+      leaf[pos_of[i]].y = keys[nodes[i].value].leaf_y;
+    }
+  return true;
+}
+
+uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+
+bool is_trie_type(uint32_t t) { return t == T_NORMAL || t == T_USER_DEFINED || t == T_UNUSED; }
+
+// charsmap statistics: first-two-bytes filter and worst-case expansion.
+void scan_charsmap(HostModel *m) {
+  m->cm_first2.assign(65536 / 32, 0);
+  m->expansion = 3;  // ' ' -> U+2581 and a malformed byte -> U+FFFD are both 1 -> 3
+  if (m->cm_n == 0) { m->cm_first2.clear(); return; }
+  const uint32_t *a = m->cm_units;
+  const uint32_t n = m->cm_n;
+  struct Item { uint32_t pos; int depth; uint32_t b0, b1; };
+  std::vector<Item> stack;
+  stack.push_back(Item{du_offset(a[0]), 0, 0, 0});
+  while (!stack.empty()) {
+    const Item it = stack.back();
+    stack.pop_back();
+    for (uint32_t c = 0; c < 256; ++c) {
+      const uint32_t p = it.pos ^ c;
+      if (p >= n) continue;
+      const uint32_t u = a[p];
+      if (du_label(u) != c) continue;
+      const uint32_t np = p ^ du_offset(u);
+      const int depth = it.depth + 1;
+      const uint32_t b0 = depth == 1 ? c : it.b0, b1 = depth == 2 ? c : it.b1;
+      if (depth == 2) m->cm_first2[((b0 << 8) | b1) >> 5] |= 1u << (((b0 << 8) | b1) & 31);
+      if ((u >> 8) & 1) {
+        if (depth == 1)
+          for (uint32_t x = 0; x < 256; ++x) m->cm_first2[((b0 << 8) | x) >> 5] |= 1u << (((b0 << 8) | x) & 31);
+        if (np < n) {
+          const uint32_t v = a[np] & 0x7FFFFFFFu;
+          if (v < m->cm_pool_size) {
+            int outb = 0;
+            for (const uint8_t *q = m->cm_pool + v; q < m->cm_pool + m->cm_pool_size && *q; ++q)
+              outb += (*q == ' ') ? 3 : 1;
+            const int ratio = (outb + depth - 1) / depth;
+            if (ratio > m->expansion) m->expansion = ratio;
+          }
+        }
+      }
+      if (depth < 64 && np < n) stack.push_back(Item{np, depth, b0, b1});
+    }
+  }
+}
+
+}  // namespace
+
+int piece_to_id(const HostModel &m, const std::string &piece) {
+  // reserved_id_map_ and pieces_ are disjoint key sets over all pieces, so a
+  // linear probe by string is the same lookup; only used at option-parse time.
+  for (size_t i = 0; i < m.piece.size(); ++i)
+    if (m.piece[i] == piece) return (int)i;
+  return m.unk_id;
+}
+
+void refresh_leaf_types(HostModel *m) {
+  m->has_unused = false;
+  for (auto t : m->type) if (t == T_UNUSED) m->has_unused = true;
+  for (auto &lf : m->pieces.leaf)
+    if (lf.x != 0xFFFFFFFFu) {
+      const uint32_t id = lf.x & 0x0FFFFFFFu;
+      lf.x = id | ((uint32_t)m->type[id] << 28);
+    }
+}
+
+int build_host_model(const void *data, size_t len, HostModel *m) {
+  if (data == nullptr || len == 0) { m->error = "model is empty."; return kInternal; }
+  if (!parse_proto(data, len, m)) { m->error = "could not parse ModelProto"; return kInternal; }
+  if (m->model_type != M_UNIGRAM && m->model_type != M_BPE) {
+    m->error = "model_type WORD/CHAR is outside the GPU batch-encode path";
+    return kUnimplemented;
+  }
+  const size_t V = m->piece.size();
+  if (V == 0) { m->error = "no pieces are loaded."; return kInternal; }
+  if (V >= (1u << 28)) { m->error = "vocabulary too large"; return kUnimplemented; }
+  // InitializePieces (src/model_interface.cc:101-144)
+  std::map<std::string, int> seen_normal, seen_reserved;
+  m->unk_id = -1;
+  for (size_t i = 0; i < V; ++i) {
+    if (m->piece[i].empty()) { m->error = "piece must not be empty."; return kInternal; }
+    auto &dst = is_trie_type(m->type[i]) ? seen_normal : seen_reserved;
+    if (!dst.emplace(m->piece[i], (int)i).second) { m->error = m->piece[i] + " is already defined."; return kInternal; }
+    if (m->type[i] == T_UNKNOWN) {
+      if (m->unk_id >= 0) { m->error = "unk is already defined."; return kInternal; }
+      m->unk_id = (int)i;
+    }
+    m->max_piece_bytes = std::max<int>(m->max_piece_bytes, (int)m->piece[i].size());
+  }
+  if (m->unk_id < 0) { m->error = "unk is not defined."; return kInternal; }
+  if (m->max_piece_bytes > 4000) { m->error = "piece longer than 4000 bytes"; return kUnimplemented; }
+  // min/max over NORMAL (src/unigram_model.cc:682-689; max starts at FLT_MIN)
+  m->min_score = FLT_MAX;
+  m->max_score = FLT_MIN;
+  for (size_t i = 0; i < V; ++i)
+    if (m->type[i] == T_NORMAL) {
+      m->min_score = std::min(m->min_score, m->score[i]);
+      m->max_score = std::max(m->max_score, m->score[i]);
+    }
+  // piece trie.  A string present both as a reserved and as a normal piece keeps
+  // the reserved id for PieceToId (reserved map is consulted first) -- the
+  // reference allows that combination, we do not.
+  std::vector<Key> keys, ukeys;
+  for (size_t i = 0; i < V; ++i) {
+    if (!is_trie_type(m->type[i]) && seen_normal.count(m->piece[i])) {
+      m->error = m->piece[i] + " is defined both as a reserved and a normal piece";
+      return kUnimplemented;
+    }
+    // weight: unigram log-prob, or BPE merge rank (score = -rank)
+    const double w = m->model_type == M_UNIGRAM ? exp((double)m->score[i]) : 1.0 / (2.0 + fabs((double)m->score[i]));
+    keys.push_back(Key{m->piece[i], (uint32_t)i | ((uint32_t)m->type[i] << 28), f2u(m->score[i]), w});
+    if (m->type[i] == T_USER_DEFINED) {
+      ukeys.push_back(Key{m->piece[i], (uint32_t)i | ((uint32_t)T_USER_DEFINED << 28), 0, 1.0});
+      m->user_first[(uint8_t)m->piece[i][0] >> 5] |= 1u << ((uint8_t)m->piece[i][0] & 31);
+    }
+  }
+  if (!build_xda(keys, &m->pieces, &m->error)) return kUnimplemented;
+  if (!build_xda(ukeys, &m->user, &m->error)) return kUnimplemented;
+  refresh_leaf_types(m);
+  // charsmap blob (src/normalizer.cc:318-337)
+  m->cm_n = 0;
+  if (!m->charsmap.empty()) {
+    uint32_t tb = 0;
+    if (m->charsmap.size() <= 4) { m->error = "Blob for normalization rule is broken."; return kInternal; }
+    memcpy(&tb, m->charsmap.data(), 4);
+    if (tb >= m->charsmap.size() || tb < 4 || (tb & 3)) { m->error = "Blob for normalization rule is broken."; return kInternal; }
+    m->cm_units = (const uint32_t *)(m->charsmap.data() + 4);
+    m->cm_n = tb / 4;
+    m->cm_pool = (const uint8_t *)m->charsmap.data() + 4 + tb;
+    m->cm_pool_size = (uint32_t)(m->charsmap.size() - 4 - tb);
+  }
+  scan_charsmap(m);
+  m->ring = 8;
+  while (m->ring < m->max_piece_bytes + 5) m->ring <<= 1;
+  float smax = fabsf(m->min_score - 10.0f);
+  for (size_t i = 0; i < V; ++i) smax = std::max(smax, fabsf(m->score[i]));
+  smax = std::max(smax, (float)m->max_piece_bytes * fabsf(m->max_score) + 1.0f);
+  m->smax = smax;
+  return kOk;
+}
+
+}  // namespace spmb

@@ -1,0 +1,63 @@
+// Host-side model loader: reads an unmodified SentencePiece .model protobuf and
+// flattens it into the arrays the kernels use (replaces the load-time work of
+// src/sentencepiece_processor.cc:119-157, src/model_interface.cc:101-144,
+// src/unigram_model.cc:624-695 and src/normalizer.cc:61-80).
+#pragma once
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "spm_core.cuh"
+
+namespace spmb {
+
+// util::error::Code values (src/sentencepiece_processor.h:101-119)
+enum StatusCode {
+  kOk = 0, kInvalidArgument = 3, kNotFound = 5, kResourceExhausted = 8, kOutOfRange = 11,
+  kUnimplemented = 12, kInternal = 13,
+};
+
+struct HostTrie {
+  std::vector<uint32_t> units;
+  std::vector<uint2> leaf;
+};
+
+struct HostModel {
+  // ---- parsed (src/sentencepiece_model.proto)
+  std::vector<std::string> piece;
+  std::vector<float> score;
+  std::vector<uint8_t> type;
+  int model_type = M_UNIGRAM;
+  bool ws_suffix = false, add_dummy_prefix = true, remove_extra_ws = true, escape_ws = true;
+  std::string charsmap;  // precompiled_charsmap blob
+  std::string unk_piece = "<unk>", bos_piece = "<s>", eos_piece = "</s>", pad_piece = "<pad>";
+  // ---- derived
+  int unk_id = -1;
+  float min_score = 0, max_score = 0;
+  HostTrie pieces, user;
+  std::vector<uint32_t> cm_first2;
+  uint32_t user_first[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const uint32_t *cm_units = nullptr;  // into charsmap
+  uint32_t cm_n = 0;
+  const uint8_t *cm_pool = nullptr;
+  uint32_t cm_pool_size = 0;
+  int max_piece_bytes = 0;
+  int ring = 8;
+  float smax = 0;
+  int expansion = 3;  // upper bound of normalized bytes per input byte
+  bool has_unused = false;
+  std::string error;
+};
+
+// Parses + builds everything; returns a StatusCode and fills m->error.
+int build_host_model(const void *data, size_t len, HostModel *m);
+
+// Re-derives the leaf tables after piece types changed (SetVocabulary,
+// src/sentencepiece_processor.cc:203-231; min/max scores stay as loaded).
+void refresh_leaf_types(HostModel *m);
+
+// id of a piece by string as ModelInterface::PieceToId (model_interface.cc:87-97)
+int piece_to_id(const HostModel &m, const std::string &piece);
+
+}  // namespace spmb

@@ -1,0 +1,107 @@
+// TEST HARNESS ONLY (built by tests/conftest.py into tests/_build/, never
+// shipped, never loaded by the product package): compiles the kernels'
+// __host__ __device__ core (spm_core.cuh) and the host model loader for the
+// CPU, so the exact arithmetic that runs on the GPU can be compared with the
+// oracle in a container without a GPU.  The product library has no host
+// encode path.
+#include <stdint.h>
+#include <string.h>
+
+#include <vector>
+
+#include "spm_core.cuh"
+#include "spm_model.h"
+
+using namespace spmb;
+
+namespace {
+struct Handle {
+  HostModel hm;
+  ModelView mv;
+};
+void make_view(Handle *h) {
+  HostModel &m = h->hm;
+  ModelView &v = h->mv;
+  memset(&v, 0, sizeof(v));
+  v.pieces.units = m.pieces.units.data(); v.pieces.leaf = m.pieces.leaf.data(); v.pieces.n = (uint32_t)m.pieces.units.size();
+  v.user.units = m.user.units.data(); v.user.leaf = m.user.leaf.data(); v.user.n = (uint32_t)m.user.units.size();
+  v.cm_units = m.cm_units; v.cm_pool = m.cm_pool; v.cm_n = m.cm_n;
+  v.cm_first2 = m.cm_first2.empty() ? nullptr : m.cm_first2.data();
+  memcpy(v.user_first, m.user_first, sizeof(v.user_first));
+  v.model_type = m.model_type; v.unk_id = m.unk_id;
+  v.unk_score = m.min_score - 10.0f; v.max_score = m.max_score; v.smax = m.smax; v.ring = m.ring;
+  v.add_dummy_prefix = m.add_dummy_prefix; v.remove_extra_ws = m.remove_extra_ws;
+  v.escape_ws = m.escape_ws; v.ws_suffix = m.ws_suffix; v.has_unused = m.has_unused;
+}
+}  // namespace
+
+extern "C" {
+
+void *hc_load(const void *data, size_t len, int *code) {
+  Handle *h = new Handle;
+  *code = build_host_model(data, len, &h->hm);
+  if (*code) { delete h; return nullptr; }
+  make_view(h);
+  return h;
+}
+void hc_free(void *p) { delete (Handle *)p; }
+int hc_expansion(void *p) { return ((Handle *)p)->hm.expansion; }
+int hc_trie_units(void *p) { return (int)((Handle *)p)->hm.pieces.units.size(); }
+void hc_set_piece_types(void *p, const uint8_t *t, int n) {
+  Handle *h = (Handle *)p;
+  for (int i = 0; i < n && i < (int)h->hm.type.size(); ++i) h->hm.type[i] = t[i];
+  refresh_leaf_types(&h->hm);
+  make_view(h);
+}
+
+int64_t hc_normalize(void *p, const uint8_t *in, int64_t n, uint8_t *out, int64_t cap) {
+  return normalize_sentence(((Handle *)p)->mv, in, n, out, cap);
+}
+
+// capc: candidate capacity of the unigram tier to emulate (1, 4 or 16).
+// status[n] receives the per-sentence status bits.
+int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n, uint32_t opts, int capc,
+                    int32_t *ids, int64_t cap, int64_t *id_off, uint32_t *status) {
+  Handle *h = (Handle *)p;
+  const ModelView &mv = h->mv;
+  const ExtraPlan plan = make_extra_plan(opts, piece_to_id(h->hm, h->hm.bos_piece), piece_to_id(h->hm, h->hm.eos_piece));
+  std::vector<uint8_t> norm;
+  std::vector<int32_t> words, core;
+  id_off[0] = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const int64_t len = off[i + 1] - off[i];
+    const int64_t ncap = (int64_t)h->hm.expansion * len + 8;
+    norm.resize(ncap);
+    uint32_t st = 0;
+    int32_t nl = normalize_sentence(mv, text + off[i], len, norm.data(), ncap);
+    int32_t cnt = 0;
+    if (nl < 0) { st |= ST_NORM_OVERFLOW; nl = 0; }
+    core.resize(nl + 1);
+    if (mv.model_type == M_UNIGRAM) {
+      words.assign(uni_scratch_words(mv.ring, capc, nl), 0);
+      UniScratch sc;
+      int32_t *w = words.data();
+      sc.ringM = (float *)w; w += mv.ring;
+      sc.ringCnt = (uint32_t *)w; w += mv.ring;
+      sc.candBt = (float *)w; w += mv.ring * capc;
+      w += ((w - words.data()) & 1);
+      sc.candRec = (uint64_t *)w; w += 2 * mv.ring * capc;
+      sc.back = (uint64_t *)w;
+      sc.stride = nl + 1;
+      if (capc == 1) cnt = unigram_encode<1>(mv, norm.data(), nl, sc, core.data(), nl, &st);
+      else if (capc == 4) cnt = unigram_encode<4>(mv, norm.data(), nl, sc, core.data(), nl, &st);
+      else cnt = unigram_encode<16>(mv, norm.data(), nl, sc, core.data(), nl, &st);
+    } else {
+      words.assign(bpe_scratch_words(nl), 0);
+      cnt = bpe_encode(mv, norm.data(), nl, words.data(), core.data(), nl, &st);
+    }
+    status[i] = st;
+    const int32_t fc = final_count(plan, cnt);
+    if (id_off[i] + fc > cap) return 8;
+    for (int32_t j = 0; j < fc; ++j) ids[id_off[i] + j] = final_id_at(plan, core.data(), cnt, j);
+    id_off[i + 1] = id_off[i] + fc;
+  }
+  return 0;
+}
+
+}  // extern "C"
