@@ -81,6 +81,11 @@ int spm_cuda_model_bos_id(const spm_cuda_model *model);
 int spm_cuda_model_eos_id(const spm_cuda_model *model);
 int spm_cuda_model_pad_id(const spm_cuda_model *model);
 
+/* Validation half of SetEncodeExtraOptions / ParseExtraOptions
+ * (src/sentencepiece_processor.cc:991-1023): INTERNAL when a requested bos/eos
+ * piece resolves to the unknown id. */
+int spm_cuda_model_check_extra_options(const spm_cuda_model *model, uint32_t extra_options);
+
 /* Statistics of the last encode call on this model (for bench.py / profiling):
  * stats[0] kernel launches, [1] sentences sent to the exact fallback tier,
  * [2] device-side milliseconds between first and last launch (CUDA events on

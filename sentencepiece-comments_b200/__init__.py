@@ -1,0 +1,279 @@
+"""B200-native batch encoder for SentencePiece models.
+
+Python mirror of the reference's `sentencepiece.SentencePieceProcessor`
+(python/sentencepiece.i:138-276 wraps src/sentencepiece_processor.h:176-447)
+for the encode path: same method names, argument meaning and error behaviour
+(the SWIG build raises on a non-OK util::Status, sentencepiece_processor.h:316-320),
+plus the batch entry points the GPU path is built for.  Everything goes through
+the C ABI of include/spm_cuda.h (libspm_cuda.so); there is no CPU fallback --
+importing works without a GPU, loading a model does not.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = _build.LIB
+
+HOST, DEVICE = 0, 1
+_OPT_CODES = {"bos": 1, "eos": 2, "reverse": 3}
+NORMAL, UNKNOWN, CONTROL, USER_DEFINED, UNUSED = 1, 2, 3, 4, 5
+
+_lib = None
+
+
+def lib():
+    """The C-ABI library; fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libspm_cuda.so is not built: run `python __graft_entry__.py` "
+                               "(there is no CPU fallback)")
+        L = ctypes.CDLL(LIB_PATH)
+        vp, i64, i32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int
+        L.spm_cuda_model_load.argtypes = [ctypes.c_char_p, ctypes.c_size_t, i32, ctypes.POINTER(vp)]
+        L.spm_cuda_model_free.argtypes = [vp]
+        L.spm_cuda_model_set_piece_types.argtypes = [vp, vp, i32]
+        L.spm_cuda_encode_batch.argtypes = [vp, vp, vp, i64, ctypes.c_uint32, vp, i64, vp, i32, vp]
+        L.spm_cuda_model_piece_size.argtypes = [vp]
+        L.spm_cuda_model_piece.argtypes = [vp, i32, ctypes.POINTER(i32)]
+        L.spm_cuda_model_piece.restype = ctypes.c_void_p
+        L.spm_cuda_model_score.argtypes = [vp, i32]
+        L.spm_cuda_model_score.restype = ctypes.c_float
+        L.spm_cuda_model_piece_type.argtypes = [vp, i32]
+        L.spm_cuda_model_piece_to_id.argtypes = [vp, ctypes.c_char_p, ctypes.c_size_t]
+        for f in ("type", "unk_id", "bos_id", "eos_id", "pad_id"):
+            getattr(L, "spm_cuda_model_" + f).argtypes = [vp]
+        L.spm_cuda_model_check_extra_options.argtypes = [vp, ctypes.c_uint32]
+        L.spm_cuda_last_stats.argtypes = [vp, vp, i32]
+        L.spm_cuda_last_error.restype = ctypes.c_char_p
+        _lib = L
+    return _lib
+
+
+class StatusError(RuntimeError):
+    """A non-OK util::Status (code = util::error::Code)."""
+
+    def __init__(self, code, message):
+        super().__init__("%s (code %d)" % (message, code))
+        self.code = code
+
+
+def _check(rc):
+    if rc != 0:
+        raise StatusError(rc, lib().spm_cuda_last_error().decode("utf-8", "replace"))
+
+
+def pack_extra_options(opts):
+    """'bos:eos:reverse' -> packed option list (include/spm_cuda.h); validates
+    names as ParseExtraOptions does (src/sentencepiece_processor.cc:991-1023)."""
+    v = 0
+    if not opts:
+        return 0
+    names = opts.split(":")
+    if len(names) > 16:
+        raise StatusError(3, "too many extra options")
+    for k, name in enumerate(names):
+        if name not in _OPT_CODES:
+            raise StatusError(13, 'option "%s" is not available.' % name)
+        v |= _OPT_CODES[name] << (2 * k)
+    return v
+
+
+class SentencePieceProcessor:
+    def __init__(self, model_file=None, device=0):
+        self._h = None
+        self._device = device
+        self._opts = 0
+        self._base_types = None
+        if model_file is not None:
+            self.Load(model_file)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().spm_cuda_model_free(self._h)
+            self._h = None
+
+    # ---- loading (sentencepiece_processor.h:183-203)
+    def Load(self, filename):
+        try:
+            with open(filename, "rb") as f:
+                data = f.read()
+        except OSError:
+            raise StatusError(5, '"%s": No such file or directory' % filename)
+        return self.LoadFromSerializedProto(data)
+
+    def LoadFromSerializedProto(self, serialized):
+        h = ctypes.c_void_p()
+        _check(lib().spm_cuda_model_load(serialized, len(serialized), self._device, ctypes.byref(h)))
+        if self._h:
+            lib().spm_cuda_model_free(self._h)
+        self._h = h
+        n = self.GetPieceSize()
+        self._base_types = np.array([lib().spm_cuda_model_piece_type(h, i) for i in range(n)], dtype=np.uint8)
+        return True
+
+    def _need(self):
+        if not self._h:
+            raise StatusError(9, "Model is not initialized.")
+
+    # ---- options (sentencepiece_processor.h:210-234)
+    def SetEncodeExtraOptions(self, extra_option):
+        self._need()
+        v = pack_extra_options(extra_option)
+        _check(lib().spm_cuda_model_check_extra_options(self._h, v))
+        self._opts = v
+        return True
+
+    def SetVocabulary(self, valid_vocab):
+        """src/sentencepiece_processor.cc:203-231: pieces outside `valid_vocab`
+        (and longer than one character) become UNUSED."""
+        self._need()
+        vocab = set(v.encode() if isinstance(v, str) else bytes(v) for v in valid_vocab)
+        types = self._base_types.copy()
+        for i in range(len(types)):
+            if types[i] in (CONTROL, UNKNOWN, USER_DEFINED):
+                continue
+            p = self._piece_bytes(i)
+            one = (1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 3, 4)[p[0] >> 4]
+            types[i] = NORMAL if (p in vocab or one == len(p)) else UNUSED
+        _check(lib().spm_cuda_model_set_piece_types(self._h, types.ctypes.data, len(types)))
+        self._types = types
+        return True
+
+    def ResetVocabulary(self):
+        self._need()
+        types = self._base_types.copy()
+        types[types == UNUSED] = NORMAL
+        _check(lib().spm_cuda_model_set_piece_types(self._h, types.ctypes.data, len(types)))
+        return True
+
+    # ---- encode (sentencepiece_processor.h:244, 333-335)
+    def Encode(self, input):
+        return self.EncodeAsIds(input)
+
+    def EncodeAsIds(self, input):
+        b = input.encode("utf-8") if isinstance(input, str) else bytes(input)
+        ids, _ = self.encode_packed(np.frombuffer(b, dtype=np.uint8), np.array([0, len(b)], dtype=np.int64))
+        return ids.tolist()
+
+    def encode_batch(self, sentences):
+        """list of str/bytes -> (ids int32[total], id_offsets int64[n+1])."""
+        bs = [s.encode("utf-8") if isinstance(s, str) else bytes(s) for s in sentences]
+        off = np.zeros(len(bs) + 1, dtype=np.int64)
+        if bs:
+            np.cumsum([len(b) for b in bs], out=off[1:])
+        text = np.frombuffer(b"".join(bs), dtype=np.uint8)
+        return self.encode_packed(text, off)
+
+    def encode_packed(self, text, offsets, ids_capacity=None, stream=None):
+        """Host CSR in, host CSR out.  text: uint8[], offsets: int64[n+1]."""
+        self._need()
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        n = len(offsets) - 1
+        id_off = np.zeros(n + 1, dtype=np.int64)
+        cap = ids_capacity if ids_capacity is not None else max(64, (int(offsets[-1] - offsets[0]) // 2) + 4 * n)
+        while True:
+            ids = np.empty(cap, dtype=np.int32)
+            rc = lib().spm_cuda_encode_batch(self._h, text.ctypes.data, offsets.ctypes.data, n, self._opts,
+                                             ids.ctypes.data, cap, id_off.ctypes.data, HOST, stream)
+            if rc == 8 and ids_capacity is None:
+                cap = int(id_off[n])
+                continue
+            _check(rc)
+            return ids[: id_off[n]], id_off
+
+    def encode_device(self, text, offsets, ids, id_offsets, stream=None):
+        """Device CSR in/out on torch CUDA tensors (uint8, int64, int32, int64);
+        runs on torch's current stream unless `stream` (a cudaStream_t int) is given."""
+        import torch
+        self._need()
+        if stream is None:
+            stream = torch.cuda.current_stream(text.device).cuda_stream
+        n = offsets.numel() - 1
+        rc = lib().spm_cuda_encode_batch(self._h, text.data_ptr(), offsets.data_ptr(), n, self._opts,
+                                         ids.data_ptr(), ids.numel(), id_offsets.data_ptr(), DEVICE, stream)
+        _check(rc)
+
+    def encode_pinned(self, text, offsets, ids, id_offsets, stream=None):
+        """Host CSR in/out on caller-owned (ideally pinned) torch/numpy buffers; no allocation."""
+        self._need()
+        ptr = lambda a: a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data
+        n = (offsets.numel() if hasattr(offsets, "numel") else len(offsets)) - 1
+        cap = ids.numel() if hasattr(ids, "numel") else len(ids)
+        rc = lib().spm_cuda_encode_batch(self._h, ptr(text), ptr(offsets), n, self._opts, ptr(ids), cap,
+                                         ptr(id_offsets), HOST, stream)
+        _check(rc)
+
+    def last_stats(self):
+        s = (ctypes.c_double * 4)()
+        lib().spm_cuda_last_stats(self._h, s, 4)
+        return {"launches": int(s[0]), "fallback_sentences": int(s[1]), "device_ms": s[2], "workspace_bytes": int(s[3])}
+
+    # ---- model introspection (sentencepiece_processor.h:397-432)
+    def GetPieceSize(self):
+        self._need()
+        return lib().spm_cuda_model_piece_size(self._h)
+
+    def _piece_bytes(self, id):
+        n = ctypes.c_int(0)
+        p = lib().spm_cuda_model_piece(self._h, id, ctypes.byref(n))
+        return ctypes.string_at(p, n.value)
+
+    def IdToPiece(self, id):
+        self._need()
+        return self._piece_bytes(id).decode("utf-8", "replace")
+
+    def PieceToId(self, piece):
+        self._need()
+        b = piece.encode("utf-8") if isinstance(piece, str) else bytes(piece)
+        return lib().spm_cuda_model_piece_to_id(self._h, b, len(b))
+
+    def GetScore(self, id):
+        self._need()
+        return lib().spm_cuda_model_score(self._h, id)
+
+    def _type(self, id):
+        self._need()
+        return lib().spm_cuda_model_piece_type(self._h, id)
+
+    def IsUnknown(self, id):
+        return self._type(id) == UNKNOWN
+
+    def IsControl(self, id):
+        return self._type(id) == CONTROL
+
+    def IsUnused(self, id):
+        return self._type(id) == UNUSED
+
+    def unk_id(self):
+        self._need()
+        return lib().spm_cuda_model_unk_id(self._h)
+
+    def bos_id(self):
+        self._need()
+        return lib().spm_cuda_model_bos_id(self._h)
+
+    def eos_id(self):
+        self._need()
+        return lib().spm_cuda_model_eos_id(self._h)
+
+    def pad_id(self):
+        self._need()
+        return lib().spm_cuda_model_pad_id(self._h)
+
+    def model_type(self):
+        self._need()
+        return lib().spm_cuda_model_type(self._h)
+
+    # snake_case aliases of the reference's python module
+    load = Load
+    encode_as_ids = EncodeAsIds
+    get_piece_size = GetPieceSize
+    piece_to_id = PieceToId
+    id_to_piece = IdToPiece
+    __len__ = GetPieceSize

@@ -147,6 +147,7 @@ bool build_xda(const std::vector<Key> &keys, HostTrie *out, std::string *err) {
   };
   grow();
   used[0] = 1; block_free[0]--;
+  base_used[0] = 1;  // base 0 would make the root (label 0 at index 0) its own child on a NUL byte
   std::vector<uint32_t> pos_of(nodes.size(), 0);
   units[0] = 0;
   typedef std::pair<double, int> QE;
@@ -270,6 +271,11 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
     m->error = "model_type WORD/CHAR is outside the GPU batch-encode path";
     return kUnimplemented;
   }
+  // empty names fall back to the defaults (src/model_interface.cc:30-48)
+  if (m->unk_piece.empty()) m->unk_piece = "<unk>";
+  if (m->bos_piece.empty()) m->bos_piece = "<s>";
+  if (m->eos_piece.empty()) m->eos_piece = "</s>";
+  if (m->pad_piece.empty()) m->pad_piece = "<pad>";
   const size_t V = m->piece.size();
   if (V == 0) { m->error = "no pieces are loaded."; return kInternal; }
   if (V >= (1u << 28)) { m->error = "vocabulary too large"; return kUnimplemented; }

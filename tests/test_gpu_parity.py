@@ -1,0 +1,150 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle, on a real GPU.
+
+Bit-exact ids and CSR offsets are required (integer/index work).  The checker
+is the unmodified reference compiled into oracle/_ref when that library is
+present (it travels with the snapshot), else the CPU restatement.
+"""
+import numpy as np
+import pytest
+
+from conftest import EDGE_SENTENCES, checker, model_bytes
+
+pytestmark = pytest.mark.gpu
+
+CASES = [
+    ("botchan_uni8k", "botchan"),      # config 1
+    ("botchan_bpe4k", "botchan"),
+    ("botchan_uni2k_ud", "botchan"),   # user-defined + control symbols
+    ("botchan_bpe2k_ud", "botchan"),
+    ("syn_uni32k", "syn_en"),          # config 2 (sample)
+    ("syn_uni32k", "syn_dirty"),
+    ("syn_bpe32k", "syn_en"),          # config 3 (sample)
+    ("syn_bpe32k", "syn_dirty"),
+    ("wagahai_uni", "wagahai"),        # config 4
+    ("ref_ja_8k", "wagahai"),
+    ("ref_en_1k", "botchan"),
+    ("syn_uni32k", "wagahai"),         # mostly-unknown text, long unk runs
+    ("syn_bpe32k", "wagahai"),
+    ("wagahai_uni", "syn_dirty"),
+]
+
+
+def ref_encode(chk, text, off):
+    try:
+        return chk.encode_batch(text, off, threads=8)
+    except TypeError:
+        return chk.encode_batch(text, off)
+
+
+def assert_same(got, want, text, off):
+    gi, go = got
+    wi, wo = want
+    if not np.array_equal(go, wo):
+        bad = np.nonzero(np.diff(go) != np.diff(wo))[0]
+        i = int(bad[0])
+        raise AssertionError("sentence %d: %d ids, want %d; text=%r" % (
+            i, go[i + 1] - go[i], wo[i + 1] - wo[i], bytes(text[off[i]:off[i + 1]])[:200]))
+    if not np.array_equal(gi, wi):
+        k = int(np.nonzero(gi != wi)[0][0])
+        i = int(np.searchsorted(wo, k, side="right") - 1)
+        raise AssertionError("sentence %d differs: got %s want %s; text=%r" % (
+            i, gi[wo[i]:wo[i + 1]][:40], wi[wo[i]:wo[i + 1]][:40], bytes(text[off[i]:off[i + 1]])[:200]))
+
+
+@pytest.mark.parametrize("model,corpus", CASES)
+def test_corpus_parity(spm_b200, corpora, model, corpus):
+    mb = model_bytes(model)
+    sp = spm_b200.SentencePieceProcessor()
+    sp.LoadFromSerializedProto(mb)
+    chk, _ = checker(mb)
+    text, off = corpora[corpus]
+    assert_same(sp.encode_packed(text, off), ref_encode(chk, text, off), text, off)
+
+
+@pytest.mark.parametrize("model", ["botchan_uni8k", "botchan_bpe4k", "botchan_uni2k_ud", "botchan_bpe2k_ud",
+                                   "syn_uni32k", "syn_bpe32k", "wagahai_uni", "ref_ja_8k"])
+def test_edge_sentences(spm_b200, corpora, model):
+    mb = model_bytes(model)
+    sp = spm_b200.SentencePieceProcessor()
+    sp.LoadFromSerializedProto(mb)
+    chk, _ = checker(mb)
+    text, off = corpora["edge"]
+    assert_same(sp.encode_packed(text, off), ref_encode(chk, text, off), text, off)
+    # single-sentence API
+    for s in EDGE_SENTENCES[:40]:
+        assert sp.EncodeAsIds(s) == chk.encode(s)
+
+
+@pytest.mark.parametrize("model", ["botchan_uni8k", "botchan_bpe4k"])
+@pytest.mark.parametrize("opts", ["bos", "eos", "reverse", "bos:eos", "reverse:bos:eos", "bos:eos:reverse",
+                                  "eos:reverse:bos:reverse:eos"])
+def test_extra_options(spm_b200, corpora, model, opts):
+    mb = model_bytes(model)
+    sp = spm_b200.SentencePieceProcessor()
+    sp.LoadFromSerializedProto(mb)
+    sp.SetEncodeExtraOptions(opts)
+    chk, _ = checker(mb)
+    chk.set_encode_extra_options(opts)
+    text, off = corpora["edge"]
+    assert_same(sp.encode_packed(text, off), ref_encode(chk, text, off), text, off)
+    text, off = corpora["botchan"]
+    assert_same(sp.encode_packed(text, off), ref_encode(chk, text, off), text, off)
+
+
+@pytest.mark.parametrize("model", ["botchan_uni8k", "botchan_bpe4k", "syn_bpe32k"])
+def test_set_vocabulary(spm_b200, corpora, model):
+    """SetVocabulary -> UNUSED pieces (unigram: skipped; BPE: resegmented through rev_merge)."""
+    from oracle import ref
+    if not ref.available():
+        pytest.skip("needs oracle/_ref (SetVocabulary lives in the reference processor)")
+    mb = model_bytes(model)
+    sp = spm_b200.SentencePieceProcessor()
+    sp.LoadFromSerializedProto(mb)
+    chk = ref.RefProcessor(mb)
+    n = sp.GetPieceSize()
+    vocab = [sp.IdToPiece(i) for i in range(n) if i % 3 != 0]
+    sp.SetVocabulary(vocab)
+    chk.set_vocabulary(vocab)
+    text, off = corpora["syn_en" if model.startswith("syn") else "botchan"]
+    text, off = text[: off[3000]], off[:3001]
+    assert_same(sp.encode_packed(text, off), ref_encode(chk, text, off), text, off)
+    sp.ResetVocabulary()
+    chk.set_vocabulary(None)
+    assert_same(sp.encode_packed(text, off), ref_encode(chk, text, off), text, off)
+
+
+def test_device_memory_space(spm_b200, corpora):
+    import torch
+    mb = model_bytes("syn_uni32k")
+    sp = spm_b200.SentencePieceProcessor()
+    sp.LoadFromSerializedProto(mb)
+    text, off = corpora["syn_en"]
+    want = sp.encode_packed(text, off)
+    dt = torch.from_numpy(text).cuda()
+    do = torch.from_numpy(off).cuda()
+    ids = torch.empty(int(want[1][-1]) + 10, dtype=torch.int32, device="cuda")
+    ido = torch.empty(len(off), dtype=torch.int64, device="cuda")
+    sp.encode_device(dt, do, ids, ido)
+    torch.cuda.synchronize()
+    assert np.array_equal(ido.cpu().numpy(), want[1])
+    assert np.array_equal(ids[: int(want[1][-1])].cpu().numpy(), want[0])
+    # capacity too small -> RESOURCE_EXHAUSTED with the needed size in id_offsets[n]
+    small = torch.empty(100, dtype=torch.int32, device="cuda")
+    with pytest.raises(spm_b200.StatusError) as e:
+        sp.encode_device(dt, do, small, ido)
+    assert e.value.code == 8
+    assert int(ido[-1].item()) == int(want[1][-1])
+
+
+def test_empty_batch_and_errors(spm_b200):
+    sp = spm_b200.SentencePieceProcessor()
+    with pytest.raises(spm_b200.StatusError):
+        sp.EncodeAsIds("x")  # model not loaded
+    with pytest.raises(spm_b200.StatusError):
+        sp.LoadFromSerializedProto(b"garbage")
+    sp.LoadFromSerializedProto(model_bytes("botchan_uni8k"))
+    ids, off = sp.encode_batch([])
+    assert len(ids) == 0 and off.tolist() == [0]
+    assert sp.EncodeAsIds("") == []
+    with pytest.raises(spm_b200.StatusError):
+        sp.SetEncodeExtraOptions("foo")
