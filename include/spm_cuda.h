@@ -89,7 +89,10 @@ int spm_cuda_model_check_extra_options(const spm_cuda_model *model, uint32_t ext
 /* Statistics of the last encode call on this model (for bench.py / profiling):
  * stats[0] kernel launches, [1] sentences sent to the exact fallback tier,
  * [2] device-side milliseconds between first and last launch (CUDA events on
- * the caller's stream), [3] bytes of workspace currently allocated. */
+ * the caller's stream), [3] bytes of workspace currently allocated, [4] device
+ * milliseconds spent in the dominant (encode) kernel, summed over its launches
+ * (CUDA events around each launch, same stream), [5] number of those launches,
+ * [6] sentences, [7] ids produced.  n <= 8. */
 int spm_cuda_last_stats(const spm_cuda_model *model, double *stats, int n);
 
 const char *spm_cuda_last_error(void);

@@ -210,9 +210,11 @@ class SentencePieceProcessor:
         _check(rc)
 
     def last_stats(self):
-        s = (ctypes.c_double * 4)()
-        lib().spm_cuda_last_stats(self._h, s, 4)
-        return {"launches": int(s[0]), "fallback_sentences": int(s[1]), "device_ms": s[2], "workspace_bytes": int(s[3])}
+        s = (ctypes.c_double * 8)()
+        lib().spm_cuda_last_stats(self._h, s, 8)
+        return {"launches": int(s[0]), "fallback_sentences": int(s[1]), "device_ms": s[2],
+                "workspace_bytes": int(s[3]), "encode_kernel_ms": s[4], "encode_kernel_launches": int(s[5]),
+                "sentences": int(s[6]), "ids": int(s[7])}
 
     # ---- model introspection (sentencepiece_processor.h:397-432)
     def GetPieceSize(self):
