@@ -1,25 +1,41 @@
 // spm_kernels.cu -- CUDA kernels (sm_100a) and the C ABI of include/spm_cuda.h.
 //
-// Pipeline of one spm_cuda_encode_batch call (sentences are independent units;
-// nothing here is GEMM-shaped, the work is byte/trie/scan traffic):
-//   k_normalize   one thread per sentence: charsmap leftmost-longest rewrite,
-//                 whitespace policy                      (src/normalizer.cc:88-300)
-//   k_scan_*      exclusive scans (scratch offsets, CSR offsets)
-//   k_encode      one thread per sentence: trie walk + on-the-fly Viterbi with
-//                 pruned candidate lists, or BPE agenda (src/unigram_model.cc:
-//                 535-604,222-261; src/bpe_model.cc:37-199), unk-run merge
-//   k_compact     one warp per sentence: extra options + CSR write
-//                                          (src/sentencepiece_processor.cc:319-330,945-979)
+// One spm_cuda_encode_batch call is cut into chunks of sentences; per chunk
+// (sentences are independent units; nothing here is GEMM-shaped, the work is
+// byte / trie / scan traffic):
+//
+//   FAST TIER (unigram models)
+//   k_normalize_fast  charsmap leftmost-longest rewrite + whitespace policy into a
+//                     padded, aligned per-sentence slot; length histogram
+//                                                     (src/normalizer.cc:88-300)
+//   k_binscan/k_scatter  counting sort of the sentences by character count
+//                     (descending), so the 32 lanes of a warp walk sentences of
+//                     equal length in lock step
+//   k_encode_fast     persistent CTAs, one thread per sentence: trie walk + Viterbi
+//                     with the hot trie prefix, the DP ring and the text window in
+//                     shared memory / registers (spm_fast.cuh;
+//                     src/unigram_model.cc:535-604,222-261)
+//   GENERAL TIER (BPE models; unigram sentences the fast tier flags: near-tied
+//                 Viterbi candidates, heavy expansion, > kFastMaxChars characters)
+//   k_gen_normalize / k_gen_encode  one thread per listed sentence, exact candidate
+//                     lists / BPE agenda in global scratch (spm_core.cuh;
+//                     src/bpe_model.cc:37-199)
+//   BOTH
+//   k_scan_*          exclusive scans (scratch offsets, CSR offsets)
+//   k_compact         one warp per sentence: extra options + CSR write
+//                     (src/sentencepiece_processor.cc:319-330,945-979)
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <string>
 #include <vector>
 
 #include "../../include/spm_cuda.h"
 #include "spm_core.cuh"
+#include "spm_fast.cuh"
 #include "spm_model.h"
 
 using namespace spmb;
@@ -38,42 +54,62 @@ thread_local std::string g_err;
   } while (0)
 
 constexpr int kCapc = 8;          // near-tie candidates kept per position by the exact tier
-constexpr int kThreads = 128;
+constexpr int kThreads = 128;     // general-tier block size
+constexpr int kFastThreads = 512; // fast-tier block size (one persistent CTA per SM)
+constexpr uint32_t ST_GEN = 1u << 16;   // sentence was encoded by the general tier (ids in gstage, forward order)
 
-// ---------------------------------------------------------------- kernels
-__device__ __forceinline__ int64_t norm_base(const int64_t *off, int64_t c0, int64_t i, int exp_) {
-  return (int64_t)exp_ * (off[i] - off[c0]) + 8 * (i - c0);
+// device-side counters of one chunk
+enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_COUNT = 8 };
+
+// ---------------------------------------------------------------- general tier
+// Sentence t of the list is sentence list[t] of the chunk (list == nullptr: t).
+__global__ void __launch_bounds__(kThreads)
+k_gen_prepare(const int64_t *off, int64_t c0, const int32_t *list, const uint32_t *count, int64_t t0, int64_t tn,
+              int exp_, int32_t *need) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= tn) return;
+  int32_t v = 0;
+  if (count == nullptr || t0 + t < (int64_t)*count) {
+    const int64_t i = c0 + (list ? list[t0 + t] : t0 + t);
+    v = (int32_t)(((int64_t)exp_ * (off[i + 1] - off[i]) + 8 + 7) & ~(int64_t)7);
+  }
+  need[t] = v;
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_normalize(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn, int exp_,
-            uint8_t *norm, int32_t *nlen, int32_t *words, uint32_t *status) {
+k_gen_normalize(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c0, const int32_t *list,
+                const uint32_t *count, int64_t t0, int64_t tn, const int32_t *need, const int64_t *noff,
+                uint8_t *norm, int32_t *nlen, int32_t *words, uint32_t *gstatus) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= cn) return;
-  const int64_t i = c0 + t;
-  const int64_t len = off[i + 1] - off[i];
-  const int64_t cap = (int64_t)exp_ * len + 8;
-  int32_t nl = normalize_sentence(mv, text + off[i], len, norm + norm_base(off, c0, i, exp_), cap);
+  if (t >= tn) return;
+  int32_t nl = 0, w = 0;
   uint32_t st = 0;
-  if (nl < 0) { nl = 0; st = ST_NORM_OVERFLOW; }
+  if (count == nullptr || t0 + t < (int64_t)*count) {
+    const int64_t i = c0 + (list ? list[t0 + t] : t0 + t);
+    nl = normalize_sentence(mv, text + off[i], off[i + 1] - off[i], norm + noff[t], need[t]);
+    if (nl < 0) { nl = 0; st = ST_NORM_OVERFLOW; }
+    const int64_t ww = mv.model_type == M_UNIGRAM ? uni_scratch_words(mv.ring, kCapc, nl) : bpe_scratch_words(nl);
+    w = (int32_t)((ww + 1) & ~(int64_t)1);  // keep 8-byte alignment of each region
+  }
   nlen[t] = nl;
-  status[t] = st;
-  int64_t w = mv.model_type == M_UNIGRAM ? uni_scratch_words(mv.ring, kCapc, nl) : bpe_scratch_words(nl);
-  words[t] = (int32_t)((w + 1) & ~(int64_t)1);  // keep 8-byte alignment of each region
+  words[t] = w;
+  gstatus[t] = st;
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_encode(ModelView mv, const int64_t *off, int64_t c0, int64_t cn, int exp_, const uint8_t *norm,
-         const int32_t *nlen, const int64_t *woff, int32_t *scratch, int32_t *stage, int32_t *cnt,
-         uint32_t *status, uint32_t *status_or) {
+k_gen_encode(ModelView mv, const int32_t *list, const uint32_t *count, int64_t t0, int64_t tn,
+             const int64_t *noff, const uint8_t *norm, const int32_t *nlen, const int64_t *woff, int64_t wbase,
+             int32_t *scratch, int32_t *gstage, const uint32_t *gstatus, int32_t *cnt, uint32_t *status, int64_t *srcoff,
+             uint32_t *status_or) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= cn) return;
-  const int64_t i = c0 + t;
-  const int64_t nb = norm_base(off, c0, i, exp_);
+  if (t >= tn) return;
+  if (count != nullptr && t0 + t >= (int64_t)*count) return;
+  const int64_t i = list ? list[t0 + t] : t0 + t;  // chunk-relative sentence index
+  const int64_t nb = noff[t];
   const int32_t nl = nlen[t];
-  uint32_t st = status[t];
+  uint32_t st = gstatus[t];
   int32_t c = 0;
-  int32_t *w = scratch + woff[t];
+  int32_t *w = scratch + (woff[t] - wbase);
   if (st == 0) {
     if (mv.model_type == M_UNIGRAM) {
       UniScratch sc;
@@ -83,14 +119,147 @@ k_encode(ModelView mv, const int64_t *off, int64_t c0, int64_t cn, int exp_, con
       sc.candRec = (uint64_t *)w; w += 2 * mv.ring * kCapc;
       sc.back = (uint64_t *)w;
       sc.stride = nl + 1;
-      c = unigram_encode<kCapc>(mv, norm + nb, nl, sc, stage + nb, nl, &st);
+      c = unigram_encode<kCapc>(mv, norm + nb, nl, sc, gstage + nb, nl, &st);
     } else {
-      c = bpe_encode(mv, norm + nb, nl, w, stage + nb, nl, &st);
+      c = bpe_encode(mv, norm + nb, nl, w, gstage + nb, nl, &st);
     }
   }
-  cnt[t] = c;
-  status[t] = st;
+  cnt[i] = c;
+  status[i] = st | ST_GEN;
+  srcoff[i] = nb;
   if (st) atomicOr(status_or, st);
+}
+
+// ---------------------------------------------------------------- fast tier
+// Slot of sentence i (chunk-relative t) in the normalized buffer: 16-byte aligned,
+// room for 3 * len + 8 normalized bytes followed by >= kNormPad zero bytes.
+__device__ __forceinline__ int64_t fast_norm_base(const int64_t *off, int64_t c0, int64_t t) {
+  return ((3 * (off[c0 + t] - off[c0]) + 15) & ~(int64_t)15) + 64 * t;
+}
+// Slot in the id staging buffer: len + 16 ids (ids <= characters <= that, else general tier).
+__device__ __forceinline__ int64_t fast_stage_base(const int64_t *off, int64_t c0, int64_t t) {
+  return (off[c0 + t] - off[c0]) + 16 * t;
+}
+
+// v2a: one thread per sentence (to be replaced by the warp-cooperative normaliser).
+__global__ void __launch_bounds__(kThreads)
+k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn, uint8_t *norm,
+                 int32_t *nlen, int32_t *nchars, int32_t *cnt, uint32_t *status, uint32_t *hist, int32_t *gen_list,
+                 uint32_t *counters) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= cn) return;
+  const int64_t i = c0 + t;
+  const int64_t len = off[i + 1] - off[i];
+  uint8_t *out = norm + fast_norm_base(off, c0, t);
+  int32_t nl = normalize_sentence(mv, text + off[i], len, out, 3 * len + 8);
+  bool general = false;
+  int32_t nc = 0;
+  if (nl < 0) {
+    general = true;
+    nl = 0;
+  } else {
+    for (int32_t p = 0; p < nl;) { p += one_char_len(out[p]); ++nc; }
+    for (int k = 0; k < kNormPad; ++k) out[nl + k] = 0;
+    if (nc > kFastMaxChars || nc > len + 16) general = true;
+  }
+  nlen[t] = nl;
+  nchars[t] = nc;
+  cnt[t] = 0;
+  status[t] = 0;
+  if (general) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
+  else if (nc > 0) atomicAdd(&hist[nc], 1u);
+  if (general) nchars[t] = -1;
+}
+
+// hist[1..kFastMaxChars] -> first slot of each bin in DESCENDING key order; total -> counters[C_NFAST]
+__global__ void __launch_bounds__(1024) k_binscan(uint32_t *hist, uint32_t *bincur, uint32_t *counters) {
+  __shared__ uint32_t wsum[32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int key = kFastMaxChars - tid;  // tid 0 -> longest
+  const uint32_t v = key >= 1 ? hist[key] : 0;
+  uint32_t inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+    if (lane >= d) inc += y;
+  }
+  if (lane == 31) wsum[wid] = inc;
+  __syncthreads();
+  if (wid == 0) {
+    uint32_t s = wsum[lane];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, s, d);
+      if (lane >= d) s += y;
+    }
+    wsum[lane] = s;
+  }
+  __syncthreads();
+  const uint32_t base = wid ? wsum[wid - 1] : 0;
+  if (key >= 1) { bincur[key] = base + inc - v; hist[key] = 0; }
+  if (tid == 1023) counters[C_NFAST] = base + inc;
+}
+
+__global__ void __launch_bounds__(256)
+k_scatter(const int32_t *nchars, int64_t cn, uint32_t *bincur, int32_t *perm) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= cn) return;
+  const int32_t nc = nchars[t];
+  if (nc > 0) perm[atomicAdd(&bincur[nc], 1u)] = (int32_t)t;
+}
+
+struct FastParams {
+  const uint32_t *units;
+  const float *score;
+  const uint32_t *leaf_id;
+  uint32_t k_units, k_scores, n_units;
+  int32_t ring;
+  float unk_score, smax;
+  int32_t unk_id;
+};
+
+// Persistent CTAs (one per SM).  Shared memory: hot units | hot scores | ring_bt[R][T] | ring_bk[R][T].
+__global__ void __launch_bounds__(kFastThreads, 1)
+k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
+              const int32_t *perm, uint32_t *back, int32_t *stage, int32_t *cnt, uint32_t *status,
+              int32_t *gen_list, uint32_t *counters) {
+  extern __shared__ __align__(16) uint32_t smem[];
+  uint32_t *units_hot = smem;
+  float *score_hot = (float *)(smem + fp.k_units);
+  float *ring_bt = (float *)(smem + fp.k_units + fp.k_scores);
+  uint32_t *ring_bk = (uint32_t *)(ring_bt + (size_t)fp.ring * kFastThreads);
+  for (uint32_t k = threadIdx.x; k < fp.k_units; k += kFastThreads) units_hot[k] = fp.units[k];
+  for (uint32_t k = threadIdx.x; k < fp.k_scores; k += kFastThreads) score_hot[k] = fp.score[k];
+  __syncthreads();
+  FastView fv;
+  fv.units = fp.units; fv.score = fp.score; fv.leaf_id = fp.leaf_id;
+  fv.units_hot = units_hot; fv.score_hot = score_hot;
+  fv.k_units = fp.k_units; fv.k_scores = fp.k_scores; fv.n_units = fp.n_units;
+  fv.ring = fp.ring; fv.unk_score = fp.unk_score; fv.smax = fp.smax; fv.unk_id = fp.unk_id;
+  const uint32_t nfast = counters[C_NFAST];
+  const int lane = threadIdx.x & 31;
+  const int64_t bstride = (int64_t)gridDim.x * kFastThreads;
+  uint32_t *myback = back + (int64_t)blockIdx.x * kFastThreads + threadIdx.x;
+  for (;;) {
+    uint32_t w = 0;
+    if (lane == 0) w = atomicAdd(&counters[C_WORK], 1u);
+    w = __shfl_sync(0xFFFFFFFFu, w, 0);
+    const uint32_t idx = w * 32 + lane;
+    if (w * 32 >= nfast) break;
+    if (idx < nfast) {
+      const int32_t t = perm[idx];
+      uint32_t st = 0;
+      const int32_t c = fast_unigram(fv, norm + fast_norm_base(off, c0, t), nlen[t], ring_bt + threadIdx.x,
+                                     ring_bk + threadIdx.x, kFastThreads, myback, bstride,
+                                     stage + fast_stage_base(off, c0, t), &st);
+      if (st) {
+        gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
+      } else {
+        cnt[t] = c;
+      }
+    }
+    __syncwarp();
+  }
 }
 
 // ---- exclusive scan of f(in[i]) over one chunk: int32 -> int64, with carry
@@ -176,18 +345,21 @@ k_scan_final(const int32_t *in, int64_t n, Op op, const int64_t *partial, const 
   if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = *carry;
 }
 
-// one warp per sentence: final layout (extra options) into the CSR values
+// one warp per sentence: final layout (extra options) into the CSR values.  Fast-tier
+// sentences were staged in reverse order, general-tier ones forward.
 __global__ void __launch_bounds__(256)
-k_compact(ExtraPlan plan, const int64_t *off, int64_t c0, int64_t cn, int exp_, const int32_t *stage,
-          const int32_t *cnt, const int64_t *id_off, int32_t *ids, int64_t capacity) {
+k_compact(ExtraPlan plan, const int64_t *off, int64_t c0, int64_t cn, const int32_t *stage, const int32_t *gstage,
+          const int64_t *srcoff, const uint32_t *status, const int32_t *cnt, const int64_t *id_off, int32_t *ids,
+          int64_t capacity) {
   const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (t >= cn) return;
-  const int64_t i = c0 + t;
   const int32_t core = cnt[t];
   const int32_t fc = final_count(plan, core);
-  const int32_t *src = stage + norm_base(off, c0, i, exp_);
-  const int64_t dst = id_off[i];
+  const bool gen = status[t] & ST_GEN;
+  const int32_t *src = gen ? gstage + srcoff[t] : stage + fast_stage_base(off, c0, t);
+  if (!gen) plan.flip ^= 1;
+  const int64_t dst = id_off[c0 + t];
   for (int32_t j = lane; j < fc; j += 32)
     if (dst + j < capacity) ids[dst + j] = final_id_at(plan, src, core, j);
 }
@@ -214,16 +386,30 @@ struct spm_cuda_model {
   HostModel hm;
   int device = 0;
   ModelView mv;
-  DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2;
+  FastParams fp;
+  bool fast = false;       // unigram model that fits the fast tier
+  int sm_count = 1;
+  size_t fast_smem = 0;
+  DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2, d_funits, d_fscore, d_fleaf;
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
-  mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_words, w_cnt, w_status,
-      w_woff, w_scratch, w_partial, w_scalars;
-  mutable std::vector<int64_t> h_off;
+  mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
+      w_perm, w_genlist, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
+      g_nlen, g_words, g_woff, g_scratch, g_status;
+  mutable std::vector<int64_t> h_off, h_woff;
   mutable double stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   mutable cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   mutable std::vector<cudaEvent_t> kev;  // event pairs around the dominant (encode) kernel launches
+  mutable size_t nk = 0;
   int bos_id = 0, eos_id = 0, pad_id = 0;
+  std::vector<DevBuf *> all_bufs() const {
+    spm_cuda_model *m = const_cast<spm_cuda_model *>(this);
+    return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2,
+            &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
+            &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
+            &m->w_genlist, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
+            &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status};
+  }
 };
 
 namespace {
@@ -233,6 +419,15 @@ int upload(DevBuf *b, const void *src, size_t bytes) {
   int rc = b->ensure(bytes);
   if (rc) return rc;
   CUDA_TRY(cudaMemcpy(b->p, src, bytes, cudaMemcpyHostToDevice));
+  return kOk;
+}
+
+int upload_fast_view(spm_cuda_model *M) {
+  HostModel &hm = M->hm;
+  int rc;
+  if ((rc = upload(&M->d_funits, hm.funits.data(), hm.funits.size() * 4))) return rc;
+  if ((rc = upload(&M->d_fscore, hm.fscore.data(), hm.fscore.size() * 4))) return rc;
+  if ((rc = upload(&M->d_fleaf, hm.fleaf.data(), hm.fleaf.size() * 4))) return rc;
   return kOk;
 }
 
@@ -261,6 +456,30 @@ int upload_model(spm_cuda_model *M) {
   v.max_score = hm.max_score; v.smax = hm.smax; v.ring = hm.ring;
   v.add_dummy_prefix = hm.add_dummy_prefix; v.remove_extra_ws = hm.remove_extra_ws;
   v.escape_ws = hm.escape_ws; v.ws_suffix = hm.ws_suffix; v.has_unused = hm.has_unused;
+
+  // fast tier: shared-memory budget = hot trie prefix + DP rings of kFastThreads sentences
+  M->fast = false;
+  int smem_max = 0;
+  CUDA_TRY(cudaDeviceGetAttribute(&M->sm_count, cudaDevAttrMultiProcessorCount, M->device));
+  CUDA_TRY(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, M->device));
+  const int R = hm.max_piece_chars + 1;
+  const size_t ring_bytes = (size_t)R * kFastThreads * 8;
+  if (hm.fast_ok && ring_bytes + 32768 <= (size_t)smem_max) {
+    if ((rc = upload_fast_view(M))) return rc;
+    const size_t n_units = hm.funits.size();
+    const size_t hot_words = ((size_t)smem_max - ring_bytes - 256) / 4;
+    size_t ku = std::min(n_units, hot_words * 2 / 3 & ~(size_t)3);
+    size_t ks = std::min(n_units, (hot_words - ku) & ~(size_t)3);
+    if (ks == n_units) ku = std::min(n_units, (hot_words - ks) & ~(size_t)3);
+    FastParams &fp = M->fp;
+    fp.units = (const uint32_t *)M->d_funits.p; fp.score = (const float *)M->d_fscore.p;
+    fp.leaf_id = (const uint32_t *)M->d_fleaf.p;
+    fp.k_units = (uint32_t)ku; fp.k_scores = (uint32_t)ks; fp.n_units = (uint32_t)n_units;
+    fp.ring = R; fp.unk_score = v.unk_score; fp.smax = v.smax; fp.unk_id = v.unk_id;
+    M->fast_smem = (ku + ks) * 4 + ring_bytes;
+    CUDA_TRY(cudaFuncSetAttribute(k_encode_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)M->fast_smem));
+    M->fast = true;
+  }
   return kOk;
 }
 
@@ -276,6 +495,91 @@ int run_scan(const spm_cuda_model *M, cudaStream_t st, const int32_t *in, int64_
   k_scan_final<Op><<<(unsigned)nb, kScanThreads, 0, st>>>(in, n, op, partial, carry, out);
   *launches += 3;
   CUDA_TRY(cudaGetLastError());
+  return kOk;
+}
+
+int kev_record(const spm_cuda_model *M, cudaStream_t st, int which) {
+  while (M->kev.size() < 2 * (M->nk + 1)) {
+    cudaEvent_t a;
+    CUDA_TRY(cudaEventCreate(&a));
+    M->kev.push_back(a);
+  }
+  CUDA_TRY(cudaEventRecord(M->kev[2 * M->nk + which], st));
+  if (which == 1) ++M->nk;
+  return kOk;
+}
+
+// General tier over `gcount` sentences of the chunk (list: device array of
+// chunk-relative indices, or nullptr for "all sentences 0..gcount-1").
+// `timed`: this is the dominant kernel of a non-fast model (event pair recorded).
+int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text, const int64_t *d_off, int64_t c0,
+                const int32_t *list, int64_t gcount, bool timed, double *launches) {
+  if (gcount <= 0) return kOk;
+  int rc;
+  const int exp_ = M->hm.expansion;
+  if ((rc = M->g_need.ensure(gcount * 4))) return rc;
+  if ((rc = M->g_noff.ensure((gcount + 1) * 8))) return rc;
+  if ((rc = M->g_nlen.ensure(gcount * 4))) return rc;
+  if ((rc = M->g_words.ensure(gcount * 4))) return rc;
+  if ((rc = M->g_woff.ensure((gcount + 1) * 8))) return rc;
+  if ((rc = M->g_status.ensure(gcount * 4))) return rc;
+  int64_t *d_tot = (int64_t *)M->w_scalars.p + 4;  // [4] norm bytes, [5] scratch words
+  const unsigned grid = (unsigned)((gcount + kThreads - 1) / kThreads);
+  k_gen_prepare<<<grid, kThreads, 0, st>>>(d_off, c0, list, nullptr, 0, gcount, exp_, (int32_t *)M->g_need.p);
+  *launches += 1;
+  if ((rc = run_scan(M, st, (const int32_t *)M->g_need.p, gcount, IdentityOp(), (int64_t *)M->g_noff.p, d_tot, 0,
+                     launches)))
+    return rc;
+  int64_t total_norm = 0;
+  CUDA_TRY(cudaMemcpyAsync(&total_norm, d_tot, 8, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  if ((rc = M->g_norm.ensure((size_t)total_norm + 64))) return rc;
+  if ((rc = M->g_stage.ensure((size_t)total_norm * 4 + 64))) return rc;
+  k_gen_normalize<<<grid, kThreads, 0, st>>>(M->mv, d_text, d_off, c0, list, nullptr, 0, gcount,
+                                             (const int32_t *)M->g_need.p, (const int64_t *)M->g_noff.p,
+                                             (uint8_t *)M->g_norm.p, (int32_t *)M->g_nlen.p,
+                                             (int32_t *)M->g_words.p, (uint32_t *)M->g_status.p);
+  *launches += 1;
+  if ((rc = run_scan(M, st, (const int32_t *)M->g_words.p, gcount, IdentityOp(), (int64_t *)M->g_woff.p, d_tot + 1,
+                     0, launches)))
+    return rc;
+  int64_t total_words = 0;
+  CUDA_TRY(cudaMemcpyAsync(&total_words, d_tot + 1, 8, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  const int64_t kScratchBudgetWords = (int64_t)1 << 30;  // 4 GiB of Viterbi / agenda scratch per launch
+  uint32_t *d_stor = (uint32_t *)((int64_t *)M->w_scalars.p + 2);  // OR of all status words of the call
+  auto launch = [&](int64_t a, int64_t b, int64_t wbase) -> int {
+    const int64_t tn = b - a;
+    const unsigned g = (unsigned)((tn + kThreads - 1) / kThreads);
+    if (timed && (rc = kev_record(M, st, 0))) return rc;
+    k_gen_encode<<<g, kThreads, 0, st>>>(M->mv, list, nullptr, a, tn, (const int64_t *)M->g_noff.p + a,
+                                         (const uint8_t *)M->g_norm.p, (const int32_t *)M->g_nlen.p + a,
+                                         (const int64_t *)M->g_woff.p + a, wbase, (int32_t *)M->g_scratch.p,
+                                         (int32_t *)M->g_stage.p, (const uint32_t *)M->g_status.p + a,
+                                         (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
+                                         (int64_t *)M->w_srcoff.p, d_stor);
+    *launches += 1;
+    if (timed && (rc = kev_record(M, st, 1))) return rc;
+    CUDA_TRY(cudaGetLastError());
+    return kOk;
+  };
+  if (total_words <= kScratchBudgetWords) {
+    if ((rc = M->g_scratch.ensure((size_t)total_words * 4 + 64))) return rc;
+    return launch(0, gcount, 0);
+  }
+  // rare: slice the list so each launch stays within the scratch budget
+  M->h_woff.resize(gcount + 1);
+  CUDA_TRY(cudaMemcpyAsync(M->h_woff.data(), M->g_woff.p, (gcount + 1) * 8, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  int64_t max_one = 0;
+  for (int64_t t = 0; t < gcount; ++t) max_one = std::max(max_one, M->h_woff[t + 1] - M->h_woff[t]);
+  if ((rc = M->g_scratch.ensure((size_t)std::max(max_one, kScratchBudgetWords) * 4 + 64))) return rc;
+  for (int64_t a = 0; a < gcount;) {
+    int64_t b = a + 1;
+    while (b < gcount && M->h_woff[b + 1] - M->h_woff[a] <= kScratchBudgetWords) ++b;
+    if ((rc = launch(a, b, M->h_woff[a]))) return rc;
+    a = b;
+  }
   return kOk;
 }
 
@@ -314,11 +618,7 @@ int spm_cuda_model_load(const void *serialized_model, size_t len, int device, sp
 void spm_cuda_model_free(spm_cuda_model *M) {
   if (!M) return;
   cudaSetDevice(M->device);
-  DevBuf *bufs[] = {&M->d_units, &M->d_leaf, &M->d_uunits, &M->d_uleaf, &M->d_cm_units, &M->d_cm_pool,
-                    &M->d_first2, &M->w_text, &M->w_off, &M->w_ids, &M->w_idoff, &M->w_norm, &M->w_stage,
-                    &M->w_nlen, &M->w_words, &M->w_cnt, &M->w_status, &M->w_woff, &M->w_scratch,
-                    &M->w_partial, &M->w_scalars};
-  for (DevBuf *b : bufs) b->release();
+  for (DevBuf *b : M->all_bufs()) b->release();
   if (M->ev0) cudaEventDestroy(M->ev0);
   if (M->ev1) cudaEventDestroy(M->ev1);
   for (cudaEvent_t e : M->kev) cudaEventDestroy(e);
@@ -340,6 +640,10 @@ int spm_cuda_model_set_piece_types(spm_cuda_model *M, const uint8_t *types, int 
   CUDA_TRY(cudaSetDevice(M->device));
   CUDA_TRY(cudaMemcpy(M->d_leaf.p, M->hm.pieces.leaf.data(), M->hm.pieces.leaf.size() * 8, cudaMemcpyHostToDevice));
   M->mv.has_unused = M->hm.has_unused;
+  if (M->fast) {
+    int rc = upload_fast_view(M);
+    if (rc) return rc;
+  }
   return kOk;
 }
 
@@ -420,8 +724,10 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     CUDA_TRY(cudaStreamSynchronize(st));
   }
   const int64_t *ho = M->h_off.data();
-  for (int64_t i = 0; i < n; ++i)
+  for (int64_t i = 0; i < n; ++i) {
     if (ho[i + 1] < ho[i]) { g_err = "text_offsets must be non-decreasing"; return kInvalidArgument; }
+    if (ho[i + 1] - ho[i] > ((int64_t)1 << 26)) { g_err = "sentence longer than 64 MiB"; return kOutOfRange; }
+  }
   const int64_t text_lo = ho[0], text_hi = ho[n];
   if (host) {
     if ((rc = M->w_off.ensure((n + 1) * 8))) return rc;
@@ -449,75 +755,91 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   }
 
   if ((rc = M->w_scalars.ensure(64))) return rc;
-  int64_t *d_carry = (int64_t *)M->w_scalars.p;        // running CSR total
-  int64_t *d_wtotal = d_carry + 1;                      // scratch words of the chunk
-  uint32_t *d_stor = (uint32_t *)(d_carry + 2);         // OR of all status words
+  if ((rc = M->w_counters.ensure(C_COUNT * 4))) return rc;
+  int64_t *d_carry = (int64_t *)M->w_scalars.p;        // [0] running CSR total
+  uint32_t *d_counters = (uint32_t *)M->w_counters.p;
   CUDA_TRY(cudaMemsetAsync(M->w_scalars.p, 0, 64, st));
+  if (M->fast && M->w_hist.cap == 0) {
+    if ((rc = M->w_hist.ensure((kFastMaxChars + 2) * 8))) return rc;   // hist | bincur
+    CUDA_TRY(cudaMemsetAsync(M->w_hist.p, 0, (kFastMaxChars + 2) * 8, st));
+    if ((rc = M->w_back.ensure((size_t)(kFastMaxChars + 2) * M->sm_count * kFastThreads * 4))) return rc;
+  }
+  uint32_t *d_hist = (uint32_t *)M->w_hist.p, *d_bincur = d_hist ? d_hist + kFastMaxChars + 2 : nullptr;
+  M->nk = 0;
   CUDA_TRY(cudaEventRecord(M->ev0, st));
 
   const ExtraPlan plan = make_extra_plan(extra_options, M->bos_id, M->eos_id);
   const int exp_ = M->hm.expansion;
-  const int64_t kNormBudget = 256ll << 20, kMaxChunk = 1 << 20;
+  const int64_t kRawBudget = 256ll << 20, kMaxChunk = 1 << 21;
+  uint32_t stor = 0;
+  int64_t n_general = 0;
   int64_t c0 = 0;
-  size_t nk = 0;
   while (c0 < n) {
     int64_t c1 = c0, bytes = 0;
     while (c1 < n && c1 - c0 < kMaxChunk) {
-      const int64_t need = (int64_t)exp_ * (ho[c1 + 1] - ho[c1]) + 8;
-      if (c1 > c0 && bytes + need > kNormBudget) break;
+      const int64_t len = ho[c1 + 1] - ho[c1];
+      const int64_t need = M->fast ? len + 64 : (int64_t)exp_ * len + 8;
+      if (c1 > c0 && bytes + need > kRawBudget) break;
       bytes += need;
       ++c1;
     }
-    const int64_t cn = c1 - c0;
-    if ((rc = M->w_norm.ensure(bytes + 16))) return rc;
-    if ((rc = M->w_stage.ensure(bytes * 4 + 16))) return rc;
-    if ((rc = M->w_nlen.ensure(cn * 4))) return rc;
-    if ((rc = M->w_words.ensure(cn * 4))) return rc;
+    const int64_t cn = c1 - c0, raw = ho[c1] - ho[c0];
     if ((rc = M->w_cnt.ensure(cn * 4))) return rc;
     if ((rc = M->w_status.ensure(cn * 4))) return rc;
-    if ((rc = M->w_woff.ensure((cn + 1) * 8))) return rc;
-    const unsigned grid = (unsigned)((cn + kThreads - 1) / kThreads);
-    k_normalize<<<grid, kThreads, 0, st>>>(M->mv, d_text, d_off, c0, cn, exp_, (uint8_t *)M->w_norm.p,
-                                           (int32_t *)M->w_nlen.p, (int32_t *)M->w_words.p,
-                                           (uint32_t *)M->w_status.p);
-    launches += 1;
-    if ((rc = run_scan(M, st, (const int32_t *)M->w_words.p, cn, IdentityOp(), (int64_t *)M->w_woff.p, d_wtotal, 0,
-                       &launches)))
-      return rc;
-    int64_t wtotal = 0;
-    CUDA_TRY(cudaMemcpyAsync(&wtotal, d_wtotal, 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
-    if ((rc = M->w_scratch.ensure((size_t)wtotal * 4 + 16))) return rc;
-    if (M->kev.size() < 2 * (nk + 1)) {
-      cudaEvent_t a, b;
-      CUDA_TRY(cudaEventCreate(&a));
-      CUDA_TRY(cudaEventCreate(&b));
-      M->kev.push_back(a); M->kev.push_back(b);
+    if ((rc = M->w_srcoff.ensure(cn * 8))) return rc;
+    CUDA_TRY(cudaMemsetAsync(d_counters, 0, C_COUNT * 4, st));
+    if (M->fast) {
+      if ((rc = M->w_norm.ensure((size_t)(3 * raw + 64 * cn + 256)))) return rc;
+      if ((rc = M->w_stage.ensure((size_t)(raw + 16 * cn + 64) * 4))) return rc;
+      if ((rc = M->w_nlen.ensure(cn * 4))) return rc;
+      if ((rc = M->w_nchars.ensure(cn * 4))) return rc;
+      if ((rc = M->w_perm.ensure(cn * 4))) return rc;
+      if ((rc = M->w_genlist.ensure(cn * 4))) return rc;
+      const unsigned grid = (unsigned)((cn + kThreads - 1) / kThreads);
+      k_normalize_fast<<<grid, kThreads, 0, st>>>(M->mv, d_text, d_off, c0, cn, (uint8_t *)M->w_norm.p,
+                                                  (int32_t *)M->w_nlen.p, (int32_t *)M->w_nchars.p,
+                                                  (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
+                                                  (int32_t *)M->w_genlist.p, d_counters);
+      k_binscan<<<1, 1024, 0, st>>>(d_hist, d_bincur, d_counters);
+      k_scatter<<<(unsigned)((cn + 255) / 256), 256, 0, st>>>((const int32_t *)M->w_nchars.p, cn, d_bincur,
+                                                              (int32_t *)M->w_perm.p);
+      if ((rc = kev_record(M, st, 0))) return rc;
+      k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
+          M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+          (const int32_t *)M->w_perm.p, (uint32_t *)M->w_back.p, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
+          (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+      if ((rc = kev_record(M, st, 1))) return rc;
+      launches += 4;
+      CUDA_TRY(cudaGetLastError());
+      uint32_t hc[C_COUNT];
+      CUDA_TRY(cudaMemcpyAsync(hc, d_counters, sizeof(hc), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaStreamSynchronize(st));
+      n_general += hc[C_NGEN];
+      if ((rc = run_general(M, st, d_text, d_off, c0, (const int32_t *)M->w_genlist.p, hc[C_NGEN], false,
+                            &launches)))
+        return rc;
+    } else {
+      n_general += cn;
+      if ((rc = run_general(M, st, d_text, d_off, c0, nullptr, cn, true, &launches))) return rc;
     }
-    CUDA_TRY(cudaEventRecord(M->kev[2 * nk], st));
-    k_encode<<<grid, kThreads, 0, st>>>(M->mv, d_off, c0, cn, exp_, (const uint8_t *)M->w_norm.p,
-                                        (const int32_t *)M->w_nlen.p, (const int64_t *)M->w_woff.p,
-                                        (int32_t *)M->w_scratch.p, (int32_t *)M->w_stage.p,
-                                        (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_stor);
-    CUDA_TRY(cudaEventRecord(M->kev[2 * nk + 1], st));
-    ++nk;
-    launches += 1;
     FinalCountOp fop;
     fop.extra = plan.npre + plan.nsuf;
     if ((rc = run_scan(M, st, (const int32_t *)M->w_cnt.p, cn, fop, d_idoff + c0, d_carry, 1, &launches))) return rc;
     const unsigned cgrid = (unsigned)((cn * 32 + 255) / 256);
-    k_compact<<<cgrid, 256, 0, st>>>(plan, d_off, c0, cn, exp_, (const int32_t *)M->w_stage.p,
-                                     (const int32_t *)M->w_cnt.p, d_idoff, d_ids, d_cap);
+    k_compact<<<cgrid, 256, 0, st>>>(plan, d_off, c0, cn, (const int32_t *)M->w_stage.p,
+                                     (const int32_t *)M->g_stage.p, (const int64_t *)M->w_srcoff.p,
+                                     (const uint32_t *)M->w_status.p, (const int32_t *)M->w_cnt.p, d_idoff, d_ids,
+                                     d_cap);
     launches += 1;
     CUDA_TRY(cudaGetLastError());
     c0 = c1;
   }
   CUDA_TRY(cudaEventRecord(M->ev1, st));
-  int64_t hs[3] = {0, 0, 0};
-  CUDA_TRY(cudaMemcpyAsync(hs, M->w_scalars.p, 24, cudaMemcpyDeviceToHost, st));
+  int64_t hsc[3] = {0, 0, 0};
+  CUDA_TRY(cudaMemcpyAsync(hsc, M->w_scalars.p, 24, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
-  const int64_t total = hs[0];
-  const uint32_t stor = (uint32_t)hs[2];
+  const int64_t total = hsc[0];
+  stor = (uint32_t)hsc[2];
   if (n == 0) {
     const int64_t z = 0;
     if (host) id_offsets[0] = 0;
@@ -532,22 +854,20 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   float ms = 0;
   cudaEventElapsedTime(&ms, M->ev0, M->ev1);
   M->stats[0] = launches;
-  M->stats[1] = (double)n;  // v1: every sentence goes through the exact tier
+  M->stats[1] = (double)n_general;
   M->stats[2] = ms;
   double kms = 0;
-  for (size_t k = 0; k < nk; ++k) {
+  for (size_t k = 0; k < M->nk; ++k) {
     float t = 0;
     cudaEventElapsedTime(&t, M->kev[2 * k], M->kev[2 * k + 1]);
     kms += t;
   }
   M->stats[4] = kms;
-  M->stats[5] = (double)nk;
+  M->stats[5] = (double)M->nk;
   M->stats[6] = (double)n;
   M->stats[7] = (double)total;
   size_t ws = 0;
-  const DevBuf *bufs[] = {&M->w_text, &M->w_off, &M->w_ids, &M->w_idoff, &M->w_norm, &M->w_stage, &M->w_nlen,
-                          &M->w_words, &M->w_cnt, &M->w_status, &M->w_woff, &M->w_scratch, &M->w_partial, &M->w_scalars};
-  for (const DevBuf *b : bufs) ws += b->cap;
+  for (const DevBuf *b : M->all_bufs()) ws += b->cap;
   M->stats[3] = (double)ws;
   if (stor & (ST_NORM_OVERFLOW | ST_CAND_OVERFLOW | ST_IDS_OVERFLOW)) {
     g_err = "internal capacity exceeded in the exact tier (status " + std::to_string(stor) + ")";

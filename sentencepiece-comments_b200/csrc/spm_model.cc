@@ -135,6 +135,22 @@ bool build_xda(const std::vector<Key> &keys, HostTrie *out, std::string *err) {
     }
     nodes[cur].value = (int)k;
   }
+  // Text positions inside a word also start walks: every character-boundary
+  // suffix of a key is a fragment the walks see about as often as the key, so
+  // its path through the trie earns the key's weight too.
+  for (size_t k = 0; k < keys.size(); ++k) {
+    const std::string &s = keys[k].s;
+    for (size_t b = 1; b < s.size(); ++b) {
+      if (((unsigned char)s[b] & 0xC0) == 0x80) continue;
+      int cur = 0;
+      for (size_t i = b; i < s.size(); ++i) {
+        auto it = nodes[cur].kids.find((unsigned char)s[i]);
+        if (it == nodes[cur].kids.end()) break;
+        cur = it->second;
+        nodes[cur].weight += keys[k].weight;
+      }
+    }
+  }
   std::vector<uint32_t> &units = out->units;
   std::vector<uint2> &leaf = out->leaf;
   std::vector<uint8_t> used, base_used;
@@ -254,6 +270,12 @@ int piece_to_id(const HostModel &m, const std::string &piece) {
   return m.unk_id;
 }
 
+static int char_count(const std::string &s) {
+  int n = 0;
+  for (size_t i = 0; i < s.size();) { i += one_char_len((uint8_t)s[i]); ++n; }
+  return n;
+}
+
 void refresh_leaf_types(HostModel *m) {
   m->has_unused = false;
   for (auto t : m->type) if (t == T_UNUSED) m->has_unused = true;
@@ -262,6 +284,30 @@ void refresh_leaf_types(HostModel *m) {
       const uint32_t id = lf.x & 0x0FFFFFFFu;
       lf.x = id | ((uint32_t)m->type[id] << 28);
     }
+  // fast view (unigram): a node is a hit iff PopulateNodes would insert it
+  // (src/unigram_model.cc:582-595: UNUSED skipped; reserved pieces are not in trie_)
+  const size_t n = m->pieces.units.size();
+  m->funits = m->pieces.units;
+  m->fscore.assign(n, 0.0f);
+  m->fleaf.assign(n, 0);
+  for (size_t i = 0; i < n; ++i) {
+    const uint2 lf = m->pieces.leaf[i];
+    if (lf.x == 0xFFFFFFFFu) continue;
+    const uint32_t id = lf.x & 0x0FFFFFFFu, type = lf.x >> 28;
+    m->fleaf[i] = id;
+    if (type == T_NORMAL) {
+      m->fscore[i] = m->score[id];
+    } else if (type == T_USER_DEFINED) {
+      // length * max_score_ + 1.0: float product, double add, float store (:590-591)
+      const float len = (float)char_count(m->piece[id]);
+      volatile float prod = len * m->max_score;
+      m->fscore[i] = (float)((double)prod + 1.0);
+    } else {
+      m->funits[i] &= ~0x100u;
+      // a node that is neither a hit nor a parent must stop the walk
+      if (!(m->funits[i] & 0x200u)) m->funits[i] = 0;
+    }
+  }
 }
 
 int build_host_model(const void *data, size_t len, HostModel *m) {
@@ -291,6 +337,7 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
       m->unk_id = (int)i;
     }
     m->max_piece_bytes = std::max<int>(m->max_piece_bytes, (int)m->piece[i].size());
+    m->max_piece_chars = std::max<int>(m->max_piece_chars, char_count(m->piece[i]));
   }
   if (m->unk_id < 0) { m->error = "unk is not defined."; return kInternal; }
   if (m->max_piece_bytes > 4000) { m->error = "piece longer than 4000 bytes"; return kUnimplemented; }
@@ -341,6 +388,7 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
   for (size_t i = 0; i < V; ++i) smax = std::max(smax, fabsf(m->score[i]));
   smax = std::max(smax, (float)m->max_piece_bytes * fabsf(m->max_score) + 1.0f);
   m->smax = smax;
+  m->fast_ok = m->model_type == M_UNIGRAM && m->pieces.units.size() < 0x00FFFFFFu && m->max_piece_chars < 200;
   return kOk;
 }
 

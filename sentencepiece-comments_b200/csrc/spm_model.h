@@ -47,6 +47,12 @@ struct HostModel {
   float smax = 0;
   int expansion = 3;  // upper bound of normalized bytes per input byte
   bool has_unused = false;
+  // ---- fast view of the piece trie for the unigram fast tier (spm_fast.cuh)
+  std::vector<uint32_t> funits;   // pieces.units with has_leaf only where PopulateNodes inserts a node
+  std::vector<float> fscore;      // node score (USER_DEFINED bonus pre-computed)
+  std::vector<uint32_t> fleaf;    // node -> piece id
+  int max_piece_chars = 0;
+  bool fast_ok = false;           // the model fits the fast tier's packed records
   std::string error;
 };
 

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "spm_core.cuh"
+#include "spm_fast.cuh"
 #include "spm_model.h"
 
 using namespace spmb;
@@ -77,7 +78,42 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
     int32_t cnt = 0;
     if (nl < 0) { st |= ST_NORM_OVERFLOW; nl = 0; }
     core.resize(nl + 1);
-    if (mv.model_type == M_UNIGRAM) {
+    if (mv.model_type == M_UNIGRAM && capc == 0) {
+      // fast tier (spm_fast.cuh): padded, 8-byte aligned text; flagged sentences fall
+      // back to the exact tier exactly as the library does
+      if (!h->hm.fast_ok) return 12;
+      FastView fv;
+      fv.units = fv.units_hot = h->hm.funits.data();
+      fv.score = fv.score_hot = h->hm.fscore.data();
+      fv.leaf_id = h->hm.fleaf.data();
+      fv.n_units = (uint32_t)h->hm.funits.size();
+      fv.k_units = fv.n_units / 3; fv.k_scores = fv.n_units / 5;  // exercise both the hot and the cold branch
+      fv.ring = h->hm.max_piece_chars + 1;
+      fv.unk_score = mv.unk_score; fv.smax = mv.smax; fv.unk_id = mv.unk_id;
+      std::vector<uint64_t> tbuf((nl + kNormPad + 15) / 8 + 1, 0);
+      memcpy(tbuf.data(), norm.data(), nl);
+      std::vector<float> rbt(fv.ring);
+      std::vector<uint32_t> rbk(fv.ring), back(nl + 2);
+      std::vector<int32_t> rev(nl + 1);
+      cnt = fast_unigram(fv, (const uint8_t *)tbuf.data(), nl, rbt.data(), rbk.data(), 1, back.data(), 1, rev.data(), &st);
+      if (st & ST_CAND_OVERFLOW) {
+        st = ST_CAND_OVERFLOW;  // reported; result comes from the exact tier
+        words.assign(uni_scratch_words(mv.ring, 16, nl), 0);
+        UniScratch sc;
+        int32_t *w = words.data();
+        sc.ringM = (float *)w; w += mv.ring;
+        sc.ringCnt = (uint32_t *)w; w += mv.ring;
+        sc.candBt = (float *)w; w += mv.ring * 16;
+        w += ((w - words.data()) & 1);
+        sc.candRec = (uint64_t *)w; w += 2 * mv.ring * 16;
+        sc.back = (uint64_t *)w;
+        sc.stride = nl + 1;
+        uint32_t st2 = 0;
+        cnt = unigram_encode<16>(mv, norm.data(), nl, sc, core.data(), nl, &st2);
+      } else {
+        for (int32_t j = 0; j < cnt; ++j) core[j] = rev[cnt - 1 - j];
+      }
+    } else if (mv.model_type == M_UNIGRAM) {
       words.assign(uni_scratch_words(mv.ring, capc, nl), 0);
       UniScratch sc;
       int32_t *w = words.data();
