@@ -28,7 +28,8 @@
 namespace spmb {
 
 constexpr uint32_t kFastUnk = 0x00FFFFFFu;   // node field of an UNK back record
-constexpr int kFastMaxChars = 1024;          // longest sentence (characters) of the fast tier
+constexpr int kFastMaxRaw = 4096;            // fast tier: raw sentence length < this (bytes); also the sort key range
+constexpr int kFastExtraChars = 16;          // fast tier: characters <= raw bytes + this
 constexpr int kNormPad = 40;                 // zero bytes guaranteed after a normalized sentence
 
 struct FastView {
@@ -144,6 +145,164 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
   }
   *status |= flag;
   return cnt;
+}
+
+
+// ------------------------------------------------------------------ normaliser
+// 8 bytes at the 8-byte aligned address a, never touching memory outside [lo, hi)
+// (the caller's text buffer): whole-word load when it fits, guarded bytes at the edges.
+SPM_HD uint64_t fast_load8_guard(const uint8_t *a, const uint8_t *lo, const uint8_t *hi) {
+  if (a >= lo && a + 8 <= hi) return *reinterpret_cast<const uint64_t *>(a);
+  uint64_t v = 0;
+  for (int j = 7; j >= 0; --j) v = (v << 8) | ((a + j >= lo && a + j < hi) ? a[j] : 0);
+  return v;
+}
+
+// Output byte stream: accumulates into a 64-bit register, stores aligned 8-byte words.
+struct FastOut {
+  uint8_t *base;     // 8-byte aligned slot
+  uint64_t acc;
+  int32_t len;       // bytes appended so far
+  SPM_HD void put(uint32_t v, int k) {  // k in 1..4 bytes, little-endian in v
+    const int f = len & 7;
+    acc |= (uint64_t)v << (8 * f);
+    if (f + k >= 8) {
+      *reinterpret_cast<uint64_t *>(base + (len & ~7)) = acc;
+      acc = f + k > 8 ? (uint64_t)v >> (8 * (8 - f)) : 0;
+    }
+    len += k;
+  }
+  SPM_HD void flush() {
+    if (len & 7) *reinterpret_cast<uint64_t *>(base + (len & ~7)) = acc;
+  }
+};
+
+// Whole-sentence normalisation (src/normalizer.cc:88-211), same results as
+// normalize_sentence() of spm_core.cuh, restructured for one thread per sentence:
+// the raw text is read through a register window, the common case (no charsmap
+// rule / user symbol can start at this byte pair: 64 Kbit filter `first2`) is
+// resolved from the window alone, and output goes out as aligned 8-byte words.
+// in[0..n) lies inside the buffer [lo, hi).  out: 8-byte aligned slot of capacity
+// `cap` bytes + kNormPad + 8.  Returns the normalized length (the kNormPad bytes
+// after it are zeroed), or -1 when the text does not fit (caller: general tier).
+// *nchars_ub: upper bound of the character count.
+SPM_HDN int32_t fast_normalize(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t n,
+                               const uint8_t *lo, const uint8_t *hi, uint8_t *out, int32_t cap,
+                               int32_t *nchars_ub) {
+  *nchars_ub = 0;
+  if (n == 0) return 0;
+  const bool esc = m.escape_ws, rws = m.remove_extra_ws;
+  const uint32_t WS = esc ? 0x8196E2u : 0x20u;  // U+2581 little-endian, or ' '
+  const int WSL = esc ? 3 : 1;
+  const uint8_t *q = (const uint8_t *)((uintptr_t)in & ~(uintptr_t)7);
+  int r = (int)(in - q);
+  uint64_t a0 = fast_load8_guard(q, lo, hi), a1 = fast_load8_guard(q + 8, lo, hi);
+  FastOut o;
+  o.base = out; o.acc = 0; o.len = 0;
+  int32_t nch = 0;
+  bool lead = rws;          // still stripping leading spaces (:103-112)
+  bool started = false;     // dummy prefix emitted
+  bool prev_space = rws;    // is_prev_space
+  bool overflow = false;
+  int64_t p = 0;
+  while (p < n) {
+    const uint64_t w = fast_window(a0, a1, r);
+    const uint32_t b0 = (uint32_t)w & 0xFF, b1 = ((uint32_t)w >> 8) & 0xFF;
+    int consumed;
+    // ---- what does NormalizePrefix return here?
+    bool slow = m.user.n != 0 && ((m.user_first[b0 >> 5] >> (b0 & 31)) & 1);
+    if (!slow && m.cm_n != 0) {
+      const uint32_t key = (b0 << 8) | b1;
+      slow = n - p < 2 || ((first2[key >> 5] >> (key & 31)) & 1);  // first2 may live in shared memory
+    }
+    if (!slow) {
+      // one character straight from the window (src/normalizer.cc:271-291)
+      uint32_t v; int k;
+      if (b0 < 0x80) { v = b0; k = 1; }
+      else {
+        int mb;
+        uint8_t tmp[4] = {(uint8_t)b0, (uint8_t)b1, (uint8_t)(w >> 16), (uint8_t)(w >> 24)};
+        if (valid_decode_utf8(tmp, n - p, &mb)) { k = mb; v = (uint32_t)w & (mb == 4 ? 0xFFFFFFFFu : ((1u << (8 * mb)) - 1)); }
+        else { k = 3; v = 0xBDBFEFu; mb = 1; }   // U+FFFD, one byte consumed
+        consumed = mb;
+      }
+      if (b0 < 0x80) consumed = 1;
+      const bool is_space = b0 == 0x20;
+      if (lead && is_space) { p += 1; r += 1; goto advance; }   // np == " ": keep stripping
+      lead = false;
+      if (!started) {  // first real content: dummy prefix (:132-153)
+        started = true;
+        if (!m.ws_suffix && m.add_dummy_prefix) { o.put(WS, WSL); ++nch; }
+      }
+      if (is_space) {
+        if (!prev_space) { o.put(WS, WSL); ++nch; prev_space = true; }
+      } else {
+        o.put(v, k); ++nch;
+        prev_space = false;
+      }
+      if (!rws) prev_space = false;
+      p += consumed; r += consumed;
+    } else {
+      // a rule or a user-defined symbol may start here: the general step
+      const uint8_t *rep; int rl;
+      consumed = normalize_prefix(m, in + p, n - p, &rep, &rl);
+      const bool one_space = rep != nullptr && rl == 1 && rep[0] == ' ';
+      if (lead && one_space) { p += consumed; r += consumed; goto advance; }
+      lead = false;
+      if (!started) {
+        started = true;
+        if (!m.ws_suffix && m.add_dummy_prefix) { o.put(WS, WSL); ++nch; }
+      }
+      if (rep == nullptr) {
+        o.put(0xBDBFEFu, 3); ++nch;
+        prev_space = false;
+      } else {
+        int k = 0;
+        while (prev_space && k < rl && rep[k] == ' ') ++k;
+        if (k < rl) {
+          // keep room for the worst case of everything still to come (3 bytes per raw byte + suffix)
+          if ((int64_t)o.len + 3 * (rl - k) + 3 * (n - p - consumed) + 3 > cap) { overflow = true; break; }
+          for (; k < rl; ++k) {
+            const uint8_t b = rep[k];
+            if (b == ' ') o.put(WS, WSL); else o.put(b, 1);
+            ++nch;
+          }
+          prev_space = rep[rl - 1] == ' ';
+        }
+      }
+      if (!rws) prev_space = false;
+      p += consumed; r += consumed;
+    }
+  advance:
+    while (r >= 8) { a0 = a1; q += 8; a1 = fast_load8_guard(q + 8, lo, hi); r -= 8; }
+  }
+  if (overflow) return -1;
+  o.flush();
+  int32_t len = o.len;
+  if (rws) {  // strip trailing whitespace symbols (:191-201): re-read our own tail
+    if (esc) { while (len >= 3 && out[len - 3] == 0xE2 && out[len - 2] == 0x96 && out[len - 1] == 0x81) { len -= 3; --nch; } }
+    else { while (len >= 1 && out[len - 1] == ' ') { len -= 1; --nch; } }
+  }
+  if (m.ws_suffix && m.add_dummy_prefix && started) {
+    o.len = len;
+    o.acc = (len & 7) ? *reinterpret_cast<uint64_t *>(out + (len & ~7)) & ((1ull << (8 * (len & 7))) - 1) : 0;
+    o.put(WS, WSL); ++nch;
+    o.flush();
+    len = o.len;
+  }
+  // zero padding: finish the current word, then kNormPad more bytes
+  {
+    const int f = len & 7;
+    int32_t z = len;
+    if (f) {
+      uint64_t *wp = reinterpret_cast<uint64_t *>(out + (len & ~7));
+      *wp &= (1ull << (8 * f)) - 1;
+      z = (len & ~7) + 8;
+    }
+    for (int32_t k = 0; k < kNormPad; k += 8) *reinterpret_cast<uint64_t *>(out + z + k) = 0;
+  }
+  *nchars_ub = nch;
+  return len;
 }
 
 }  // namespace spmb

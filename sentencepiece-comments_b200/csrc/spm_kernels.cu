@@ -16,7 +16,7 @@
 //                     shared memory / registers (spm_fast.cuh;
 //                     src/unigram_model.cc:535-604,222-261)
 //   GENERAL TIER (BPE models; unigram sentences the fast tier flags: near-tied
-//                 Viterbi candidates, heavy expansion, > kFastMaxChars characters)
+//                 Viterbi candidates, heavy expansion, >= kFastMaxRaw bytes)
 //   k_gen_normalize / k_gen_encode  one thread per listed sentence, exact candidate
 //                     lists / BPE agenda in global scratch (spm_core.cuh;
 //                     src/bpe_model.cc:37-199)
@@ -131,53 +131,43 @@ k_gen_encode(ModelView mv, const int32_t *list, const uint32_t *count, int64_t t
 }
 
 // ---------------------------------------------------------------- fast tier
-// Slot of sentence i (chunk-relative t) in the normalized buffer: 16-byte aligned,
-// room for 3 * len + 8 normalized bytes followed by >= kNormPad zero bytes.
+// Slot of sentence t (chunk-relative) in the normalized buffer: 16-byte aligned, room
+// for 3 * len + 72 normalized bytes, kNormPad zero bytes and word-granular stores.
 __device__ __forceinline__ int64_t fast_norm_base(const int64_t *off, int64_t c0, int64_t t) {
-  return ((3 * (off[c0 + t] - off[c0]) + 15) & ~(int64_t)15) + 64 * t;
+  return ((3 * (off[c0 + t] - off[c0]) + 15) & ~(int64_t)15) + 160 * t;
 }
-// Slot in the id staging buffer: len + 16 ids (ids <= characters <= that, else general tier).
+// Slot in the id staging buffer: len + kFastExtraChars ids (ids <= characters).
 __device__ __forceinline__ int64_t fast_stage_base(const int64_t *off, int64_t c0, int64_t t) {
-  return (off[c0 + t] - off[c0]) + 16 * t;
+  return (off[c0 + t] - off[c0]) + kFastExtraChars * t;
 }
 
-// v2a: one thread per sentence (to be replaced by the warp-cooperative normaliser).
-__global__ void __launch_bounds__(kThreads)
-k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn, uint8_t *norm,
-                 int32_t *nlen, int32_t *nchars, int32_t *cnt, uint32_t *status, uint32_t *hist, int32_t *gen_list,
-                 uint32_t *counters) {
+// Sort key = raw length.  Empty sentences produce nothing; sentences of kFastMaxRaw bytes
+// or more go straight to the general tier.
+__global__ void __launch_bounds__(256)
+k_hist(const int64_t *off, int64_t c0, int64_t cn, int32_t *cnt, uint32_t *status, uint32_t *hist,
+       int32_t *gen_list, uint32_t *counters) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= cn) return;
-  const int64_t i = c0 + t;
-  const int64_t len = off[i + 1] - off[i];
-  uint8_t *out = norm + fast_norm_base(off, c0, t);
-  int32_t nl = normalize_sentence(mv, text + off[i], len, out, 3 * len + 8);
-  bool general = false;
-  int32_t nc = 0;
-  if (nl < 0) {
-    general = true;
-    nl = 0;
-  } else {
-    for (int32_t p = 0; p < nl;) { p += one_char_len(out[p]); ++nc; }
-    for (int k = 0; k < kNormPad; ++k) out[nl + k] = 0;
-    if (nc > kFastMaxChars || nc > len + 16) general = true;
-  }
-  nlen[t] = nl;
-  nchars[t] = nc;
+  const int64_t len = off[c0 + t + 1] - off[c0 + t];
   cnt[t] = 0;
   status[t] = 0;
-  if (general) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
-  else if (nc > 0) atomicAdd(&hist[nc], 1u);
-  if (general) nchars[t] = -1;
+  if (len >= kFastMaxRaw) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
+  else if (len > 0) atomicAdd(&hist[len], 1u);
 }
 
-// hist[1..kFastMaxChars] -> first slot of each bin in DESCENDING key order; total -> counters[C_NFAST]
+// hist[1..kFastMaxRaw-1] -> first slot of each bin in DESCENDING key order; total -> counters[C_NFAST]
 __global__ void __launch_bounds__(1024) k_binscan(uint32_t *hist, uint32_t *bincur, uint32_t *counters) {
   __shared__ uint32_t wsum[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int key = kFastMaxChars - tid;  // tid 0 -> longest
-  const uint32_t v = key >= 1 ? hist[key] : 0;
-  uint32_t inc = v;
+  constexpr int kPer = kFastMaxRaw / 1024;
+  uint32_t v[kPer], sum = 0;
+#pragma unroll
+  for (int j = 0; j < kPer; ++j) {  // thread 0 owns the longest keys
+    const int key = kFastMaxRaw - 1 - (tid * kPer + j);
+    v[j] = key >= 1 ? hist[key] : 0;
+    sum += v[j];
+  }
+  uint32_t inc = sum;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
@@ -195,17 +185,47 @@ __global__ void __launch_bounds__(1024) k_binscan(uint32_t *hist, uint32_t *binc
     wsum[lane] = s;
   }
   __syncthreads();
-  const uint32_t base = wid ? wsum[wid - 1] : 0;
-  if (key >= 1) { bincur[key] = base + inc - v; hist[key] = 0; }
-  if (tid == 1023) counters[C_NFAST] = base + inc;
+  uint32_t run = (wid ? wsum[wid - 1] : 0) + inc - sum;
+#pragma unroll
+  for (int j = 0; j < kPer; ++j) {
+    const int key = kFastMaxRaw - 1 - (tid * kPer + j);
+    if (key >= 1) { bincur[key] = run; hist[key] = 0; }
+    run += v[j];
+  }
+  if (tid == 1023) counters[C_NFAST] = run;
 }
 
 __global__ void __launch_bounds__(256)
-k_scatter(const int32_t *nchars, int64_t cn, uint32_t *bincur, int32_t *perm) {
+k_scatter(const int64_t *off, int64_t c0, int64_t cn, uint32_t *bincur, int32_t *perm) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= cn) return;
-  const int32_t nc = nchars[t];
-  if (nc > 0) perm[atomicAdd(&bincur[nc], 1u)] = (int32_t)t;
+  const int64_t len = off[c0 + t + 1] - off[c0 + t];
+  if (len > 0 && len < kFastMaxRaw) perm[atomicAdd(&bincur[len], 1u)] = (int32_t)t;
+}
+
+// One thread per sentence, in sorted order (lanes of a warp: equal raw lengths).
+constexpr int kNormThreads = 256;
+__global__ void __launch_bounds__(kNormThreads)
+k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c0, const uint8_t *lo,
+                 const uint8_t *hi, const int32_t *perm, uint8_t *norm, int32_t *nlen, int32_t *gen_list,
+                 uint32_t *counters) {
+  __shared__ uint32_t first2[2048];
+  if (mv.cm_first2 != nullptr)
+    for (int k = threadIdx.x; k < 2048; k += kNormThreads) first2[k] = mv.cm_first2[k];
+  __syncthreads();
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)counters[C_NFAST]) return;
+  const int32_t t = perm[idx];
+  const int64_t i = c0 + t;
+  const int64_t len = off[i + 1] - off[i];
+  int32_t nc = 0;
+  int32_t nl = fast_normalize(mv, first2, text + off[i], len, lo, hi, norm + fast_norm_base(off, c0, t),
+                              (int32_t)(3 * len + 72), &nc);
+  if (nl < 0 || nc > len + kFastExtraChars) {
+    gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
+    nl = -1;
+  }
+  nlen[t] = nl;
 }
 
 struct FastParams {
@@ -249,7 +269,9 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
     if (idx < nfast) {
       const int32_t t = perm[idx];
       uint32_t st = 0;
-      const int32_t c = fast_unigram(fv, norm + fast_norm_base(off, c0, t), nlen[t], ring_bt + threadIdx.x,
+      const int32_t nl = nlen[t];
+      const int32_t c = nl <= 0 ? 0 :
+                        fast_unigram(fv, norm + fast_norm_base(off, c0, t), nl, ring_bt + threadIdx.x,
                                      ring_bk + threadIdx.x, kFastThreads, myback, bstride,
                                      stage + fast_stage_base(off, c0, t), &st);
       if (st) {
@@ -760,11 +782,10 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   uint32_t *d_counters = (uint32_t *)M->w_counters.p;
   CUDA_TRY(cudaMemsetAsync(M->w_scalars.p, 0, 64, st));
   if (M->fast && M->w_hist.cap == 0) {
-    if ((rc = M->w_hist.ensure((kFastMaxChars + 2) * 8))) return rc;   // hist | bincur
-    CUDA_TRY(cudaMemsetAsync(M->w_hist.p, 0, (kFastMaxChars + 2) * 8, st));
-    if ((rc = M->w_back.ensure((size_t)(kFastMaxChars + 2) * M->sm_count * kFastThreads * 4))) return rc;
+    if ((rc = M->w_hist.ensure((size_t)kFastMaxRaw * 8))) return rc;   // hist | bincur
+    CUDA_TRY(cudaMemsetAsync(M->w_hist.p, 0, (size_t)kFastMaxRaw * 8, st));
   }
-  uint32_t *d_hist = (uint32_t *)M->w_hist.p, *d_bincur = d_hist ? d_hist + kFastMaxChars + 2 : nullptr;
+  uint32_t *d_hist = (uint32_t *)M->w_hist.p, *d_bincur = d_hist ? d_hist + kFastMaxRaw : nullptr;
   M->nk = 0;
   CUDA_TRY(cudaEventRecord(M->ev0, st));
 
@@ -789,20 +810,27 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     if ((rc = M->w_srcoff.ensure(cn * 8))) return rc;
     CUDA_TRY(cudaMemsetAsync(d_counters, 0, C_COUNT * 4, st));
     if (M->fast) {
-      if ((rc = M->w_norm.ensure((size_t)(3 * raw + 64 * cn + 256)))) return rc;
-      if ((rc = M->w_stage.ensure((size_t)(raw + 16 * cn + 64) * 4))) return rc;
+      if ((rc = M->w_norm.ensure((size_t)(3 * raw + 160 * cn + 256)))) return rc;
+      if ((rc = M->w_stage.ensure((size_t)(raw + kFastExtraChars * cn + 64) * 4))) return rc;
       if ((rc = M->w_nlen.ensure(cn * 4))) return rc;
-      if ((rc = M->w_nchars.ensure(cn * 4))) return rc;
       if ((rc = M->w_perm.ensure(cn * 4))) return rc;
       if ((rc = M->w_genlist.ensure(cn * 4))) return rc;
-      const unsigned grid = (unsigned)((cn + kThreads - 1) / kThreads);
-      k_normalize_fast<<<grid, kThreads, 0, st>>>(M->mv, d_text, d_off, c0, cn, (uint8_t *)M->w_norm.p,
-                                                  (int32_t *)M->w_nlen.p, (int32_t *)M->w_nchars.p,
-                                                  (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
-                                                  (int32_t *)M->w_genlist.p, d_counters);
+      int64_t max_raw = 0;
+      for (int64_t i = c0; i < c1; ++i) {
+        const int64_t len = ho[i + 1] - ho[i];
+        if (len < kFastMaxRaw && len > max_raw) max_raw = len;
+      }
+      // back-pointer rows: one per character (<= raw + kFastExtraChars) + BOS/EOS rows
+      if ((rc = M->w_back.ensure((size_t)(max_raw + kFastExtraChars + 2) * M->sm_count * kFastThreads * 4))) return rc;
+      const unsigned g256 = (unsigned)((cn + 255) / 256);
+      k_hist<<<g256, 256, 0, st>>>(d_off, c0, cn, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
+                                   (int32_t *)M->w_genlist.p, d_counters);
       k_binscan<<<1, 1024, 0, st>>>(d_hist, d_bincur, d_counters);
-      k_scatter<<<(unsigned)((cn + 255) / 256), 256, 0, st>>>((const int32_t *)M->w_nchars.p, cn, d_bincur,
-                                                              (int32_t *)M->w_perm.p);
+      k_scatter<<<g256, 256, 0, st>>>(d_off, c0, cn, d_bincur, (int32_t *)M->w_perm.p);
+      k_normalize_fast<<<(unsigned)((cn + kNormThreads - 1) / kNormThreads), kNormThreads, 0, st>>>(
+          M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p,
+          (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
+      launches += 1;
       if ((rc = kev_record(M, st, 0))) return rc;
       k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
           M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,

@@ -59,6 +59,27 @@ int64_t hc_normalize(void *p, const uint8_t *in, int64_t n, uint8_t *out, int64_
   return normalize_sentence(((Handle *)p)->mv, in, n, out, cap);
 }
 
+// fast-tier normaliser (spm_fast.cuh) on a copy of the text placed at an odd address
+// inside a guard-banded buffer; returns the length or -1 (does not fit: general tier).
+int64_t hc_normalize_fast(void *p, const uint8_t *in, int64_t n, uint8_t *out, int64_t cap, int32_t *nchars) {
+  Handle *h = (Handle *)p;
+  if (n == 0) return 0;  // the kernels never see empty sentences
+  std::vector<uint64_t> ibuf((n + 64) / 8 + 2, 0x5A5A5A5A5A5A5A5Aull);  // junk around the text must not leak in
+  uint8_t *src = (uint8_t *)ibuf.data() + 11;
+  memcpy(src, in, n);
+  const int32_t fcap = (int32_t)(3 * n + 72);
+  std::vector<uint64_t> obuf((fcap + kNormPad + 16) / 8 + 2, 0x7777777777777777ull);
+  int32_t nc = 0;
+  const int32_t nl = fast_normalize(h->mv, h->mv.cm_first2, src, n, src, src + n, (uint8_t *)obuf.data(), fcap, &nc);
+  if (nchars) *nchars = nc;
+  if (nl < 0) return -1;
+  const uint8_t *o = (const uint8_t *)obuf.data();
+  for (int k = 0; k < kNormPad; ++k) if (o[nl + k] != 0) return -2;  // padding contract
+  if (nl > cap) return -3;
+  memcpy(out, o, nl);
+  return nl;
+}
+
 // capc: candidate capacity of the unigram tier to emulate (1, 4 or 16).
 // status[n] receives the per-sentence status bits.
 int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n, uint32_t opts, int capc,
@@ -78,6 +99,14 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
     int32_t cnt = 0;
     if (nl < 0) { st |= ST_NORM_OVERFLOW; nl = 0; }
     core.resize(nl + 1);
+    if (mv.model_type == M_UNIGRAM && capc == 0 && len > 0) {
+      // same routing as the library: fast normaliser first, general tier when it does not fit
+      std::vector<uint8_t> fn(3 * len + 72 + 8);
+      int32_t fnc = 0;
+      const int64_t fl = hc_normalize_fast(h, text + off[i], len, fn.data(), 3 * len + 72, &fnc);
+      if (fl < -1) return 100 - (int)fl;
+      if (fl >= 0 && (fl != nl || memcmp(fn.data(), norm.data(), nl) != 0)) return 99;
+    }
     if (mv.model_type == M_UNIGRAM && capc == 0) {
       // fast tier (spm_fast.cuh): padded, 8-byte aligned text; flagged sentences fall
       // back to the exact tier exactly as the library does
