@@ -17,12 +17,15 @@
 //     match in the reference either: darts keys are NUL-terminated);
 //   * the DP keeps, per pending end position (a ring of max-piece-chars + 1
 //     character slots), the best backtrace score and its (node, chars) record;
-//     the record of a position is final when the scan arrives there and is
-//     stored to a back-pointer row that the 32 lanes of a warp write together
-//     (lanes advance one character per iteration in lock step).
+//     the record of a position is final when the scan arrives there and goes to
+//     the thread's own back-pointer array, four records per 16-byte store;
+//   * the loop is flattened (one trie step OR one character advance per
+//     iteration), so the lanes of a warp never wait for the deepest walk.
 // Everything is `__host__ __device__` so tests/host_core.cc can run the very
 // same code on the CPU against the oracle.
 #pragma once
+#include <string.h>
+
 #include "spm_core.cuh"
 
 namespace spmb {
@@ -38,6 +41,7 @@ struct FastView {
   const uint32_t *leaf_id;    // global: node -> piece id (valid where has_leaf)
   const uint32_t *units_hot;  // first k_units entries (shared memory on the device)
   const float *score_hot;     // first k_scores entries
+  uint32_t units_hot_saddr, score_hot_saddr;  // device: 32-bit shared addresses of the hot copies
   uint32_t k_units, k_scores, n_units;
   int32_t ring;               // R = max piece characters + 1
   float unk_score, smax;
@@ -52,91 +56,143 @@ SPM_HD uint64_t fast_window(uint64_t lo, uint64_t hi, int r) {
   const int sh = r * 8;
   return (lo >> sh) | ((hi << 1) << (63 - sh));
 }
+// bytes [r, r+4) of the 8-byte little-endian pair (lo, hi), r in [0, 4): one PRMT
+SPM_HD uint32_t fast_window4(uint32_t lo, uint32_t hi, uint32_t sel) {
+#if defined(__CUDA_ARCH__)
+  return __byte_perm(lo, hi, sel);
+#else
+  const int sh = (int)(sel & 7) * 8;   // sel = 0x3210 + 0x1111 * r
+  return sh ? (lo >> sh) | (hi << (32 - sh)) : lo;
+#endif
+}
+// table[idx]: the first `k` entries live in the hot copy (shared memory on the
+// device, addressed by its 32-bit shared address `hot_saddr`), the rest in global.
+// Two predicated loads, no branch.
+template <class T>
+SPM_HD T fast_ld_tiered(const T *hot, uint32_t hot_saddr, const T *cold, uint32_t idx, uint32_t k) {
+#if defined(__CUDA_ARCH__)
+  uint32_t v;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\t"
+      "@p ld.shared.u32 %0, [%3];\n\t@!p ld.global.nc.u32 %0, [%4];\n\t}"
+      : "=r"(v)
+      : "r"(idx), "r"(k), "r"(hot_saddr + idx * 4u), "l"(cold + idx));
+  T out;
+  memcpy(&out, &v, 4);
+  return out;
+#else
+  (void)hot_saddr;
+  return idx < k ? hot[idx] : cold[idx];
+#endif
+}
 
-// One sentence.  s: normalized text (8-byte aligned, followed by >= kNormPad zero
-// bytes), n bytes.  ring_bt / ring_bk: R slots, element k at [k * rstride].
-// back: rows of back records, row c at [c * bstride]; rows 0..nchars are written.
+// One sentence.  s: normalized VALID UTF-8 text (8-byte aligned, followed by >= kNormPad
+// zero bytes), n bytes.  ring_bt / ring_bk: R slots, element k at [k * rstride].
+// back: this thread's own back-record array (nchars + 2 entries).
 // out: ids in REVERSE order (at most nchars); returns their count.
+//
+// The loop is flattened: every iteration is either one trie step of the walk that
+// starts at the current character, or -- when that walk has ended -- the move to
+// the next character (all nodes ending there are known by then, so its backtrace
+// score is final).  Lanes of a warp therefore never wait for the deepest walk.
 SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, float *ring_bt,
-                             uint32_t *ring_bk, int rstride, uint32_t *back, int64_t bstride,
-                             int32_t *out, uint32_t *status) {
+                             uint32_t *ring_bk, int rstride, uint32_t *back, int32_t *out,
+                             uint32_t *status) {
   if (n <= 0) return 0;
   const int R = fv.ring;
-  const float NEG = -INFINITY;
+  const float NEG = -3.0e38f;     // "no node ends here yet" (finite, so the tie tolerance stays finite)
+  const float TOL = 9.5367431640625e-07f;  // 2^-20, see unigram_encode() in spm_core.cuh
   for (int k = 0; k < R; ++k) ring_bt[k * rstride] = NEG;
-  ring_bt[0] = 0.0f;
-  ring_bk[0] = 0;
   const uint32_t root = fv.units_hot[0];
+  const uint32_t *sw = reinterpret_cast<const uint32_t *>(s);
   uint32_t flag = 0;
-  int32_t p = 0, ci = 0, ridx = 0, q = 0;
-  uint64_t a0 = fast_load8(s), a1 = fast_load8(s + 8), a2 = fast_load8(s + 16);
-  while (p < n) {
-    const float bt_p = ring_bt[ridx * rstride];
-    back[(int64_t)ci * bstride] = ring_bk[ridx * rstride];
-    ring_bt[ridx * rstride] = NEG;
-    const int r = p - q;
-    uint64_t cur = fast_window(a0, a1, r);
-    int cl = one_char_len((uint8_t)cur);
-    if (cl > n - p) cl = n - p;
-    int nb = cl, k = 1, d = 0;
-    bool single = false;
-    uint32_t u = root;
-    for (;;) {
-      const uint32_t c = (uint32_t)cur & 0xFFu;
-      if (!(u & 0x200u) || c == 0) break;
-      const uint32_t child = (u >> 10) ^ c;
-      u = child < fv.k_units ? fv.units_hot[child] : SPM_LDG(fv.units + child);
-      if ((u & 0xFFu) != c || !(u & 0x300u)) break;
-      if (d == nb) { nb = d + one_char_len((uint8_t)c); ++k; }
+  int32_t p = 0, ci = 0, ridx = 0;
+  // text window: words w0..w3 = bytes [4*qw, 4*qw + 16), w4 prefetched; r = p - 4*qw in [0, 4)
+  int32_t qw = 0;
+  uint32_t w0 = sw[0], w1 = sw[1], w2 = sw[2], w3 = sw[3], w4 = sw[4];
+  uint32_t r = 0, sel = 0x3210u;
+  float bt_p = 0.0f;              // BOS
+  uint32_t cur = w0;
+  int cl = one_char_len((uint8_t)cur);
+  uint32_t u = root;
+  int d = 0, k = 0;
+  bool single = false;
+  for (;;) {
+    const uint32_t c = cur & 0xFFu;
+    bool ok = (u & 0x200u) && c != 0;
+    uint32_t child = 0, v = 0;
+    if (ok) {
+      child = (u >> 10) ^ c;
+      v = fast_ld_tiered(fv.units_hot, fv.units_hot_saddr, fv.units, child, fv.k_units);
+      ok = (v & 0xFFu) == c && (v & 0x300u) != 0;
+    }
+    if (ok) {
+      // ---- one step down the trie
+      u = v;
       ++d;
-      if (u & 0x100u) {
-        const float sc = child < fv.k_scores ? fv.score_hot[child] : SPM_LDG(fv.score + child);
+      if ((c & 0xC0u) != 0x80u) ++k;       // characters started so far (text is valid UTF-8)
+      cur >>= 8;
+      if (v & 0x100u) {                    // a piece ends here: node (ci -> ci + k)
+        const float sc = fast_ld_tiered(fv.score_hot, fv.score_hot_saddr, fv.score, child, fv.k_scores);
         const float bt = bt_p + sc;
         int slot = ridx + k;
         if (slot >= R) slot -= R;
         const float M = ring_bt[slot * rstride];
-        if (bt > M) {
-          if (M != NEG && bt - M <= (fmaxf(fabsf(M), fabsf(bt)) + fv.smax) * 9.5367431640625e-07f) flag = ST_CAND_OVERFLOW;
+        const float diff = bt - M;
+        if (fabsf(diff) <= (fmaxf(fabsf(M), fabsf(bt)) + fv.smax) * TOL && diff != 0.0f) flag = ST_CAND_OVERFLOW;
+        if (diff > 0.0f) {                 // strict '>' keeps the first (longest) of equals
           ring_bt[slot * rstride] = bt;
           ring_bk[slot * rstride] = child | ((uint32_t)k << 24);
-        } else if (bt < M) {
-          if (M - bt <= (fmaxf(fabsf(M), fabsf(bt)) + fv.smax) * 9.5367431640625e-07f) flag = ST_CAND_OVERFLOW;
         }
         if (k == 1) single = true;
       }
-      cur >>= 8;
-      if ((d & 7) == 0) {  // crossed into the next 8 bytes of text
-        if (d == 8) cur = fast_window(a1, a2, r);
-        else {             // pieces longer than 16 bytes: read the text directly
+      if ((d & 3) == 0) {                  // crossed into the next 4 bytes of text
+        if (d == 4) cur = fast_window4(w1, w2, sel);
+        else if (d == 8) cur = fast_window4(w2, w3, sel);
+        else if (d == 12) cur = fast_window4(w3, w4, sel);
+        else {                             // pieces longer than 16 bytes: read the text directly
           cur = 0;
-          for (int j = 7; j >= 0; --j) cur = (cur << 8) | (p + d + j < n ? s[p + d + j] : 0);
+          for (int j = 3; j >= 0; --j) cur = (cur << 8) | (p + d + j < n ? s[p + d + j] : 0);
         }
       }
-    }
-    if (!single) {  // UNK node of one character (unigram_model.cc:598-602)
-      const float bt = bt_p + fv.unk_score;
-      int slot = ridx + 1;
-      if (slot >= R) slot -= R;
-      const float M = ring_bt[slot * rstride];
-      if (bt > M) {
-        if (M != NEG && bt - M <= (fmaxf(fabsf(M), fabsf(bt)) + fv.smax) * 9.5367431640625e-07f) flag = ST_CAND_OVERFLOW;
-        ring_bt[slot * rstride] = bt;
-        ring_bk[slot * rstride] = kFastUnk | (1u << 24);
-      } else if (bt < M) {
-        if (M - bt <= (fmaxf(fabsf(M), fabsf(bt)) + fv.smax) * 9.5367431640625e-07f) flag = ST_CAND_OVERFLOW;
+    } else {
+      // ---- the walk from character ci is over: move to character ci + 1
+      if (!single) {  // UNK node of one character (unigram_model.cc:598-602)
+        const float bt = bt_p + fv.unk_score;
+        int slot = ridx + 1;
+        if (slot >= R) slot -= R;
+        const float M = ring_bt[slot * rstride];
+        const float diff = bt - M;
+        if (fabsf(diff) <= (fmaxf(fabsf(M), fabsf(bt)) + fv.smax) * TOL && diff != 0.0f) flag = ST_CAND_OVERFLOW;
+        if (diff > 0.0f) {
+          ring_bt[slot * rstride] = bt;
+          ring_bk[slot * rstride] = kFastUnk | (1u << 24);
+        }
       }
+      p += cl;
+      r += cl;
+      ++ci;
+      if (++ridx == R) ridx = 0;
+      bt_p = ring_bt[ridx * rstride];
+      back[ci] = ring_bk[ridx * rstride];
+      ring_bt[ridx * rstride] = NEG;
+      if (p >= n) break;
+      if (r >= 4) {                        // slide the window by one word; w4 was loaded >= 4 bytes ago
+        r -= 4; ++qw;
+        w0 = w1; w1 = w2; w2 = w3; w3 = w4;
+        w4 = sw[qw + 4];
+      }
+      sel = 0x3210u + 0x1111u * r;
+      cur = fast_window4(w0, w1, sel);
+      cl = one_char_len((uint8_t)cur);
+      u = root; d = 0; k = 0; single = false;
     }
-    p += cl;
-    ++ci;
-    if (++ridx == R) ridx = 0;
-    while (p - q >= 8) { a0 = a1; a1 = a2; a2 = fast_load8(s + q + 24); q += 8; }
   }
-  back[(int64_t)ci * bstride] = ring_bk[ridx * rstride];  // EOS picks the best node ending at n
   // backtrace; runs of unknown pieces collapse to one id (sentencepiece_processor.cc:525-529)
   int32_t cnt = 0;
   bool prev_unk = false;
   while (ci > 0) {
-    const uint32_t rec = back[(int64_t)ci * bstride];
+    const uint32_t rec = back[ci];
     const uint32_t node = rec & 0x00FFFFFFu;
     const bool is_unk = node == kFastUnk;
     if (!(is_unk && prev_unk)) out[cnt++] = is_unk ? fv.unk_id : (int32_t)SPM_LDG(fv.leaf_id + node);

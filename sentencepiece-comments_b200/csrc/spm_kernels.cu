@@ -55,7 +55,7 @@ thread_local std::string g_err;
 
 constexpr int kCapc = 8;          // near-tie candidates kept per position by the exact tier
 constexpr int kThreads = 128;     // general-tier block size
-constexpr int kFastThreads = 512; // fast-tier block size (one persistent CTA per SM)
+constexpr int kFastThreads = 768; // fast-tier block size (one persistent CTA per SM)
 constexpr uint32_t ST_GEN = 1u << 16;   // sentence was encoded by the general tier (ids in gstage, forward order)
 
 // device-side counters of one chunk
@@ -241,8 +241,8 @@ struct FastParams {
 // Persistent CTAs (one per SM).  Shared memory: hot units | hot scores | ring_bt[R][T] | ring_bk[R][T].
 __global__ void __launch_bounds__(kFastThreads, 1)
 k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
-              const int32_t *perm, uint32_t *back, int32_t *stage, int32_t *cnt, uint32_t *status,
-              int32_t *gen_list, uint32_t *counters) {
+              const int32_t *perm, uint32_t *back, int64_t back_rows, int32_t *stage, int32_t *cnt,
+              uint32_t *status, int32_t *gen_list, uint32_t *counters) {
   extern __shared__ __align__(16) uint32_t smem[];
   uint32_t *units_hot = smem;
   float *score_hot = (float *)(smem + fp.k_units);
@@ -254,12 +254,13 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
   FastView fv;
   fv.units = fp.units; fv.score = fp.score; fv.leaf_id = fp.leaf_id;
   fv.units_hot = units_hot; fv.score_hot = score_hot;
+  fv.units_hot_saddr = (uint32_t)__cvta_generic_to_shared(units_hot);
+  fv.score_hot_saddr = (uint32_t)__cvta_generic_to_shared(score_hot);
   fv.k_units = fp.k_units; fv.k_scores = fp.k_scores; fv.n_units = fp.n_units;
   fv.ring = fp.ring; fv.unk_score = fp.unk_score; fv.smax = fp.smax; fv.unk_id = fp.unk_id;
   const uint32_t nfast = counters[C_NFAST];
   const int lane = threadIdx.x & 31;
-  const int64_t bstride = (int64_t)gridDim.x * kFastThreads;
-  uint32_t *myback = back + (int64_t)blockIdx.x * kFastThreads + threadIdx.x;
+  uint32_t *myback = back + ((int64_t)blockIdx.x * kFastThreads + threadIdx.x) * back_rows;
   for (;;) {
     uint32_t w = 0;
     if (lane == 0) w = atomicAdd(&counters[C_WORK], 1u);
@@ -272,7 +273,7 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
       const int32_t nl = nlen[t];
       const int32_t c = nl <= 0 ? 0 :
                         fast_unigram(fv, norm + fast_norm_base(off, c0, t), nl, ring_bt + threadIdx.x,
-                                     ring_bk + threadIdx.x, kFastThreads, myback, bstride,
+                                     ring_bk + threadIdx.x, kFastThreads, myback,
                                      stage + fast_stage_base(off, c0, t), &st);
       if (st) {
         gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
@@ -791,7 +792,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
 
   const ExtraPlan plan = make_extra_plan(extra_options, M->bos_id, M->eos_id);
   const int exp_ = M->hm.expansion;
-  const int64_t kRawBudget = 256ll << 20, kMaxChunk = 1 << 21;
+  const int64_t kRawBudget = M->fast ? (2048ll << 20) : (256ll << 20), kMaxChunk = 1 << 24;
   uint32_t stor = 0;
   int64_t n_general = 0;
   int64_t c0 = 0;
@@ -821,7 +822,8 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
         if (len < kFastMaxRaw && len > max_raw) max_raw = len;
       }
       // back-pointer rows: one per character (<= raw + kFastExtraChars) + BOS/EOS rows
-      if ((rc = M->w_back.ensure((size_t)(max_raw + kFastExtraChars + 2) * M->sm_count * kFastThreads * 4))) return rc;
+      const int64_t back_rows = (max_raw + kFastExtraChars + 8 + 3) & ~(int64_t)3;
+      if ((rc = M->w_back.ensure((size_t)back_rows * M->sm_count * kFastThreads * 4))) return rc;
       const unsigned g256 = (unsigned)((cn + 255) / 256);
       k_hist<<<g256, 256, 0, st>>>(d_off, c0, cn, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
                                    (int32_t *)M->w_genlist.p, d_counters);
@@ -834,8 +836,8 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       if ((rc = kev_record(M, st, 0))) return rc;
       k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
           M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-          (const int32_t *)M->w_perm.p, (uint32_t *)M->w_back.p, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
-          (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+          (const int32_t *)M->w_perm.p, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p,
+          (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
       if ((rc = kev_record(M, st, 1))) return rc;
       launches += 4;
       CUDA_TRY(cudaGetLastError());

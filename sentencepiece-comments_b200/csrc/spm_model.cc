@@ -388,7 +388,28 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
   for (size_t i = 0; i < V; ++i) smax = std::max(smax, fabsf(m->score[i]));
   smax = std::max(smax, (float)m->max_piece_bytes * fabsf(m->max_score) + 1.0f);
   m->smax = smax;
-  m->fast_ok = m->model_type == M_UNIGRAM && m->pieces.units.size() < 0x00FFFFFFu && m->max_piece_chars < 200;
+  // The fast tier counts characters by lead bytes, which equals the reference's
+  // OneCharLen jumps only on valid UTF-8.  Normalized text is valid UTF-8 unless a
+  // user-defined symbol (copied through raw) or a charsmap replacement is not.
+  auto valid_utf8 = [](const uint8_t *b, size_t n) {
+    for (size_t i = 0; i < n;) {
+      int mb = 1;
+      if (!valid_decode_utf8(b + i, (int64_t)(n - i), &mb)) return false;
+      i += mb;
+    }
+    return true;
+  };
+  bool text_valid = true;
+  for (size_t i = 0; i < V; ++i)
+    if (m->type[i] == T_USER_DEFINED && !valid_utf8((const uint8_t *)m->piece[i].data(), m->piece[i].size())) text_valid = false;
+  for (uint32_t a = 0; a < m->cm_pool_size && text_valid;) {
+    uint32_t e = a;
+    while (e < m->cm_pool_size && m->cm_pool[e] != 0) ++e;
+    if (!valid_utf8(m->cm_pool + a, e - a)) text_valid = false;
+    a = e + 1;
+  }
+  m->fast_ok = m->model_type == M_UNIGRAM && text_valid && m->pieces.units.size() < 0x00FFFFFFu &&
+               m->max_piece_chars < 200;
   return kOk;
 }
 
