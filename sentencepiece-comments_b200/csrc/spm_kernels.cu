@@ -142,17 +142,30 @@ __device__ __forceinline__ int64_t fast_stage_base(const int64_t *off, int64_t c
 }
 
 // Sort key = raw length.  Empty sentences produce nothing; sentences of kFastMaxRaw bytes
-// or more go straight to the general tier.
-__global__ void __launch_bounds__(256)
+// or more go straight to the general tier.  Block-private histogram in shared memory,
+// one global atomic per non-empty bin and block.
+constexpr int kSortThreads = 1024, kSortItems = 8, kSortTile = kSortThreads * kSortItems;
+__global__ void __launch_bounds__(kSortThreads)
 k_hist(const int64_t *off, int64_t c0, int64_t cn, int32_t *cnt, uint32_t *status, uint32_t *hist,
        int32_t *gen_list, uint32_t *counters) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= cn) return;
-  const int64_t len = off[c0 + t + 1] - off[c0 + t];
-  cnt[t] = 0;
-  status[t] = 0;
-  if (len >= kFastMaxRaw) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
-  else if (len > 0) atomicAdd(&hist[len], 1u);
+  __shared__ uint32_t sh[kFastMaxRaw];
+  for (int k = threadIdx.x; k < kFastMaxRaw; k += kSortThreads) sh[k] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * kSortTile;
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j) {
+    const int64_t t = base + j * kSortThreads + threadIdx.x;
+    if (t < cn) {
+      const int64_t len = off[c0 + t + 1] - off[c0 + t];
+      cnt[t] = 0;
+      status[t] = 0;
+      if (len >= kFastMaxRaw) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
+      else if (len > 0) atomicAdd(&sh[len], 1u);
+    }
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < kFastMaxRaw; k += kSortThreads)
+    if (sh[k]) atomicAdd(&hist[k], sh[k]);
 }
 
 // hist[1..kFastMaxRaw-1] -> first slot of each bin in DESCENDING key order; total -> counters[C_NFAST]
@@ -195,12 +208,32 @@ __global__ void __launch_bounds__(1024) k_binscan(uint32_t *hist, uint32_t *binc
   if (tid == 1023) counters[C_NFAST] = run;
 }
 
-__global__ void __launch_bounds__(256)
+// Same tiles as k_hist: the block reserves a range of every bin it touches with one global
+// atomic, then ranks its sentences inside the range with shared-memory atomics.
+__global__ void __launch_bounds__(kSortThreads)
 k_scatter(const int64_t *off, int64_t c0, int64_t cn, uint32_t *bincur, int32_t *perm) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= cn) return;
-  const int64_t len = off[c0 + t + 1] - off[c0 + t];
-  if (len > 0 && len < kFastMaxRaw) perm[atomicAdd(&bincur[len], 1u)] = (int32_t)t;
+  __shared__ uint32_t sh[kFastMaxRaw];
+  for (int k = threadIdx.x; k < kFastMaxRaw; k += kSortThreads) sh[k] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * kSortTile;
+  int32_t len[kSortItems];
+  uint32_t rank[kSortItems];
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j) {
+    const int64_t t = base + j * kSortThreads + threadIdx.x;
+    len[j] = 0;
+    if (t < cn) {
+      const int64_t l = off[c0 + t + 1] - off[c0 + t];
+      if (l > 0 && l < kFastMaxRaw) { len[j] = (int32_t)l; rank[j] = atomicAdd(&sh[l], 1u); }
+    }
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < kFastMaxRaw; k += kSortThreads)
+    if (sh[k]) sh[k] = atomicAdd(&bincur[k], sh[k]);
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j)
+    if (len[j]) perm[sh[len[j]] + rank[j]] = (int32_t)(base + j * kSortThreads + threadIdx.x);
 }
 
 // One thread per sentence, in sorted order (lanes of a warp: equal raw lengths).
@@ -226,6 +259,31 @@ k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t 
     nl = -1;
   }
   nlen[t] = nl;
+}
+
+// Checks the offsets of the whole batch on the device (no O(n) work on the host):
+// scal[3] |= 1 when offsets decrease, scal[6] = longest sentence, scal[7] = longest
+// sentence shorter than kFastMaxRaw (sizes the back-pointer arrays).
+__global__ void __launch_bounds__(256) k_validate(const int64_t *off, int64_t n, unsigned long long *scal) {
+  long long mx = 0, mxf = 0;
+  int bad = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const long long len = off[i + 1] - off[i];
+    if (len < 0) bad = 1;
+    if (len > mx) mx = len;
+    if (len < kFastMaxRaw && len > mxf) mxf = len;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, d));
+    mxf = max(mxf, __shfl_xor_sync(0xFFFFFFFFu, mxf, d));
+    bad |= __shfl_xor_sync(0xFFFFFFFFu, bad, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (bad) atomicOr(&scal[3], 1ull);
+    if (mx > 0) atomicMax(&scal[6], (unsigned long long)mx);
+    if (mxf > 0) atomicMax(&scal[7], (unsigned long long)mxf);
+  }
 }
 
 struct FastParams {
@@ -368,23 +426,46 @@ k_scan_final(const int32_t *in, int64_t n, Op op, const int64_t *partial, const 
   if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = *carry;
 }
 
-// one warp per sentence: final layout (extra options) into the CSR values.  Fast-tier
-// sentences were staged in reverse order, general-tier ones forward.
+// Final layout (extra options) into the CSR values.  Each lane reads the header of one
+// sentence (coalesced), then the warp copies the 32 sentences one after another.
+// Fast-tier sentences were staged in reverse order, general-tier ones forward.
 __global__ void __launch_bounds__(256)
-k_compact(ExtraPlan plan, const int64_t *off, int64_t c0, int64_t cn, const int32_t *stage, const int32_t *gstage,
-          const int64_t *srcoff, const uint32_t *status, const int32_t *cnt, const int64_t *id_off, int32_t *ids,
-          int64_t capacity) {
-  const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0, int64_t cn, const int32_t *stage,
+          const int32_t *gstage, const int64_t *srcoff, const uint32_t *status, const int32_t *cnt,
+          const int64_t *id_off, int32_t *ids, int64_t capacity) {
   const int lane = threadIdx.x & 31;
-  if (t >= cn) return;
-  const int32_t core = cnt[t];
-  const int32_t fc = final_count(plan, core);
-  const bool gen = status[t] & ST_GEN;
-  const int32_t *src = gen ? gstage + srcoff[t] : stage + fast_stage_base(off, c0, t);
-  if (!gen) plan.flip ^= 1;
-  const int64_t dst = id_off[c0 + t];
-  for (int32_t j = lane; j < fc; j += 32)
-    if (dst + j < capacity) ids[dst + j] = final_id_at(plan, src, core, j);
+  const int64_t t0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32;
+  if (t0 >= cn) return;
+  const int64_t t = t0 + lane;
+  int32_t my_core = -1;
+  int64_t my_src = 0, my_dst = 0;
+  int my_gen = 0;
+  if (t < cn) {
+    my_core = cnt[t];
+    my_gen = (status[t] & ST_GEN) != 0;
+    my_src = my_gen ? srcoff[t] : fast_stage_base(off, c0, t);
+    my_dst = id_off[c0 + t];
+  }
+  const bool simple = plan.npre == 0 && plan.nsuf == 0;
+  const int m = (int)min((int64_t)32, cn - t0);
+  for (int j = 0; j < m; ++j) {
+    const int32_t core = __shfl_sync(0xFFFFFFFFu, my_core, j);
+    const int gen = __shfl_sync(0xFFFFFFFFu, my_gen, j);
+    const int64_t so = __shfl_sync(0xFFFFFFFFu, my_src, j);
+    const int64_t dst = __shfl_sync(0xFFFFFFFFu, my_dst, j);
+    const int32_t *src = (gen ? gstage : stage) + so;
+    if (simple) {
+      const bool rev = (plan.flip != 0) == (gen != 0);   // fast-tier staging is already reversed
+      for (int32_t q = lane; q < core; q += 32)
+        if (dst + q < capacity) ids[dst + q] = src[rev ? core - 1 - q : q];
+    } else {
+      ExtraPlan pl = plan;
+      if (!gen) pl.flip ^= 1;
+      const int32_t fc = final_count(pl, core);
+      for (int32_t q = lane; q < fc; q += 32)
+        if (dst + q < capacity) ids[dst + q] = final_id_at(pl, src, core, q);
+    }
+  }
 }
 
 // ---------------------------------------------------------------- host side
@@ -419,7 +500,7 @@ struct spm_cuda_model {
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
       w_perm, w_genlist, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
-  mutable std::vector<int64_t> h_off, h_woff;
+  mutable std::vector<int64_t> h_woff;
   mutable double stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   mutable cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   mutable std::vector<cudaEvent_t> kev;  // event pairs around the dominant (encode) kernel launches
@@ -736,22 +817,18 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   double launches = 0;
   int rc;
 
-  // offsets on the host (chunk planning) and on the device
-  M->h_off.resize(n + 1);
+  // Offsets stay on the device; the host only ever reads a handful of them.
   const int64_t *d_off;
   const uint8_t *d_text;
+  int64_t text_lo = 0, text_hi = 0;
   if (host) {
-    memcpy(M->h_off.data(), text_offsets, (n + 1) * 8);
+    text_lo = text_offsets[0]; text_hi = text_offsets[n];
   } else {
-    CUDA_TRY(cudaMemcpyAsync(M->h_off.data(), text_offsets, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(&text_lo, text_offsets, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(&text_hi, text_offsets + n, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
   }
-  const int64_t *ho = M->h_off.data();
-  for (int64_t i = 0; i < n; ++i) {
-    if (ho[i + 1] < ho[i]) { g_err = "text_offsets must be non-decreasing"; return kInvalidArgument; }
-    if (ho[i + 1] - ho[i] > ((int64_t)1 << 26)) { g_err = "sentence longer than 64 MiB"; return kOutOfRange; }
-  }
-  const int64_t text_lo = ho[0], text_hi = ho[n];
+  if (text_hi < text_lo) { g_err = "text_offsets must be non-decreasing"; return kInvalidArgument; }
   if (host) {
     if ((rc = M->w_off.ensure((n + 1) * 8))) return rc;
     if ((rc = M->w_text.ensure((size_t)(text_hi - text_lo) + 16))) return rc;
@@ -765,6 +842,15 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     d_off = text_offsets;
     d_text = (const uint8_t *)text;
   }
+  // one offset, read by the host (chunk planning only; a single-chunk call never needs it)
+  auto read_off = [&](int64_t i, int64_t *v) -> int {
+    if (i == 0) { *v = text_lo; return kOk; }
+    if (i == n) { *v = text_hi; return kOk; }
+    if (host) { *v = text_offsets[i]; return kOk; }
+    CUDA_TRY(cudaMemcpyAsync(v, text_offsets + i, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return kOk;
+  };
   int64_t *d_idoff = host ? (int64_t *)M->w_idoff.p : id_offsets;
   int32_t *d_ids = ids;
   int64_t d_cap = ids_capacity;
@@ -782,6 +868,18 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   int64_t *d_carry = (int64_t *)M->w_scalars.p;        // [0] running CSR total
   uint32_t *d_counters = (uint32_t *)M->w_counters.p;
   CUDA_TRY(cudaMemsetAsync(M->w_scalars.p, 0, 64, st));
+  int64_t max_len = 0, max_raw = 0;
+  if (n > 0) {
+    const unsigned vgrid = (unsigned)std::min<int64_t>((n + 255) / 256, 4 * (int64_t)M->sm_count);
+    k_validate<<<vgrid, 256, 0, st>>>(d_off, n, (unsigned long long *)M->w_scalars.p);
+    launches += 1;
+    int64_t hv[8];
+    CUDA_TRY(cudaMemcpyAsync(hv, M->w_scalars.p, 64, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (hv[3]) { g_err = "text_offsets must be non-decreasing"; return kInvalidArgument; }
+    max_len = hv[6]; max_raw = hv[7];
+    if (max_len > ((int64_t)1 << 26)) { g_err = "sentence longer than 64 MiB"; return kOutOfRange; }
+  }
   if (M->fast && M->w_hist.cap == 0) {
     if ((rc = M->w_hist.ensure((size_t)kFastMaxRaw * 8))) return rc;   // hist | bincur
     CUDA_TRY(cudaMemsetAsync(M->w_hist.p, 0, (size_t)kFastMaxRaw * 8, st));
@@ -792,20 +890,21 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
 
   const ExtraPlan plan = make_extra_plan(extra_options, M->bos_id, M->eos_id);
   const int exp_ = M->hm.expansion;
-  const int64_t kRawBudget = M->fast ? (2048ll << 20) : (256ll << 20), kMaxChunk = 1 << 24;
+  // chunk = as many sentences as fit the byte budget (fast tier: the raw text; general
+  // tier: the worst-case normalized text) -- one chunk for all but huge batches
+  const int64_t kRawBudget = M->fast ? (2048ll << 20) : (256ll << 20) / exp_;
+  const int64_t kMaxChunk = M->fast ? (1 << 24) : (1 << 20);
   uint32_t stor = 0;
   int64_t n_general = 0;
-  int64_t c0 = 0;
+  int64_t c0 = 0, off_c0 = text_lo;
   while (c0 < n) {
-    int64_t c1 = c0, bytes = 0;
-    while (c1 < n && c1 - c0 < kMaxChunk) {
-      const int64_t len = ho[c1 + 1] - ho[c1];
-      const int64_t need = M->fast ? len + 64 : (int64_t)exp_ * len + 8;
-      if (c1 > c0 && bytes + need > kRawBudget) break;
-      bytes += need;
-      ++c1;
+    int64_t c1 = std::min(n, c0 + kMaxChunk), off_c1 = 0;
+    if ((rc = read_off(c1, &off_c1))) return rc;
+    while (off_c1 - off_c0 > kRawBudget && c1 - c0 > 1) {
+      c1 = c0 + (c1 - c0) / 2;
+      if ((rc = read_off(c1, &off_c1))) return rc;
     }
-    const int64_t cn = c1 - c0, raw = ho[c1] - ho[c0];
+    const int64_t cn = c1 - c0, raw = off_c1 - off_c0;
     if ((rc = M->w_cnt.ensure(cn * 4))) return rc;
     if ((rc = M->w_status.ensure(cn * 4))) return rc;
     if ((rc = M->w_srcoff.ensure(cn * 8))) return rc;
@@ -816,19 +915,14 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       if ((rc = M->w_nlen.ensure(cn * 4))) return rc;
       if ((rc = M->w_perm.ensure(cn * 4))) return rc;
       if ((rc = M->w_genlist.ensure(cn * 4))) return rc;
-      int64_t max_raw = 0;
-      for (int64_t i = c0; i < c1; ++i) {
-        const int64_t len = ho[i + 1] - ho[i];
-        if (len < kFastMaxRaw && len > max_raw) max_raw = len;
-      }
       // back-pointer rows: one per character (<= raw + kFastExtraChars) + BOS/EOS rows
       const int64_t back_rows = (max_raw + kFastExtraChars + 8 + 3) & ~(int64_t)3;
       if ((rc = M->w_back.ensure((size_t)back_rows * M->sm_count * kFastThreads * 4))) return rc;
-      const unsigned g256 = (unsigned)((cn + 255) / 256);
-      k_hist<<<g256, 256, 0, st>>>(d_off, c0, cn, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
+      const unsigned gsort = (unsigned)((cn + kSortTile - 1) / kSortTile);
+      k_hist<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
                                    (int32_t *)M->w_genlist.p, d_counters);
       k_binscan<<<1, 1024, 0, st>>>(d_hist, d_bincur, d_counters);
-      k_scatter<<<g256, 256, 0, st>>>(d_off, c0, cn, d_bincur, (int32_t *)M->w_perm.p);
+      k_scatter<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, d_bincur, (int32_t *)M->w_perm.p);
       k_normalize_fast<<<(unsigned)((cn + kNormThreads - 1) / kNormThreads), kNormThreads, 0, st>>>(
           M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p,
           (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
@@ -855,7 +949,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     FinalCountOp fop;
     fop.extra = plan.npre + plan.nsuf;
     if ((rc = run_scan(M, st, (const int32_t *)M->w_cnt.p, cn, fop, d_idoff + c0, d_carry, 1, &launches))) return rc;
-    const unsigned cgrid = (unsigned)((cn * 32 + 255) / 256);
+    const unsigned cgrid = (unsigned)((cn + 255) / 256);  // 8 warps x 32 sentences per block
     k_compact<<<cgrid, 256, 0, st>>>(plan, d_off, c0, cn, (const int32_t *)M->w_stage.p,
                                      (const int32_t *)M->g_stage.p, (const int64_t *)M->w_srcoff.p,
                                      (const uint32_t *)M->w_status.p, (const int32_t *)M->w_cnt.p, d_idoff, d_ids,
@@ -863,6 +957,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     launches += 1;
     CUDA_TRY(cudaGetLastError());
     c0 = c1;
+    off_c0 = off_c1;
   }
   CUDA_TRY(cudaEventRecord(M->ev1, st));
   int64_t hsc[3] = {0, 0, 0};
