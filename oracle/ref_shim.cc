@@ -13,6 +13,7 @@
 //   SentencePieceProcessor::SetVocabulary            src/sentencepiece_processor.h:224
 //   normalizer::Normalizer::Normalize                src/normalizer.h
 //   SentencePieceTrainer::Train(args)                src/sentencepiece_trainer.h:59
+//   normalizer::Builder::CompileCharsMap             src/builder.h (fixture charsmaps for the golden tests)
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -24,6 +25,7 @@
 #include "sentencepiece_model.pb.h"
 #include "sentencepiece_processor.h"
 #ifdef REF_WITH_TRAINER
+#include "builder.h"
 #include "sentencepiece_trainer.h"
 #include "unigram_model_trainer.h"
 #endif
@@ -166,6 +168,28 @@ int64_t ref_normalize(void *p, const char *text, int64_t len, char *out, int64_t
 }
 
 #ifdef REF_WITH_TRAINER
+// rules: n pairs of NUL-terminated UTF-8 strings (src, trg).  Writes the
+// precompiled charsmap blob (src/builder.cc:161-225) and returns its size.
+int64_t ref_compile_charsmap(const char *rules, int n, char *out, int64_t cap) {
+  using namespace sentencepiece;
+  normalizer::Builder::CharsMap cm;
+  const char *q = rules;
+  for (int i = 0; i < n; ++i) {
+    std::string a(q); q += a.size() + 1;
+    std::string b(q); q += b.size() + 1;
+    normalizer::Builder::Chars ca, cb;
+    for (const char32 c : string_util::UTF8ToUnicodeText(a)) ca.push_back(c);
+    for (const char32 c : string_util::UTF8ToUnicodeText(b)) cb.push_back(c);
+    cm[ca] = cb;
+  }
+  std::string blob;
+  auto st = normalizer::Builder::CompileCharsMap(cm, &blob);
+  if (!st.ok()) { g_err = st.ToString(); return -1; }
+  if ((int64_t)blob.size() > cap) return -2;
+  std::memcpy(out, blob.data(), blob.size());
+  return (int64_t)blob.size();
+}
+
 int ref_train(const char *args) {
   auto st = sentencepiece::SentencePieceTrainer::Train(args);
   if (!st.ok()) g_err = st.ToString();

@@ -68,7 +68,7 @@ def hostcore():
     """tests/host_core.cc: the kernels' __host__ __device__ core compiled for the CPU (test-only)."""
     csrc = os.path.join(ROOT, "sentencepiece-comments_b200", "csrc")
     srcs = [os.path.join(ROOT, "tests", "host_core.cc"), os.path.join(csrc, "spm_model.cc")]
-    deps = srcs + [os.path.join(csrc, "spm_core.cuh"), os.path.join(csrc, "spm_model.h")]
+    deps = srcs + [os.path.join(csrc, "spm_core.cuh"), os.path.join(csrc, "spm_fast.cuh"), os.path.join(csrc, "spm_model.h")]
     out = os.path.join(ROOT, "tests", "_build", "libspm_hostcore.so")
     _build_lib(deps, out, ["-I", csrc] + srcs)
     L = ctypes.CDLL(out)
@@ -79,6 +79,9 @@ def hostcore():
     L.hc_set_piece_types.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     L.hc_normalize.restype = ctypes.c_int64
     L.hc_normalize.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int64]
+    L.hc_normalize_fast.restype = ctypes.c_int64
+    L.hc_normalize_fast.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int64,
+                                    ctypes.c_void_p]
     L.hc_encode_batch.argtypes = [ctypes.c_void_p] * 3 + [ctypes.c_int64, ctypes.c_uint32, ctypes.c_int,
                                                          ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p,
                                                          ctypes.c_void_p]
@@ -108,6 +111,15 @@ class HostCore:
         n = self.L.hc_normalize(self.h, b, len(b), out, cap)
         assert n >= 0
         return out.raw[:n]
+
+    def normalize_fast(self, b):
+        """fast-tier normaliser; None when the sentence is routed to the general tier."""
+        cap = 3 * len(b) + 80
+        out = ctypes.create_string_buffer(cap)
+        nc = ctypes.c_int32(0)
+        n = self.L.hc_normalize_fast(self.h, b, len(b), out, cap, ctypes.byref(nc))
+        assert n >= -1, n
+        return None if n < 0 else (out.raw[:n], nc.value)
 
     def encode_batch(self, text, off, opts=0, capc=4):
         text = np.ascontiguousarray(text, dtype=np.uint8)

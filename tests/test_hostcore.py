@@ -1,0 +1,115 @@
+"""The kernels' __host__ __device__ arithmetic (spm_core.cuh exact tier,
+spm_fast.cuh fast tier, host model loader) compiled for the CPU by
+tests/host_core.cc and compared with the reference fixtures / the oracle.
+This is how every kernel change is parity-checked in the GPU-less container
+before it runs on a B200; the shipped library has no host encode path."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import EDGE_SENTENCES, GOLDEN, checker, model_bytes
+from oracle import port
+
+import sys
+sys.path.insert(0, GOLDEN)
+import make_fixtures as mf  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def ref_ids():
+    return np.load(os.path.join(GOLDEN, "ref_ids.npz"))
+
+
+def is_unigram(model):
+    return "bpe" not in model
+
+
+@pytest.mark.parametrize("model,corpus,first", mf.CASES)
+def test_core_matches_reference_fixture(make_hostcore, corpora, ref_ids, model, corpus, first):
+    text, off = corpora[corpus]
+    first = min(first or len(off) - 1, 2000)
+    text, off = text[: off[first]], off[: first + 1]
+    wo = ref_ids["%s__%s__off" % (model, corpus)][: first + 1]
+    wi = ref_ids["%s__%s__ids" % (model, corpus)][: wo[-1]]
+    hc = make_hostcore(model_bytes(model))
+    tiers = [4, 16] + ([0] if is_unigram(model) else [])   # exact tier (2 capacities), fast tier
+    for capc in tiers:
+        gi, go, st = hc.encode_batch(text, off, capc=capc)
+        assert np.array_equal(go, wo) and np.array_equal(gi, wi), (model, corpus, capc)
+        if capc == 16:
+            assert not (st & 4).any(), "exact tier overflowed its candidate list"
+
+
+@pytest.mark.parametrize("model", mf.EDGE_MODELS)
+def test_core_edge_sentences(make_hostcore, corpora, ref_ids, model):
+    text, off = corpora["edge"]
+    hc = make_hostcore(model_bytes(model))
+    for capc in [4] + ([0] if is_unigram(model) else []):
+        gi, go, _ = hc.encode_batch(text, off, capc=capc)
+        assert np.array_equal(go, ref_ids[model + "__edge__off"]), (model, capc)
+        assert np.array_equal(gi, ref_ids[model + "__edge__ids"]), (model, capc)
+
+
+@pytest.mark.parametrize("model", ["botchan_uni8k", "botchan_uni2k_ud", "ref_ja_8k", "botchan_bpe2k_ud"])
+def test_normalizers_match_reference(make_hostcore, corpora, model):
+    """normalize_sentence (general tier) and fast_normalize (fast tier) vs the reference strings."""
+    norm = np.load(os.path.join(GOLDEN, "ref_norm.npz"))
+    hc = make_hostcore(model_bytes(model))
+    text, off = norm[model + "__text"], norm[model + "__off"]
+    routed = 0
+    for k, s in enumerate(EDGE_SENTENCES):
+        want = bytes(text[off[k]:off[k + 1]])
+        assert hc.normalize(s) == want, (model, s)
+        f = hc.normalize_fast(s)
+        if f is None:
+            routed += 1
+        else:
+            assert f[0] == want, (model, s)
+            assert f[1] >= len(want.decode("utf-8", "replace")), "nchars must be an upper bound"
+    assert routed <= 4   # only the heavy-expansion inputs may leave the fast tier
+    # and against the oracle on a dirty synthetic sample
+    op = port.OracleProcessor(model_bytes(model))
+    t, o = corpora["syn_dirty"]
+    for i in range(0, 3000):
+        s = bytes(t[o[i]:o[i + 1]])
+        want = op.normalize(s)[0]
+        assert hc.normalize(s) == want
+        f = hc.normalize_fast(s)
+        assert f is None or f[0] == want, s
+
+
+@pytest.mark.parametrize("opts", ["bos", "eos:reverse", "reverse:bos:eos", "eos:reverse:bos:reverse:eos"])
+def test_extra_options(make_hostcore, corpora, opts):
+    mb = model_bytes("botchan_uni8k")
+    chk, _ = checker(mb)
+    chk.set_encode_extra_options(opts)
+    text, off = corpora["edge"]
+    wi, wo = chk.encode_batch(text, off)
+    gi, go, _ = make_hostcore(mb).encode_batch(text, off, opts=port.pack_options(opts), capc=0)
+    assert np.array_equal(go, wo) and np.array_equal(gi, wi)
+
+
+def test_set_piece_types(make_hostcore, corpora):
+    """SetVocabulary semantics (UNUSED pieces) through the fast view rebuild."""
+    mb = model_bytes("botchan_uni8k")
+    op = port.OracleProcessor(mb)
+    t = op.piece_types()
+    t[(np.arange(len(t)) % 3 == 0) & (t == 1)] = 5
+    op.set_piece_types(t)
+    hc = make_hostcore(mb)
+    hc.set_piece_types(t)
+    text, off = corpora["botchan"]
+    text, off = text[: off[800]], off[:801]
+    wi, wo = op.encode_batch(text, off)
+    for capc in (0, 4):
+        gi, go, _ = hc.encode_batch(text, off, capc=capc)
+        assert np.array_equal(go, wo) and np.array_equal(gi, wi), capc
+
+
+def test_loader_rejects_bad_models(hostcore):
+    import ctypes
+    for blob in (b"", b"garbage\xff\xff", b"\x0a\x03abc"):
+        code = ctypes.c_int(0)
+        h = hostcore.hc_load(blob, len(blob), ctypes.byref(code))
+        assert not h and code.value != 0
