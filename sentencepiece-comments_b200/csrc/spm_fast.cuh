@@ -86,6 +86,23 @@ SPM_HD T fast_ld_tiered(const T *hot, uint32_t hot_saddr, const T *cold, uint32_
 #endif
 }
 
+// Text prefetch: the next word of the sentence travels global -> shared with cp.async
+// (no register is tied up while it is in flight); the host build just loads it.
+SPM_HD void fast_prefetch_word(uint32_t *slot, uint32_t slot_saddr, const uint32_t *g) {
+#if defined(__CUDA_ARCH__)
+  (void)slot;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(slot_saddr), "l"(g) : "memory");
+#else
+  (void)slot_saddr;
+  *slot = *g;
+#endif
+}
+SPM_HD void fast_prefetch_wait() {
+#if defined(__CUDA_ARCH__)
+  asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
+}
+
 // One sentence.  s: normalized VALID UTF-8 text (8-byte aligned, followed by >= kNormPad
 // zero bytes), n bytes.  ring_bt / ring_bk: R slots, element k at [k * rstride].
 // back: this thread's own back-record array (nchars + 2 entries).
@@ -95,8 +112,9 @@ SPM_HD T fast_ld_tiered(const T *hot, uint32_t hot_saddr, const T *cold, uint32_
 // starts at the current character, or -- when that walk has ended -- the move to
 // the next character (all nodes ending there are known by then, so its backtrace
 // score is final).  Lanes of a warp therefore never wait for the deepest walk.
+// txt: two words of per-thread staging for the text prefetch, element j at [j * rstride].
 SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, float *ring_bt,
-                             uint32_t *ring_bk, int rstride, uint32_t *back, int32_t *out,
+                             uint32_t *ring_bk, uint32_t *txt, int rstride, uint32_t *back, int32_t *out,
                              uint32_t *status) {
   if (n <= 0) return 0;
   const int R = fv.ring;
@@ -111,6 +129,13 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
   int32_t qw = 0;
   uint32_t w0 = sw[0], w1 = sw[1], w2 = sw[2], w3 = sw[3], w4 = sw[4];
   uint32_t r = 0, sel = 0x3210u;
+#if defined(__CUDA_ARCH__)
+  const uint32_t txt_saddr = (uint32_t)__cvta_generic_to_shared(txt);
+#else
+  const uint32_t txt_saddr = 0;
+#endif
+  uint32_t tslot = 0;             // staging slot that holds word qw + 5
+  fast_prefetch_word(txt, txt_saddr, sw + 5);
   float bt_p = 0.0f;              // BOS
   uint32_t cur = w0;
   int cl = one_char_len((uint8_t)cur);
@@ -177,10 +202,13 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
       back[ci] = ring_bk[ridx * rstride];
       ring_bt[ridx * rstride] = NEG;
       if (p >= n) break;
-      if (r >= 4) {                        // slide the window by one word; w4 was loaded >= 4 bytes ago
+      if (r >= 4) {                        // slide the window by one word; word qw + 5 was requested one slide ago
         r -= 4; ++qw;
+        fast_prefetch_wait();
         w0 = w1; w1 = w2; w2 = w3; w3 = w4;
-        w4 = sw[qw + 4];
+        w4 = txt[tslot * rstride];
+        tslot ^= 1;
+        fast_prefetch_word(txt + tslot * rstride, txt_saddr + tslot * rstride * 4, sw + qw + 5);
       }
       sel = 0x3210u + 0x1111u * r;
       cur = fast_window4(w0, w1, sel);

@@ -306,6 +306,7 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
   float *score_hot = (float *)(smem + fp.k_units);
   float *ring_bt = (float *)(smem + fp.k_units + fp.k_scores);
   uint32_t *ring_bk = (uint32_t *)(ring_bt + (size_t)fp.ring * kFastThreads);
+  uint32_t *txt = ring_bk + (size_t)fp.ring * kFastThreads;   // [2][kFastThreads] text prefetch staging
   for (uint32_t k = threadIdx.x; k < fp.k_units; k += kFastThreads) units_hot[k] = fp.units[k];
   for (uint32_t k = threadIdx.x; k < fp.k_scores; k += kFastThreads) score_hot[k] = fp.score[k];
   __syncthreads();
@@ -331,7 +332,7 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
       const int32_t nl = nlen[t];
       const int32_t c = nl <= 0 ? 0 :
                         fast_unigram(fv, norm + fast_norm_base(off, c0, t), nl, ring_bt + threadIdx.x,
-                                     ring_bk + threadIdx.x, kFastThreads, myback,
+                                     ring_bk + threadIdx.x, txt + threadIdx.x, kFastThreads, myback,
                                      stage + fast_stage_base(off, c0, t), &st);
       if (st) {
         gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
@@ -567,7 +568,7 @@ int upload_model(spm_cuda_model *M) {
   CUDA_TRY(cudaDeviceGetAttribute(&M->sm_count, cudaDevAttrMultiProcessorCount, M->device));
   CUDA_TRY(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, M->device));
   const int R = hm.max_piece_chars + 1;
-  const size_t ring_bytes = (size_t)R * kFastThreads * 8;
+  const size_t ring_bytes = (size_t)R * kFastThreads * 8 + 2 * kFastThreads * 4;  // DP rings + text staging
   if (hm.fast_ok && ring_bytes + 32768 <= (size_t)smem_max) {
     if ((rc = upload_fast_view(M))) return rc;
     const size_t n_units = hm.funits.size();

@@ -123,9 +123,9 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
       std::vector<uint64_t> tbuf((nl + kNormPad + 15) / 8 + 1, 0);
       memcpy(tbuf.data(), norm.data(), nl);
       std::vector<float> rbt(fv.ring);
-      std::vector<uint32_t> rbk(fv.ring), back(nl + 12);
+      std::vector<uint32_t> rbk(fv.ring), back(nl + 12), txt(2);
       std::vector<int32_t> rev(nl + 1);
-      cnt = fast_unigram(fv, (const uint8_t *)tbuf.data(), nl, rbt.data(), rbk.data(), 1, (uint32_t *)(((uintptr_t)back.data() + 15) & ~(uintptr_t)15), rev.data(), &st);
+      cnt = fast_unigram(fv, (const uint8_t *)tbuf.data(), nl, rbt.data(), rbk.data(), txt.data(), 1, (uint32_t *)(((uintptr_t)back.data() + 15) & ~(uintptr_t)15), rev.data(), &st);
       if (st & ST_CAND_OVERFLOW) {
         st = ST_CAND_OVERFLOW;  // reported; result comes from the exact tier
         words.assign(uni_scratch_words(mv.ring, 16, nl), 0);
