@@ -232,6 +232,193 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
 }
 
 
+// ------------------------------------------------------------------ BPE fast tier
+constexpr int kBpeMaxSyms = 20;    // symbols (characters) per whitespace-delimited word
+constexpr int kBpeMaxBytes = 48;   // bytes per word
+constexpr int kBpeWordsPerThread = kBpeMaxSyms * 2 + kBpeMaxBytes / 4 + (kBpeMaxSyms + 4) / 4;  // smem words
+
+// Per-thread scratch of one word, element j of every array at [j * stride].
+struct BpeScratch {
+  uint32_t *node;   // [kBpeMaxSyms] trie node of symbol i (kFastUnk: not a trie path)
+  float *ps;        // [kBpeMaxSyms] score of the pair (symbol i, next alive symbol) or NEG
+  uint32_t *text;   // [kBpeMaxBytes / 4] bytes of the word
+  uint32_t *cb;     // [(kBpeMaxSyms + 4) / 4] byte offset of symbol i inside the word (u8 each)
+  int stride;
+};
+SPM_HD uint32_t bpe_get_u8(const uint32_t *a, int stride, int j) {
+  return (a[(j >> 2) * stride] >> ((j & 3) * 8)) & 0xFFu;
+}
+SPM_HD void bpe_set_u8(uint32_t *a, int stride, int j, uint32_t v) {
+  uint32_t &w = a[(j >> 2) * stride];
+  const int sh = (j & 3) * 8;
+  w = (w & ~(0xFFu << sh)) | (v << sh);
+}
+
+// Walks bytes [b, e) of the word from trie node `nd` (unit word `u`).  Returns false when
+// the path leaves the trie.
+SPM_HD bool bpe_walk(const FastView &fv, const BpeScratch &sc, uint32_t *nd, uint32_t *u, int b, int e) {
+  for (int j = b; j < e; ++j) {
+    const uint32_t c = bpe_get_u8(sc.text, sc.stride, j);
+    if (!(*u & 0x200u)) return false;
+    const uint32_t child = (*u >> 10) ^ c;
+    const uint32_t v = fast_ld_tiered(fv.units_hot, fv.units_hot_saddr, fv.units, child, fv.k_units);
+    if ((v & 0xFFu) != c || !(v & 0x300u)) return false;
+    *u = v; *nd = child;
+  }
+  return true;
+}
+// score of the piece (symbol at node nd) + bytes [b, e), or NEG when it is not a piece
+SPM_HD float bpe_pair_score(const FastView &fv, const BpeScratch &sc, uint32_t nd, int b, int e, float NEG) {
+  if (nd == kFastUnk) return NEG;
+  uint32_t u = fast_ld_tiered(fv.units_hot, fv.units_hot_saddr, fv.units, nd, fv.k_units);
+  if (!bpe_walk(fv, sc, &nd, &u, b, e) || !(u & 0x100u)) return NEG;
+  return fast_ld_tiered(fv.score_hot, fv.score_hot_saddr, fv.score, nd, fv.k_scores);
+}
+
+// One sentence with a BPE model whose pieces never carry U+2581 at a non-initial position
+// (so no merge can cross a word boundary) and that has no USER_DEFINED / UNUSED pieces:
+// bpe::Model::Encode (src/bpe_model.cc:37-199) word by word.  Inside a word the agenda
+// semantics are restated exactly as "merge the adjacent pair that forms a piece with the
+// highest score, leftmost on ties, until none is left" (the agenda's live entries are
+// exactly the current adjacent pairs; stale ones are skipped, :148-152).
+// s: normalized valid UTF-8 text (escaped whitespace), padded as for fast_unigram.
+// out: ids in FORWARD order.  A word longer than the scratch sets ST_TOO_LONG (the
+// caller re-runs the sentence on the general tier).
+// txt: two words of per-thread staging for the text prefetch (as in fast_unigram).
+SPM_HDN int32_t fast_bpe(const FastView &fv, const uint8_t *s, int32_t n, const BpeScratch &sc, uint32_t *txt,
+                         int32_t *out, uint32_t *status) {
+  const float NEG = -3.0e38f;
+  const uint32_t root = fv.units_hot[0];
+  const uint32_t *sw = reinterpret_cast<const uint32_t *>(s);
+  // text window (see fast_unigram): words w0..w4 = bytes [4*qw, 4*qw + 20), r = q - 4*qw
+  int32_t qw = 0;
+  uint32_t w0 = sw[0], w1 = sw[1], w2 = sw[2], w3 = sw[3], w4 = sw[4];
+  uint32_t r = 0;
+#if defined(__CUDA_ARCH__)
+  const uint32_t txt_saddr = (uint32_t)__cvta_generic_to_shared(txt);
+#else
+  const uint32_t txt_saddr = 0;
+#endif
+  uint32_t tslot = 0;
+  fast_prefetch_word(txt, txt_saddr, sw + 5);
+  int32_t cnt = 0, p = 0;
+  bool prev_unk = false;
+  while (p < n) {
+    // ---- split the word into characters; single-character nodes and initial pair scores
+    int nsym = 0, wlen = 0;
+    uint32_t prev_nd = kFastUnk, prev_u = 0;
+    for (;;) {
+      if (p + wlen >= n) break;
+      const uint32_t cur = fast_window4(w0, w1, 0x3210u + 0x1111u * r);   // 4 bytes at p + wlen
+      if (nsym > 0 && (cur & 0x00FFFFFFu) == 0x008196E2u) break;          // U+2581: the next word
+      const int cl = one_char_len((uint8_t)cur);
+      if (nsym == kBpeMaxSyms || wlen + cl > kBpeMaxBytes) { *status |= ST_TOO_LONG; return 0; }
+      for (int j = 0; j < cl; ++j) bpe_set_u8(sc.text, sc.stride, wlen + j, (cur >> (8 * j)) & 0xFFu);
+      bpe_set_u8(sc.cb, sc.stride, nsym, (uint32_t)wlen);
+      // node of the character alone, and of (previous symbol + this character)
+      uint32_t nd = 0, u = root, pn = prev_nd, pu = prev_u;
+      bool ok1 = true, ok2 = prev_nd != kFastUnk;
+      for (int j = 0; j < cl; ++j) {
+        const uint32_t c = (cur >> (8 * j)) & 0xFFu;
+        if (ok1) {
+          ok1 = (u & 0x200u) != 0;
+          if (ok1) {
+            const uint32_t child = (u >> 10) ^ c;
+            const uint32_t v = fast_ld_tiered(fv.units_hot, fv.units_hot_saddr, fv.units, child, fv.k_units);
+            ok1 = (v & 0xFFu) == c && (v & 0x300u) != 0;
+            u = v; nd = child;
+          }
+        }
+        if (ok2) {
+          ok2 = (pu & 0x200u) != 0;
+          if (ok2) {
+            const uint32_t child = (pu >> 10) ^ c;
+            const uint32_t v = fast_ld_tiered(fv.units_hot, fv.units_hot_saddr, fv.units, child, fv.k_units);
+            ok2 = (v & 0xFFu) == c && (v & 0x300u) != 0;
+            pu = v; pn = child;
+          }
+        }
+      }
+      if (!ok1) nd = kFastUnk;
+      sc.node[nsym * sc.stride] = nd;
+      if (nsym > 0) {
+        float v = NEG;
+        if (ok2 && (pu & 0x100u)) v = fast_ld_tiered(fv.score_hot, fv.score_hot_saddr, fv.score, pn, fv.k_scores);
+        sc.ps[(nsym - 1) * sc.stride] = v;
+      }
+      prev_nd = nd; prev_u = u;
+      ++nsym;
+      wlen += cl;
+      r += cl;
+      if (r >= 4) {
+        r -= 4; ++qw;
+        fast_prefetch_wait();
+        w0 = w1; w1 = w2; w2 = w3; w3 = w4;
+        w4 = txt[tslot * sc.stride];
+        tslot ^= 1;
+        fast_prefetch_word(txt + tslot * sc.stride, txt_saddr + tslot * sc.stride * 4, sw + qw + 5);
+      }
+    }
+    sc.ps[(nsym - 1) * sc.stride] = NEG;
+    // ---- merges
+    uint32_t alive = nsym >= 32 ? 0xFFFFFFFFu : ((1u << nsym) - 1u);
+    for (;;) {
+      float best = NEG;
+      int bi = -1;
+      for (uint32_t m = alive; m;) {
+        int i = 0;
+        while (!((m >> i) & 1u)) ++i;
+        m &= m - 1;
+        if (!m) break;                       // the last alive symbol has no right neighbour
+        const float v = sc.ps[i * sc.stride];
+        if (v > best) { best = v; bi = i; }  // strict '>' keeps the leftmost of equals (:55-61)
+      }
+      if (bi < 0) break;
+      int r = bi + 1;
+      while (!((alive >> r) & 1u)) ++r;
+      int nr = r + 1;                        // symbol after r (nsym: none)
+      while (nr < nsym && !((alive >> nr) & 1u)) ++nr;
+      const int rb = (int)bpe_get_u8(sc.cb, sc.stride, r);
+      const int re = nr < nsym ? (int)bpe_get_u8(sc.cb, sc.stride, nr) : wlen;
+      uint32_t nd = sc.node[bi * sc.stride];
+      uint32_t u = fast_ld_tiered(fv.units_hot, fv.units_hot_saddr, fv.units, nd, fv.k_units);
+      bpe_walk(fv, sc, &nd, &u, rb, re);     // succeeds: the pair was scored
+      sc.node[bi * sc.stride] = nd;
+      alive &= ~(1u << r);
+      // the two new pairs (:167-168)
+      float v = NEG;
+      if (nr < nsym) {
+        int ne = nr + 1;
+        while (ne < nsym && !((alive >> ne) & 1u)) ++ne;
+        const int nre = ne < nsym ? (int)bpe_get_u8(sc.cb, sc.stride, ne) : wlen;
+        uint32_t n2 = nd, u2 = u;
+        if (bpe_walk(fv, sc, &n2, &u2, re, nre) && (u2 & 0x100u))
+          v = fast_ld_tiered(fv.score_hot, fv.score_hot_saddr, fv.score, n2, fv.k_scores);
+      }
+      sc.ps[bi * sc.stride] = v;
+      int pl = bi - 1;
+      while (pl >= 0 && !((alive >> pl) & 1u)) --pl;
+      if (pl >= 0)
+        sc.ps[pl * sc.stride] = bpe_pair_score(fv, sc, sc.node[pl * sc.stride],
+                                               (int)bpe_get_u8(sc.cb, sc.stride, bi), re, NEG);
+    }
+    // ---- emit (PieceToId, src/model_interface.cc:87-97; unk runs merge, processor.cc:525-529)
+    for (int i = 0; i < nsym; ++i) {
+      if (!((alive >> i) & 1u)) continue;
+      const uint32_t nd = sc.node[i * sc.stride];
+      bool is_unk = nd == kFastUnk;
+      if (!is_unk) {
+        const uint32_t u = fast_ld_tiered(fv.units_hot, fv.units_hot_saddr, fv.units, nd, fv.k_units);
+        is_unk = !(u & 0x100u);
+      }
+      if (!(is_unk && prev_unk)) out[cnt++] = is_unk ? fv.unk_id : (int32_t)SPM_LDG(fv.leaf_id + nd);
+      prev_unk = is_unk;
+    }
+    p += wlen;
+  }
+  return cnt;
+}
+
 // ------------------------------------------------------------------ normaliser
 // 8 bytes at the 8-byte aligned address a, never touching memory outside [lo, hi)
 // (the caller's text buffer): whole-word load when it fits, guarded bytes at the edges.

@@ -56,7 +56,9 @@ thread_local std::string g_err;
 constexpr int kCapc = 8;          // near-tie candidates kept per position by the exact tier
 constexpr int kThreads = 128;     // general-tier block size
 constexpr int kFastThreads = 768; // fast-tier block size (one persistent CTA per SM)
+constexpr int kBpeThreads = 512;  // BPE fast-tier block size
 constexpr uint32_t ST_GEN = 1u << 16;   // sentence was encoded by the general tier (ids in gstage, forward order)
+constexpr uint32_t ST_FWD = 1u << 17;   // fast-tier ids were staged in forward order (BPE)
 
 // device-side counters of one chunk
 enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_COUNT = 8 };
@@ -344,6 +346,58 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
   }
 }
 
+// BPE fast tier: same scheduling as k_encode_fast.  Shared memory: hot units | hot scores |
+// node[S][T] | ps[S][T] | text[B/4][T] | cb[..][T] | txt[2][T]  (T = kBpeThreads).
+__global__ void __launch_bounds__(kBpeThreads, 1)
+k_encode_bpe_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
+                  const int32_t *perm, int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *gen_list,
+                  uint32_t *counters) {
+  extern __shared__ __align__(16) uint32_t smem[];
+  uint32_t *units_hot = smem;
+  float *score_hot = (float *)(smem + fp.k_units);
+  uint32_t *scr = smem + fp.k_units + fp.k_scores;
+  for (uint32_t k = threadIdx.x; k < fp.k_units; k += kBpeThreads) units_hot[k] = fp.units[k];
+  for (uint32_t k = threadIdx.x; k < fp.k_scores; k += kBpeThreads) score_hot[k] = fp.score[k];
+  __syncthreads();
+  FastView fv;
+  fv.units = fp.units; fv.score = fp.score; fv.leaf_id = fp.leaf_id;
+  fv.units_hot = units_hot; fv.score_hot = score_hot;
+  fv.units_hot_saddr = (uint32_t)__cvta_generic_to_shared(units_hot);
+  fv.score_hot_saddr = (uint32_t)__cvta_generic_to_shared(score_hot);
+  fv.k_units = fp.k_units; fv.k_scores = fp.k_scores; fv.n_units = fp.n_units;
+  fv.ring = 0; fv.unk_score = 0; fv.smax = 0; fv.unk_id = fp.unk_id;
+  BpeScratch bs;
+  bs.stride = kBpeThreads;
+  bs.node = scr + threadIdx.x;
+  bs.ps = (float *)(bs.node + kBpeMaxSyms * kBpeThreads);
+  bs.text = bs.node + 2 * kBpeMaxSyms * kBpeThreads;
+  bs.cb = bs.text + (kBpeMaxBytes / 4) * kBpeThreads;
+  uint32_t *txt = bs.cb + ((kBpeMaxSyms + 4) / 4) * kBpeThreads;
+  const uint32_t nfast = counters[C_NFAST];
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    uint32_t w = 0;
+    if (lane == 0) w = atomicAdd(&counters[C_WORK], 1u);
+    w = __shfl_sync(0xFFFFFFFFu, w, 0);
+    const uint32_t idx = w * 32 + lane;
+    if (w * 32 >= nfast) break;
+    if (idx < nfast) {
+      const int32_t t = perm[idx];
+      uint32_t st = 0;
+      const int32_t nl = nlen[t];
+      const int32_t c = nl <= 0 ? 0 : fast_bpe(fv, norm + fast_norm_base(off, c0, t), nl, bs, txt,
+                                               stage + fast_stage_base(off, c0, t), &st);
+      if (st) {
+        gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
+      } else {
+        cnt[t] = c;
+        status[t] = ST_FWD;
+      }
+    }
+    __syncwarp();
+  }
+}
+
 // ---- exclusive scan of f(in[i]) over one chunk: int32 -> int64, with carry
 struct IdentityOp { __device__ int64_t operator()(int32_t v) const { return v; } };
 struct FinalCountOp {
@@ -443,8 +497,8 @@ k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0
   int my_gen = 0;
   if (t < cn) {
     my_core = cnt[t];
-    my_gen = (status[t] & ST_GEN) != 0;
-    my_src = my_gen ? srcoff[t] : fast_stage_base(off, c0, t);
+    my_gen = (status[t] & ST_GEN) != 0 ? 1 : ((status[t] & ST_FWD) ? 2 : 0);   // 2: fast tier, forward
+    my_src = my_gen == 1 ? srcoff[t] : fast_stage_base(off, c0, t);
     my_dst = id_off[c0 + t];
   }
   const bool simple = plan.npre == 0 && plan.nsuf == 0;
@@ -454,9 +508,9 @@ k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0
     const int gen = __shfl_sync(0xFFFFFFFFu, my_gen, j);
     const int64_t so = __shfl_sync(0xFFFFFFFFu, my_src, j);
     const int64_t dst = __shfl_sync(0xFFFFFFFFu, my_dst, j);
-    const int32_t *src = (gen ? gstage : stage) + so;
+    const int32_t *src = (gen == 1 ? gstage : stage) + so;
     if (simple) {
-      const bool rev = (plan.flip != 0) == (gen != 0);   // fast-tier staging is already reversed
+      const bool rev = (plan.flip != 0) == (gen != 0);   // unigram fast-tier staging is already reversed
       for (int32_t q = lane; q < core; q += 32)
         if (dst + q < capacity) ids[dst + q] = src[rev ? core - 1 - q : q];
     } else {
@@ -492,7 +546,8 @@ struct spm_cuda_model {
   int device = 0;
   ModelView mv;
   FastParams fp;
-  bool fast = false;       // unigram model that fits the fast tier
+  bool fast = false;       // a fast tier is usable
+  int fast_kind = 0;       // 1: unigram (k_encode_fast), 2: BPE (k_encode_bpe_fast)
   int sm_count = 1;
   size_t fast_smem = 0;
   DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2, d_funits, d_fscore, d_fleaf;
@@ -536,6 +591,42 @@ int upload_fast_view(spm_cuda_model *M) {
   return kOk;
 }
 
+// Chooses the fast tier the model can use (it can change with SetVocabulary: UNUSED pieces
+// switch BPE to the general tier) and sizes its shared memory: hot trie prefix + per-thread state.
+int configure_fast(spm_cuda_model *M) {
+  HostModel &hm = M->hm;
+  int rc;
+  M->fast = false;
+  M->fast_kind = 0;
+  int smem_max = 0;
+  CUDA_TRY(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, M->device));
+  const int R = hm.max_piece_chars + 1;
+  size_t state_bytes = 0;
+  int kind = 0;
+  if (hm.fast_ok) { kind = 1; state_bytes = (size_t)R * kFastThreads * 8 + 2 * kFastThreads * 4; }  // DP rings + text staging
+  else if (hm.bpe_fast_ok) { kind = 2; state_bytes = (size_t)(kBpeWordsPerThread + 2) * kBpeThreads * 4; }
+  if (kind == 0 || state_bytes + 32768 > (size_t)smem_max) return kOk;
+  if ((rc = upload_fast_view(M))) return rc;
+  const size_t n_units = hm.funits.size();
+  const size_t hot_words = ((size_t)smem_max - state_bytes - 256) / 4;
+  size_t ku = std::min(n_units, hot_words * 2 / 3 & ~(size_t)3);
+  size_t ks = std::min(n_units, (hot_words - ku) & ~(size_t)3);
+  if (ks == n_units) ku = std::min(n_units, (hot_words - ks) & ~(size_t)3);
+  FastParams &fp = M->fp;
+  fp.units = (const uint32_t *)M->d_funits.p; fp.score = (const float *)M->d_fscore.p;
+  fp.leaf_id = (const uint32_t *)M->d_fleaf.p;
+  fp.k_units = (uint32_t)ku; fp.k_scores = (uint32_t)ks; fp.n_units = (uint32_t)n_units;
+  fp.ring = R; fp.unk_score = M->mv.unk_score; fp.smax = M->mv.smax; fp.unk_id = M->mv.unk_id;
+  M->fast_smem = (ku + ks) * 4 + state_bytes;
+  if (kind == 1)
+    CUDA_TRY(cudaFuncSetAttribute(k_encode_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)M->fast_smem));
+  else
+    CUDA_TRY(cudaFuncSetAttribute(k_encode_bpe_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)M->fast_smem));
+  M->fast = true;
+  M->fast_kind = kind;
+  return kOk;
+}
+
 int upload_model(spm_cuda_model *M) {
   HostModel &hm = M->hm;
   int rc;
@@ -562,30 +653,8 @@ int upload_model(spm_cuda_model *M) {
   v.add_dummy_prefix = hm.add_dummy_prefix; v.remove_extra_ws = hm.remove_extra_ws;
   v.escape_ws = hm.escape_ws; v.ws_suffix = hm.ws_suffix; v.has_unused = hm.has_unused;
 
-  // fast tier: shared-memory budget = hot trie prefix + DP rings of kFastThreads sentences
-  M->fast = false;
-  int smem_max = 0;
   CUDA_TRY(cudaDeviceGetAttribute(&M->sm_count, cudaDevAttrMultiProcessorCount, M->device));
-  CUDA_TRY(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, M->device));
-  const int R = hm.max_piece_chars + 1;
-  const size_t ring_bytes = (size_t)R * kFastThreads * 8 + 2 * kFastThreads * 4;  // DP rings + text staging
-  if (hm.fast_ok && ring_bytes + 32768 <= (size_t)smem_max) {
-    if ((rc = upload_fast_view(M))) return rc;
-    const size_t n_units = hm.funits.size();
-    const size_t hot_words = ((size_t)smem_max - ring_bytes - 256) / 4;
-    size_t ku = std::min(n_units, hot_words * 2 / 3 & ~(size_t)3);
-    size_t ks = std::min(n_units, (hot_words - ku) & ~(size_t)3);
-    if (ks == n_units) ku = std::min(n_units, (hot_words - ks) & ~(size_t)3);
-    FastParams &fp = M->fp;
-    fp.units = (const uint32_t *)M->d_funits.p; fp.score = (const float *)M->d_fscore.p;
-    fp.leaf_id = (const uint32_t *)M->d_fleaf.p;
-    fp.k_units = (uint32_t)ku; fp.k_scores = (uint32_t)ks; fp.n_units = (uint32_t)n_units;
-    fp.ring = R; fp.unk_score = v.unk_score; fp.smax = v.smax; fp.unk_id = v.unk_id;
-    M->fast_smem = (ku + ks) * 4 + ring_bytes;
-    CUDA_TRY(cudaFuncSetAttribute(k_encode_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)M->fast_smem));
-    M->fast = true;
-  }
-  return kOk;
+  return configure_fast(M);
 }
 
 template <class Op>
@@ -745,11 +814,7 @@ int spm_cuda_model_set_piece_types(spm_cuda_model *M, const uint8_t *types, int 
   CUDA_TRY(cudaSetDevice(M->device));
   CUDA_TRY(cudaMemcpy(M->d_leaf.p, M->hm.pieces.leaf.data(), M->hm.pieces.leaf.size() * 8, cudaMemcpyHostToDevice));
   M->mv.has_unused = M->hm.has_unused;
-  if (M->fast) {
-    int rc = upload_fast_view(M);
-    if (rc) return rc;
-  }
-  return kOk;
+  return configure_fast(M);
 }
 
 int spm_cuda_model_piece_size(const spm_cuda_model *M) { return (int)M->hm.piece.size(); }
@@ -918,7 +983,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       if ((rc = M->w_genlist.ensure(cn * 4))) return rc;
       // back-pointer rows: one per character (<= raw + kFastExtraChars) + BOS/EOS rows
       const int64_t back_rows = (max_raw + kFastExtraChars + 8 + 3) & ~(int64_t)3;
-      if ((rc = M->w_back.ensure((size_t)back_rows * M->sm_count * kFastThreads * 4))) return rc;
+      if (M->fast_kind == 1 && (rc = M->w_back.ensure((size_t)back_rows * M->sm_count * kFastThreads * 4))) return rc;
       const unsigned gsort = (unsigned)((cn + kSortTile - 1) / kSortTile);
       k_hist<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
                                    (int32_t *)M->w_genlist.p, d_counters);
@@ -929,10 +994,16 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
           (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
       launches += 1;
       if ((rc = kev_record(M, st, 0))) return rc;
-      k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
-          M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-          (const int32_t *)M->w_perm.p, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p,
-          (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+      if (M->fast_kind == 1)
+        k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
+            M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+            (const int32_t *)M->w_perm.p, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p,
+            (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+      else
+        k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
+            M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+            (const int32_t *)M->w_perm.p, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
+            (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
       if ((rc = kev_record(M, st, 1))) return rc;
       launches += 4;
       CUDA_TRY(cudaGetLastError());

@@ -308,6 +308,20 @@ void refresh_leaf_types(HostModel *m) {
       if (!(m->funits[i] & 0x200u)) m->funits[i] = 0;
     }
   }
+  // fast_bpe() preconditions: escaped whitespace as a word prefix, no piece carries U+2581
+  // at a non-initial position (no merge crosses a word boundary), no frozen (USER_DEFINED)
+  // symbols, no UNUSED pieces to re-split, no single-character reserved piece (PieceToId of
+  // a lone character consults the reserved map first, src/model_interface.cc:87-97).
+  bool ok = m->model_type == M_BPE && m->text_valid && m->escape_ws && !m->ws_suffix &&
+            m->pieces.units.size() < 0x00FFFFFFu;
+  for (size_t i = 0; i < m->piece.size() && ok; ++i) {
+    const std::string &pc = m->piece[i];
+    const uint8_t t = m->type[i];
+    if (t == T_USER_DEFINED || t == T_UNUSED) ok = false;
+    if (t != T_NORMAL && char_count(pc) == 1) ok = false;
+    if (pc.find("\xE2\x96\x81", 1) != std::string::npos) ok = false;
+  }
+  m->bpe_fast_ok = ok;
 }
 
 int build_host_model(const void *data, size_t len, HostModel *m) {
@@ -408,8 +422,10 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
     if (!valid_utf8(m->cm_pool + a, e - a)) text_valid = false;
     a = e + 1;
   }
+  m->text_valid = text_valid;
   m->fast_ok = m->model_type == M_UNIGRAM && text_valid && m->pieces.units.size() < 0x00FFFFFFu &&
                m->max_piece_chars < 200;
+  refresh_leaf_types(m);  // (re)derives bpe_fast_ok as well
   return kOk;
 }
 

@@ -53,6 +53,8 @@ struct HostModel {
   std::vector<uint32_t> fleaf;    // node -> piece id
   int max_piece_chars = 0;
   bool fast_ok = false;           // the model fits the fast tier's packed records
+  bool text_valid = true;         // normalized text is always valid UTF-8
+  bool bpe_fast_ok = false;       // BPE model whose merges never cross a word boundary (fast_bpe)
   std::string error;
 };
 

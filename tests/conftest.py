@@ -76,6 +76,7 @@ def hostcore():
     L.hc_load.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p]
     L.hc_free.argtypes = [ctypes.c_void_p]
     L.hc_expansion.argtypes = [ctypes.c_void_p]
+    L.hc_fast_flags.argtypes = [ctypes.c_void_p]
     L.hc_set_piece_types.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     L.hc_normalize.restype = ctypes.c_int64
     L.hc_normalize.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int64]
@@ -100,6 +101,9 @@ class HostCore:
     def __del__(self):
         if getattr(self, "h", None):
             self.L.hc_free(self.h)
+
+    def fast_flags(self):
+        return self.L.hc_fast_flags(self.h)
 
     def set_piece_types(self, t):
         t = np.ascontiguousarray(t, dtype=np.uint8)

@@ -47,6 +47,8 @@ void *hc_load(const void *data, size_t len, int *code) {
 }
 void hc_free(void *p) { delete (Handle *)p; }
 int hc_expansion(void *p) { return ((Handle *)p)->hm.expansion; }
+// bit 0: unigram fast tier usable, bit 1: BPE fast tier usable
+int hc_fast_flags(void *p) { return (((Handle *)p)->hm.fast_ok ? 1 : 0) | (((Handle *)p)->hm.bpe_fast_ok ? 2 : 0); }
 int hc_trie_units(void *p) { return (int)((Handle *)p)->hm.pieces.units.size(); }
 void hc_set_piece_types(void *p, const uint8_t *t, int n) {
   Handle *h = (Handle *)p;
@@ -142,6 +144,31 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
         cnt = unigram_encode<16>(mv, norm.data(), nl, sc, core.data(), nl, &st2);
       } else {
         for (int32_t j = 0; j < cnt; ++j) core[j] = rev[cnt - 1 - j];
+      }
+    } else if (mv.model_type == M_BPE && capc == 0 && h->hm.bpe_fast_ok) {
+      // fast BPE tier (spm_fast.cuh) with the library's routing: too-long words -> general tier
+      FastView fv;
+      fv.units_hot_saddr = fv.score_hot_saddr = 0;
+      fv.units = fv.units_hot = h->hm.funits.data();
+      fv.score = fv.score_hot = h->hm.fscore.data();
+      fv.leaf_id = h->hm.fleaf.data();
+      fv.n_units = (uint32_t)h->hm.funits.size();
+      fv.k_units = fv.n_units / 3; fv.k_scores = fv.n_units / 5;
+      fv.ring = 0; fv.unk_score = 0; fv.smax = 0; fv.unk_id = mv.unk_id;
+      std::vector<uint64_t> tbuf((nl + kNormPad + 15) / 8 + 1, 0);
+      memcpy(tbuf.data(), norm.data(), nl);
+      std::vector<uint32_t> scr(kBpeWordsPerThread, 0);
+      BpeScratch bs;
+      bs.stride = 1;
+      bs.node = scr.data(); bs.ps = (float *)(scr.data() + kBpeMaxSyms);
+      bs.text = scr.data() + 2 * kBpeMaxSyms; bs.cb = bs.text + kBpeMaxBytes / 4;
+      uint32_t txt2[2] = {0, 0};
+      cnt = fast_bpe(fv, (const uint8_t *)tbuf.data(), nl, bs, txt2, core.data(), &st);
+      if (st & ST_TOO_LONG) {
+        words.assign(bpe_scratch_words(nl), 0);
+        uint32_t st2 = 0;
+        cnt = bpe_encode(mv, norm.data(), nl, words.data(), core.data(), nl, &st2);
+        st |= st2;
       }
     } else if (mv.model_type == M_UNIGRAM) {
       words.assign(uni_scratch_words(mv.ring, capc, nl), 0);

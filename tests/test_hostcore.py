@@ -33,7 +33,7 @@ def test_core_matches_reference_fixture(make_hostcore, corpora, ref_ids, model, 
     wo = ref_ids["%s__%s__off" % (model, corpus)][: first + 1]
     wi = ref_ids["%s__%s__ids" % (model, corpus)][: wo[-1]]
     hc = make_hostcore(model_bytes(model))
-    tiers = [4, 16] + ([0] if is_unigram(model) else [])   # exact tier (2 capacities), fast tier
+    tiers = [4, 16, 0]   # exact tier (2 capacities); 0 = fast tier (unigram / word-wise BPE where the model allows)
     for capc in tiers:
         gi, go, st = hc.encode_batch(text, off, capc=capc)
         assert np.array_equal(go, wo) and np.array_equal(gi, wi), (model, corpus, capc)
@@ -45,7 +45,7 @@ def test_core_matches_reference_fixture(make_hostcore, corpora, ref_ids, model, 
 def test_core_edge_sentences(make_hostcore, corpora, ref_ids, model):
     text, off = corpora["edge"]
     hc = make_hostcore(model_bytes(model))
-    for capc in [4] + ([0] if is_unigram(model) else []):
+    for capc in [4, 0]:
         gi, go, _ = hc.encode_batch(text, off, capc=capc)
         assert np.array_equal(go, ref_ids[model + "__edge__off"]), (model, capc)
         assert np.array_equal(gi, ref_ids[model + "__edge__ids"]), (model, capc)
@@ -105,6 +105,14 @@ def test_set_piece_types(make_hostcore, corpora):
     for capc in (0, 4):
         gi, go, _ = hc.encode_batch(text, off, capc=capc)
         assert np.array_equal(go, wo) and np.array_equal(gi, wi), capc
+
+
+def test_fast_tier_eligibility(make_hostcore):
+    """Which fixture models run on the fast tiers (the rest take the general tier)."""
+    want = {"botchan_uni8k": 1, "syn_uni32k": 1, "wagahai_uni": 1, "ref_ja_8k": 1, "ref_en_1k": 1, "botchan_uni2k_ud": 1,
+            "botchan_bpe4k": 2, "syn_bpe32k": 2, "botchan_bpe2k_ud": 0}   # user-defined symbols freeze BPE symbols
+    for name, flags in want.items():
+        assert make_hostcore(model_bytes(name)).fast_flags() == flags, name
 
 
 def test_loader_rejects_bad_models(hostcore):
