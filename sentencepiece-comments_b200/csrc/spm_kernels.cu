@@ -26,9 +26,11 @@
 //                     (src/sentencepiece_processor.cc:319-330,945-979)
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -98,20 +100,10 @@ k_gen_normalize(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c
   gstatus[t] = st;
 }
 
-__global__ void __launch_bounds__(kThreads)
-k_gen_encode(ModelView mv, const int32_t *list, const uint32_t *count, int64_t t0, int64_t tn,
-             const int64_t *noff, const uint8_t *norm, const int32_t *nlen, const int64_t *woff, int64_t wbase,
-             int32_t *scratch, int32_t *gstage, const uint32_t *gstatus, int32_t *cnt, uint32_t *status, int64_t *srcoff,
-             uint32_t *status_or) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= tn) return;
-  if (count != nullptr && t0 + t >= (int64_t)*count) return;
-  const int64_t i = list ? list[t0 + t] : t0 + t;  // chunk-relative sentence index
-  const int64_t nb = noff[t];
-  const int32_t nl = nlen[t];
-  uint32_t st = gstatus[t];
+__device__ __forceinline__ void gen_encode_one(const ModelView &mv, int64_t i, int64_t nb, int32_t nl, uint32_t st,
+                                               int32_t *w, const uint8_t *norm, int32_t *gstage, int32_t *cnt,
+                                               uint32_t *status, int64_t *srcoff, uint32_t *status_or) {
   int32_t c = 0;
-  int32_t *w = scratch + (woff[t] - wbase);
   if (st == 0) {
     if (mv.model_type == M_UNIGRAM) {
       UniScratch sc;
@@ -130,6 +122,36 @@ k_gen_encode(ModelView mv, const int32_t *list, const uint32_t *count, int64_t t
   status[i] = st | ST_GEN;
   srcoff[i] = nb;
   if (st) atomicOr(status_or, st);
+}
+
+// throughput variant: one thread per listed sentence, scratch in global memory
+__global__ void __launch_bounds__(kThreads)
+k_gen_encode(ModelView mv, const int32_t *list, const uint32_t *count, int64_t t0, int64_t tn,
+             const int64_t *noff, const uint8_t *norm, const int32_t *nlen, const int64_t *woff, int64_t wbase,
+             int32_t *scratch, int32_t *gstage, const uint32_t *gstatus, int32_t *cnt, uint32_t *status, int64_t *srcoff,
+             uint32_t *status_or) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= tn) return;
+  if (count != nullptr && t0 + t >= (int64_t)*count) return;
+  const int64_t i = list ? list[t0 + t] : t0 + t;  // chunk-relative sentence index
+  gen_encode_one(mv, i, noff[t], nlen[t], gstatus[t], scratch + (woff[t] - wbase), norm, gstage, cnt, status, srcoff,
+                 status_or);
+}
+
+// latency variant for short lists (the sentences the fast tier flags): one block per
+// sentence, one working thread, scratch in shared memory when it fits -- the dependent
+// accesses of the exact tier then cost ~30 cycles instead of an L2 round trip each.
+constexpr int kGenSmemWords = 12288;   // 48 KB
+__global__ void __launch_bounds__(32)
+k_gen_encode_block(ModelView mv, const int32_t *list, int64_t tn, const int64_t *noff, const uint8_t *norm,
+                   const int32_t *nlen, const int32_t *words, const int64_t *woff, int32_t *scratch, int32_t *gstage,
+                   const uint32_t *gstatus, int32_t *cnt, uint32_t *status, int64_t *srcoff, uint32_t *status_or) {
+  __shared__ __align__(16) int32_t sm[kGenSmemWords];
+  const int64_t t = blockIdx.x;
+  if (t >= tn || threadIdx.x != 0) return;
+  const int64_t i = list ? list[t] : t;
+  int32_t *w = words[t] <= kGenSmemWords ? sm : scratch + woff[t];
+  gen_encode_one(mv, i, noff[t], nlen[t], gstatus[t], w, norm, gstage, cnt, status, srcoff, status_or);
 }
 
 // ---------------------------------------------------------------- fast tier
@@ -286,6 +308,17 @@ __global__ void __launch_bounds__(256) k_validate(const int64_t *off, int64_t n,
     if (mx > 0) atomicMax(&scal[6], (unsigned long long)mx);
     if (mxf > 0) atomicMax(&scal[7], (unsigned long long)mxf);
   }
+}
+
+// Host-visible snapshot of the small device-side scalars.  The host reads them from
+// MAPPED pinned memory after a stream sync, so no tiny copy ever queues behind the bulk
+// PCIe transfers of the copy-in / copy-out streams.
+// out[0..7] = counters, out[8..15] = scalars, out[16 + slot] = scalars[0] (running id total).
+__global__ void k_publish(const uint32_t *counters, const int64_t *scalars, volatile int64_t *out, int slot) {
+  const int k = threadIdx.x;
+  if (k < 8) out[k] = counters ? (int64_t)counters[k] : 0;
+  else if (k < 16) out[k] = scalars[k - 8];
+  else if (k == 16 && slot >= 0) out[16 + slot] = scalars[0];
 }
 
 struct FastParams {
@@ -561,6 +594,12 @@ struct spm_cuda_model {
   mutable cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   mutable std::vector<cudaEvent_t> kev;  // event pairs around the dominant (encode) kernel launches
   mutable size_t nk = 0;
+  // host-memory calls: copy-in / copy-out streams so that PCIe traffic overlaps the kernels
+  mutable cudaStream_t s_in = nullptr, s_out = nullptr;
+  mutable std::vector<cudaEvent_t> ev_in, ev_done;
+  mutable cudaEvent_t ev_start = nullptr, ev_out = nullptr;
+  mutable int64_t *h_pin = nullptr;   // mapped pinned memory: snapshots written by k_publish
+  mutable int64_t *d_pin = nullptr;   // its device address
   int bos_id = 0, eos_id = 0, pad_id = 0;
   std::vector<DevBuf *> all_bufs() const {
     spm_cuda_model *m = const_cast<spm_cuda_model *>(this);
@@ -704,9 +743,9 @@ int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text,
   if ((rc = run_scan(M, st, (const int32_t *)M->g_need.p, gcount, IdentityOp(), (int64_t *)M->g_noff.p, d_tot, 0,
                      launches)))
     return rc;
-  int64_t total_norm = 0;
-  CUDA_TRY(cudaMemcpyAsync(&total_norm, d_tot, 8, cudaMemcpyDeviceToHost, st));
+  k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
   CUDA_TRY(cudaStreamSynchronize(st));
+  const int64_t total_norm = M->h_pin[8 + 4];
   if ((rc = M->g_norm.ensure((size_t)total_norm + 64))) return rc;
   if ((rc = M->g_stage.ensure((size_t)total_norm * 4 + 64))) return rc;
   k_gen_normalize<<<grid, kThreads, 0, st>>>(M->mv, d_text, d_off, c0, list, nullptr, 0, gcount,
@@ -717,9 +756,9 @@ int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text,
   if ((rc = run_scan(M, st, (const int32_t *)M->g_words.p, gcount, IdentityOp(), (int64_t *)M->g_woff.p, d_tot + 1,
                      0, launches)))
     return rc;
-  int64_t total_words = 0;
-  CUDA_TRY(cudaMemcpyAsync(&total_words, d_tot + 1, 8, cudaMemcpyDeviceToHost, st));
+  k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
   CUDA_TRY(cudaStreamSynchronize(st));
+  const int64_t total_words = M->h_pin[8 + 5];
   const int64_t kScratchBudgetWords = (int64_t)1 << 30;  // 4 GiB of Viterbi / agenda scratch per launch
   uint32_t *d_stor = (uint32_t *)((int64_t *)M->w_scalars.p + 2);  // OR of all status words of the call
   auto launch = [&](int64_t a, int64_t b, int64_t wbase) -> int {
@@ -739,7 +778,17 @@ int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text,
   };
   if (total_words <= kScratchBudgetWords) {
     if ((rc = M->g_scratch.ensure((size_t)total_words * 4 + 64))) return rc;
-    return launch(0, gcount, 0);
+    if (gcount > 16384) return launch(0, gcount, 0);
+    if (timed && (rc = kev_record(M, st, 0))) return rc;
+    k_gen_encode_block<<<(unsigned)gcount, 32, 0, st>>>(
+        M->mv, list, gcount, (const int64_t *)M->g_noff.p, (const uint8_t *)M->g_norm.p,
+        (const int32_t *)M->g_nlen.p, (const int32_t *)M->g_words.p, (const int64_t *)M->g_woff.p,
+        (int32_t *)M->g_scratch.p, (int32_t *)M->g_stage.p, (const uint32_t *)M->g_status.p, (int32_t *)M->w_cnt.p,
+        (uint32_t *)M->w_status.p, (int64_t *)M->w_srcoff.p, d_stor);
+    *launches += 1;
+    if (timed && (rc = kev_record(M, st, 1))) return rc;
+    CUDA_TRY(cudaGetLastError());
+    return kOk;
   }
   // rare: slice the list so each launch stays within the scratch budget
   M->h_woff.resize(gcount + 1);
@@ -783,6 +832,12 @@ int spm_cuda_model_load(const void *serialized_model, size_t len, int device, sp
   if (cudaSetDevice(device) != cudaSuccess) { g_err = "cudaSetDevice failed"; delete M; return kInternal; }
   rc = upload_model(M);
   if (rc) { spm_cuda_model_free(M); return rc; }
+  if (cudaHostAlloc((void **)&M->h_pin, (16 + 4096) * 8, cudaHostAllocMapped) != cudaSuccess ||
+      cudaHostGetDevicePointer((void **)&M->d_pin, M->h_pin, 0) != cudaSuccess) {
+    g_err = "cudaHostAlloc failed";
+    spm_cuda_model_free(M);
+    return kInternal;
+  }
   cudaEventCreate(&M->ev0);
   cudaEventCreate(&M->ev1);
   *out = M;
@@ -793,6 +848,13 @@ void spm_cuda_model_free(spm_cuda_model *M) {
   if (!M) return;
   cudaSetDevice(M->device);
   for (DevBuf *b : M->all_bufs()) b->release();
+  if (M->s_in) cudaStreamDestroy(M->s_in);
+  if (M->s_out) cudaStreamDestroy(M->s_out);
+  for (cudaEvent_t e : M->ev_in) cudaEventDestroy(e);
+  for (cudaEvent_t e : M->ev_done) cudaEventDestroy(e);
+  if (M->ev_start) cudaEventDestroy(M->ev_start);
+  if (M->ev_out) cudaEventDestroy(M->ev_out);
+  if (M->h_pin) cudaFreeHost(M->h_pin);
   if (M->ev0) cudaEventDestroy(M->ev0);
   if (M->ev1) cudaEventDestroy(M->ev1);
   for (cudaEvent_t e : M->kev) cudaEventDestroy(e);
@@ -879,6 +941,13 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   std::lock_guard<std::mutex> lk(M->mu);
   CUDA_TRY(cudaSetDevice(M->device));
   cudaStream_t st = (cudaStream_t)cuda_stream;
+  static const bool trace = getenv("SPM_CUDA_TRACE") != nullptr;   // host-side timeline on stderr
+  const auto t_begin = std::chrono::steady_clock::now();
+  auto tr = [&](const char *what, long k) {
+    if (trace)
+      fprintf(stderr, "[spm_cuda] %8.3f ms  %s %ld\n",
+              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count(), what, k);
+  };
   const bool host = memory_space == SPM_CUDA_HOST;
   double launches = 0;
   int rc;
@@ -900,9 +969,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     if ((rc = M->w_text.ensure((size_t)(text_hi - text_lo) + 16))) return rc;
     if ((rc = M->w_idoff.ensure((n + 1) * 8))) return rc;
     CUDA_TRY(cudaMemcpyAsync(M->w_off.p, text_offsets, (n + 1) * 8, cudaMemcpyHostToDevice, st));
-    if (text_hi > text_lo)
-      CUDA_TRY(cudaMemcpyAsync(M->w_text.p, text + text_lo, text_hi - text_lo, cudaMemcpyHostToDevice, st));
-    d_off = (const int64_t *)M->w_off.p;
+    d_off = (const int64_t *)M->w_off.p;   // (the text follows chunk by chunk on the copy-in stream)
     d_text = (const uint8_t *)M->w_text.p - text_lo;  // indexed by absolute offsets
   } else {
     d_off = text_offsets;
@@ -939,9 +1006,10 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     const unsigned vgrid = (unsigned)std::min<int64_t>((n + 255) / 256, 4 * (int64_t)M->sm_count);
     k_validate<<<vgrid, 256, 0, st>>>(d_off, n, (unsigned long long *)M->w_scalars.p);
     launches += 1;
-    int64_t hv[8];
-    CUDA_TRY(cudaMemcpyAsync(hv, M->w_scalars.p, 64, cudaMemcpyDeviceToHost, st));
+    k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
     CUDA_TRY(cudaStreamSynchronize(st));
+    const int64_t *hv = M->h_pin + 8;
+    tr("validated", n);
     if (hv[3]) { g_err = "text_offsets must be non-decreasing"; return kInvalidArgument; }
     max_len = hv[6]; max_raw = hv[7];
     if (max_len > ((int64_t)1 << 26)) { g_err = "sentence longer than 64 MiB"; return kOutOfRange; }
@@ -962,14 +1030,75 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   const int64_t kMaxChunk = M->fast ? (1 << 24) : (1 << 20);
   uint32_t stor = 0;
   int64_t n_general = 0;
-  int64_t c0 = 0, off_c0 = text_lo;
-  while (c0 < n) {
-    int64_t c1 = std::min(n, c0 + kMaxChunk), off_c1 = 0;
-    if ((rc = read_off(c1, &off_c1))) return rc;
-    while (off_c1 - off_c0 > kRawBudget && c1 - c0 > 1) {
-      c1 = c0 + (c1 - c0) / 2;
+  struct Chunk { int64_t c0, c1, o0, o1; };
+  std::vector<Chunk> chunks;
+  {
+    // host-memory calls of some size are cut into ~8 chunks so copies and kernels pipeline
+    int64_t want = kMaxChunk;
+    if (host && n >= (1 << 20)) want = std::min(kMaxChunk, (n + 7) / 8);
+    int64_t c0 = 0, off_c0 = text_lo;
+    while (c0 < n) {
+      int64_t c1 = std::min(n, c0 + want), off_c1 = 0;
       if ((rc = read_off(c1, &off_c1))) return rc;
+      while (off_c1 - off_c0 > kRawBudget && c1 - c0 > 1) {
+        c1 = c0 + (c1 - c0) / 2;
+        if ((rc = read_off(c1, &off_c1))) return rc;
+      }
+      chunks.push_back(Chunk{c0, c1, off_c0, off_c1});
+      c0 = c1;
+      off_c0 = off_c1;
     }
+  }
+  const size_t nch = chunks.size();
+  if (host && nch > 0) {
+    if (!M->s_in) {
+      CUDA_TRY(cudaStreamCreateWithFlags(&M->s_in, cudaStreamNonBlocking));
+      CUDA_TRY(cudaStreamCreateWithFlags(&M->s_out, cudaStreamNonBlocking));
+      CUDA_TRY(cudaEventCreateWithFlags(&M->ev_start, cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&M->ev_out, cudaEventDisableTiming));
+    }
+    if (nch + 1 > 4096) { g_err = "too many chunks"; return kOutOfRange; }
+    while (M->ev_in.size() < nch) {
+      cudaEvent_t a, b2;
+      CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&b2, cudaEventDisableTiming));
+      M->ev_in.push_back(a);
+      M->ev_done.push_back(b2);
+    }
+    // all text copies are queued now; chunk k's kernels wait for ev_in[k] only
+    CUDA_TRY(cudaEventRecord(M->ev_start, st));
+    CUDA_TRY(cudaStreamWaitEvent(M->s_in, M->ev_start, 0));
+    CUDA_TRY(cudaStreamWaitEvent(M->s_out, M->ev_start, 0));
+    for (size_t k = 0; k < nch; ++k) {
+      const Chunk &ch = chunks[k];
+      if (ch.o1 > ch.o0)
+        CUDA_TRY(cudaMemcpyAsync((uint8_t *)M->w_text.p + (ch.o0 - text_lo), text + ch.o0, ch.o1 - ch.o0,
+                                 cudaMemcpyHostToDevice, M->s_in));
+      CUDA_TRY(cudaEventRecord(M->ev_in[k], M->s_in));
+    }
+  }
+  // copy-out of finished chunks (host mode): ids and offsets of chunk k leave on s_out as
+  // soon as its running total has reached the host, while later chunks compute
+  size_t flushed = 0;
+  int64_t ids_done = 0;
+  auto flush_outputs = [&](size_t upto) -> int {   // chunks [flushed, upto) have their totals in h_pin
+    for (; flushed < upto; ++flushed) {
+      const Chunk &ch = chunks[flushed];
+      const int64_t tot = M->h_pin[16 + flushed];
+      CUDA_TRY(cudaStreamWaitEvent(M->s_out, M->ev_done[flushed], 0));
+      CUDA_TRY(cudaMemcpyAsync(id_offsets + ch.c0, d_idoff + ch.c0, (ch.c1 - ch.c0 + 1) * 8, cudaMemcpyDeviceToHost,
+                               M->s_out));
+      const int64_t hi = std::min(tot, ids_capacity);
+      if (hi > ids_done)
+        CUDA_TRY(cudaMemcpyAsync(ids + ids_done, d_ids + ids_done, (hi - ids_done) * 4, cudaMemcpyDeviceToHost,
+                                 M->s_out));
+      ids_done = std::max(ids_done, hi);
+    }
+    return kOk;
+  };
+  for (size_t kc = 0; kc < nch; ++kc) {
+    const int64_t c0 = chunks[kc].c0, c1 = chunks[kc].c1, off_c0 = chunks[kc].o0, off_c1 = chunks[kc].o1;
+    if (host) CUDA_TRY(cudaStreamWaitEvent(st, M->ev_in[kc], 0));
     const int64_t cn = c1 - c0, raw = off_c1 - off_c0;
     if ((rc = M->w_cnt.ensure(cn * 4))) return rc;
     if ((rc = M->w_status.ensure(cn * 4))) return rc;
@@ -1007,9 +1136,12 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       if ((rc = kev_record(M, st, 1))) return rc;
       launches += 4;
       CUDA_TRY(cudaGetLastError());
-      uint32_t hc[C_COUNT];
-      CUDA_TRY(cudaMemcpyAsync(hc, d_counters, sizeof(hc), cudaMemcpyDeviceToHost, st));
+      k_publish<<<1, 32, 0, st>>>(d_counters, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
       CUDA_TRY(cudaStreamSynchronize(st));
+      int64_t hc[C_COUNT];
+      for (int k = 0; k < C_COUNT; ++k) hc[k] = M->h_pin[k];
+      tr("fast kernel done, chunk", (long)kc);
+      if (host && (rc = flush_outputs(kc))) return rc;   // earlier chunks are complete by now
       n_general += hc[C_NGEN];
       if ((rc = run_general(M, st, d_text, d_off, c0, (const int32_t *)M->w_genlist.p, hc[C_NGEN], false,
                             &launches)))
@@ -1028,13 +1160,16 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
                                      d_cap);
     launches += 1;
     CUDA_TRY(cudaGetLastError());
-    c0 = c1;
-    off_c0 = off_c1;
+    tr("chunk enqueued", (long)kc);
+    if (host) {
+      k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, (int)kc);
+      CUDA_TRY(cudaEventRecord(M->ev_done[kc], st));
+    }
   }
   CUDA_TRY(cudaEventRecord(M->ev1, st));
-  int64_t hsc[3] = {0, 0, 0};
-  CUDA_TRY(cudaMemcpyAsync(hsc, M->w_scalars.p, 24, cudaMemcpyDeviceToHost, st));
+  k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
   CUDA_TRY(cudaStreamSynchronize(st));
+  const int64_t hsc[3] = {M->h_pin[8], M->h_pin[9], M->h_pin[10]};
   const int64_t total = hsc[0];
   stor = (uint32_t)hsc[2];
   if (n == 0) {
@@ -1043,11 +1178,13 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     else CUDA_TRY(cudaMemcpyAsync(id_offsets, &z, 8, cudaMemcpyHostToDevice, st));
   }
   if (host && n > 0) {
-    CUDA_TRY(cudaMemcpyAsync(id_offsets, d_idoff, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
-    const int64_t ncopy = total < ids_capacity ? total : ids_capacity;
-    if (ncopy > 0) CUDA_TRY(cudaMemcpyAsync(ids, d_ids, ncopy * 4, cudaMemcpyDeviceToHost, st));
+    if ((rc = flush_outputs(nch))) return rc;      // st is synchronized: every total is on the host
+    CUDA_TRY(cudaEventRecord(M->ev_out, M->s_out));
+    CUDA_TRY(cudaStreamWaitEvent(st, M->ev_out, 0));
   }
+  tr("kernels done", 0);
   CUDA_TRY(cudaStreamSynchronize(st));
+  tr("all done", 0);
   float ms = 0;
   cudaEventElapsedTime(&ms, M->ev0, M->ev1);
   M->stats[0] = launches;
