@@ -23,7 +23,8 @@ def build(force=False, verbose=False):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     os.makedirs(os.path.dirname(LIB), exist_ok=True)
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+    extra = os.environ.get("SPM_EXTRA_NVCC_FLAGS", "").split()   # tuning experiments only
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
         [os.path.join(CSRC, s) for s in SOURCES] + ["-o", LIB]
     subprocess.check_call(cmd)
     return LIB

@@ -137,11 +137,18 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
   uint32_t tslot = 0;             // staging slot that holds word qw + 5
   fast_prefetch_word(txt, txt_saddr, sw + 5);
   float bt_p = 0.0f;              // BOS
+  // Near-tie tolerance of the walk that starts at the current character.  A push is flagged
+  // when |bt - M| <= 2^-20 (max(|M|,|bt|) + smax) and bt != M (see unigram_encode()); since
+  // |bt| <= |bt_p| + smax and a near-tied M is within the tolerance of bt, the per-character
+  // bound 2^-20 (|bt_p| + 2 smax + 1) flags a superset -- cheaper, still exact after the
+  // exact tier re-runs the flagged sentences.
+  float tol_p = (2.0f * fv.smax + 1.0f) * TOL;
   uint32_t cur = w0;
   int cl = one_char_len((uint8_t)cur);
   uint32_t u = root;
   int d = 0, k = 0;
   bool single = false;
+  uint32_t *bp = back;            // back record of character ci goes to bp[0]
   for (;;) {
     const uint32_t c = cur & 0xFFu;
     bool ok = (u & 0x200u) && c != 0;
@@ -164,7 +171,7 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
         if (slot >= R) slot -= R;
         const float M = ring_bt[slot * rstride];
         const float diff = bt - M;
-        if (fabsf(diff) <= (fmaxf(fabsf(M), fabsf(bt)) + fv.smax) * TOL && diff != 0.0f) flag = ST_CAND_OVERFLOW;
+        if (fabsf(diff) <= tol_p && diff != 0.0f) flag = ST_CAND_OVERFLOW;
         if (diff > 0.0f) {                 // strict '>' keeps the first (longest) of equals
           ring_bt[slot * rstride] = bt;
           ring_bk[slot * rstride] = child | ((uint32_t)k << 24);
@@ -188,7 +195,7 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
         if (slot >= R) slot -= R;
         const float M = ring_bt[slot * rstride];
         const float diff = bt - M;
-        if (fabsf(diff) <= (fmaxf(fabsf(M), fabsf(bt)) + fv.smax) * TOL && diff != 0.0f) flag = ST_CAND_OVERFLOW;
+        if (fabsf(diff) <= tol_p && diff != 0.0f) flag = ST_CAND_OVERFLOW;
         if (diff > 0.0f) {
           ring_bt[slot * rstride] = bt;
           ring_bk[slot * rstride] = kFastUnk | (1u << 24);
@@ -197,11 +204,13 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
       p += cl;
       r += cl;
       ++ci;
+      ++bp;
       if (++ridx == R) ridx = 0;
       bt_p = ring_bt[ridx * rstride];
-      back[ci] = ring_bk[ridx * rstride];
+      *bp = ring_bk[ridx * rstride];
       ring_bt[ridx * rstride] = NEG;
       if (p >= n) break;
+      tol_p = (fabsf(bt_p) + 2.0f * fv.smax + 1.0f) * TOL;
       if (r >= 4) {                        // slide the window by one word; word qw + 5 was requested one slide ago
         r -= 4; ++qw;
         fast_prefetch_wait();

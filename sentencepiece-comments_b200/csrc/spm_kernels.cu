@@ -57,7 +57,10 @@ thread_local std::string g_err;
 
 constexpr int kCapc = 8;          // near-tie candidates kept per position by the exact tier
 constexpr int kThreads = 128;     // general-tier block size
-constexpr int kFastThreads = 768; // fast-tier block size (one persistent CTA per SM)
+#ifndef SPM_FAST_THREADS
+#define SPM_FAST_THREADS 768
+#endif
+constexpr int kFastThreads = SPM_FAST_THREADS; // fast-tier block size (one persistent CTA per SM)
 constexpr int kBpeThreads = 512;  // BPE fast-tier block size
 constexpr uint32_t ST_GEN = 1u << 16;   // sentence was encoded by the general tier (ids in gstage, forward order)
 constexpr uint32_t ST_FWD = 1u << 17;   // fast-tier ids were staged in forward order (BPE)
