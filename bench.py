@@ -311,6 +311,7 @@ def run_b200(args):
                            "parallelism": "sentence-sharded x%d, no collective" % world},
                 "input_gb_per_s": bytes_all * args.steps / (ms_all * 1e-3) / 1e9,
                 "ids_per_s": ids_all * args.steps / (ms_all * 1e-3),
+                "general_tier_sentences_per_step": st["fallback_sentences"],
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": None, "kernel": "encode kernel(s)",
                              "kernel_ms_per_launch": k_avg_ms, "kernel_launches": kern_launches,

@@ -33,6 +33,7 @@ namespace spmb {
 constexpr uint32_t kFastUnk = 0x00FFFFFFu;   // node field of an UNK back record
 constexpr int kFastMaxRaw = 4096;            // fast tier: raw sentence length < this (bytes); also the sort key range
 constexpr int kFastExtraChars = 16;          // fast tier: characters <= raw bytes + this
+constexpr int kLongMaxRaw = 65536;           // long lines (kFastMaxRaw <= bytes < this): same kernels, few threads
 constexpr int kNormPad = 40;                 // zero bytes guaranteed after a normalized sentence
 
 struct FastView {

@@ -58,7 +58,7 @@ thread_local std::string g_err;
 constexpr int kCapc = 8;          // near-tie candidates kept per position by the exact tier
 constexpr int kThreads = 128;     // general-tier block size
 #ifndef SPM_FAST_THREADS
-#define SPM_FAST_THREADS 768
+#define SPM_FAST_THREADS 1024
 #endif
 constexpr int kFastThreads = SPM_FAST_THREADS; // fast-tier block size (one persistent CTA per SM)
 constexpr int kBpeThreads = 512;  // BPE fast-tier block size
@@ -66,7 +66,7 @@ constexpr uint32_t ST_GEN = 1u << 16;   // sentence was encoded by the general t
 constexpr uint32_t ST_FWD = 1u << 17;   // fast-tier ids were staged in forward order (BPE)
 
 // device-side counters of one chunk
-enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_COUNT = 8 };
+enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_WORK_LONG = 4, C_NLONG = 5, C_COUNT = 8 };
 
 // ---------------------------------------------------------------- general tier
 // Sentence t of the list is sentence list[t] of the chunk (list == nullptr: t).
@@ -174,7 +174,7 @@ __device__ __forceinline__ int64_t fast_stage_base(const int64_t *off, int64_t c
 constexpr int kSortThreads = 1024, kSortItems = 8, kSortTile = kSortThreads * kSortItems;
 __global__ void __launch_bounds__(kSortThreads)
 k_hist(const int64_t *off, int64_t c0, int64_t cn, int32_t *cnt, uint32_t *status, uint32_t *hist,
-       int32_t *gen_list, uint32_t *counters) {
+       int32_t *gen_list, int32_t *long_list, uint32_t *counters) {
   __shared__ uint32_t sh[kFastMaxRaw];
   for (int k = threadIdx.x; k < kFastMaxRaw; k += kSortThreads) sh[k] = 0;
   __syncthreads();
@@ -186,7 +186,8 @@ k_hist(const int64_t *off, int64_t c0, int64_t cn, int32_t *cnt, uint32_t *statu
       const int64_t len = off[c0 + t + 1] - off[c0 + t];
       cnt[t] = 0;
       status[t] = 0;
-      if (len >= kFastMaxRaw) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
+      if (len >= kLongMaxRaw) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
+      else if (len >= kFastMaxRaw) long_list[atomicAdd(&counters[C_NLONG], 1u)] = (int32_t)t;
       else if (len > 0) atomicAdd(&sh[len], 1u);
     }
   }
@@ -267,14 +268,14 @@ k_scatter(const int64_t *off, int64_t c0, int64_t cn, uint32_t *bincur, int32_t 
 constexpr int kNormThreads = 256;
 __global__ void __launch_bounds__(kNormThreads)
 k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c0, const uint8_t *lo,
-                 const uint8_t *hi, const int32_t *perm, uint8_t *norm, int32_t *nlen, int32_t *gen_list,
-                 uint32_t *counters) {
+                 const uint8_t *hi, const int32_t *perm, int count_idx, uint8_t *norm, int32_t *nlen,
+                 int32_t *gen_list, uint32_t *counters) {
   __shared__ uint32_t first2[2048];
   if (mv.cm_first2 != nullptr)
     for (int k = threadIdx.x; k < 2048; k += kNormThreads) first2[k] = mv.cm_first2[k];
   __syncthreads();
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)counters[C_NFAST]) return;
+  if (idx >= (int64_t)counters[count_idx]) return;
   const int32_t t = perm[idx];
   const int64_t i = c0 + t;
   const int64_t len = off[i + 1] - off[i];
@@ -290,26 +291,30 @@ k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t 
 
 // Checks the offsets of the whole batch on the device (no O(n) work on the host):
 // scal[3] |= 1 when offsets decrease, scal[6] = longest sentence, scal[7] = longest
-// sentence shorter than kFastMaxRaw (sizes the back-pointer arrays).
+// sentence shorter than kFastMaxRaw, scal[1] = longest sentence shorter than kLongMaxRaw
+// (both size the back-pointer arrays).
 __global__ void __launch_bounds__(256) k_validate(const int64_t *off, int64_t n, unsigned long long *scal) {
-  long long mx = 0, mxf = 0;
+  long long mx = 0, mxf = 0, mxl = 0;
   int bad = 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const long long len = off[i + 1] - off[i];
     if (len < 0) bad = 1;
     if (len > mx) mx = len;
     if (len < kFastMaxRaw && len > mxf) mxf = len;
+    if (len < kLongMaxRaw && len > mxl) mxl = len;
   }
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) {
     mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, d));
     mxf = max(mxf, __shfl_xor_sync(0xFFFFFFFFu, mxf, d));
+    mxl = max(mxl, __shfl_xor_sync(0xFFFFFFFFu, mxl, d));
     bad |= __shfl_xor_sync(0xFFFFFFFFu, bad, d);
   }
   if ((threadIdx.x & 31) == 0) {
     if (bad) atomicOr(&scal[3], 1ull);
     if (mx > 0) atomicMax(&scal[6], (unsigned long long)mx);
     if (mxf > 0) atomicMax(&scal[7], (unsigned long long)mxf);
+    if (mxl > 0) atomicMax(&scal[1], (unsigned long long)mxl);
   }
 }
 
@@ -334,11 +339,22 @@ struct FastParams {
   int32_t unk_id;
 };
 
+// Work units of the persistent encode kernels: `lpu` consecutive list entries per warp fetch.
+// The length-sorted main pass always takes 32; the long-line pass has few, unsorted entries
+// and spreads them over every resident warp (a warp with 4 busy lanes is as fast as one with
+// 32 -- the kernels are latency bound).
+__device__ __forceinline__ uint32_t fast_lanes_per_unit(uint32_t count, int warps_per_cta) {
+  if (warps_per_cta * 32 == (int)blockDim.x) return 32u;
+  const uint32_t warps = gridDim.x * (uint32_t)warps_per_cta;
+  const uint32_t per = (count + warps - 1) / warps;
+  return per < 1u ? 1u : (per > 32u ? 32u : per);
+}
+
 // Persistent CTAs (one per SM).  Shared memory: hot units | hot scores | ring_bt[R][T] | ring_bk[R][T].
 __global__ void __launch_bounds__(kFastThreads, 1)
 k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
-              const int32_t *perm, uint32_t *back, int64_t back_rows, int32_t *stage, int32_t *cnt,
-              uint32_t *status, int32_t *gen_list, uint32_t *counters) {
+              const int32_t *perm, int count_idx, int work_idx, int max_warps, uint32_t *back, int64_t back_rows,
+              int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *gen_list, uint32_t *counters) {
   extern __shared__ __align__(16) uint32_t smem[];
   uint32_t *units_hot = smem;
   float *score_hot = (float *)(smem + fp.k_units);
@@ -355,16 +371,18 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
   fv.score_hot_saddr = (uint32_t)__cvta_generic_to_shared(score_hot);
   fv.k_units = fp.k_units; fv.k_scores = fp.k_scores; fv.n_units = fp.n_units;
   fv.ring = fp.ring; fv.unk_score = fp.unk_score; fv.smax = fp.smax; fv.unk_id = fp.unk_id;
-  const uint32_t nfast = counters[C_NFAST];
+  const uint32_t nfast = counters[count_idx];
   const int lane = threadIdx.x & 31;
-  uint32_t *myback = back + ((int64_t)blockIdx.x * kFastThreads + threadIdx.x) * back_rows;
+  if ((int)(threadIdx.x >> 5) >= max_warps) return;   // long lines run on a few warps per SM (back arrays are big)
+  const uint32_t lpu = fast_lanes_per_unit(nfast, max_warps);
+  uint32_t *myback = back + ((int64_t)blockIdx.x * max_warps * 32 + threadIdx.x) * back_rows;
   for (;;) {
     uint32_t w = 0;
-    if (lane == 0) w = atomicAdd(&counters[C_WORK], 1u);
+    if (lane == 0) w = atomicAdd(&counters[work_idx], 1u);
     w = __shfl_sync(0xFFFFFFFFu, w, 0);
-    const uint32_t idx = w * 32 + lane;
-    if (w * 32 >= nfast) break;
-    if (idx < nfast) {
+    const uint32_t idx = w * lpu + lane;
+    if (w * lpu >= nfast) break;
+    if ((uint32_t)lane < lpu && idx < nfast) {
       const int32_t t = perm[idx];
       uint32_t st = 0;
       const int32_t nl = nlen[t];
@@ -386,8 +404,8 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
 // node[S][T] | ps[S][T] | text[B/4][T] | cb[..][T] | txt[2][T]  (T = kBpeThreads).
 __global__ void __launch_bounds__(kBpeThreads, 1)
 k_encode_bpe_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
-                  const int32_t *perm, int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *gen_list,
-                  uint32_t *counters) {
+                  const int32_t *perm, int count_idx, int work_idx, int max_warps, int32_t *stage, int32_t *cnt,
+                  uint32_t *status, int32_t *gen_list, uint32_t *counters) {
   extern __shared__ __align__(16) uint32_t smem[];
   uint32_t *units_hot = smem;
   float *score_hot = (float *)(smem + fp.k_units);
@@ -409,15 +427,17 @@ k_encode_bpe_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *
   bs.text = bs.node + 2 * kBpeMaxSyms * kBpeThreads;
   bs.cb = bs.text + (kBpeMaxBytes / 4) * kBpeThreads;
   uint32_t *txt = bs.cb + ((kBpeMaxSyms + 4) / 4) * kBpeThreads;
-  const uint32_t nfast = counters[C_NFAST];
+  const uint32_t nfast = counters[count_idx];
   const int lane = threadIdx.x & 31;
+  if ((int)(threadIdx.x >> 5) >= max_warps) return;
+  const uint32_t lpu = fast_lanes_per_unit(nfast, max_warps);
   for (;;) {
     uint32_t w = 0;
-    if (lane == 0) w = atomicAdd(&counters[C_WORK], 1u);
+    if (lane == 0) w = atomicAdd(&counters[work_idx], 1u);
     w = __shfl_sync(0xFFFFFFFFu, w, 0);
-    const uint32_t idx = w * 32 + lane;
-    if (w * 32 >= nfast) break;
-    if (idx < nfast) {
+    const uint32_t idx = w * lpu + lane;
+    if (w * lpu >= nfast) break;
+    if ((uint32_t)lane < lpu && idx < nfast) {
       const int32_t t = perm[idx];
       uint32_t st = 0;
       const int32_t nl = nlen[t];
@@ -590,7 +610,7 @@ struct spm_cuda_model {
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
-      w_perm, w_genlist, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
+      w_perm, w_genlist, w_longlist, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
   mutable std::vector<int64_t> h_woff;
   mutable double stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -609,7 +629,7 @@ struct spm_cuda_model {
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
             &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
-            &m->w_genlist, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
+            &m->w_genlist, &m->w_longlist, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status};
   }
 };
@@ -1004,7 +1024,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   int64_t *d_carry = (int64_t *)M->w_scalars.p;        // [0] running CSR total
   uint32_t *d_counters = (uint32_t *)M->w_counters.p;
   CUDA_TRY(cudaMemsetAsync(M->w_scalars.p, 0, 64, st));
-  int64_t max_len = 0, max_raw = 0;
+  int64_t max_len = 0, max_raw = 0, max_long = 0;
   if (n > 0) {
     const unsigned vgrid = (unsigned)std::min<int64_t>((n + 255) / 256, 4 * (int64_t)M->sm_count);
     k_validate<<<vgrid, 256, 0, st>>>(d_off, n, (unsigned long long *)M->w_scalars.p);
@@ -1014,7 +1034,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     const int64_t *hv = M->h_pin + 8;
     tr("validated", n);
     if (hv[3]) { g_err = "text_offsets must be non-decreasing"; return kInvalidArgument; }
-    max_len = hv[6]; max_raw = hv[7];
+    max_len = hv[6]; max_raw = hv[7]; max_long = hv[1];
     if (max_len > ((int64_t)1 << 26)) { g_err = "sentence longer than 64 MiB"; return kOutOfRange; }
   }
   if (M->fast && M->w_hist.cap == 0) {
@@ -1115,29 +1135,61 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       if ((rc = M->w_genlist.ensure(cn * 4))) return rc;
       // back-pointer rows: one per character (<= raw + kFastExtraChars) + BOS/EOS rows
       const int64_t back_rows = (max_raw + kFastExtraChars + 8 + 3) & ~(int64_t)3;
-      if (M->fast_kind == 1 && (rc = M->w_back.ensure((size_t)back_rows * M->sm_count * kFastThreads * 4))) return rc;
+      // long lines (kFastMaxRaw <= bytes < kLongMaxRaw): same kernels over long_list, on as
+      // many warps per SM as a 2 GiB back-pointer budget allows
+      const bool has_long = max_len >= kFastMaxRaw && max_long >= kFastMaxRaw;
+      const int64_t back_rows_long = (max_long + kFastExtraChars + 8 + 3) & ~(int64_t)3;
+      int long_warps = M->fast_kind == 1 ? kFastThreads / 32 : kBpeThreads / 32;
+      if (M->fast_kind == 1)
+        long_warps = (int)std::max<int64_t>(
+            1, std::min<int64_t>(long_warps, (2048ll << 20) / (back_rows_long * 4 * 32 * M->sm_count)));
+      size_t back_bytes = (size_t)back_rows * M->sm_count * kFastThreads * 4;
+      if (has_long) back_bytes = std::max(back_bytes, (size_t)back_rows_long * M->sm_count * long_warps * 32 * 4);
+      if (M->fast_kind == 1 && (rc = M->w_back.ensure(back_bytes))) return rc;
+      if (has_long && (rc = M->w_longlist.ensure((size_t)std::min<int64_t>(cn, raw / kFastMaxRaw + 1) * 4))) return rc;
       const unsigned gsort = (unsigned)((cn + kSortTile - 1) / kSortTile);
       k_hist<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
-                                   (int32_t *)M->w_genlist.p, d_counters);
+                                   (int32_t *)M->w_genlist.p, (int32_t *)M->w_longlist.p, d_counters);
       k_binscan<<<1, 1024, 0, st>>>(d_hist, d_bincur, d_counters);
       k_scatter<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, d_bincur, (int32_t *)M->w_perm.p);
       k_normalize_fast<<<(unsigned)((cn + kNormThreads - 1) / kNormThreads), kNormThreads, 0, st>>>(
-          M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p,
+          M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p, C_NFAST,
           (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
       launches += 1;
+      if (has_long) {
+        // the grid covers the most long lines the chunk's bytes can hold
+        const int64_t max_n_long = std::min<int64_t>(cn, raw / kFastMaxRaw + 1);
+        k_normalize_fast<<<(unsigned)((max_n_long + kNormThreads - 1) / kNormThreads), kNormThreads, 0, st>>>(
+            M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_longlist.p, C_NLONG,
+            (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
+        launches += 1;
+      }
       if ((rc = kev_record(M, st, 0))) return rc;
-      if (M->fast_kind == 1)
+      if (M->fast_kind == 1) {
         k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-            (const int32_t *)M->w_perm.p, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p,
-            (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
-      else
+            (const int32_t *)M->w_perm.p, C_NFAST, C_WORK, kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows,
+            (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p,
+            d_counters);
+        if (has_long)
+          k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
+              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+              (const int32_t *)M->w_longlist.p, C_NLONG, C_WORK_LONG, long_warps, (uint32_t *)M->w_back.p,
+              back_rows_long, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
+              (int32_t *)M->w_genlist.p, d_counters);
+      } else {
         k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-            (const int32_t *)M->w_perm.p, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
-            (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+            (const int32_t *)M->w_perm.p, C_NFAST, C_WORK, kBpeThreads / 32, (int32_t *)M->w_stage.p,
+            (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+        if (has_long)
+          k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
+              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+              (const int32_t *)M->w_longlist.p, C_NLONG, C_WORK_LONG, long_warps, (int32_t *)M->w_stage.p,
+              (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+      }
       if ((rc = kev_record(M, st, 1))) return rc;
-      launches += 4;
+      launches += has_long ? 5 : 4;
       CUDA_TRY(cudaGetLastError());
       k_publish<<<1, 32, 0, st>>>(d_counters, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
       CUDA_TRY(cudaStreamSynchronize(st));

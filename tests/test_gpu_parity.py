@@ -148,3 +148,51 @@ def test_empty_batch_and_errors(spm_b200):
     assert sp.EncodeAsIds("") == []
     with pytest.raises(spm_b200.StatusError):
         sp.SetEncodeExtraOptions("foo")
+
+
+@pytest.mark.parametrize("model,corpus", [("botchan_uni8k", "botchan"), ("botchan_bpe4k", "botchan"),
+                                          ("ref_ja_8k", "wagahai"), ("syn_bpe32k", "syn_dirty")])
+def test_long_lines(spm_b200, corpora, model, corpus):
+    """Lines around the tier boundaries (4096 and 65536 raw bytes) among short ones."""
+    mb = model_bytes(model)
+    sp = spm_b200.SentencePieceProcessor()
+    sp.LoadFromSerializedProto(mb)
+    chk, _ = checker(mb)
+    text, off = corpora[corpus]
+    reps = -(-(2 << 20) // len(text))
+    off = np.concatenate([[0]] + [off[1:] + r * len(text) for r in range(reps)]).astype(np.int64)
+    text = np.tile(text, reps)
+    rng = np.random.default_rng(5)
+    n = len(off) - 1
+    # glue runs of consecutive sentences into long lines
+    cuts = [0]
+    targets = [4095, 4096, 4097, 5000, 9000, 20000, 33000, 65535, 65536, 70000, 150000]
+    k = 0
+    i = 0
+    while i < n:
+        if k < 200 and rng.random() < 0.05:
+            want = targets[k % len(targets)] if k < 2 * len(targets) else int(rng.integers(4096, 40000))
+            k += 1
+            j = i
+            while j < n and off[j] - off[i] < want:
+                j += 1
+            # exact byte length where the text allows it (cut inside a sentence: keep UTF-8 whole)
+            end = min(int(off[i]) + want, int(off[n]))
+            while end < int(off[n]) and (text[end] & 0xC0) == 0x80:
+                end += 1
+            cuts.append(end)
+            i = int(np.searchsorted(off, end, side="left"))
+            if i <= n and i < len(off) and off[i] != end:
+                cuts.append(int(off[i]))
+        else:
+            i += 1
+            cuts.append(int(off[i]))
+    cuts = np.unique(np.asarray(cuts, dtype=np.int64))
+    lens = np.diff(cuts)
+    assert (lens >= 4096).sum() >= 10 and (lens >= 65536).sum() >= 1
+    got = sp.encode_packed(text, cuts)
+    assert_same(got, ref_encode(chk, text, cuts), text, cuts)
+    st = sp.last_stats()
+    # only the >= 64 KiB lines (and the rare flagged ones) may take the general tier
+    if corpus != "syn_dirty":   # (dirty text: an over-long word sends the whole line to the general tier)
+        assert st["fallback_sentences"] < (lens >= 4096).sum()
