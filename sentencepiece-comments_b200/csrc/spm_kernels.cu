@@ -38,6 +38,7 @@
 #include "../../include/spm_cuda.h"
 #include "spm_core.cuh"
 #include "spm_fast.cuh"
+#include "spm_memo.cuh"
 #include "spm_model.h"
 
 using namespace spmb;
@@ -66,7 +67,10 @@ constexpr uint32_t ST_GEN = 1u << 16;   // sentence was encoded by the general t
 constexpr uint32_t ST_FWD = 1u << 17;   // fast-tier ids were staged in forward order (BPE)
 
 // device-side counters of one chunk
-enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_WORK_LONG = 4, C_NLONG = 5, C_COUNT = 8 };
+enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_WORK_LONG = 4, C_NLONG = 5,
+       C_NVIT = 6, C_WORK_VIT = 7, C_NVITL = 8, C_WORK_VITL = 9, C_NNEW = 10, C_COUNT = 16 };
+// k_publish snapshot (int64 slots): counters | scalars | running id total of chunk k
+constexpr int kPubScal = C_COUNT, kPubTot = C_COUNT + 8;
 
 // ---------------------------------------------------------------- general tier
 // Sentence t of the list is sentence list[t] of the chunk (list == nullptr: t).
@@ -321,12 +325,13 @@ __global__ void __launch_bounds__(256) k_validate(const int64_t *off, int64_t n,
 // Host-visible snapshot of the small device-side scalars.  The host reads them from
 // MAPPED pinned memory after a stream sync, so no tiny copy ever queues behind the bulk
 // PCIe transfers of the copy-in / copy-out streams.
-// out[0..7] = counters, out[8..15] = scalars, out[16 + slot] = scalars[0] (running id total).
+// out[0..C_COUNT) = counters, out[kPubScal..+8) = scalars, out[kPubTot + slot] = scalars[0]
+// (running id total).
 __global__ void k_publish(const uint32_t *counters, const int64_t *scalars, volatile int64_t *out, int slot) {
   const int k = threadIdx.x;
-  if (k < 8) out[k] = counters ? (int64_t)counters[k] : 0;
-  else if (k < 16) out[k] = scalars[k - 8];
-  else if (k == 16 && slot >= 0) out[16 + slot] = scalars[0];
+  if (k < C_COUNT) out[k] = counters ? (int64_t)counters[k] : 0;
+  else if (k < C_COUNT + 8) out[k] = scalars[k - C_COUNT];
+  if (k == 0 && slot >= 0) out[kPubTot + slot] = scalars[0];
 }
 
 struct FastParams {
@@ -451,6 +456,108 @@ k_encode_bpe_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *
       }
     }
     __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------- word-memo tier (spm_memo.cuh)
+// k_memo_collect: one thread per sentence (sorted order) keys its words and records their
+// table slots; nwords[t] = word count, -1 = not memoisable (goes to the Viterbi tier),
+// -2 = nothing to do (already routed to the general tier).
+constexpr int kMemoThreads = 256;
+__global__ void __launch_bounds__(kMemoThreads)
+k_memo_collect(MemoTable tb, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
+               const int32_t *perm, int count_idx, uint32_t *wslots, int32_t *nwords, const uint32_t *counters) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)counters[count_idx]) return;
+  const int32_t t = perm[idx];
+  const int32_t nl = nlen[t];
+  int32_t nw = -2;
+  if (nl >= 0)
+    nw = memo_collect(tb, norm + fast_norm_base(off, c0, t), nl, wslots + fast_stage_base(off, c0, t));
+  nwords[t] = nw;
+}
+
+__device__ __forceinline__ FastView memo_cold_view(const FastParams &fp) {
+  FastView fv;
+  fv.units = fp.units; fv.score = fp.score; fv.leaf_id = fp.leaf_id;
+  fv.units_hot = fp.units; fv.score_hot = fp.score;     // nothing staged in shared memory here
+  fv.units_hot_saddr = 0; fv.score_hot_saddr = 0;
+  fv.k_units = 0; fv.k_scores = 0; fv.n_units = fp.n_units;
+  fv.ring = fp.ring; fv.unk_score = fp.unk_score; fv.smax = fp.smax; fv.unk_id = fp.unk_id;
+  return fv;
+}
+
+// One thread per word claimed in this pass.
+__global__ void __launch_bounds__(kMemoThreads)
+k_memo_words_unigram(FastParams fp, int neg_only, MemoTable tb) {
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t n_new = min(*tb.n_new, tb.max_new);
+  if (idx >= n_new) return;
+  const FastView fv = memo_cold_view(fp);
+  memo_unigram_word(fv, neg_only != 0, tb, idx);
+}
+
+// BPE: the word text goes to a 64-byte global slot first (fast_bpe prefetches its text with
+// cp.async from global memory); the merges run in the next kernel.
+__global__ void __launch_bounds__(kMemoThreads) k_memo_words_text(MemoTable tb, uint8_t *wtext, int32_t *wlen) {
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t n_new = min(*tb.n_new, tb.max_new);
+  if (idx >= n_new) return;
+  const MemoEntry *e = tb.e + tb.new_list[idx];
+  __align__(16) uint8_t buf[64];
+  const int nb = memo_word_bytes(tb.e, e, buf, 64);
+  uint4 *dst = reinterpret_cast<uint4 *>(wtext + (size_t)idx * 64);
+  const uint4 *src = reinterpret_cast<const uint4 *>(buf);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) dst[j] = src[j];
+  wlen[idx] = nb;
+}
+
+constexpr int kMemoBpeThreads = 128;
+__global__ void __launch_bounds__(kMemoBpeThreads)
+k_memo_words_bpe(FastParams fp, MemoTable tb, const uint8_t *wtext, const int32_t *wlen) {
+  __shared__ uint32_t scr[(kBpeWordsPerThread + 2) * kMemoBpeThreads];
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t n_new = min(*tb.n_new, tb.max_new);
+  if (idx >= n_new) return;
+  FastView fv = memo_cold_view(fp);
+  fv.ring = 0; fv.unk_score = 0; fv.smax = 0;
+  BpeScratch bs;
+  bs.stride = kMemoBpeThreads;
+  bs.node = scr + threadIdx.x;
+  bs.ps = (float *)(bs.node + kBpeMaxSyms * kMemoBpeThreads);
+  bs.text = bs.node + 2 * kBpeMaxSyms * kMemoBpeThreads;
+  bs.cb = bs.text + (kBpeMaxBytes / 4) * kMemoBpeThreads;
+  uint32_t *txt = bs.cb + ((kBpeMaxSyms + 4) / 4) * kMemoBpeThreads;
+  MemoEntry *e = tb.e + tb.new_list[idx];
+  int32_t ids[kBpeMaxSyms];
+  uint32_t st = 0;
+  const int32_t nb = wlen[idx];
+  const int32_t c = nb > 0 ? fast_bpe(fv, wtext + (size_t)idx * 64, nb, bs, txt, ids, &st) : 0;
+  memo_store_ids(tb, e, idx, ids, c, st != 0, fv.unk_id);
+}
+
+// k_memo_emit: ids of every memoised sentence (forward order) into the staging area; the
+// rest joins the list of the Viterbi tier.
+__global__ void __launch_bounds__(kMemoThreads)
+k_memo_emit(const MemoEntry *tab, const int32_t *overflow, int unigram, const int64_t *off, int64_t c0, const int32_t *perm, int count_idx,
+            int list_idx, const uint32_t *wslots, const int32_t *nwords, int32_t *stage, int32_t *cnt,
+            uint32_t *status, int32_t *vit_list, uint32_t *counters) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)counters[count_idx]) return;
+  const int32_t t = perm[idx];
+  const int32_t nw = nwords[t];
+  if (nw == -2) return;
+  int32_t c = -1;
+  if (nw >= 0) {
+    const int64_t base = fast_stage_base(off, c0, t);
+    c = memo_emit(tab, overflow, wslots + base, nw, unigram != 0, stage + base);
+  }
+  if (c < 0) {
+    vit_list[atomicAdd(&counters[list_idx], 1u)] = t;
+  } else {
+    cnt[t] = c;
+    status[t] = ST_FWD;
   }
 }
 
@@ -610,12 +717,13 @@ struct spm_cuda_model {
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
-      w_perm, w_genlist, w_longlist, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
+      w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_movf, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
   mutable std::vector<int64_t> h_woff;
-  mutable double stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  mutable double stats[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   mutable cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  mutable std::vector<cudaEvent_t> kev;  // event pairs around the dominant (encode) kernel launches
+  mutable std::vector<cudaEvent_t> kev;  // event pairs around the stages of a call
+  mutable std::vector<int> kev_tag;
   mutable size_t nk = 0;
   // host-memory calls: copy-in / copy-out streams so that PCIe traffic overlaps the kernels
   mutable cudaStream_t s_in = nullptr, s_out = nullptr;
@@ -629,7 +737,8 @@ struct spm_cuda_model {
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
             &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
-            &m->w_genlist, &m->w_longlist, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
+            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_movf,
+            &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status};
   }
 };
@@ -734,13 +843,17 @@ int run_scan(const spm_cuda_model *M, cudaStream_t st, const int32_t *in, int64_
   return kOk;
 }
 
-int kev_record(const spm_cuda_model *M, cudaStream_t st, int which) {
+// Event pairs around the stages of a call; `which` 0 opens a pair tagged `tag`, 1 closes it.
+enum { T_ENCODE = 0, T_NORMALIZE = 1, T_MEMO_COLLECT = 2, T_MEMO_WORDS = 3, T_MEMO_EMIT = 4, T_COMPACT = 5, T_COUNT = 6 };
+int kev_record(const spm_cuda_model *M, cudaStream_t st, int which, int tag = T_ENCODE) {
   while (M->kev.size() < 2 * (M->nk + 1)) {
     cudaEvent_t a;
     CUDA_TRY(cudaEventCreate(&a));
     M->kev.push_back(a);
   }
+  if (M->kev_tag.size() < M->nk + 1) M->kev_tag.resize(M->nk + 1);
   CUDA_TRY(cudaEventRecord(M->kev[2 * M->nk + which], st));
+  if (which == 0) M->kev_tag[M->nk] = tag;
   if (which == 1) ++M->nk;
   return kOk;
 }
@@ -768,7 +881,7 @@ int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text,
     return rc;
   k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
   CUDA_TRY(cudaStreamSynchronize(st));
-  const int64_t total_norm = M->h_pin[8 + 4];
+  const int64_t total_norm = M->h_pin[kPubScal + 4];
   if ((rc = M->g_norm.ensure((size_t)total_norm + 64))) return rc;
   if ((rc = M->g_stage.ensure((size_t)total_norm * 4 + 64))) return rc;
   k_gen_normalize<<<grid, kThreads, 0, st>>>(M->mv, d_text, d_off, c0, list, nullptr, 0, gcount,
@@ -781,7 +894,7 @@ int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text,
     return rc;
   k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
   CUDA_TRY(cudaStreamSynchronize(st));
-  const int64_t total_words = M->h_pin[8 + 5];
+  const int64_t total_words = M->h_pin[kPubScal + 5];
   const int64_t kScratchBudgetWords = (int64_t)1 << 30;  // 4 GiB of Viterbi / agenda scratch per launch
   uint32_t *d_stor = (uint32_t *)((int64_t *)M->w_scalars.p + 2);  // OR of all status words of the call
   auto launch = [&](int64_t a, int64_t b, int64_t wbase) -> int {
@@ -855,7 +968,7 @@ int spm_cuda_model_load(const void *serialized_model, size_t len, int device, sp
   if (cudaSetDevice(device) != cudaSuccess) { g_err = "cudaSetDevice failed"; delete M; return kInternal; }
   rc = upload_model(M);
   if (rc) { spm_cuda_model_free(M); return rc; }
-  if (cudaHostAlloc((void **)&M->h_pin, (16 + 4096) * 8, cudaHostAllocMapped) != cudaSuccess ||
+  if (cudaHostAlloc((void **)&M->h_pin, (kPubTot + 4096) * 8, cudaHostAllocMapped) != cudaSuccess ||
       cudaHostGetDevicePointer((void **)&M->d_pin, M->h_pin, 0) != cudaSuccess) {
     g_err = "cudaHostAlloc failed";
     spm_cuda_model_free(M);
@@ -948,7 +1061,7 @@ int spm_cuda_model_check_extra_options(const spm_cuda_model *M, uint32_t opts) {
 int spm_cuda_last_stats(const spm_cuda_model *M, double *stats, int n) {
   if (!M || !stats) return kInvalidArgument;
   std::lock_guard<std::mutex> lk(M->mu);
-  for (int i = 0; i < n && i < 8; ++i) stats[i] = M->stats[i];
+  for (int i = 0; i < n && i < 16; ++i) stats[i] = M->stats[i];
   return kOk;
 }
 
@@ -1031,7 +1144,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     launches += 1;
     k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
     CUDA_TRY(cudaStreamSynchronize(st));
-    const int64_t *hv = M->h_pin + 8;
+    const int64_t *hv = M->h_pin + kPubScal;
     tr("validated", n);
     if (hv[3]) { g_err = "text_offsets must be non-decreasing"; return kInvalidArgument; }
     max_len = hv[6]; max_raw = hv[7]; max_long = hv[1];
@@ -1047,12 +1160,37 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
 
   const ExtraPlan plan = make_extra_plan(extra_options, M->bos_id, M->eos_id);
   const int exp_ = M->hm.expansion;
+  // word memo (spm_memo.cuh): one table per call, zeroed here -- nothing survives the call.
+  // SPM_CUDA_NO_MEMO=1 switches the tier off (measurement of the Viterbi / merge kernels alone).
+  static const bool no_memo = getenv("SPM_CUDA_NO_MEMO") != nullptr;
+  const bool memo = M->fast && M->hm.memo_ok && !no_memo && n > 0;
+  MemoTable memo_tb;
+  memset(&memo_tb, 0, sizeof(memo_tb));
+  if (memo) {
+    const uint64_t want = 2 * (uint64_t)n + (uint64_t)(text_hi - text_lo) / 16;
+    uint64_t entries = 1 << 12;
+    while (entries < want && entries < (1ull << 23)) entries <<= 1;
+    if ((rc = M->w_memo.ensure(entries * sizeof(MemoEntry)))) return rc;
+    if ((rc = M->w_newlist.ensure(entries / 2 * 4))) return rc;
+    CUDA_TRY(cudaMemsetAsync(M->w_memo.p, 0, entries * sizeof(MemoEntry), st));
+    memo_tb.e = (MemoEntry *)M->w_memo.p;
+    memo_tb.mask = (uint32_t)(entries - 1);
+    memo_tb.new_list = (uint32_t *)M->w_newlist.p;
+    memo_tb.max_new = (uint32_t)(entries / 2);
+    if ((rc = M->w_movf.ensure((size_t)memo_tb.max_new * kMemoOverflowIds * 4))) return rc;
+    memo_tb.overflow = (int32_t *)M->w_movf.p;
+    if (M->fast_kind == 2) {
+      if ((rc = M->w_wtext.ensure((size_t)memo_tb.max_new * 64))) return rc;
+      if ((rc = M->w_wlen.ensure((size_t)memo_tb.max_new * 4))) return rc;
+    }
+    launches += 1;
+  }
   // chunk = as many sentences as fit the byte budget (fast tier: the raw text; general
   // tier: the worst-case normalized text) -- one chunk for all but huge batches
   const int64_t kRawBudget = M->fast ? (2048ll << 20) : (256ll << 20) / exp_;
   const int64_t kMaxChunk = M->fast ? (1 << 24) : (1 << 20);
   uint32_t stor = 0;
-  int64_t n_general = 0;
+  int64_t n_general = 0, n_viterbi = 0, n_memo_words = 0;
   struct Chunk { int64_t c0, c1, o0, o1; };
   std::vector<Chunk> chunks;
   {
@@ -1107,7 +1245,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   auto flush_outputs = [&](size_t upto) -> int {   // chunks [flushed, upto) have their totals in h_pin
     for (; flushed < upto; ++flushed) {
       const Chunk &ch = chunks[flushed];
-      const int64_t tot = M->h_pin[16 + flushed];
+      const int64_t tot = M->h_pin[kPubTot + flushed];
       CUDA_TRY(cudaStreamWaitEvent(M->s_out, M->ev_done[flushed], 0));
       CUDA_TRY(cudaMemcpyAsync(id_offsets + ch.c0, d_idoff + ch.c0, (ch.c1 - ch.c0 + 1) * 8, cudaMemcpyDeviceToHost,
                                M->s_out));
@@ -1147,49 +1285,95 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       if (has_long) back_bytes = std::max(back_bytes, (size_t)back_rows_long * M->sm_count * long_warps * 32 * 4);
       if (M->fast_kind == 1 && (rc = M->w_back.ensure(back_bytes))) return rc;
       if (has_long && (rc = M->w_longlist.ensure((size_t)std::min<int64_t>(cn, raw / kFastMaxRaw + 1) * 4))) return rc;
+      const int64_t max_n_long = has_long ? std::min<int64_t>(cn, raw / kFastMaxRaw + 1) : 0;
       const unsigned gsort = (unsigned)((cn + kSortTile - 1) / kSortTile);
+      const unsigned gsent = (unsigned)((cn + 255) / 256), glong = (unsigned)((max_n_long + 255) / 256);
+      static_assert(kNormThreads == 256 && kMemoThreads == 256, "grids below assume 256 threads");
       k_hist<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
                                    (int32_t *)M->w_genlist.p, (int32_t *)M->w_longlist.p, d_counters);
       k_binscan<<<1, 1024, 0, st>>>(d_hist, d_bincur, d_counters);
       k_scatter<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, d_bincur, (int32_t *)M->w_perm.p);
-      k_normalize_fast<<<(unsigned)((cn + kNormThreads - 1) / kNormThreads), kNormThreads, 0, st>>>(
+      if ((rc = kev_record(M, st, 0, T_NORMALIZE))) return rc;
+      k_normalize_fast<<<gsent, kNormThreads, 0, st>>>(
           M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p, C_NFAST,
           (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
-      launches += 1;
-      if (has_long) {
-        // the grid covers the most long lines the chunk's bytes can hold
-        const int64_t max_n_long = std::min<int64_t>(cn, raw / kFastMaxRaw + 1);
-        k_normalize_fast<<<(unsigned)((max_n_long + kNormThreads - 1) / kNormThreads), kNormThreads, 0, st>>>(
+      if (has_long)   // the grid covers the most long lines the chunk's bytes can hold
+        k_normalize_fast<<<glong, kNormThreads, 0, st>>>(
             M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_longlist.p, C_NLONG,
             (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
-        launches += 1;
-      }
-      if ((rc = kev_record(M, st, 0))) return rc;
-      if (M->fast_kind == 1) {
-        k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
-            M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-            (const int32_t *)M->w_perm.p, C_NFAST, C_WORK, kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows,
-            (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p,
-            d_counters);
-        if (has_long)
-          k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
-              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-              (const int32_t *)M->w_longlist.p, C_NLONG, C_WORK_LONG, long_warps, (uint32_t *)M->w_back.p,
-              back_rows_long, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
-              (int32_t *)M->w_genlist.p, d_counters);
-      } else {
-        k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
-            M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-            (const int32_t *)M->w_perm.p, C_NFAST, C_WORK, kBpeThreads / 32, (int32_t *)M->w_stage.p,
-            (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
-        if (has_long)
-          k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
-              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-              (const int32_t *)M->w_longlist.p, C_NLONG, C_WORK_LONG, long_warps, (int32_t *)M->w_stage.p,
-              (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
-      }
       if ((rc = kev_record(M, st, 1))) return rc;
       launches += has_long ? 5 : 4;
+      // lists of the Viterbi / merge kernels: everything, or what the word memo leaves over
+      const int32_t *list_a = (const int32_t *)M->w_perm.p, *list_b = (const int32_t *)M->w_longlist.p;
+      int cnt_a = C_NFAST, work_a = C_WORK, cnt_b = C_NLONG, work_b = C_WORK_LONG;
+      if (memo) {
+        if ((rc = M->w_wslots.ensure((size_t)(raw + kFastExtraChars * cn + 64) * 4))) return rc;
+        if ((rc = M->w_nwords.ensure(cn * 4))) return rc;
+        if ((rc = M->w_vit.ensure(cn * 4))) return rc;
+        if (has_long && (rc = M->w_vitl.ensure(max_n_long * 4))) return rc;
+        MemoTable tb = memo_tb;
+        tb.n_new = d_counters + C_NNEW;
+        const unsigned gnew = (tb.max_new + 255) / 256;
+        if ((rc = kev_record(M, st, 0, T_MEMO_COLLECT))) return rc;
+        k_memo_collect<<<gsent, kMemoThreads, 0, st>>>(
+            tb, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, (const int32_t *)M->w_perm.p,
+            C_NFAST, (uint32_t *)M->w_wslots.p, (int32_t *)M->w_nwords.p, d_counters);
+        if (has_long)
+          k_memo_collect<<<glong, kMemoThreads, 0, st>>>(
+              tb, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+              (const int32_t *)M->w_longlist.p, C_NLONG, (uint32_t *)M->w_wslots.p, (int32_t *)M->w_nwords.p,
+              d_counters);
+        if ((rc = kev_record(M, st, 1))) return rc;
+        if ((rc = kev_record(M, st, 0, T_MEMO_WORDS))) return rc;
+        if (M->fast_kind == 1) {
+          k_memo_words_unigram<<<gnew, kMemoThreads, 0, st>>>(M->fp, M->hm.neg_only ? 1 : 0, tb);
+          launches += 1;
+        } else {
+          k_memo_words_text<<<gnew, kMemoThreads, 0, st>>>(tb, (uint8_t *)M->w_wtext.p, (int32_t *)M->w_wlen.p);
+          k_memo_words_bpe<<<(tb.max_new + kMemoBpeThreads - 1) / kMemoBpeThreads, kMemoBpeThreads, 0, st>>>(
+              M->fp, tb, (const uint8_t *)M->w_wtext.p, (const int32_t *)M->w_wlen.p);
+          launches += 2;
+        }
+        if ((rc = kev_record(M, st, 1))) return rc;
+        if ((rc = kev_record(M, st, 0, T_MEMO_EMIT))) return rc;
+        k_memo_emit<<<gsent, kMemoThreads, 0, st>>>(
+            tb.e, tb.overflow, M->fast_kind == 1, d_off, c0, (const int32_t *)M->w_perm.p, C_NFAST, C_NVIT,
+            (const uint32_t *)M->w_wslots.p, (const int32_t *)M->w_nwords.p, (int32_t *)M->w_stage.p,
+            (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p, d_counters);
+        if (has_long)
+          k_memo_emit<<<glong, kMemoThreads, 0, st>>>(
+              tb.e, tb.overflow, M->fast_kind == 1, d_off, c0, (const int32_t *)M->w_longlist.p, C_NLONG, C_NVITL,
+              (const uint32_t *)M->w_wslots.p, (const int32_t *)M->w_nwords.p, (int32_t *)M->w_stage.p,
+              (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vitl.p, d_counters);
+        if ((rc = kev_record(M, st, 1))) return rc;
+        launches += has_long ? 4 : 2;
+        list_a = (const int32_t *)M->w_vit.p; cnt_a = C_NVIT; work_a = C_WORK_VIT;
+        list_b = (const int32_t *)M->w_vitl.p; cnt_b = C_NVITL; work_b = C_WORK_VITL;
+      }
+      if ((rc = kev_record(M, st, 0, T_ENCODE))) return rc;
+      if (M->fast_kind == 1) {
+        k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
+            M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
+            kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
+            (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+        if (has_long)
+          k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
+              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
+              long_warps, (uint32_t *)M->w_back.p, back_rows_long, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
+              (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+      } else {
+        k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
+            M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
+            kBpeThreads / 32, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
+            (int32_t *)M->w_genlist.p, d_counters);
+        if (has_long)
+          k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
+              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
+              long_warps, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
+              (int32_t *)M->w_genlist.p, d_counters);
+      }
+      if ((rc = kev_record(M, st, 1))) return rc;
+      launches += has_long ? 2 : 1;
       CUDA_TRY(cudaGetLastError());
       k_publish<<<1, 32, 0, st>>>(d_counters, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
       CUDA_TRY(cudaStreamSynchronize(st));
@@ -1198,6 +1382,8 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       tr("fast kernel done, chunk", (long)kc);
       if (host && (rc = flush_outputs(kc))) return rc;   // earlier chunks are complete by now
       n_general += hc[C_NGEN];
+      n_viterbi += memo ? hc[C_NVIT] + hc[C_NVITL] : hc[C_NFAST] + hc[C_NLONG];
+      n_memo_words += hc[C_NNEW];
       if ((rc = run_general(M, st, d_text, d_off, c0, (const int32_t *)M->w_genlist.p, hc[C_NGEN], false,
                             &launches)))
         return rc;
@@ -1224,7 +1410,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   CUDA_TRY(cudaEventRecord(M->ev1, st));
   k_publish<<<1, 32, 0, st>>>(nullptr, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
   CUDA_TRY(cudaStreamSynchronize(st));
-  const int64_t hsc[3] = {M->h_pin[8], M->h_pin[9], M->h_pin[10]};
+  const int64_t hsc[3] = {M->h_pin[kPubScal], M->h_pin[kPubScal + 1], M->h_pin[kPubScal + 2]};
   const int64_t total = hsc[0];
   stor = (uint32_t)hsc[2];
   if (n == 0) {
@@ -1245,14 +1431,22 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   M->stats[0] = launches;
   M->stats[1] = (double)n_general;
   M->stats[2] = ms;
-  double kms = 0;
+  double tms[T_COUNT] = {0, 0, 0, 0, 0, 0};
+  int tn[T_COUNT] = {0, 0, 0, 0, 0, 0};
   for (size_t k = 0; k < M->nk; ++k) {
     float t = 0;
     cudaEventElapsedTime(&t, M->kev[2 * k], M->kev[2 * k + 1]);
-    kms += t;
+    tms[M->kev_tag[k]] += t;
+    ++tn[M->kev_tag[k]];
   }
-  M->stats[4] = kms;
-  M->stats[5] = (double)M->nk;
+  int dom = 0;
+  for (int k = 1; k < T_COUNT; ++k) if (tms[k] > tms[dom]) dom = k;
+  M->stats[4] = tms[dom];            // the dominant stage of this call
+  M->stats[5] = (double)tn[dom];
+  M->stats[8] = (double)dom;
+  for (int k = 0; k < T_COUNT; ++k) M->stats[9 + k] = tms[k];
+  M->stats[15] = (double)n_viterbi;
+  (void)n_memo_words;
   M->stats[6] = (double)n;
   M->stats[7] = (double)total;
   size_t ws = 0;

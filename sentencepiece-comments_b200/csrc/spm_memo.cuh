@@ -1,0 +1,346 @@
+// spm_memo.cuh -- the word-memo tier: every distinct whitespace-delimited word of
+// a batch is segmented once, every occurrence copies the ids.
+//
+// Why this is exact.  The tier is only used for models in which no piece carries
+// U+2581 at a non-initial position.  Every piece that covers a U+2581 character of
+// the normalized text then starts there, so every lattice path (unigram,
+// src/unigram_model.cc:535-604) and every merge (BPE, src/bpe_model.cc:37-199) is
+// confined to one "word" = [U+2581, next U+2581).
+//   * BPE: the merge order inside a word depends on pair scores only, so the pieces
+//     of a word are a pure function of its bytes.
+//   * Unigram: in exact arithmetic the best path of the sentence is the concatenation
+//     of the best paths of its words.  In the reference's float arithmetic the
+//     backtrace score B accumulated before the word shifts every candidate of the
+//     word by the same amount but rounds each one differently, so a decision inside
+//     the word is context-free only while its margin exceeds the rounding noise:
+//     with k = characters of the word + 1 additions per candidate,
+//         margin > 2 k 2^-24 (|B| + mag_best + mag_other)
+//     (each float addition errs by at most 2^-24 of its result, both in the
+//     sentence and in the stand-alone evaluation).  memo_unigram_word() therefore
+//     returns, next to the ids, bmax = the largest |B| for which EVERY decision of
+//     the word (on or off the best path) keeps that margin with a 2x safety factor;
+//     memo_emit() tracks an upper bound of |B| along the sentence and sends the
+//     sentence to the Viterbi tier (fast_unigram) the moment a word's bmax is
+//     exceeded.  Exactly tied candidates have margin 0 and are never memoised.
+//
+// The table is built per call (no state survives spm_cuda_encode_batch), keyed by
+// the EXACT bytes of the word (<= kMemoMaxBytes after the U+2581 prefix; longer
+// words send their sentence to the Viterbi tier), claimed with one 128-bit CAS.
+// Everything is `__host__ __device__` so tests/host_core.cc runs the same code.
+#pragma once
+#include "spm_fast.cuh"
+
+namespace spmb {
+
+constexpr int kMemoKeyBytes = 14;      // word bytes held by one key
+constexpr int kMemoTailBytes = 10;     // bytes held by the key of a tail entry (next to the head's slot)
+constexpr int kMemoMaxBytes = kMemoKeyBytes + kMemoTailBytes;   // word bytes after the U+2581 prefix
+constexpr int kMemoInlineIds = 8;      // ids kept inside the entry
+constexpr int kMemoOverflowIds = 16;   // further ids of a long word (overflow row of the entry's list index)
+constexpr int kMemoMaxIds = kMemoInlineIds + kMemoOverflowIds;
+constexpr int kMemoProbes = 24;        // linear probes before giving up
+constexpr uint32_t kMemoReady = 0x100u;   // meta: entry encoded
+constexpr uint32_t kMemoBad = 0x200u;     // meta: the word cannot be memoised
+constexpr uint32_t kMemoFirstUnk = 0x400u;  // meta: first id is the unknown id
+constexpr uint32_t kMemoLastUnk = 0x800u;   // meta: last id is the unknown id
+
+// Key of a word of <= 14 bytes: meta | bytes 0..6  /  bytes 7..13 | meta << 56, with
+// meta = length << 1 | has-prefix (1..29).  A longer word is keyed in two steps: a HEAD
+// entry (meta 0x40 | prefix) for its first 14 bytes, then the word's own TAIL entry
+// (meta 0x80 | rest length) whose key holds the head's slot (3 bytes) and the <= 10 bytes
+// that are left.  Both halves of every key carry the non-zero meta byte; (0, 0) = empty.
+struct alignas(64) MemoEntry {
+  uint64_t k0, k1;
+  uint32_t meta;       // id count | kMemo* flags
+  float bmax;          // unigram: largest |backtrace score at the word start| that keeps the word context-free
+  float sabs;          // unigram: bound of |best-path score of the word|
+  uint32_t ovf;        // overflow row (index into MemoTable::overflow / kMemoOverflowIds) when count > kMemoInlineIds
+  int32_t ids[kMemoInlineIds];
+};
+
+struct MemoTable {
+  MemoEntry *e;
+  uint32_t mask;        // entries - 1 (power of two)
+  uint32_t *new_list;   // slots claimed in this pass
+  uint32_t *n_new;      // their count (may exceed max_new: the excess is never encoded)
+  uint32_t max_new;
+  int32_t *overflow;    // max_new rows of kMemoOverflowIds ids
+};
+
+SPM_HD uint32_t memo_hash(uint64_t k0, uint64_t k1) {
+  uint64_t h = k0 * 0x9E3779B97F4A7C15ull ^ (k1 + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full;
+  h ^= h >> 29;
+  h *= 0xBF58476D1CE4E5B9ull;
+  return (uint32_t)(h >> 32);
+}
+
+// compare-and-swap of the 16-byte key against "empty"; returns the previous key
+SPM_HD void memo_claim(MemoEntry *e, uint64_t k0, uint64_t k1, uint64_t *o0, uint64_t *o1) {
+#if defined(__CUDA_ARCH__)
+  asm volatile(
+      "{\n\t.reg .b128 c, s, d;\n\t"
+      "mov.b128 c, {%3, %4};\n\tmov.b128 s, {%5, %6};\n\t"
+      "atom.relaxed.gpu.global.cas.b128 d, [%2], c, s;\n\t"
+      "mov.b128 {%0, %1}, d;\n\t}"
+      : "=l"(*o0), "=l"(*o1)
+      : "l"(e), "l"(0ull), "l"(0ull), "l"(k0), "l"(k1)
+      : "memory");
+#else
+  *o0 = e->k0; *o1 = e->k1;
+  if (*o0 == 0 && *o1 == 0) { e->k0 = k0; e->k1 = k1; }
+#endif
+}
+
+// Slot of the word with key (k0, k1), inserting it when absent; 0xFFFFFFFF when the
+// probe sequence is exhausted.  A (cached, possibly stale or torn) plain load decides the
+// common case: both key halves carry the non-zero meta byte, so a half-written entry can
+// never compare equal, and entries are immutable once written; "looks empty" is settled
+// by the CAS itself.
+SPM_HD uint32_t memo_find_or_insert(const MemoTable &tb, uint64_t k0, uint64_t k1) {
+  uint32_t slot = memo_hash(k0, k1) & tb.mask;
+  for (int probe = 0; probe < kMemoProbes; ++probe, slot = (slot + 1) & tb.mask) {
+    MemoEntry *e = tb.e + slot;
+#if defined(__CUDA_ARCH__)
+    uint64_t e0, e1;
+    asm volatile("ld.global.v2.u64 {%0, %1}, [%2];" : "=l"(e0), "=l"(e1) : "l"(e) : "memory");
+#else
+    uint64_t e0 = e->k0, e1 = e->k1;
+#endif
+    if (e0 == k0 && e1 == k1) return slot;
+    if (e0 == 0 && e1 == 0) {
+      memo_claim(e, k0, k1, &e0, &e1);
+      if (e0 == 0 && e1 == 0) {
+#if defined(__CUDA_ARCH__)
+        const uint32_t idx = atomicAdd(tb.n_new, 1u);
+#else
+        const uint32_t idx = (*tb.n_new)++;
+#endif
+        if (idx < tb.max_new) tb.new_list[idx] = slot;
+        return slot;
+      }
+      if (e0 == k0 && e1 == k1) return slot;
+    }
+  }
+  return 0xFFFFFFFFu;
+}
+
+// Splits one normalized sentence (8-byte aligned, zero padded as for fast_unigram) into
+// words and writes the table slot of each to slots[]; returns the word count, or -1 when
+// a word cannot be keyed (longer than kMemoMaxBytes, table full).
+SPM_HDN int32_t memo_collect(const MemoTable &tb, const uint8_t *s, int32_t n, uint32_t *slots) {
+  if (n <= 0) return 0;
+  const uint64_t *sw = reinterpret_cast<const uint64_t *>(s);
+  uint64_t lo = sw[0], hi = sw[1];
+  int32_t q = 1;            // hi = sw[q]
+  int r = 0;                // window = bytes at 8 (q - 1) + r
+  int32_t p = 0, nw = 0;
+  uint64_t k0 = 0, k1 = 0;  // bytes of the current key (head: 14, tail: slot + 10)
+  int len = 0, prefix = 0;
+  bool tail = false;        // the current key is the tail of a long word
+  bool started = false;     // the current word has a prefix or a byte
+  for (;;) {
+    const uint64_t win = fast_window(lo, hi, r);
+    const bool end = p >= n;
+    const bool mark = !end && (win & 0xFFFFFFull) == 0x8196E2ull;
+    if (end || mark) {
+      if (started) {
+        const uint64_t mb = tail ? (uint64_t)(0x80 | len) : (uint64_t)((len << 1) | prefix);
+        const uint32_t slot = memo_find_or_insert(tb, k0 | mb, k1 | (mb << 56));
+        if (slot == 0xFFFFFFFFu) return -1;
+        slots[nw++] = slot;
+      }
+      if (end) break;
+      k0 = 0; k1 = 0; len = 0; prefix = 1; started = true; tail = false;
+      p += 3; r += 3;
+    } else {
+      const uint64_t b = win & 0xFFull;
+      if (!tail && len == kMemoKeyBytes) {       // the word goes on: key its head, start the tail
+        const uint64_t mb = (uint64_t)(0x40 | prefix);
+        const uint32_t hs = memo_find_or_insert(tb, k0 | mb, k1 | (mb << 56));
+        if (hs == 0xFFFFFFFFu) return -1;
+        k0 = (uint64_t)hs << 8; k1 = 0; len = 0; tail = true;
+      }
+      if (tail) {
+        if (len >= kMemoTailBytes) return -1;
+        if (len < 4) k0 |= b << (8 * (len + 4));
+        else k1 |= b << (8 * (len - 4));
+      } else {
+        if (len < 7) k0 |= b << (8 * (len + 1));
+        else k1 |= b << (8 * (len - 7));
+      }
+      ++len; started = true;
+      ++p; ++r;
+    }
+    if (r >= 8) { r -= 8; lo = hi; hi = sw[++q]; }
+  }
+  return nw;
+}
+
+// Bytes of the word of an entry: U+2581 prefix (when keyed with one) + content, zero
+// padded to `cap` (>= 40) bytes.  Returns the byte count; 0 for a head entry (not a word).
+SPM_HD int memo_word_bytes(const MemoEntry *tab, const MemoEntry *e, uint8_t *out, int cap) {
+  uint64_t k0 = e->k0, k1 = e->k1;
+  const int mb = (int)(k0 & 0xFFu);
+  int nb = 0;
+  if (mb & 0x40) {
+    nb = 0;
+  } else {
+    uint64_t t0 = 0, t1 = 0;
+    int tl = 0;
+    if (mb & 0x80) {   // tail: fetch the head (immutable once claimed)
+      t0 = k0; t1 = k1; tl = mb & 0x3F;
+      const MemoEntry *h = tab + ((k0 >> 8) & 0xFFFFFFu);
+      k0 = h->k0; k1 = h->k1;
+    }
+    const int hb = (int)(k0 & 0xFFu);
+    const int len = (hb & 0x40) ? kMemoKeyBytes : (hb >> 1), prefix = hb & 1;
+    if (prefix) { out[0] = 0xE2; out[1] = 0x96; out[2] = 0x81; nb = 3; }
+    for (int j = 0; j < len; ++j)
+      out[nb++] = (uint8_t)(j < 7 ? (k0 >> (8 * (j + 1))) : (k1 >> (8 * (j - 7))));
+    for (int j = 0; j < tl; ++j)
+      out[nb++] = (uint8_t)(j < 4 ? (t0 >> (8 * (j + 4))) : (t1 >> (8 * (j - 4))));
+  }
+  for (int j = nb; j < cap; ++j) out[j] = 0;
+  return nb;
+}
+
+// Stores ids (forward order), flags and bounds of an encoded word; `row` = its list index.
+SPM_HD void memo_store(const MemoTable &tb, MemoEntry *e, uint32_t row, const int32_t *ids, int32_t cnt, bool bad,
+                       int32_t unk_id, float bmax, float sabs) {
+  uint32_t meta = kMemoReady;
+  if (bad || cnt <= 0 || cnt > kMemoMaxIds) { meta |= kMemoBad; cnt = 0; }
+  for (int j = 0; j < cnt && j < kMemoInlineIds; ++j) e->ids[j] = ids[j];
+  for (int j = kMemoInlineIds; j < cnt; ++j) tb.overflow[(size_t)row * kMemoOverflowIds + (j - kMemoInlineIds)] = ids[j];
+  if (cnt > 0 && ids[0] == unk_id) meta |= kMemoFirstUnk;
+  if (cnt > 0 && ids[cnt - 1] == unk_id) meta |= kMemoLastUnk;
+  e->ovf = row;
+  e->bmax = bmax;
+  e->sabs = sabs;
+  e->meta = meta | (uint32_t)cnt;
+}
+// a word whose segmentation does not depend on its context (BPE)
+SPM_HD void memo_store_ids(const MemoTable &tb, MemoEntry *e, uint32_t row, const int32_t *ids, int32_t cnt, bool bad,
+                           int32_t unk_id) {
+  memo_store(tb, e, row, ids, cnt, bad, unk_id, 3.0e38f, 0.0f);
+}
+
+// Unigram: Viterbi of one stand-alone word with the margin bookkeeping described above.
+// Same lattice as fast_unigram() (nodes of the fast view + the one-character UNK node,
+// candidates of an end position in begin order, strict '>').
+SPM_HDN void memo_unigram_word(const FastView &fv, bool neg_only, const MemoTable &tb, uint32_t row) {
+  MemoEntry *e = tb.e + tb.new_list[row];
+  const MemoEntry *tab = tb.e;
+  constexpr int kMaxChars = kMemoMaxBytes + 1;
+  const float NEG = -3.0e38f;
+  uint8_t txt[40];
+  const int nb = memo_word_bytes(tab, e, txt, 40);
+  if (nb == 0) { e->meta = kMemoReady | kMemoBad; return; }   // a head entry
+  float b1[kMaxChars + 1], b2[kMaxChars + 1];
+  uint32_t rec[kMaxChars + 1];
+  int cstart[kMaxChars + 1];
+  int m = 0;
+  for (int p = 0; p < nb; p += one_char_len(txt[p])) cstart[m++] = p;
+  cstart[m] = nb;
+  for (int k = 0; k <= m; ++k) { b1[k] = NEG; b2[k] = NEG; rec[k] = 0; }
+  b1[0] = 0.0f;
+  const uint32_t root = fv.units[0];
+  for (int ci = 0; ci < m; ++ci) {
+    const float btp = b1[ci];
+    uint32_t u = root;
+    int k = 0;
+    bool single = false;
+    for (int j = cstart[ci]; j < nb; ++j) {
+      const uint32_t c = txt[j];
+      if (!(u & 0x200u) || c == 0) break;
+      const uint32_t child = (u >> 10) ^ c;
+      const uint32_t v = fv.units[child];
+      if ((v & 0xFFu) != c || (v & 0x300u) == 0) break;
+      u = v;
+      if ((c & 0xC0u) != 0x80u) ++k;
+      if (v & 0x100u) {
+        const float val = btp + fv.score[child];
+        const int t = ci + k;
+        if (val > b1[t]) { b2[t] = b1[t]; b1[t] = val; rec[t] = child | ((uint32_t)k << 24); }
+        else if (val > b2[t]) b2[t] = val;
+        if (k == 1) single = true;
+      }
+    }
+    if (!single) {
+      const float val = btp + fv.unk_score;
+      const int t = ci + 1;
+      if (val > b1[t]) { b2[t] = b1[t]; b1[t] = val; rec[t] = kFastUnk | (1u << 24); }
+      else if (val > b2[t]) b2[t] = val;
+    }
+  }
+  // margins -> bmax
+  const float K = (float)(m + 1) * 2.384185791015625e-07f;   // k 2^-22 = 2 x (2 k 2^-24)
+  const float magw = (float)m * fv.smax;
+  float bmax = 3.0e38f;
+  for (int t = 1; t <= m; ++t) {
+    if (b2[t] <= NEG) continue;                 // a single candidate: nothing to decide
+    const float gap = b1[t] - b2[t];
+    // all scores <= 0: partial sums are monotone, |other| = |best| + gap
+    const float allow = neg_only ? (gap * (1.0f - K) / K - 2.0f * fabsf(b1[t])) : (gap / K - 2.0f * magw);
+    if (allow < bmax) bmax = allow;
+  }
+  // backtrace (reverse), unknown runs collapse (sentencepiece_processor.cc:525-529)
+  int32_t rev[kMaxChars];
+  int cnt = 0;
+  bool prev_unk = false;
+  for (int ci = m; ci > 0;) {
+    const uint32_t node = rec[ci] & 0x00FFFFFFu;
+    const bool is_unk = node == kFastUnk;
+    if (!(is_unk && prev_unk)) rev[cnt++] = is_unk ? fv.unk_id : (int32_t)fv.leaf_id[node];
+    prev_unk = is_unk;
+    ci -= (int)(rec[ci] >> 24);
+  }
+  int32_t fwd[kMaxChars];
+  for (int j = 0; j < cnt; ++j) fwd[j] = rev[cnt - 1 - j];
+  memo_store(tb, e, row, fwd, cnt, !(bmax > 0.0f), fv.unk_id, bmax,
+             (neg_only ? fabsf(b1[m]) : magw) * 1.001f + 1.0e-3f);
+}
+
+// Ids of one sentence from the slots of its words (forward order).  Returns the id count,
+// or -1 when a word is not memoised / not context-free at this point of the sentence.
+SPM_HDN int32_t memo_emit(const MemoEntry *tab, const int32_t *overflow, const uint32_t *slots, int32_t nw,
+                          bool unigram, int32_t *out) {
+  int32_t cnt = 0;
+  float bub = 0.0f;          // upper bound of |backtrace score| at the start of the next word
+  bool prev_unk = false;
+  for (int32_t w = 0; w < nw; ++w) {
+    const MemoEntry *e = tab + slots[w];
+#if defined(__CUDA_ARCH__)
+    const uint4 h = __ldg(reinterpret_cast<const uint4 *>(e) + 1);   // meta, bmax, sabs, ovf
+    const uint32_t meta = h.x, ovf = h.w;
+    const float bmax = __uint_as_float(h.y), sabs = __uint_as_float(h.z);
+#else
+    const uint32_t meta = e->meta, ovf = e->ovf;
+    const float bmax = e->bmax, sabs = e->sabs;
+#endif
+    if ((meta & (kMemoReady | kMemoBad)) != kMemoReady) return -1;
+    if (unigram) {
+      if (!(bub < bmax)) return -1;
+      bub += sabs;
+    }
+    const int k = (int)(meta & 0xFFu);
+    int j = 0;
+    if (prev_unk && (meta & kMemoFirstUnk)) j = 1;   // an unknown run continues across the boundary
+#if defined(__CUDA_ARCH__)
+    const int4 a = __ldg(reinterpret_cast<const int4 *>(e) + 2);
+    const int32_t v4[4] = {a.x, a.y, a.z, a.w};
+    for (; j < k && j < 4; ++j) out[cnt++] = v4[j];
+    if (k > 4) {
+      const int4 b = __ldg(reinterpret_cast<const int4 *>(e) + 3);
+      const int32_t w4[4] = {b.x, b.y, b.z, b.w};
+      for (; j < k && j < 8; ++j) out[cnt++] = w4[j - 4];
+    }
+#else
+    for (; j < k && j < kMemoInlineIds; ++j) out[cnt++] = e->ids[j];
+#endif
+    for (; j < k; ++j) out[cnt++] = overflow[(size_t)ovf * kMemoOverflowIds + (j - kMemoInlineIds)];
+    prev_unk = (meta & kMemoLastUnk) != 0;
+  }
+  return cnt;
+}
+
+}  // namespace spmb

@@ -322,6 +322,18 @@ void refresh_leaf_types(HostModel *m) {
     if (pc.find("\xE2\x96\x81", 1) != std::string::npos) ok = false;
   }
   m->bpe_fast_ok = ok;
+  // word memo (spm_memo.cuh): every node that covers a U+2581 must start there
+  bool inner = false;
+  for (size_t i = 0; i < m->piece.size() && !inner; ++i) {
+    const uint8_t t = m->type[i];
+    if ((t == T_NORMAL || t == T_USER_DEFINED) && m->piece[i].find("\xE2\x96\x81", 1) != std::string::npos)
+      inner = true;
+  }
+  m->memo_ok = (m->model_type == M_UNIGRAM ? m->fast_ok : m->bpe_fast_ok) && !inner;
+  bool neg = m->min_score - 10.0f <= 0.0f;
+  for (size_t i = 0; i < n && neg; ++i)
+    if ((m->funits[i] & 0x100u) && !(m->fscore[i] <= 0.0f)) neg = false;
+  m->neg_only = neg;
 }
 
 int build_host_model(const void *data, size_t len, HostModel *m) {

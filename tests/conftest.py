@@ -68,7 +68,8 @@ def hostcore():
     """tests/host_core.cc: the kernels' __host__ __device__ core compiled for the CPU (test-only)."""
     csrc = os.path.join(ROOT, "sentencepiece-comments_b200", "csrc")
     srcs = [os.path.join(ROOT, "tests", "host_core.cc"), os.path.join(csrc, "spm_model.cc")]
-    deps = srcs + [os.path.join(csrc, "spm_core.cuh"), os.path.join(csrc, "spm_fast.cuh"), os.path.join(csrc, "spm_model.h")]
+    deps = srcs + [os.path.join(csrc, "spm_core.cuh"), os.path.join(csrc, "spm_fast.cuh"), os.path.join(csrc, "spm_memo.cuh"),
+                   os.path.join(csrc, "spm_model.h")]
     out = os.path.join(ROOT, "tests", "_build", "libspm_hostcore.so")
     _build_lib(deps, out, ["-I", csrc] + srcs)
     L = ctypes.CDLL(out)

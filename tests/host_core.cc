@@ -5,12 +5,14 @@
 // oracle in a container without a GPU.  The product library has no host
 // encode path.
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
 
 #include "spm_core.cuh"
 #include "spm_fast.cuh"
+#include "spm_memo.cuh"
 #include "spm_model.h"
 
 using namespace spmb;
@@ -47,8 +49,12 @@ void *hc_load(const void *data, size_t len, int *code) {
 }
 void hc_free(void *p) { delete (Handle *)p; }
 int hc_expansion(void *p) { return ((Handle *)p)->hm.expansion; }
-// bit 0: unigram fast tier usable, bit 1: BPE fast tier usable
-int hc_fast_flags(void *p) { return (((Handle *)p)->hm.fast_ok ? 1 : 0) | (((Handle *)p)->hm.bpe_fast_ok ? 2 : 0); }
+// bit 0: unigram fast tier usable, bit 1: BPE fast tier usable, bit 2: word memo usable,
+// bit 3: all node scores <= 0
+int hc_fast_flags(void *p) {
+  const HostModel &m = ((Handle *)p)->hm;
+  return (m.fast_ok ? 1 : 0) | (m.bpe_fast_ok ? 2 : 0) | (m.memo_ok ? 4 : 0) | (m.neg_only ? 8 : 0);
+}
 int hc_trie_units(void *p) { return (int)((Handle *)p)->hm.pieces.units.size(); }
 void hc_set_piece_types(void *p, const uint8_t *t, int n) {
   Handle *h = (Handle *)p;
@@ -82,12 +88,40 @@ int64_t hc_normalize_fast(void *p, const uint8_t *in, int64_t n, uint8_t *out, i
   return nl;
 }
 
-// capc: candidate capacity of the unigram tier to emulate (1, 4 or 16).
-// status[n] receives the per-sentence status bits.
-int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n, uint32_t opts, int capc,
+// capc: candidate capacity of the unigram tier to emulate (1, 4 or 16); 0: the fast tiers
+// with the library's routing; -1: the word memo in front of them (sentences it served carry
+// status bit 20).  status[n] receives the per-sentence status bits.
+int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n, uint32_t opts, int capc_arg,
                     int32_t *ids, int64_t cap, int64_t *id_off, uint32_t *status) {
   Handle *h = (Handle *)p;
   const ModelView &mv = h->mv;
+  const bool use_memo = capc_arg == -1 && h->hm.memo_ok;
+  const int capc = capc_arg == -1 ? 0 : capc_arg;
+  // word memo state of this call (small table: probe-exhaustion paths get exercised too)
+  std::vector<MemoEntry> mtab;
+  std::vector<uint32_t> mnew;
+  std::vector<int32_t> movf;
+  uint32_t m_n_new = 0, m_done = 0;
+  MemoTable tb;
+  memset(&tb, 0, sizeof(tb));
+  FastView mfv;
+  memset(&mfv, 0, sizeof(mfv));
+  if (use_memo) {
+    mtab.resize(getenv("HC_MEMO_SMALL") ? (1 << 10) : (1 << 19));
+    memset((void *)mtab.data(), 0, mtab.size() * sizeof(MemoEntry));
+    mnew.resize(mtab.size() / 2);
+    tb.e = mtab.data(); tb.mask = (uint32_t)mtab.size() - 1; tb.new_list = mnew.data(); tb.n_new = &m_n_new;
+    tb.max_new = (uint32_t)mnew.size();
+    movf.resize(mnew.size() * kMemoOverflowIds);
+    tb.overflow = movf.data();
+    mfv.units = mfv.units_hot = h->hm.funits.data();
+    mfv.score = mfv.score_hot = h->hm.fscore.data();
+    mfv.leaf_id = h->hm.fleaf.data();
+    mfv.n_units = (uint32_t)h->hm.funits.size();
+    mfv.k_units = 0; mfv.k_scores = 0;
+    mfv.ring = h->hm.max_piece_chars + 1;
+    mfv.unk_score = mv.unk_score; mfv.smax = mv.smax; mfv.unk_id = mv.unk_id;
+  }
   const ExtraPlan plan = make_extra_plan(opts, piece_to_id(h->hm, h->hm.bos_piece), piece_to_id(h->hm, h->hm.eos_piece));
   std::vector<uint8_t> norm;
   std::vector<int32_t> words, core;
@@ -109,7 +143,44 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
       if (fl < -1) return 100 - (int)fl;
       if (fl >= 0 && (fl != nl || memcmp(fn.data(), norm.data(), nl) != 0)) return 99;
     }
-    if (mv.model_type == M_UNIGRAM && capc == 0) {
+    bool memo_served = false;
+    if (use_memo && nl > 0) {
+      std::vector<uint64_t> tbuf((nl + kNormPad + 15) / 8 + 1, 0);
+      memcpy(tbuf.data(), norm.data(), nl);
+      std::vector<uint32_t> slots(nl + 2);
+      const int32_t nw = memo_collect(tb, (const uint8_t *)tbuf.data(), nl, slots.data());
+      for (; m_done < m_n_new && m_done < tb.max_new; ++m_done) {   // the "words" kernels
+        MemoEntry *e = tb.e + tb.new_list[m_done];
+        if (mv.model_type == M_UNIGRAM) {
+          memo_unigram_word(mfv, h->hm.neg_only, tb, m_done);
+        } else {
+          uint64_t wt[8];
+          const int nb = memo_word_bytes(tb.e, e, (uint8_t *)wt, 64);
+          std::vector<uint32_t> scr(kBpeWordsPerThread, 0);
+          BpeScratch bs;
+          bs.stride = 1;
+          bs.node = scr.data(); bs.ps = (float *)(scr.data() + kBpeMaxSyms);
+          bs.text = scr.data() + 2 * kBpeMaxSyms; bs.cb = bs.text + kBpeMaxBytes / 4;
+          uint32_t txt2[2] = {0, 0};
+          int32_t wid[kBpeMaxSyms];
+          uint32_t wst = 0;
+          FastView bfv = mfv;
+          bfv.ring = 0; bfv.unk_score = 0; bfv.smax = 0;
+          const int32_t c = nb > 0 ? fast_bpe(bfv, (const uint8_t *)wt, nb, bs, txt2, wid, &wst) : 0;
+          memo_store_ids(tb, e, m_done, wid, c, wst != 0, mv.unk_id);
+        }
+      }
+      if (nw >= 0) {
+        const int32_t c = memo_emit(tb.e, tb.overflow, slots.data(), nw, mv.model_type == M_UNIGRAM, core.data());
+        if (c >= 0) { cnt = c; memo_served = true; st |= 1u << 20; }
+        else st |= 1u << 22;    // a word was not context-free here / not memoisable
+      } else {
+        st |= 1u << 21;         // a word could not be keyed
+      }
+    }
+    if (memo_served) {
+      // ids are in core[] already
+    } else if (mv.model_type == M_UNIGRAM && capc == 0) {
       // fast tier (spm_fast.cuh): padded, 8-byte aligned text; flagged sentences fall
       // back to the exact tier exactly as the library does
       if (!h->hm.fast_ok) return 12;

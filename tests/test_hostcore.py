@@ -33,7 +33,9 @@ def test_core_matches_reference_fixture(make_hostcore, corpora, ref_ids, model, 
     wo = ref_ids["%s__%s__off" % (model, corpus)][: first + 1]
     wi = ref_ids["%s__%s__ids" % (model, corpus)][: wo[-1]]
     hc = make_hostcore(model_bytes(model))
-    tiers = [4, 16, 0]   # exact tier (2 capacities); 0 = fast tier (unigram / word-wise BPE where the model allows)
+    # exact tier (2 capacities); 0 = fast tier (unigram / word-wise BPE where the model allows);
+    # -1 = word memo in front of the fast tier
+    tiers = [4, 16, 0, -1]
     for capc in tiers:
         gi, go, st = hc.encode_batch(text, off, capc=capc)
         assert np.array_equal(go, wo) and np.array_equal(gi, wi), (model, corpus, capc)
@@ -45,7 +47,7 @@ def test_core_matches_reference_fixture(make_hostcore, corpora, ref_ids, model, 
 def test_core_edge_sentences(make_hostcore, corpora, ref_ids, model):
     text, off = corpora["edge"]
     hc = make_hostcore(model_bytes(model))
-    for capc in [4, 0]:
+    for capc in [4, 0, -1]:
         gi, go, _ = hc.encode_batch(text, off, capc=capc)
         assert np.array_equal(go, ref_ids[model + "__edge__off"]), (model, capc)
         assert np.array_equal(gi, ref_ids[model + "__edge__ids"]), (model, capc)
@@ -102,7 +104,7 @@ def test_set_piece_types(make_hostcore, corpora):
     text, off = corpora["botchan"]
     text, off = text[: off[800]], off[:801]
     wi, wo = op.encode_batch(text, off)
-    for capc in (0, 4):
+    for capc in (0, 4, -1):
         gi, go, _ = hc.encode_batch(text, off, capc=capc)
         assert np.array_equal(go, wo) and np.array_equal(gi, wi), capc
 
@@ -112,7 +114,27 @@ def test_fast_tier_eligibility(make_hostcore):
     want = {"botchan_uni8k": 1, "syn_uni32k": 1, "wagahai_uni": 1, "ref_ja_8k": 1, "ref_en_1k": 1, "botchan_uni2k_ud": 1,
             "botchan_bpe4k": 2, "syn_bpe32k": 2, "botchan_bpe2k_ud": 0}   # user-defined symbols freeze BPE symbols
     for name, flags in want.items():
-        assert make_hostcore(model_bytes(name)).fast_flags() == flags, name
+        assert make_hostcore(model_bytes(name)).fast_flags() & 3 == flags, name
+
+
+def test_word_memo_serves_and_matches(make_hostcore, corpora):
+    """The word memo (spm_memo.cuh) serves most sentences of word-delimited text and agrees
+    with the reference; CJK lines without spaces fall through to the Viterbi tier."""
+    for model, corpus, lo in [("syn_uni32k", "syn_en", 0.95), ("syn_bpe32k", "syn_en", 0.95),
+                              ("botchan_uni8k", "botchan", 0.9), ("botchan_bpe4k", "botchan", 0.9),
+                              ("syn_uni32k", "syn_dirty", 0.0), ("ref_ja_8k", "wagahai", 0.0)]:
+        mb = model_bytes(model)
+        hc = make_hostcore(mb)
+        assert hc.fast_flags() & 4, model
+        text, off = corpora[corpus]
+        m = min(3000, len(off) - 1)
+        text, off = text[: off[m]], off[: m + 1]
+        chk, _ = checker(mb)
+        wi, wo = chk.encode_batch(text, off)
+        gi, go, st = hc.encode_batch(text, off, capc=-1)
+        assert np.array_equal(go, wo) and np.array_equal(gi, wi), (model, corpus)
+        served = float(((st >> 20) & 1).mean())
+        assert served >= lo, (model, corpus, served)
 
 
 def test_loader_rejects_bad_models(hostcore):
