@@ -87,12 +87,16 @@ int spm_cuda_model_pad_id(const spm_cuda_model *model);
 int spm_cuda_model_check_extra_options(const spm_cuda_model *model, uint32_t extra_options);
 
 /* Statistics of the last encode call on this model (for bench.py / profiling):
- * stats[0] kernel launches, [1] sentences sent to the exact fallback tier,
+ * stats[0] kernel launches, [1] sentences sent to the exact (general) tier,
  * [2] device-side milliseconds between first and last launch (CUDA events on
  * the caller's stream), [3] bytes of workspace currently allocated, [4] device
- * milliseconds spent in the dominant (encode) kernel, summed over its launches
- * (CUDA events around each launch, same stream), [5] number of those launches,
- * [6] sentences, [7] ids produced.  n <= 8. */
+ * milliseconds spent in the dominant stage, summed over its launches (CUDA
+ * events around each stage, same stream), [5] number of those event pairs,
+ * [6] sentences, [7] ids produced, [8] which stage is the dominant one and
+ * [9..14] milliseconds of every stage: 0 Viterbi / merge kernels (or the general
+ * tier for a model without a fast tier), 1 normalizer, 2 word-memo collect,
+ * 3 word-memo words, 4 word-memo emit, 5 compaction; [15] sentences the word memo
+ * left to the Viterbi / merge kernels.  n <= 16. */
 int spm_cuda_last_stats(const spm_cuda_model *model, double *stats, int n);
 
 const char *spm_cuda_last_error(void);

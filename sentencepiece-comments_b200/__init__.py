@@ -209,12 +209,17 @@ class SentencePieceProcessor:
                                          ptr(id_offsets), HOST, stream)
         _check(rc)
 
+    STAGES = ("encode", "normalize", "memo_collect", "memo_words", "memo_emit", "compact")
+
     def last_stats(self):
-        s = (ctypes.c_double * 8)()
-        lib().spm_cuda_last_stats(self._h, s, 8)
+        """Counters of the last encode call (include/spm_cuda.h, spm_cuda_last_stats)."""
+        s = (ctypes.c_double * 16)()
+        lib().spm_cuda_last_stats(self._h, s, 16)
         return {"launches": int(s[0]), "fallback_sentences": int(s[1]), "device_ms": s[2],
                 "workspace_bytes": int(s[3]), "encode_kernel_ms": s[4], "encode_kernel_launches": int(s[5]),
-                "sentences": int(s[6]), "ids": int(s[7])}
+                "sentences": int(s[6]), "ids": int(s[7]), "dominant_stage": self.STAGES[int(s[8])],
+                "stage_ms": {name: s[9 + k] for k, name in enumerate(self.STAGES)},
+                "viterbi_tier_sentences": int(s[15])}
 
     # ---- model introspection (sentencepiece_processor.h:397-432)
     def GetPieceSize(self):

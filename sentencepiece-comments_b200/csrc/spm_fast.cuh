@@ -49,6 +49,13 @@ struct FastView {
   int32_t unk_id;
 };
 
+SPM_HD int ffs64(uint64_t x) {   // 1-based index of the lowest set bit, 0 for x == 0
+#if defined(__CUDA_ARCH__)
+  return __ffsll((long long)x);
+#else
+  return x ? __builtin_ctzll(x) + 1 : 0;
+#endif
+}
 SPM_HD uint64_t fast_load8(const uint8_t *p) {  // p is 8-byte aligned
   return *reinterpret_cast<const uint64_t *>(p);
 }
@@ -444,6 +451,11 @@ struct FastOut {
   uint8_t *base;     // 8-byte aligned slot
   uint64_t acc;
   int32_t len;       // bytes appended so far
+  int32_t cap;       // capacity of the slot
+  SPM_HD bool room(int64_t more) const { return (int64_t)len + more <= cap; }   // can `more` bytes still follow?
+  SPM_HD bool done() const { return false; }
+  static constexpr bool kRuns = false;           // no bulk path for runs of plain bytes
+  SPM_HD int take(uint64_t, int) { return 0; }
   SPM_HD void put(uint32_t v, int k) {  // k in 1..4 bytes, little-endian in v
     const int f = len & 7;
     acc |= (uint64_t)v << (8 * f);
@@ -467,19 +479,19 @@ struct FastOut {
 // `cap` bytes + kNormPad + 8.  Returns the normalized length (the kNormPad bytes
 // after it are zeroed), or -1 when the text does not fit (caller: general tier).
 // *nchars_ub: upper bound of the character count.
-SPM_HDN int32_t fast_normalize(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t n,
-                               const uint8_t *lo, const uint8_t *hi, uint8_t *out, int32_t cap,
-                               int32_t *nchars_ub) {
-  *nchars_ub = 0;
-  if (n == 0) return 0;
+// The scan itself, writing every normalized character to `o` (FastOut: the padded text
+// slot; MemoSink of spm_memo.cuh: straight into word keys).  Returns false when the sink
+// ran out of room; *nchars_ub counts the characters written.
+template <class Sink>
+SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t n,
+                                 const uint8_t *lo, const uint8_t *hi, Sink &o, int32_t *nchars_ub,
+                                 bool *content) {   // *content: something other than leading spaces was seen
   const bool esc = m.escape_ws, rws = m.remove_extra_ws;
   const uint32_t WS = esc ? 0x8196E2u : 0x20u;  // U+2581 little-endian, or ' '
   const int WSL = esc ? 3 : 1;
   const uint8_t *q = (const uint8_t *)((uintptr_t)in & ~(uintptr_t)7);
   int r = (int)(in - q);
   uint64_t a0 = fast_load8_guard(q, lo, hi), a1 = fast_load8_guard(q + 8, lo, hi);
-  FastOut o;
-  o.base = out; o.acc = 0; o.len = 0;
   int32_t nch = 0;
   bool lead = rws;          // still stripping leading spaces (:103-112)
   bool started = false;     // dummy prefix emitted
@@ -487,7 +499,28 @@ SPM_HDN int32_t fast_normalize(const ModelView &m, const uint32_t *first2, const
   bool overflow = false;
   int64_t p = 0;
   while (p < n) {
-    const uint64_t w = fast_window(a0, a1, r);
+    uint64_t w = fast_window(a0, a1, r);
+    if (Sink::kRuns && m.ascii_plain && started) {
+      // A run of printable ASCII (0x21..0x7E) inside a word: no rule, user symbol or whitespace
+      // handling applies to a byte whose successor is ASCII as well (HostModel::ascii_plain),
+      // so the run goes to the sink in one piece.  SWAR: 0x80 marks bytes < 0x21 or > 0x7E
+      // (borrows / carries only disturb bytes above the first marked one).
+      const uint64_t np = (((w - 0x2121212121212121ull) & ~w) | ((w + 0x0101010101010101ull) | w)) & 0x8080808080808080ull;
+      int run = np ? (ffs64(np) - 1) >> 3 : 8;
+      if (run > n - p) run = (int)(n - p);
+      // the successor of the last byte must be known to be ASCII (or the end of the sentence)
+      if (run == 8 || (run < n - p && ((w >> (8 * run)) & 0x80u))) --run;
+      if (run > 0) {
+        run = o.take(w, run);
+        if (run > 0) {
+          lead = false; prev_space = false;
+          nch += run; p += run; r += run;
+          while (r >= 8) { a0 = a1; q += 8; a1 = fast_load8_guard(q + 8, lo, hi); r -= 8; }
+          if (p >= n) break;
+          w = fast_window(a0, a1, r);
+        }
+      }
+    }
     const uint32_t b0 = (uint32_t)w & 0xFF, b1 = ((uint32_t)w >> 8) & 0xFF;
     int consumed;
     // ---- what does NormalizePrefix return here?
@@ -542,7 +575,7 @@ SPM_HDN int32_t fast_normalize(const ModelView &m, const uint32_t *first2, const
         while (prev_space && k < rl && rep[k] == ' ') ++k;
         if (k < rl) {
           // keep room for the worst case of everything still to come (3 bytes per raw byte + suffix)
-          if ((int64_t)o.len + 3 * (rl - k) + 3 * (n - p - consumed) + 3 > cap) { overflow = true; break; }
+          if (!o.room(3 * (rl - k) + 3 * (n - p - consumed) + 3)) { overflow = true; break; }
           for (; k < rl; ++k) {
             const uint8_t b = rep[k];
             if (b == ' ') o.put(WS, WSL); else o.put(b, 1);
@@ -555,9 +588,27 @@ SPM_HDN int32_t fast_normalize(const ModelView &m, const uint32_t *first2, const
       p += consumed; r += consumed;
     }
   advance:
+    if (o.done()) break;   // the sink gave up on the sentence
     while (r >= 8) { a0 = a1; q += 8; a1 = fast_load8_guard(q + 8, lo, hi); r -= 8; }
   }
-  if (overflow) return -1;
+  *nchars_ub = nch;
+  *content = started;
+  return !overflow;
+}
+
+SPM_HDN int32_t fast_normalize(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t n,
+                               const uint8_t *lo, const uint8_t *hi, uint8_t *out, int32_t cap,
+                               int32_t *nchars_ub) {
+  *nchars_ub = 0;
+  if (n == 0) return 0;
+  const bool esc = m.escape_ws, rws = m.remove_extra_ws;
+  const uint32_t WS = esc ? 0x8196E2u : 0x20u;
+  const int WSL = esc ? 3 : 1;
+  FastOut o;
+  o.base = out; o.acc = 0; o.len = 0; o.cap = cap;
+  int32_t nch = 0;
+  bool started = false;
+  if (!fast_normalize_scan(m, first2, in, n, lo, hi, o, &nch, &started)) return -1;
   o.flush();
   int32_t len = o.len;
   if (rws) {  // strip trailing whitespace symbols (:191-201): re-read our own tail

@@ -177,19 +177,25 @@ __device__ __forceinline__ int64_t fast_stage_base(const int64_t *off, int64_t c
 // one global atomic per non-empty bin and block.
 constexpr int kSortThreads = 1024, kSortItems = 8, kSortTile = kSortThreads * kSortItems;
 __global__ void __launch_bounds__(kSortThreads)
-k_hist(const int64_t *off, int64_t c0, int64_t cn, int32_t *cnt, uint32_t *status, uint32_t *hist,
-       int32_t *gen_list, int32_t *long_list, uint32_t *counters) {
+k_hist(const int64_t *off, int64_t c0, int64_t cn, const int32_t *list, int list_cnt, int32_t *cnt,
+       uint32_t *status, uint32_t *hist, int32_t *gen_list, int32_t *long_list, uint32_t *counters) {
+  // list == nullptr: all cn sentences of the chunk; else the counters[list_cnt] listed ones
+  // (what the word memo left over; their cnt / status are initialised already)
   __shared__ uint32_t sh[kFastMaxRaw];
   for (int k = threadIdx.x; k < kFastMaxRaw; k += kSortThreads) sh[k] = 0;
   __syncthreads();
   const int64_t base = (int64_t)blockIdx.x * kSortTile;
+  const int64_t m = list ? (int64_t)counters[list_cnt] : cn;
 #pragma unroll
   for (int j = 0; j < kSortItems; ++j) {
-    const int64_t t = base + j * kSortThreads + threadIdx.x;
-    if (t < cn) {
+    const int64_t i = base + j * kSortThreads + threadIdx.x;
+    if (i < m) {
+      const int64_t t = list ? list[i] : i;
       const int64_t len = off[c0 + t + 1] - off[c0 + t];
-      cnt[t] = 0;
-      status[t] = 0;
+      if (!list) {
+        cnt[t] = 0;
+        status[t] = 0;
+      }
       if (len >= kLongMaxRaw) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
       else if (len >= kFastMaxRaw) long_list[atomicAdd(&counters[C_NLONG], 1u)] = (int32_t)t;
       else if (len > 0) atomicAdd(&sh[len], 1u);
@@ -243,19 +249,23 @@ __global__ void __launch_bounds__(1024) k_binscan(uint32_t *hist, uint32_t *binc
 // Same tiles as k_hist: the block reserves a range of every bin it touches with one global
 // atomic, then ranks its sentences inside the range with shared-memory atomics.
 __global__ void __launch_bounds__(kSortThreads)
-k_scatter(const int64_t *off, int64_t c0, int64_t cn, uint32_t *bincur, int32_t *perm) {
+k_scatter(const int64_t *off, int64_t c0, int64_t cn, const int32_t *list, int list_cnt, uint32_t *bincur,
+          int32_t *perm, const uint32_t *counters) {
   __shared__ uint32_t sh[kFastMaxRaw];
   for (int k = threadIdx.x; k < kFastMaxRaw; k += kSortThreads) sh[k] = 0;
   __syncthreads();
   const int64_t base = (int64_t)blockIdx.x * kSortTile;
-  int32_t len[kSortItems];
+  const int64_t m = list ? (int64_t)counters[list_cnt] : cn;
+  int32_t len[kSortItems], who[kSortItems];
   uint32_t rank[kSortItems];
 #pragma unroll
   for (int j = 0; j < kSortItems; ++j) {
-    const int64_t t = base + j * kSortThreads + threadIdx.x;
+    const int64_t i = base + j * kSortThreads + threadIdx.x;
     len[j] = 0;
-    if (t < cn) {
+    if (i < m) {
+      const int64_t t = list ? list[i] : i;
       const int64_t l = off[c0 + t + 1] - off[c0 + t];
+      who[j] = (int32_t)t;
       if (l > 0 && l < kFastMaxRaw) { len[j] = (int32_t)l; rank[j] = atomicAdd(&sh[l], 1u); }
     }
   }
@@ -265,7 +275,7 @@ k_scatter(const int64_t *off, int64_t c0, int64_t cn, uint32_t *bincur, int32_t 
   __syncthreads();
 #pragma unroll
   for (int j = 0; j < kSortItems; ++j)
-    if (len[j]) perm[sh[len[j]] + rank[j]] = (int32_t)(base + j * kSortThreads + threadIdx.x);
+    if (len[j]) perm[sh[len[j]] + rank[j]] = who[j];
 }
 
 // One thread per sentence, in sorted order (lanes of a warp: equal raw lengths).
@@ -460,21 +470,69 @@ k_encode_bpe_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *
 }
 
 // ---------------------------------------------------------------- word-memo tier (spm_memo.cuh)
-// k_memo_collect: one thread per sentence (sorted order) keys its words and records their
-// table slots; nwords[t] = word count, -1 = not memoisable (goes to the Viterbi tier),
-// -2 = nothing to do (already routed to the general tier).
+// Slots of the words of sentence t: at most len / 2 + 2 words come from the raw text
+// itself; a charsmap expansion that adds more makes the sink give up on the sentence.
+__device__ __forceinline__ int64_t memo_wslot_base(const int64_t *off, int64_t c0, int64_t t) {
+  return ((off[c0 + t] - off[c0]) >> 1) + 4 * t;
+}
+
+// k_memo_scan: one thread per sentence in ORIGINAL order -- the 32 sentences of a warp are
+// one contiguous piece of the text buffer, which the warp copies to shared memory with
+// coalesced 16-byte loads (when it fits) before every lane normalizes its own sentence
+// straight into word keys (fast_normalize_scan + MemoSink): no normalized text is written.
+// nwords[t] = word count, or -1 = the memo cannot serve this sentence.
+constexpr int kScanWarps = 8, kScanWarpBytes = 5120;
 constexpr int kMemoThreads = 256;
-__global__ void __launch_bounds__(kMemoThreads)
-k_memo_collect(MemoTable tb, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
-               const int32_t *perm, int count_idx, uint32_t *wslots, int32_t *nwords, const uint32_t *counters) {
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)counters[count_idx]) return;
-  const int32_t t = perm[idx];
-  const int32_t nl = nlen[t];
-  int32_t nw = -2;
-  if (nl >= 0)
-    nw = memo_collect(tb, norm + fast_norm_base(off, c0, t), nl, wslots + fast_stage_base(off, c0, t));
+__global__ void __launch_bounds__(kScanWarps * 32)
+k_memo_scan(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn,
+            const uint8_t *lo, const uint8_t *hi, uint32_t *wslots, int32_t *nwords, int32_t *cnt, uint32_t *status) {
+  __shared__ uint32_t first2[2048];
+  __shared__ __align__(16) uint8_t stage[kScanWarps][kScanWarpBytes];
+  if (mv.cm_first2 != nullptr)
+    for (int k = threadIdx.x; k < 2048; k += kScanWarps * 32) first2[k] = mv.cm_first2[k];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t tw = ((int64_t)blockIdx.x * kScanWarps + wid) * 32;
+  if (tw >= cn) return;
+  const int64_t t = tw + lane;
+  const int64_t a = off[c0 + tw], b = off[c0 + min(tw + 32, cn)];
+  const uint8_t *src = (const uint8_t *)((uintptr_t)(text + a) & ~(uintptr_t)15);
+  const int64_t span = (text + b) - src;
+  const bool staged = span <= kScanWarpBytes - 16;
+  if (staged) {
+    for (int64_t i = lane * 16; i < span; i += 512) {
+      const uint8_t *p = src + i;
+      uint4 v;
+      if (p >= lo && p + 16 <= hi) {
+        v = *reinterpret_cast<const uint4 *>(p);
+      } else {
+        uint8_t tmp[16];
+        for (int j = 0; j < 16; ++j) tmp[j] = (p + j >= lo && p + j < hi) ? p[j] : 0;
+        memcpy(&v, tmp, 16);
+      }
+      *reinterpret_cast<uint4 *>(&stage[wid][i]) = v;
+    }
+    __syncwarp();
+  }
+  if (t >= cn) return;
+  const int64_t o0 = off[c0 + t], len = off[c0 + t + 1] - o0;
+  int32_t nw = 0;
+  if (len >= kLongMaxRaw) {
+    nw = -1;
+  } else if (len > 0) {
+    MemoSink sink;
+    sink.init(tb, wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4);
+    int32_t nc = 0;
+    bool content = false;
+    const uint8_t *in = staged ? &stage[wid][0] + ((text + o0) - src) : text + o0;
+    const uint8_t *l2 = staged ? &stage[wid][0] : lo;
+    const uint8_t *h2 = staged ? &stage[wid][0] + ((span + 15) & ~(int64_t)15) : hi;
+    fast_normalize_scan(mv, first2, in, len, l2, h2, sink, &nc, &content);
+    nw = sink.finish(mv.remove_extra_ws != 0);
+  }
   nwords[t] = nw;
+  cnt[t] = 0;
+  status[t] = 0;
 }
 
 __device__ __forceinline__ FastView memo_cold_view(const FastParams &fp) {
@@ -503,9 +561,8 @@ __global__ void __launch_bounds__(kMemoThreads) k_memo_words_text(MemoTable tb, 
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t n_new = min(*tb.n_new, tb.max_new);
   if (idx >= n_new) return;
-  const MemoEntry *e = tb.e + tb.new_list[idx];
   __align__(16) uint8_t buf[64];
-  const int nb = memo_word_bytes(tb.e, e, buf, 64);
+  const int nb = memo_word_bytes(tb.keys, tb.new_list[idx], buf, 64);
   uint4 *dst = reinterpret_cast<uint4 *>(wtext + (size_t)idx * 64);
   const uint4 *src = reinterpret_cast<const uint4 *>(buf);
 #pragma unroll
@@ -529,35 +586,103 @@ k_memo_words_bpe(FastParams fp, MemoTable tb, const uint8_t *wtext, const int32_
   bs.text = bs.node + 2 * kBpeMaxSyms * kMemoBpeThreads;
   bs.cb = bs.text + (kBpeMaxBytes / 4) * kMemoBpeThreads;
   uint32_t *txt = bs.cb + ((kBpeMaxSyms + 4) / 4) * kMemoBpeThreads;
-  MemoEntry *e = tb.e + tb.new_list[idx];
   int32_t ids[kBpeMaxSyms];
   uint32_t st = 0;
   const int32_t nb = wlen[idx];
   const int32_t c = nb > 0 ? fast_bpe(fv, wtext + (size_t)idx * 64, nb, bs, txt, ids, &st) : 0;
-  memo_store_ids(tb, e, idx, ids, c, st != 0, fv.unk_id);
+  memo_store_ids(tb, idx, ids, c, st != 0 || nb == 0, fv.unk_id);
 }
 
-// k_memo_emit: ids of every memoised sentence (forward order) into the staging area; the
-// rest joins the list of the Viterbi tier.
+// k_memo_emit: one 16-lane tile per sentence, one lane per word (memo_emit() of spm_memo.cuh
+// restated with tile scans): lanes fetch the 32-byte result records of their words, a
+// prefix sum places the ids (forward order) in the staging area.  A sentence with a word
+// that is not memoised / not context-free here joins the list of the Viterbi tier.
+constexpr int kEmitTile = 16;
 __global__ void __launch_bounds__(kMemoThreads)
-k_memo_emit(const MemoEntry *tab, const int32_t *overflow, int unigram, const int64_t *off, int64_t c0, const int32_t *perm, int count_idx,
-            int list_idx, const uint32_t *wslots, const int32_t *nwords, int32_t *stage, int32_t *cnt,
-            uint32_t *status, int32_t *vit_list, uint32_t *counters) {
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)counters[count_idx]) return;
-  const int32_t t = perm[idx];
-  const int32_t nw = nwords[t];
-  if (nw == -2) return;
-  int32_t c = -1;
-  if (nw >= 0) {
-    const int64_t base = fast_stage_base(off, c0, t);
-    c = memo_emit(tab, overflow, wslots + base, nw, unigram != 0, stage + base);
-  }
-  if (c < 0) {
-    vit_list[atomicAdd(&counters[list_idx], 1u)] = t;
-  } else {
-    cnt[t] = c;
-    status[t] = ST_FWD;
+k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t cn, const uint32_t *wslots,
+            const int32_t *nwords, int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *vit_list,
+            uint32_t *counters, int list_idx) {
+  const int lane = threadIdx.x & (kEmitTile - 1);
+  const unsigned tmask = 0xFFFFu << (threadIdx.x & 16);     // the lanes of this tile inside the warp
+  const int64_t tiles = (int64_t)gridDim.x * (kMemoThreads / kEmitTile);
+  for (int64_t t = (int64_t)blockIdx.x * (kMemoThreads / kEmitTile) + threadIdx.x / kEmitTile; t < cn; t += tiles) {
+    const int32_t nw = nwords[t];
+    if (nw == 0) {
+      if (lane == 0) status[t] = ST_FWD;
+      continue;
+    }
+    bool bad = nw < 0;
+    int32_t total = 0;
+    if (!bad) {
+      const int64_t o0 = off[c0 + t];
+      const int32_t cap = (int32_t)(off[c0 + t + 1] - o0) + kFastExtraChars;
+      const uint32_t *sl = wslots + memo_wslot_base(off, c0, t);
+      int32_t *out = stage + fast_stage_base(off, c0, t);
+      float bub = 0.0f;
+      bool carry_unk = false;
+      for (int32_t w0 = 0; w0 < nw && !bad; w0 += kEmitTile) {
+        const bool active = w0 + lane < nw;
+        uint32_t meta = kMemoReady;
+        float bmax = 3.0e38f, sabs = 0.0f;
+        int4 lo4 = make_int4(0, 0, 0, 0), hi4 = make_int4(0, 0, 0, 0);
+        if (active) {
+          const int4 *r = reinterpret_cast<const int4 *>(tb.res + sl[w0 + lane]);
+          lo4 = __ldg(r); hi4 = __ldg(r + 1);
+          meta = (uint32_t)lo4.x; bmax = __int_as_float(lo4.y); sabs = __int_as_float(lo4.z);
+        }
+        bool ok = (meta & (kMemoReady | kMemoBad)) == kMemoReady;
+        // exclusive prefix of sabs inside the tile (+ what came before)
+        float inc = sabs;
+#pragma unroll
+        for (int d = 1; d < kEmitTile; d <<= 1) {
+          const float y = __shfl_up_sync(tmask, inc, d, kEmitTile);
+          if (lane >= d) inc += y;
+        }
+        if (unigram && active && !(bub + (inc - sabs) < bmax)) ok = false;
+        // an unknown run continues across a word boundary: drop the repeated id
+        const bool last_unk = (meta & kMemoLastUnk) != 0;
+        bool prev_unk = __shfl_up_sync(tmask, last_unk, 1, kEmitTile);
+        if (lane == 0) prev_unk = carry_unk;
+        const int k = active ? (int)(meta & 0xFFu) : 0;
+        const int drop = (active && prev_unk && (meta & kMemoFirstUnk)) ? 1 : 0;
+        int pos = k - drop;
+#pragma unroll
+        for (int d = 1; d < kEmitTile; d <<= 1) {
+          const int y = __shfl_up_sync(tmask, pos, d, kEmitTile);
+          if (lane >= d) pos += y;
+        }
+        const int tile_ids = __shfl_sync(tmask, pos, kEmitTile - 1, kEmitTile);
+        pos += total - (k - drop);                       // exclusive, sentence-wide
+        if (total + tile_ids > cap) ok = false;
+        if (__any_sync(tmask, !ok)) { bad = true; break; }
+        if (k > 0) {
+          const int32_t v[kMemoInlineIds] = {lo4.w, hi4.x, hi4.y, hi4.z, hi4.w};
+          if (k <= kMemoInlineIds) {
+#pragma unroll
+            for (int j = 0; j < kMemoInlineIds; ++j)
+              if (j >= drop && j < k) out[pos + j - drop] = v[j];
+          } else {
+            const int32_t *ov = tb.overflow + (size_t)v[kMemoInlineIds - 1] * kMemoOverflowIds;
+#pragma unroll
+            for (int j = 0; j < kMemoInlineIds - 1; ++j)
+              if (j >= drop) out[pos + j - drop] = v[j];
+            for (int j = kMemoInlineIds - 1; j < k; ++j) out[pos + j - drop] = ov[j - (kMemoInlineIds - 1)];
+          }
+        }
+        total += tile_ids;
+        bub += __shfl_sync(tmask, inc, kEmitTile - 1, kEmitTile);
+        const int last_active = min(nw - w0, kEmitTile) - 1;
+        carry_unk = __shfl_sync(tmask, last_unk, last_active, kEmitTile);
+      }
+    }
+    if (lane == 0) {
+      if (bad) {
+        vit_list[atomicAdd(&counters[list_idx], 1u)] = (int32_t)t;
+      } else {
+        cnt[t] = total;
+        status[t] = ST_FWD;
+      }
+    }
   }
 }
 
@@ -717,7 +842,7 @@ struct spm_cuda_model {
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
-      w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_movf, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
+      w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
   mutable std::vector<int64_t> h_woff;
   mutable double stats[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -737,7 +862,7 @@ struct spm_cuda_model {
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
             &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
-            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_movf,
+            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status};
   }
@@ -823,6 +948,7 @@ int upload_model(spm_cuda_model *M) {
   v.max_score = hm.max_score; v.smax = hm.smax; v.ring = hm.ring;
   v.add_dummy_prefix = hm.add_dummy_prefix; v.remove_extra_ws = hm.remove_extra_ws;
   v.escape_ws = hm.escape_ws; v.ws_suffix = hm.ws_suffix; v.has_unused = hm.has_unused;
+  v.ascii_plain = hm.ascii_plain;
 
   CUDA_TRY(cudaDeviceGetAttribute(&M->sm_count, cudaDevAttrMultiProcessorCount, M->device));
   return configure_fast(M);
@@ -1170,10 +1296,14 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     const uint64_t want = 2 * (uint64_t)n + (uint64_t)(text_hi - text_lo) / 16;
     uint64_t entries = 1 << 12;
     while (entries < want && entries < (1ull << 23)) entries <<= 1;
-    if ((rc = M->w_memo.ensure(entries * sizeof(MemoEntry)))) return rc;
+    if ((rc = M->w_memo.ensure(entries * sizeof(MemoKey)))) return rc;
+    if ((rc = M->w_mres.ensure(entries * sizeof(MemoRes)))) return rc;
     if ((rc = M->w_newlist.ensure(entries / 2 * 4))) return rc;
-    CUDA_TRY(cudaMemsetAsync(M->w_memo.p, 0, entries * sizeof(MemoEntry), st));
-    memo_tb.e = (MemoEntry *)M->w_memo.p;
+    // keys: empty; results: meta 0 = "not encoded" (claimed beyond max_new, never served)
+    CUDA_TRY(cudaMemsetAsync(M->w_memo.p, 0, entries * sizeof(MemoKey), st));
+    CUDA_TRY(cudaMemsetAsync(M->w_mres.p, 0, entries * sizeof(MemoRes), st));
+    memo_tb.keys = (MemoKey *)M->w_memo.p;
+    memo_tb.res = (MemoRes *)M->w_mres.p;
     memo_tb.mask = (uint32_t)(entries - 1);
     memo_tb.new_list = (uint32_t *)M->w_newlist.p;
     memo_tb.max_new = (uint32_t)(entries / 2);
@@ -1288,41 +1418,21 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       const int64_t max_n_long = has_long ? std::min<int64_t>(cn, raw / kFastMaxRaw + 1) : 0;
       const unsigned gsort = (unsigned)((cn + kSortTile - 1) / kSortTile);
       const unsigned gsent = (unsigned)((cn + 255) / 256), glong = (unsigned)((max_n_long + 255) / 256);
-      static_assert(kNormThreads == 256 && kMemoThreads == 256, "grids below assume 256 threads");
-      k_hist<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, d_hist,
-                                   (int32_t *)M->w_genlist.p, (int32_t *)M->w_longlist.p, d_counters);
-      k_binscan<<<1, 1024, 0, st>>>(d_hist, d_bincur, d_counters);
-      k_scatter<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, d_bincur, (int32_t *)M->w_perm.p);
-      if ((rc = kev_record(M, st, 0, T_NORMALIZE))) return rc;
-      k_normalize_fast<<<gsent, kNormThreads, 0, st>>>(
-          M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p, C_NFAST,
-          (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
-      if (has_long)   // the grid covers the most long lines the chunk's bytes can hold
-        k_normalize_fast<<<glong, kNormThreads, 0, st>>>(
-            M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_longlist.p, C_NLONG,
-            (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
-      if ((rc = kev_record(M, st, 1))) return rc;
-      launches += has_long ? 5 : 4;
-      // lists of the Viterbi / merge kernels: everything, or what the word memo leaves over
-      const int32_t *list_a = (const int32_t *)M->w_perm.p, *list_b = (const int32_t *)M->w_longlist.p;
-      int cnt_a = C_NFAST, work_a = C_WORK, cnt_b = C_NLONG, work_b = C_WORK_LONG;
+      static_assert(kNormThreads == 256 && kMemoThreads == 256 && kScanWarps * 32 == 256, "grids assume 256 threads");
+      // Word memo first (spm_memo.cuh): what it cannot serve is listed in w_vit and takes the
+      // sort -> normalize -> Viterbi / merge path below, like every sentence does without the memo.
+      const int32_t *todo = nullptr;     // nullptr: all sentences of the chunk
       if (memo) {
-        if ((rc = M->w_wslots.ensure((size_t)(raw + kFastExtraChars * cn + 64) * 4))) return rc;
+        if ((rc = M->w_wslots.ensure((size_t)(raw / 2 + 4 * cn + 64) * 4))) return rc;
         if ((rc = M->w_nwords.ensure(cn * 4))) return rc;
         if ((rc = M->w_vit.ensure(cn * 4))) return rc;
-        if (has_long && (rc = M->w_vitl.ensure(max_n_long * 4))) return rc;
         MemoTable tb = memo_tb;
         tb.n_new = d_counters + C_NNEW;
         const unsigned gnew = (tb.max_new + 255) / 256;
         if ((rc = kev_record(M, st, 0, T_MEMO_COLLECT))) return rc;
-        k_memo_collect<<<gsent, kMemoThreads, 0, st>>>(
-            tb, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, (const int32_t *)M->w_perm.p,
-            C_NFAST, (uint32_t *)M->w_wslots.p, (int32_t *)M->w_nwords.p, d_counters);
-        if (has_long)
-          k_memo_collect<<<glong, kMemoThreads, 0, st>>>(
-              tb, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-              (const int32_t *)M->w_longlist.p, C_NLONG, (uint32_t *)M->w_wslots.p, (int32_t *)M->w_nwords.p,
-              d_counters);
+        k_memo_scan<<<gsent, kScanWarps * 32, 0, st>>>(
+            M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
+            (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p);
         if ((rc = kev_record(M, st, 1))) return rc;
         if ((rc = kev_record(M, st, 0, T_MEMO_WORDS))) return rc;
         if (M->fast_kind == 1) {
@@ -1336,20 +1446,33 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
         }
         if ((rc = kev_record(M, st, 1))) return rc;
         if ((rc = kev_record(M, st, 0, T_MEMO_EMIT))) return rc;
-        k_memo_emit<<<gsent, kMemoThreads, 0, st>>>(
-            tb.e, tb.overflow, M->fast_kind == 1, d_off, c0, (const int32_t *)M->w_perm.p, C_NFAST, C_NVIT,
-            (const uint32_t *)M->w_wslots.p, (const int32_t *)M->w_nwords.p, (int32_t *)M->w_stage.p,
-            (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p, d_counters);
-        if (has_long)
-          k_memo_emit<<<glong, kMemoThreads, 0, st>>>(
-              tb.e, tb.overflow, M->fast_kind == 1, d_off, c0, (const int32_t *)M->w_longlist.p, C_NLONG, C_NVITL,
-              (const uint32_t *)M->w_wslots.p, (const int32_t *)M->w_nwords.p, (int32_t *)M->w_stage.p,
-              (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vitl.p, d_counters);
+        const unsigned gemit = (unsigned)std::min<int64_t>((cn + 15) / 16, 8 * (int64_t)M->sm_count);
+        k_memo_emit<<<gemit, kMemoThreads, 0, st>>>(
+            tb, M->fast_kind == 1, d_off, c0, cn, (const uint32_t *)M->w_wslots.p, (const int32_t *)M->w_nwords.p,
+            (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
+            d_counters, C_NVIT);
         if ((rc = kev_record(M, st, 1))) return rc;
-        launches += has_long ? 4 : 2;
-        list_a = (const int32_t *)M->w_vit.p; cnt_a = C_NVIT; work_a = C_WORK_VIT;
-        list_b = (const int32_t *)M->w_vitl.p; cnt_b = C_NVITL; work_b = C_WORK_VITL;
+        launches += 2;
+        todo = (const int32_t *)M->w_vit.p;
       }
+      k_hist<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, todo, C_NVIT, (int32_t *)M->w_cnt.p,
+                                   (uint32_t *)M->w_status.p, d_hist, (int32_t *)M->w_genlist.p,
+                                   (int32_t *)M->w_longlist.p, d_counters);
+      k_binscan<<<1, 1024, 0, st>>>(d_hist, d_bincur, d_counters);
+      k_scatter<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, todo, C_NVIT, d_bincur, (int32_t *)M->w_perm.p,
+                                      d_counters);
+      if ((rc = kev_record(M, st, 0, T_NORMALIZE))) return rc;
+      k_normalize_fast<<<gsent, kNormThreads, 0, st>>>(
+          M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p, C_NFAST,
+          (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
+      if (has_long)   // the grid covers the most long lines the chunk's bytes can hold
+        k_normalize_fast<<<glong, kNormThreads, 0, st>>>(
+            M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_longlist.p, C_NLONG,
+            (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
+      if ((rc = kev_record(M, st, 1))) return rc;
+      launches += has_long ? 5 : 4;
+      const int32_t *list_a = (const int32_t *)M->w_perm.p, *list_b = (const int32_t *)M->w_longlist.p;
+      const int cnt_a = C_NFAST, work_a = C_WORK, cnt_b = C_NLONG, work_b = C_WORK_LONG;
       if ((rc = kev_record(M, st, 0, T_ENCODE))) return rc;
       if (M->fast_kind == 1) {
         k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
@@ -1382,7 +1505,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       tr("fast kernel done, chunk", (long)kc);
       if (host && (rc = flush_outputs(kc))) return rc;   // earlier chunks are complete by now
       n_general += hc[C_NGEN];
-      n_viterbi += memo ? hc[C_NVIT] + hc[C_NVITL] : hc[C_NFAST] + hc[C_NLONG];
+      n_viterbi += hc[C_NFAST] + hc[C_NLONG];
       n_memo_words += hc[C_NNEW];
       if ((rc = run_general(M, st, d_text, d_off, c0, (const int32_t *)M->w_genlist.p, hc[C_NGEN], false,
                             &launches)))
@@ -1391,6 +1514,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       n_general += cn;
       if ((rc = run_general(M, st, d_text, d_off, c0, nullptr, cn, true, &launches))) return rc;
     }
+    if ((rc = kev_record(M, st, 0, T_COMPACT))) return rc;
     FinalCountOp fop;
     fop.extra = plan.npre + plan.nsuf;
     if ((rc = run_scan(M, st, (const int32_t *)M->w_cnt.p, cn, fop, d_idoff + c0, d_carry, 1, &launches))) return rc;
@@ -1399,6 +1523,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
                                      (const int32_t *)M->g_stage.p, (const int64_t *)M->w_srcoff.p,
                                      (const uint32_t *)M->w_status.p, (const int32_t *)M->w_cnt.p, d_idoff, d_ids,
                                      d_cap);
+    if ((rc = kev_record(M, st, 1))) return rc;
     launches += 1;
     CUDA_TRY(cudaGetLastError());
     tr("chunk enqueued", (long)kc);

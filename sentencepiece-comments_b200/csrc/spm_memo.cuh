@@ -35,11 +35,11 @@ namespace spmb {
 constexpr int kMemoKeyBytes = 14;      // word bytes held by one key
 constexpr int kMemoTailBytes = 10;     // bytes held by the key of a tail entry (next to the head's slot)
 constexpr int kMemoMaxBytes = kMemoKeyBytes + kMemoTailBytes;   // word bytes after the U+2581 prefix
-constexpr int kMemoInlineIds = 8;      // ids kept inside the entry
-constexpr int kMemoOverflowIds = 16;   // further ids of a long word (overflow row of the entry's list index)
-constexpr int kMemoMaxIds = kMemoInlineIds + kMemoOverflowIds;
+constexpr int kMemoInlineIds = 5;      // ids kept inside the result record
+constexpr int kMemoOverflowIds = 20;   // ids 4.. of a longer word (overflow row of the word's list index)
+constexpr int kMemoMaxIds = kMemoInlineIds - 1 + kMemoOverflowIds;
 constexpr int kMemoProbes = 24;        // linear probes before giving up
-constexpr uint32_t kMemoReady = 0x100u;   // meta: entry encoded
+constexpr uint32_t kMemoReady = 0x100u;   // meta: word encoded
 constexpr uint32_t kMemoBad = 0x200u;     // meta: the word cannot be memoised
 constexpr uint32_t kMemoFirstUnk = 0x400u;  // meta: first id is the unknown id
 constexpr uint32_t kMemoLastUnk = 0x800u;   // meta: last id is the unknown id
@@ -49,18 +49,21 @@ constexpr uint32_t kMemoLastUnk = 0x800u;   // meta: last id is the unknown id
 // entry (meta 0x40 | prefix) for its first 14 bytes, then the word's own TAIL entry
 // (meta 0x80 | rest length) whose key holds the head's slot (3 bytes) and the <= 10 bytes
 // that are left.  Both halves of every key carry the non-zero meta byte; (0, 0) = empty.
-struct alignas(64) MemoEntry {
+struct alignas(16) MemoKey {
   uint64_t k0, k1;
+};
+// What an occurrence of the word copies: one 32-byte sector.
+struct alignas(32) MemoRes {
   uint32_t meta;       // id count | kMemo* flags
   float bmax;          // unigram: largest |backtrace score at the word start| that keeps the word context-free
   float sabs;          // unigram: bound of |best-path score of the word|
-  uint32_t ovf;        // overflow row (index into MemoTable::overflow / kMemoOverflowIds) when count > kMemoInlineIds
-  int32_t ids[kMemoInlineIds];
+  int32_t ids[kMemoInlineIds];   // count <= 5: all ids; else ids 0..3 and the overflow row in ids[4]
 };
 
 struct MemoTable {
-  MemoEntry *e;
-  uint32_t mask;        // entries - 1 (power of two)
+  MemoKey *keys;
+  MemoRes *res;
+  uint32_t mask;        // slots - 1 (power of two)
   uint32_t *new_list;   // slots claimed in this pass
   uint32_t *n_new;      // their count (may exceed max_new: the excess is never encoded)
   uint32_t max_new;
@@ -75,7 +78,7 @@ SPM_HD uint32_t memo_hash(uint64_t k0, uint64_t k1) {
 }
 
 // compare-and-swap of the 16-byte key against "empty"; returns the previous key
-SPM_HD void memo_claim(MemoEntry *e, uint64_t k0, uint64_t k1, uint64_t *o0, uint64_t *o1) {
+SPM_HD void memo_claim(MemoKey *e, uint64_t k0, uint64_t k1, uint64_t *o0, uint64_t *o1) {
 #if defined(__CUDA_ARCH__)
   asm volatile(
       "{\n\t.reg .b128 c, s, d;\n\t"
@@ -93,13 +96,13 @@ SPM_HD void memo_claim(MemoEntry *e, uint64_t k0, uint64_t k1, uint64_t *o0, uin
 
 // Slot of the word with key (k0, k1), inserting it when absent; 0xFFFFFFFF when the
 // probe sequence is exhausted.  A (cached, possibly stale or torn) plain load decides the
-// common case: both key halves carry the non-zero meta byte, so a half-written entry can
-// never compare equal, and entries are immutable once written; "looks empty" is settled
+// common case: both key halves carry the non-zero meta byte, so a half-written key can
+// never compare equal, and keys are immutable once written; "looks empty" is settled
 // by the CAS itself.
 SPM_HD uint32_t memo_find_or_insert(const MemoTable &tb, uint64_t k0, uint64_t k1) {
   uint32_t slot = memo_hash(k0, k1) & tb.mask;
   for (int probe = 0; probe < kMemoProbes; ++probe, slot = (slot + 1) & tb.mask) {
-    MemoEntry *e = tb.e + slot;
+    MemoKey *e = tb.keys + slot;
 #if defined(__CUDA_ARCH__)
     uint64_t e0, e1;
     asm volatile("ld.global.v2.u64 {%0, %1}, [%2];" : "=l"(e0), "=l"(e1) : "l"(e) : "memory");
@@ -124,62 +127,106 @@ SPM_HD uint32_t memo_find_or_insert(const MemoTable &tb, uint64_t k0, uint64_t k
   return 0xFFFFFFFFu;
 }
 
-// Splits one normalized sentence (8-byte aligned, zero padded as for fast_unigram) into
-// words and writes the table slot of each to slots[]; returns the word count, or -1 when
-// a word cannot be keyed (longer than kMemoMaxBytes, table full).
-SPM_HDN int32_t memo_collect(const MemoTable &tb, const uint8_t *s, int32_t n, uint32_t *slots) {
-  if (n <= 0) return 0;
-  const uint64_t *sw = reinterpret_cast<const uint64_t *>(s);
-  uint64_t lo = sw[0], hi = sw[1];
-  int32_t q = 1;            // hi = sw[q]
-  int r = 0;                // window = bytes at 8 (q - 1) + r
-  int32_t p = 0, nw = 0;
-  uint64_t k0 = 0, k1 = 0;  // bytes of the current key (head: 14, tail: slot + 10)
-  int len = 0, prefix = 0;
-  bool tail = false;        // the current key is the tail of a long word
-  bool started = false;     // the current word has a prefix or a byte
-  for (;;) {
-    const uint64_t win = fast_window(lo, hi, r);
-    const bool end = p >= n;
-    const bool mark = !end && (win & 0xFFFFFFull) == 0x8196E2ull;
-    if (end || mark) {
-      if (started) {
-        const uint64_t mb = tail ? (uint64_t)(0x80 | len) : (uint64_t)((len << 1) | prefix);
-        const uint32_t slot = memo_find_or_insert(tb, k0 | mb, k1 | (mb << 56));
-        if (slot == 0xFFFFFFFFu) return -1;
-        slots[nw++] = slot;
-      }
-      if (end) break;
-      k0 = 0; k1 = 0; len = 0; prefix = 1; started = true; tail = false;
-      p += 3; r += 3;
-    } else {
-      const uint64_t b = win & 0xFFull;
-      if (!tail && len == kMemoKeyBytes) {       // the word goes on: key its head, start the tail
-        const uint64_t mb = (uint64_t)(0x40 | prefix);
-        const uint32_t hs = memo_find_or_insert(tb, k0 | mb, k1 | (mb << 56));
-        if (hs == 0xFFFFFFFFu) return -1;
-        k0 = (uint64_t)hs << 8; k1 = 0; len = 0; tail = true;
-      }
-      if (tail) {
-        if (len >= kMemoTailBytes) return -1;
-        if (len < 4) k0 |= b << (8 * (len + 4));
-        else k1 |= b << (8 * (len - 4));
-      } else {
-        if (len < 7) k0 |= b << (8 * (len + 1));
-        else k1 |= b << (8 * (len - 7));
-      }
-      ++len; started = true;
-      ++p; ++r;
-    }
-    if (r >= 8) { r -= 8; lo = hi; hi = sw[++q]; }
+// Output sink of fast_normalize_scan(): the normalized characters of a sentence go
+// straight into word keys (the normalized text itself is only materialised for the
+// sentences the memo cannot serve).  slots[] receives the table slot of every word.
+struct MemoSink {
+  MemoTable tb;
+  uint32_t *slots;
+  int32_t cap;              // capacity of slots[]
+  int32_t nw;
+  uint64_t c0, c1;          // head: content bytes 0..7 / 8..13; tail: the tail key without its meta byte
+  int len, prefix;
+  bool tail;                // the current key is the tail of a long word
+  bool started;             // the current word has a prefix or a byte
+  bool fail;                // a word cannot be keyed (too long, table full, too many words)
+  int32_t pending;          // bare U+2581 words not yet written to slots[]
+  static constexpr bool kRuns = true;
+  SPM_HD void init(const MemoTable &t, uint32_t *s, int32_t c) {
+    tb = t; slots = s; cap = c; nw = 0; c0 = 0; c1 = 0; len = 0; prefix = 0;
+    tail = false; started = false; fail = false; pending = 0;
   }
-  return nw;
-}
+  SPM_HD bool room(int64_t) const { return true; }
+  SPM_HD bool done() const { return fail; }
+  SPM_HD uint32_t lookup(uint64_t mb) {
+    if (tail) return memo_find_or_insert(tb, c0 | mb, c1 | (mb << 56));
+    return memo_find_or_insert(tb, mb | (c0 << 8), (c0 >> 56) | (c1 << 8) | (mb << 56));
+  }
+  SPM_HD void close_word() {
+    const uint32_t slot = lookup(tail ? (uint64_t)(0x80 | len) : (uint64_t)((len << 1) | prefix));
+    if (slot == 0xFFFFFFFFu || nw >= cap) { fail = true; return; }
+    slots[nw++] = slot;
+  }
+  // words that are a bare U+2581 wait here: at the end of the sentence they are trailing
+  // whitespace, which remove_extra_whitespaces strips (src/normalizer.cc:191-201)
+  SPM_HD void flush_bare() {
+    for (; pending > 0 && !fail; --pending) {
+      const uint32_t slot = memo_find_or_insert(tb, 1ull, 1ull << 56);   // length 0, prefix 1
+      if (slot == 0xFFFFFFFFu || nw >= cap) { fail = true; return; }
+      slots[nw++] = slot;
+    }
+  }
+  SPM_HD bool bare() const { return prefix == 1 && len == 0 && !tail; }
+  SPM_HD void put_byte(uint64_t b) {
+    if (pending) flush_bare();
+    if (!tail && len == kMemoKeyBytes) {       // the word goes on: key its head, start the tail
+      const uint32_t hs = lookup((uint64_t)(0x40 | prefix));
+      if (hs == 0xFFFFFFFFu) { fail = true; return; }
+      c0 = (uint64_t)hs << 8; c1 = 0; len = 0; tail = true;
+    }
+    if (tail) {
+      if (len >= kMemoTailBytes) { fail = true; return; }
+      if (len < 4) c0 |= b << (8 * (len + 4));
+      else c1 |= b << (8 * (len - 4));
+    } else {
+      if (len < 8) c0 |= b << (8 * len);
+      else c1 |= b << (8 * (len - 8));
+    }
+    ++len; started = true;
+  }
+  // up to `run` (1..8) bytes of one word at once (the low bytes of w); returns how many were taken
+  SPM_HD int take(uint64_t w, int run) {
+    if (fail || tail) return 0;
+    if (pending) { flush_bare(); if (fail) return 0; }
+    if (run > kMemoKeyBytes - len) run = kMemoKeyBytes - len;
+    if (run <= 0) return 0;
+    const uint64_t wm = run == 8 ? w : (w & ((1ull << (8 * run)) - 1));
+    if (len < 8) {
+      c0 |= wm << (8 * len);
+      if (len + run > 8) c1 |= wm >> (8 * (8 - len));
+    } else {
+      c1 |= wm << (8 * (len - 8));
+    }
+    len += run; started = true;
+    return run;
+  }
+  SPM_HD void put(uint32_t v, int k) {  // one character, k in 1..4 bytes, little-endian in v
+    if (fail) return;
+    if (k == 3 && v == 0x8196E2u) {     // U+2581: the next word starts here
+      if (started) {
+        if (bare()) ++pending; else close_word();
+      }
+      c0 = 0; c1 = 0; len = 0; prefix = 1; started = true; tail = false;
+      return;
+    }
+    for (int j = 0; j < k && !fail; ++j) put_byte((v >> (8 * j)) & 0xFFu);
+  }
+  // end of the sentence.  Returns the word count or -1.
+  SPM_HD int32_t finish(bool strip_trailing) {
+    if (fail) return -1;
+    if (started) {
+      if (bare()) ++pending; else close_word();
+    }
+    if (strip_trailing) pending = 0;
+    flush_bare();
+    return fail ? -1 : nw;
+  }
+};
 
-// Bytes of the word of an entry: U+2581 prefix (when keyed with one) + content, zero
+// Bytes of the word in slot `slot`: U+2581 prefix (when keyed with one) + content, zero
 // padded to `cap` (>= 40) bytes.  Returns the byte count; 0 for a head entry (not a word).
-SPM_HD int memo_word_bytes(const MemoEntry *tab, const MemoEntry *e, uint8_t *out, int cap) {
-  uint64_t k0 = e->k0, k1 = e->k1;
+SPM_HD int memo_word_bytes(const MemoKey *keys, uint32_t slot, uint8_t *out, int cap) {
+  uint64_t k0 = keys[slot].k0, k1 = keys[slot].k1;
   const int mb = (int)(k0 & 0xFFu);
   int nb = 0;
   if (mb & 0x40) {
@@ -189,7 +236,7 @@ SPM_HD int memo_word_bytes(const MemoEntry *tab, const MemoEntry *e, uint8_t *ou
     int tl = 0;
     if (mb & 0x80) {   // tail: fetch the head (immutable once claimed)
       t0 = k0; t1 = k1; tl = mb & 0x3F;
-      const MemoEntry *h = tab + ((k0 >> 8) & 0xFFFFFFu);
+      const MemoKey *h = keys + ((k0 >> 8) & 0xFFFFFFu);
       k0 = h->k0; k1 = h->k1;
     }
     const int hb = (int)(k0 & 0xFFu);
@@ -205,36 +252,40 @@ SPM_HD int memo_word_bytes(const MemoEntry *tab, const MemoEntry *e, uint8_t *ou
 }
 
 // Stores ids (forward order), flags and bounds of an encoded word; `row` = its list index.
-SPM_HD void memo_store(const MemoTable &tb, MemoEntry *e, uint32_t row, const int32_t *ids, int32_t cnt, bool bad,
+SPM_HD void memo_store(const MemoTable &tb, uint32_t row, const int32_t *ids, int32_t cnt, bool bad,
                        int32_t unk_id, float bmax, float sabs) {
+  MemoRes *e = tb.res + tb.new_list[row];
   uint32_t meta = kMemoReady;
   if (bad || cnt <= 0 || cnt > kMemoMaxIds) { meta |= kMemoBad; cnt = 0; }
-  for (int j = 0; j < cnt && j < kMemoInlineIds; ++j) e->ids[j] = ids[j];
-  for (int j = kMemoInlineIds; j < cnt; ++j) tb.overflow[(size_t)row * kMemoOverflowIds + (j - kMemoInlineIds)] = ids[j];
+  if (cnt <= kMemoInlineIds) {
+    for (int j = 0; j < cnt; ++j) e->ids[j] = ids[j];
+  } else {
+    for (int j = 0; j < kMemoInlineIds - 1; ++j) e->ids[j] = ids[j];
+    e->ids[kMemoInlineIds - 1] = (int32_t)row;
+    for (int j = kMemoInlineIds - 1; j < cnt; ++j)
+      tb.overflow[(size_t)row * kMemoOverflowIds + (j - (kMemoInlineIds - 1))] = ids[j];
+  }
   if (cnt > 0 && ids[0] == unk_id) meta |= kMemoFirstUnk;
   if (cnt > 0 && ids[cnt - 1] == unk_id) meta |= kMemoLastUnk;
-  e->ovf = row;
   e->bmax = bmax;
   e->sabs = sabs;
   e->meta = meta | (uint32_t)cnt;
 }
 // a word whose segmentation does not depend on its context (BPE)
-SPM_HD void memo_store_ids(const MemoTable &tb, MemoEntry *e, uint32_t row, const int32_t *ids, int32_t cnt, bool bad,
+SPM_HD void memo_store_ids(const MemoTable &tb, uint32_t row, const int32_t *ids, int32_t cnt, bool bad,
                            int32_t unk_id) {
-  memo_store(tb, e, row, ids, cnt, bad, unk_id, 3.0e38f, 0.0f);
+  memo_store(tb, row, ids, cnt, bad, unk_id, 3.0e38f, 0.0f);
 }
 
 // Unigram: Viterbi of one stand-alone word with the margin bookkeeping described above.
 // Same lattice as fast_unigram() (nodes of the fast view + the one-character UNK node,
 // candidates of an end position in begin order, strict '>').
 SPM_HDN void memo_unigram_word(const FastView &fv, bool neg_only, const MemoTable &tb, uint32_t row) {
-  MemoEntry *e = tb.e + tb.new_list[row];
-  const MemoEntry *tab = tb.e;
   constexpr int kMaxChars = kMemoMaxBytes + 1;
   const float NEG = -3.0e38f;
   uint8_t txt[40];
-  const int nb = memo_word_bytes(tab, e, txt, 40);
-  if (nb == 0) { e->meta = kMemoReady | kMemoBad; return; }   // a head entry
+  const int nb = memo_word_bytes(tb.keys, tb.new_list[row], txt, 40);
+  if (nb == 0) { tb.res[tb.new_list[row]].meta = kMemoReady | kMemoBad; return; }   // a head entry
   float b1[kMaxChars + 1], b2[kMaxChars + 1];
   uint32_t rec[kMaxChars + 1];
   int cstart[kMaxChars + 1];
@@ -296,48 +347,34 @@ SPM_HDN void memo_unigram_word(const FastView &fv, bool neg_only, const MemoTabl
   }
   int32_t fwd[kMaxChars];
   for (int j = 0; j < cnt; ++j) fwd[j] = rev[cnt - 1 - j];
-  memo_store(tb, e, row, fwd, cnt, !(bmax > 0.0f), fv.unk_id, bmax,
+  memo_store(tb, row, fwd, cnt, !(bmax > 0.0f), fv.unk_id, bmax,
              (neg_only ? fabsf(b1[m]) : magw) * 1.001f + 1.0e-3f);
 }
 
-// Ids of one sentence from the slots of its words (forward order).  Returns the id count,
-// or -1 when a word is not memoised / not context-free at this point of the sentence.
-SPM_HDN int32_t memo_emit(const MemoEntry *tab, const int32_t *overflow, const uint32_t *slots, int32_t nw,
-                          bool unigram, int32_t *out) {
+// Ids of one sentence from the slots of its words (forward order, at most `cap`).  Returns
+// the id count, or -1 when a word is not memoised / not context-free at this point of the
+// sentence.  (Sequential statement of what k_memo_emit does with one 16-lane tile.)
+SPM_HDN int32_t memo_emit(const MemoTable &tb, const uint32_t *slots, int32_t nw, bool unigram, int32_t *out,
+                          int32_t cap) {
   int32_t cnt = 0;
   float bub = 0.0f;          // upper bound of |backtrace score| at the start of the next word
   bool prev_unk = false;
   for (int32_t w = 0; w < nw; ++w) {
-    const MemoEntry *e = tab + slots[w];
-#if defined(__CUDA_ARCH__)
-    const uint4 h = __ldg(reinterpret_cast<const uint4 *>(e) + 1);   // meta, bmax, sabs, ovf
-    const uint32_t meta = h.x, ovf = h.w;
-    const float bmax = __uint_as_float(h.y), sabs = __uint_as_float(h.z);
-#else
-    const uint32_t meta = e->meta, ovf = e->ovf;
-    const float bmax = e->bmax, sabs = e->sabs;
-#endif
+    const MemoRes *e = tb.res + slots[w];
+    const uint32_t meta = e->meta;
     if ((meta & (kMemoReady | kMemoBad)) != kMemoReady) return -1;
     if (unigram) {
-      if (!(bub < bmax)) return -1;
-      bub += sabs;
+      if (!(bub < e->bmax)) return -1;
+      bub += e->sabs;
     }
     const int k = (int)(meta & 0xFFu);
     int j = 0;
     if (prev_unk && (meta & kMemoFirstUnk)) j = 1;   // an unknown run continues across the boundary
-#if defined(__CUDA_ARCH__)
-    const int4 a = __ldg(reinterpret_cast<const int4 *>(e) + 2);
-    const int32_t v4[4] = {a.x, a.y, a.z, a.w};
-    for (; j < k && j < 4; ++j) out[cnt++] = v4[j];
-    if (k > 4) {
-      const int4 b = __ldg(reinterpret_cast<const int4 *>(e) + 3);
-      const int32_t w4[4] = {b.x, b.y, b.z, b.w};
-      for (; j < k && j < 8; ++j) out[cnt++] = w4[j - 4];
+    if (cnt + (k - j) > cap) return -1;
+    for (; j < k; ++j) {
+      if (k <= kMemoInlineIds || j < kMemoInlineIds - 1) out[cnt++] = e->ids[j];
+      else out[cnt++] = tb.overflow[(size_t)e->ids[kMemoInlineIds - 1] * kMemoOverflowIds + (j - (kMemoInlineIds - 1))];
     }
-#else
-    for (; j < k && j < kMemoInlineIds; ++j) out[cnt++] = e->ids[j];
-#endif
-    for (; j < k; ++j) out[cnt++] = overflow[(size_t)ovf * kMemoOverflowIds + (j - kMemoInlineIds)];
     prev_unk = (meta & kMemoLastUnk) != 0;
   }
   return cnt;

@@ -329,7 +329,7 @@ void refresh_leaf_types(HostModel *m) {
     if ((t == T_NORMAL || t == T_USER_DEFINED) && m->piece[i].find("\xE2\x96\x81", 1) != std::string::npos)
       inner = true;
   }
-  m->memo_ok = (m->model_type == M_UNIGRAM ? m->fast_ok : m->bpe_fast_ok) && !inner;
+  m->memo_ok = (m->model_type == M_UNIGRAM ? m->fast_ok : m->bpe_fast_ok) && !inner && !m->ws_suffix;
   bool neg = m->min_score - 10.0f <= 0.0f;
   for (size_t i = 0; i < n && neg; ++i)
     if ((m->funits[i] & 0x100u) && !(m->fscore[i] <= 0.0f)) neg = false;
@@ -408,6 +408,15 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
     m->cm_pool_size = (uint32_t)(m->charsmap.size() - 4 - tb);
   }
   scan_charsmap(m);
+  // printable ASCII passes through the normalizer untouched when no rule / user symbol can
+  // start at such a byte as long as the NEXT byte is ASCII too (fast_normalize_scan's runs)
+  m->ascii_plain = true;
+  for (uint32_t b = 0x21; b <= 0x7E && m->ascii_plain; ++b) {
+    if ((m->user_first[b >> 5] >> (b & 31)) & 1) m->ascii_plain = false;
+    if (!m->cm_first2.empty())
+      for (uint32_t x = 0; x < 0x80; ++x)
+        if ((m->cm_first2[((b << 8) | x) >> 5] >> (((b << 8) | x) & 31)) & 1) m->ascii_plain = false;
+  }
   m->ring = 8;
   while (m->ring < m->max_piece_bytes + 5) m->ring <<= 1;
   float smax = fabsf(m->min_score - 10.0f);

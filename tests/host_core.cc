@@ -35,6 +35,7 @@ void make_view(Handle *h) {
   v.unk_score = m.min_score - 10.0f; v.max_score = m.max_score; v.smax = m.smax; v.ring = m.ring;
   v.add_dummy_prefix = m.add_dummy_prefix; v.remove_extra_ws = m.remove_extra_ws;
   v.escape_ws = m.escape_ws; v.ws_suffix = m.ws_suffix; v.has_unused = m.has_unused;
+  v.ascii_plain = m.ascii_plain;
 }
 }  // namespace
 
@@ -98,7 +99,8 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
   const bool use_memo = capc_arg == -1 && h->hm.memo_ok;
   const int capc = capc_arg == -1 ? 0 : capc_arg;
   // word memo state of this call (small table: probe-exhaustion paths get exercised too)
-  std::vector<MemoEntry> mtab;
+  std::vector<MemoKey> mkeys;
+  std::vector<MemoRes> mres;
   std::vector<uint32_t> mnew;
   std::vector<int32_t> movf;
   uint32_t m_n_new = 0, m_done = 0;
@@ -107,13 +109,15 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
   FastView mfv;
   memset(&mfv, 0, sizeof(mfv));
   if (use_memo) {
-    mtab.resize(getenv("HC_MEMO_SMALL") ? (1 << 10) : (1 << 19));
-    memset((void *)mtab.data(), 0, mtab.size() * sizeof(MemoEntry));
-    mnew.resize(mtab.size() / 2);
-    tb.e = mtab.data(); tb.mask = (uint32_t)mtab.size() - 1; tb.new_list = mnew.data(); tb.n_new = &m_n_new;
-    tb.max_new = (uint32_t)mnew.size();
+    const size_t slots = getenv("HC_MEMO_SMALL") ? (1 << 10) : (1 << 19);
+    mkeys.resize(slots);
+    mres.resize(slots);
+    memset((void *)mkeys.data(), 0, slots * sizeof(MemoKey));
+    memset((void *)mres.data(), 0, slots * sizeof(MemoRes));
+    mnew.resize(slots / 2);
     movf.resize(mnew.size() * kMemoOverflowIds);
-    tb.overflow = movf.data();
+    tb.keys = mkeys.data(); tb.res = mres.data(); tb.mask = (uint32_t)slots - 1; tb.new_list = mnew.data();
+    tb.n_new = &m_n_new; tb.max_new = (uint32_t)mnew.size(); tb.overflow = movf.data();
     mfv.units = mfv.units_hot = h->hm.funits.data();
     mfv.score = mfv.score_hot = h->hm.fscore.data();
     mfv.leaf_id = h->hm.fleaf.data();
@@ -144,18 +148,21 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
       if (fl >= 0 && (fl != nl || memcmp(fn.data(), norm.data(), nl) != 0)) return 99;
     }
     bool memo_served = false;
-    if (use_memo && nl > 0) {
-      std::vector<uint64_t> tbuf((nl + kNormPad + 15) / 8 + 1, 0);
-      memcpy(tbuf.data(), norm.data(), nl);
-      std::vector<uint32_t> slots(nl + 2);
-      const int32_t nw = memo_collect(tb, (const uint8_t *)tbuf.data(), nl, slots.data());
+    if (use_memo && len > 0) {
+      // k_memo_scan: the raw sentence straight into word keys (no normalized text)
+      std::vector<uint32_t> slots(len / 2 + 4);
+      MemoSink sink;
+      sink.init(tb, slots.data(), (int32_t)(len / 2 + 4));
+      int32_t nc = 0;
+      bool content = false;
+      fast_normalize_scan(mv, mv.cm_first2, text + off[i], len, text + off[0], text + off[n], sink, &nc, &content);
+      const int32_t nw = sink.finish(mv.remove_extra_ws != 0);
       for (; m_done < m_n_new && m_done < tb.max_new; ++m_done) {   // the "words" kernels
-        MemoEntry *e = tb.e + tb.new_list[m_done];
         if (mv.model_type == M_UNIGRAM) {
           memo_unigram_word(mfv, h->hm.neg_only, tb, m_done);
         } else {
           uint64_t wt[8];
-          const int nb = memo_word_bytes(tb.e, e, (uint8_t *)wt, 64);
+          const int nb = memo_word_bytes(tb.keys, tb.new_list[m_done], (uint8_t *)wt, 64);
           std::vector<uint32_t> scr(kBpeWordsPerThread, 0);
           BpeScratch bs;
           bs.stride = 1;
@@ -167,13 +174,20 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
           FastView bfv = mfv;
           bfv.ring = 0; bfv.unk_score = 0; bfv.smax = 0;
           const int32_t c = nb > 0 ? fast_bpe(bfv, (const uint8_t *)wt, nb, bs, txt2, wid, &wst) : 0;
-          memo_store_ids(tb, e, m_done, wid, c, wst != 0, mv.unk_id);
+          memo_store_ids(tb, m_done, wid, c, wst != 0 || nb == 0, mv.unk_id);
         }
       }
       if (nw >= 0) {
-        const int32_t c = memo_emit(tb.e, tb.overflow, slots.data(), nw, mv.model_type == M_UNIGRAM, core.data());
-        if (c >= 0) { cnt = c; memo_served = true; st |= 1u << 20; }
-        else st |= 1u << 22;    // a word was not context-free here / not memoisable
+        std::vector<int32_t> mid(len + kFastExtraChars);
+        const int32_t c = memo_emit(tb, slots.data(), nw, mv.model_type == M_UNIGRAM, mid.data(),
+                                    (int32_t)len + kFastExtraChars);
+        if (c >= 0) {
+          cnt = c; memo_served = true; st |= 1u << 20;
+          core.resize(c + 1);
+          memcpy(core.data(), mid.data(), c * sizeof(int32_t));
+        } else {
+          st |= 1u << 22;    // a word was not context-free here / not memoisable
+        }
       } else {
         st |= 1u << 21;         // a word could not be keyed
       }
