@@ -68,7 +68,7 @@ constexpr uint32_t ST_FWD = 1u << 17;   // fast-tier ids were staged in forward 
 
 // device-side counters of one chunk
 enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_WORK_LONG = 4, C_NLONG = 5,
-       C_NVIT = 6, C_WORK_VIT = 7, C_NVITL = 8, C_WORK_VITL = 9, C_NNEW = 10, C_COUNT = 16 };
+       C_NVIT = 6, C_WORK_VIT = 7, C_NVITL = 8, C_WORK_VITL = 9, C_NNEW = 10, C_NSLOW = 11, C_COUNT = 16 };
 // k_publish snapshot (int64 slots): counters | scalars | running id total of chunk k
 constexpr int kPubScal = C_COUNT, kPubTot = C_COUNT + 8;
 
@@ -476,21 +476,19 @@ __device__ __forceinline__ int64_t memo_wslot_base(const int64_t *off, int64_t c
   return ((off[c0 + t] - off[c0]) >> 1) + 4 * t;
 }
 
-// k_memo_scan: one thread per sentence in ORIGINAL order -- the 32 sentences of a warp are
-// one contiguous piece of the text buffer, which the warp copies to shared memory with
-// coalesced 16-byte loads (when it fits) before every lane normalizes its own sentence
-// straight into word keys (fast_normalize_scan + MemoSink): no normalized text is written.
-// nwords[t] = word count, or -1 = the memo cannot serve this sentence.
+// k_memo_scan_plain: one thread per sentence in ORIGINAL order -- the 32 sentences of a warp
+// are one contiguous piece of the text buffer, which the warp copies to shared memory with
+// coalesced 16-byte loads before every lane runs memo_scan_plain() on its own sentence:
+// raw bytes straight into word keys, no normalized text is written.  Sentences of any other
+// shape (or warps whose text does not fit the staging buffer) are listed for k_memo_scan.
+// nwords[t] = word count, -1 = the memo cannot serve this sentence.
 constexpr int kScanWarps = 8, kScanWarpBytes = 5120;
 constexpr int kMemoThreads = 256;
 __global__ void __launch_bounds__(kScanWarps * 32)
-k_memo_scan(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn,
-            const uint8_t *lo, const uint8_t *hi, uint32_t *wslots, int32_t *nwords, int32_t *cnt, uint32_t *status) {
-  __shared__ uint32_t first2[2048];
+k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn,
+                  const uint8_t *lo, const uint8_t *hi, uint32_t *wslots, int32_t *nwords, int32_t *cnt,
+                  uint32_t *status, int32_t *slow_list, uint32_t *counters) {
   __shared__ __align__(16) uint8_t stage[kScanWarps][kScanWarpBytes];
-  if (mv.cm_first2 != nullptr)
-    for (int k = threadIdx.x; k < 2048; k += kScanWarps * 32) first2[k] = mv.cm_first2[k];
-  __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t tw = ((int64_t)blockIdx.x * kScanWarps + wid) * 32;
   if (tw >= cn) return;
@@ -498,9 +496,9 @@ k_memo_scan(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off,
   const int64_t a = off[c0 + tw], b = off[c0 + min(tw + 32, cn)];
   const uint8_t *src = (const uint8_t *)((uintptr_t)(text + a) & ~(uintptr_t)15);
   const int64_t span = (text + b) - src;
-  const bool staged = span <= kScanWarpBytes - 16;
+  const bool staged = span <= kScanWarpBytes - 32 && mv.ascii_plain && mv.escape_ws;
   if (staged) {
-    for (int64_t i = lane * 16; i < span; i += 512) {
+    for (int64_t i = lane * 16; i < span + 16; i += 512) {   // + 16: the loop reads past the last sentence
       const uint8_t *p = src + i;
       uint4 v;
       if (p >= lo && p + 16 <= hi) {
@@ -517,22 +515,37 @@ k_memo_scan(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off,
   if (t >= cn) return;
   const int64_t o0 = off[c0 + t], len = off[c0 + t + 1] - o0;
   int32_t nw = 0;
-  if (len >= kLongMaxRaw) {
-    nw = -1;
-  } else if (len > 0) {
-    MemoSink sink;
-    sink.init(tb, wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4);
-    int32_t nc = 0;
-    bool content = false;
-    const uint8_t *in = staged ? &stage[wid][0] + ((text + o0) - src) : text + o0;
-    const uint8_t *l2 = staged ? &stage[wid][0] : lo;
-    const uint8_t *h2 = staged ? &stage[wid][0] + ((span + 15) & ~(int64_t)15) : hi;
-    fast_normalize_scan(mv, first2, in, len, l2, h2, sink, &nc, &content);
-    nw = sink.finish(mv.remove_extra_ws != 0);
-  }
+  if (len >= kLongMaxRaw) nw = -1;
+  else if (len > 0 && !staged) nw = -2;
+  else if (len > 0)
+    nw = memo_scan_plain(tb, &stage[wid][0] + ((text + o0) - src), (int32_t)len, mv.add_dummy_prefix ? 1 : 0,
+                         wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4);
+  if (nw == -2) slow_list[atomicAdd(&counters[C_NSLOW], 1u)] = (int32_t)t;
   nwords[t] = nw;
   cnt[t] = 0;
   status[t] = 0;
+}
+
+// k_memo_scan: the general scan (fast_normalize_scan + MemoSink: every normalizer rule,
+// user symbols, whitespace policy, long words) over the sentences k_memo_scan_plain listed.
+__global__ void __launch_bounds__(kMemoThreads)
+k_memo_scan(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off, int64_t c0, const uint8_t *lo,
+            const uint8_t *hi, const int32_t *slow_list, uint32_t *wslots, int32_t *nwords,
+            const uint32_t *counters) {
+  __shared__ uint32_t first2[2048];
+  if (mv.cm_first2 != nullptr)
+    for (int k = threadIdx.x; k < 2048; k += kMemoThreads) first2[k] = mv.cm_first2[k];
+  __syncthreads();
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)counters[C_NSLOW]) return;
+  const int64_t t = slow_list[idx];
+  const int64_t o0 = off[c0 + t], len = off[c0 + t + 1] - o0;
+  MemoSink sink;
+  sink.init(tb, wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4);
+  int32_t nc = 0;
+  bool content = false;
+  fast_normalize_scan(mv, first2, text + o0, len, lo, hi, sink, &nc, &content);
+  nwords[t] = sink.finish(mv.remove_extra_ws != 0);
 }
 
 __device__ __forceinline__ FastView memo_cold_view(const FastParams &fp) {
@@ -1430,9 +1443,14 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
         tb.n_new = d_counters + C_NNEW;
         const unsigned gnew = (tb.max_new + 255) / 256;
         if ((rc = kev_record(M, st, 0, T_MEMO_COLLECT))) return rc;
-        k_memo_scan<<<gsent, kScanWarps * 32, 0, st>>>(
+        k_memo_scan_plain<<<gsent, kScanWarps * 32, 0, st>>>(
             M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
-            (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p);
+            (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
+            d_counters);
+        k_memo_scan<<<gsent, kMemoThreads, 0, st>>>(
+            M->mv, tb, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_vit.p,
+            (uint32_t *)M->w_wslots.p, (int32_t *)M->w_nwords.p, d_counters);
+        launches += 1;
         if ((rc = kev_record(M, st, 1))) return rc;
         if ((rc = kev_record(M, st, 0, T_MEMO_WORDS))) return rc;
         if (M->fast_kind == 1) {

@@ -223,6 +223,83 @@ struct MemoSink {
   }
 };
 
+// The common sentence, without the general normalizer: printable ASCII words separated by
+// single spaces, no leading / trailing space (HostModel::ascii_plain: such bytes pass the
+// normalizer untouched; a space becomes U+2581 = the start of the next word).  One loop
+// iteration takes a run of up to 8 word bytes with SWAR and, at a space, keys the word.
+// s[0..n) must be readable in aligned 8-byte words up to 16 bytes past the end.
+// Returns the word count, -1 when the memo cannot serve the sentence, or -2 when the
+// sentence is not of this shape (the general scan, fast_normalize_scan + MemoSink, decides).
+SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n, int prefix0, uint32_t *slots,
+                                int32_t cap) {
+  const uint8_t *q = (const uint8_t *)((uintptr_t)s & ~(uintptr_t)7);
+  int r = (int)(s - q);
+  uint64_t a0 = fast_load8(q), a1 = fast_load8(q + 8);
+  int32_t p = 0, nw = 0;
+  // key bytes of the current word in (c0, c1); pos = where the next byte goes: a head key
+  // fills bytes 0..13, the tail key of a long word bytes 4..13 (after the head's slot)
+  uint64_t c0 = 0, c1 = 0;
+  int pos = 0;
+  bool tail = false;
+  uint64_t prefix = (uint64_t)prefix0;
+  for (;;) {
+    const uint64_t w = fast_window(a0, a1, r);
+    const int32_t rem = n - p;
+    // 0x80 marks bytes < 0x21 or > 0x7E (borrows / carries only disturb bytes above the first mark)
+    const uint64_t np = (((w - 0x2121212121212121ull) & ~w) | ((w + 0x0101010101010101ull) | w)) & 0x8080808080808080ull;
+    int run = np ? (ffs64(np) - 1) >> 3 : 8;
+    bool endw = false;
+    int skip = 0;
+    if (run >= rem) {
+      run = rem; endw = true;                    // the sentence ends inside the window
+    } else if (run == 8) {
+      run = 7;                                   // keep the successor in sight
+    } else {
+      const uint32_t b = (uint32_t)(w >> (8 * run)) & 0xFFu;
+      if (b != 0x20u) return -2;                 // control / non-ASCII: rules may apply
+      endw = true; skip = 1;
+      if (run + 1 >= rem) return -2;             // trailing space
+    }
+    if (run == 0) return -2;                     // leading / repeated space
+    uint64_t wm = w & (0xFFFFFFFFFFFFFFFFull >> (8 * (8 - run)));
+    int k = run;
+    if (pos + k > 14) {                          // a long word: key its head, go on in a tail key
+      if (tail) return -1;                       // longer than kMemoMaxBytes
+      const int h = 14 - pos;
+      if (h > 0) {
+        const uint64_t hm = wm & (0xFFFFFFFFFFFFFFFFull >> (8 * (8 - h)));
+        if (pos < 8) { c0 |= hm << (8 * pos); if (pos + h > 8) c1 |= hm >> (8 * (8 - pos)); }
+        else c1 |= hm << (8 * (pos - 8));
+        wm >>= 8 * h; k -= h;
+      }
+      const uint64_t mb = 0x40ull | prefix;
+      const uint32_t hs = memo_find_or_insert(tb, mb | (c0 << 8), (c0 >> 56) | (c1 << 8) | (mb << 56));
+      if (hs == 0xFFFFFFFFu) return -1;
+      c0 = (uint64_t)hs << 8; c1 = 0; pos = 4; tail = true;
+    }
+    if (pos < 8) { c0 |= wm << (8 * pos); if (pos + k > 8) c1 |= wm >> (8 * (8 - pos)); }
+    else c1 |= wm << (8 * (pos - 8));
+    pos += k;
+    p += run + skip; r += run + skip;
+    if (endw) {
+      uint32_t slot;
+      if (tail) {
+        const uint64_t mb = 0x80ull | (uint64_t)(pos - 4);
+        slot = memo_find_or_insert(tb, c0 | mb, c1 | (mb << 56));
+      } else {
+        const uint64_t mb = ((uint64_t)pos << 1) | prefix;
+        slot = memo_find_or_insert(tb, mb | (c0 << 8), (c0 >> 56) | (c1 << 8) | (mb << 56));
+      }
+      if (slot == 0xFFFFFFFFu || nw >= cap) return -1;
+      slots[nw++] = slot;
+      if (p >= n) break;
+      c0 = 0; c1 = 0; pos = 0; tail = false; prefix = 1;
+    }
+    if (r >= 8) { r -= 8; a0 = a1; q += 8; a1 = fast_load8(q + 8); }
+  }
+  return nw;
+}
+
 // Bytes of the word in slot `slot`: U+2581 prefix (when keyed with one) + content, zero
 // padded to `cap` (>= 40) bytes.  Returns the byte count; 0 for a head entry (not a word).
 SPM_HD int memo_word_bytes(const MemoKey *keys, uint32_t slot, uint8_t *out, int cap) {

@@ -151,12 +151,22 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
     if (use_memo && len > 0) {
       // k_memo_scan: the raw sentence straight into word keys (no normalized text)
       std::vector<uint32_t> slots(len / 2 + 4);
-      MemoSink sink;
-      sink.init(tb, slots.data(), (int32_t)(len / 2 + 4));
-      int32_t nc = 0;
-      bool content = false;
-      fast_normalize_scan(mv, mv.cm_first2, text + off[i], len, text + off[0], text + off[n], sink, &nc, &content);
-      const int32_t nw = sink.finish(mv.remove_extra_ws != 0);
+      int32_t nw = -2;
+      if (mv.ascii_plain && mv.escape_ws && len < kLongMaxRaw) {   // k_memo_scan_plain
+        std::vector<uint64_t> pbuf(len / 8 + 5, 0x2020202020202020ull);   // what follows must not matter
+        uint8_t *ps = (uint8_t *)pbuf.data() + (i % 8);                    // any alignment
+        memcpy(ps, text + off[i], len);
+        nw = memo_scan_plain(tb, ps, (int32_t)len, mv.add_dummy_prefix ? 1 : 0, slots.data(), (int32_t)(len / 2 + 4));
+        if (nw != -2) st |= 1u << 23;
+      }
+      if (nw == -2) {                                                  // k_memo_scan
+        MemoSink sink;
+        sink.init(tb, slots.data(), (int32_t)(len / 2 + 4));
+        int32_t nc = 0;
+        bool content = false;
+        fast_normalize_scan(mv, mv.cm_first2, text + off[i], len, text + off[0], text + off[n], sink, &nc, &content);
+        nw = sink.finish(mv.remove_extra_ws != 0);
+      }
       for (; m_done < m_n_new && m_done < tb.max_new; ++m_done) {   // the "words" kernels
         if (mv.model_type == M_UNIGRAM) {
           memo_unigram_word(mfv, h->hm.neg_only, tb, m_done);

@@ -135,6 +135,9 @@ def test_word_memo_serves_and_matches(make_hostcore, corpora):
         assert np.array_equal(go, wo) and np.array_equal(gi, wi), (model, corpus)
         served = float(((st >> 20) & 1).mean())
         assert served >= lo, (model, corpus, served)
+        plain = float(((st >> 23) & 1).mean())     # sentences keyed by memo_scan_plain
+        if corpus == "syn_en":
+            assert plain >= 0.9, (model, plain)
 
 
 def test_loader_rejects_bad_models(hostcore):
