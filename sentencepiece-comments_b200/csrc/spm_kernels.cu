@@ -1337,9 +1337,16 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   struct Chunk { int64_t c0, c1, o0, o1; };
   std::vector<Chunk> chunks;
   {
-    // host-memory calls of some size are cut into ~8 chunks so copies and kernels pipeline
+    // host-memory calls of some size are cut into 8 chunks so that copy-in, kernels and
+    // copy-out pipeline.  (More chunks shorten the un-overlapped tail but every chunk pays the
+    // fixed latency of the leftover tiers -- a few hundred rare-word sentences walk cold trie
+    // paths -- and 16 chunks measured slower than 8: profiles/r1_v5_summary.md.)
     int64_t want = kMaxChunk;
-    if (host && n >= (1 << 20)) want = std::min(kMaxChunk, (n + 7) / 8);
+    if (host && n >= (1 << 20)) {
+      static const char *env_chunks = getenv("SPM_CUDA_HOST_CHUNKS");   // tuning experiments only
+      const int64_t parts = std::max<int64_t>(1, std::min<int64_t>(64, env_chunks ? atoll(env_chunks) : 8));
+      want = std::min(kMaxChunk, (n + parts - 1) / parts);
+    }
     int64_t c0 = 0, off_c0 = text_lo;
     while (c0 < n) {
       int64_t c1 = std::min(n, c0 + want), off_c1 = 0;
