@@ -101,6 +101,30 @@ int spm_cuda_last_stats(const spm_cuda_model *model, double *stats, int n);
 
 const char *spm_cuda_last_error(void);
 
+/* ---- Unigram-trainer E-step (optional kernel) ----------------
+ * Replaces the per-thread loop of unigram::Trainer::RunEStep
+ * (src/unigram_model_trainer.cc:237-287): for every (word, freq) build the lattice of a
+ * TrainerModel over the given pieces (all NORMAL, unk id 0, UNK score = min score - 10;
+ * src/unigram_model_trainer.cc:97-119), Lattice::PopulateMarginal
+ * (src/unigram_model.cc:272-328) and the Viterbi token count.
+ *
+ * pieces: V NUL-terminated strings back to back; scores[V].
+ * words:  UTF-8 bytes of the n words, word i = [word_offsets[i], word_offsets[i+1]);
+ *         freq[i] > 0.  all_freq = the sum of freq over ALL shards (divisor of obj).
+ * expected[V] (double) += freq * marginal of every node, by piece id;
+ * obj_ntokens[0] -= sum freq * logZ / all_freq;  obj_ntokens[1] += Viterbi tokens.
+ * Both are ACCUMULATED into (the caller zeroes them; a sharded run sums them over the
+ * ranks with one all-reduce).  logz (optional, may be NULL): per-word log-likelihood.
+ * Results agree with the reference to 1e-5 relative (double accumulation here, float
+ * in the reference). */
+typedef struct spm_cuda_estep spm_cuda_estep;
+int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int device, spm_cuda_estep **out);
+void spm_cuda_estep_free(spm_cuda_estep *estep);
+int spm_cuda_estep_vocab_size(const spm_cuda_estep *estep);
+int spm_cuda_estep_run(const spm_cuda_estep *estep, const char *words, const int64_t *word_offsets,
+                       const int64_t *freq, int64_t n, double all_freq, double *expected, double *obj_ntokens,
+                       float *logz, int memory_space, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,6 +43,10 @@ def lib():
                                     ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
         if hasattr(L, "ref_train"):
             L.ref_train.argtypes = [ctypes.c_char_p]
+        if hasattr(L, "ref_estep"):
+            L.ref_estep.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p,
+                                    ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p,
+                                    ctypes.c_void_p, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -125,3 +129,25 @@ def train(args):
     rc = lib().ref_train(args.encode())
     if rc:
         raise RuntimeError("reference spm_train failed: %s" % lib().ref_last_error().decode())
+
+
+def estep(pieces, scores, words, freq):
+    """Reference E-step (TrainerModel + Lattice::PopulateMarginal + Viterbi count, the loop of
+    Trainer::RunEStep, src/unigram_model_trainer.cc:256-267) over (word, freq) pairs.
+    pieces / words: lists of bytes without NUL.  Returns (expected f32[V], logz f32[n], obj, ntokens)."""
+    L = lib()
+    if not hasattr(L, "ref_estep"):
+        raise RuntimeError("reference library was built without the trainer")
+    scores = np.ascontiguousarray(scores, dtype=np.float32)
+    freq = np.ascontiguousarray(freq, dtype=np.int64)
+    pb = b"".join(p + b"\0" for p in pieces)
+    wb = b"".join(w + b"\0" for w in words)
+    expected = np.zeros(len(pieces), dtype=np.float32)
+    logz = np.zeros(len(words), dtype=np.float32)
+    obj = ctypes.c_double(0)
+    nt = ctypes.c_int64(0)
+    rc = L.ref_estep(pb, scores.ctypes.data, len(pieces), wb, freq.ctypes.data, len(words),
+                     expected.ctypes.data, logz.ctypes.data, ctypes.byref(obj), ctypes.byref(nt))
+    if rc:
+        raise RuntimeError("ref_estep failed")
+    return expected, logz, obj.value, nt.value

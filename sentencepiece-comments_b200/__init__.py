@@ -50,6 +50,10 @@ def lib():
         L.spm_cuda_model_check_extra_options.argtypes = [vp, ctypes.c_uint32]
         L.spm_cuda_last_stats.argtypes = [vp, vp, i32]
         L.spm_cuda_last_error.restype = ctypes.c_char_p
+        L.spm_cuda_estep_create.argtypes = [ctypes.c_char_p, vp, i32, i32, ctypes.POINTER(vp)]
+        L.spm_cuda_estep_free.argtypes = [vp]
+        L.spm_cuda_estep_vocab_size.argtypes = [vp]
+        L.spm_cuda_estep_run.argtypes = [vp, vp, vp, vp, i64, ctypes.c_double, vp, vp, vp, i32, vp]
         _lib = L
     return _lib
 
@@ -284,3 +288,62 @@ class SentencePieceProcessor:
     piece_to_id = PieceToId
     id_to_piece = IdToPiece
     __len__ = GetPieceSize
+
+
+class UnigramEStep:
+    """The E-step of the unigram trainer on one GPU (include/spm_cuda.h, spm_cuda_estep_*):
+    what the worker threads of unigram::Trainer::RunEStep compute
+    (src/unigram_model_trainer.cc:237-287) for the (word, freq) pairs given to run().
+    The sum over threads that the reference does serially (:274-280) is, across GPUs, one
+    all-reduce of the packed [expected | obj | ntokens] vector: sharding.allreduce_estep()."""
+
+    def __init__(self, pieces, scores, device=0):
+        import numpy as np
+        self._h = None
+        self._np = np
+        ps = [p if isinstance(p, bytes) else p.encode("utf-8") for p in pieces]
+        if any(b"\0" in p for p in ps):
+            raise StatusError(3, "piece contains NUL")
+        sc = np.ascontiguousarray(scores, dtype=np.float32)
+        if len(sc) != len(ps):
+            raise StatusError(3, "pieces and scores differ in length")
+        blob = b"".join(p + b"\0" for p in ps)
+        h = ctypes.c_void_p()
+        _check(lib().spm_cuda_estep_create(blob, sc.ctypes.data, len(ps), device, ctypes.byref(h)))
+        self._h = h
+        self.vocab_size = len(ps)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().spm_cuda_estep_free(self._h)
+            self._h = None
+
+    def run(self, words, offsets, freq, all_freq=None, want_logz=False, stream=None):
+        """words: uint8 array (all words back to back), offsets int64[n+1], freq int64[n] (host
+        numpy arrays).  all_freq: sum of freq over ALL shards (default: this shard's).
+        Returns (expected float64[V], obj, ntokens[, logz float32[n]])."""
+        np = self._np
+        words = np.ascontiguousarray(words, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        freq = np.ascontiguousarray(freq, dtype=np.int64)
+        n = len(offsets) - 1
+        if len(freq) != n:
+            raise StatusError(3, "freq and offsets differ in length")
+        if all_freq is None:
+            all_freq = float(freq.sum())
+        expected = np.zeros(self.vocab_size, dtype=np.float64)
+        out = np.zeros(2, dtype=np.float64)
+        logz = np.zeros(max(n, 1), dtype=np.float32) if want_logz else None
+        _check(lib().spm_cuda_estep_run(self._h, words.ctypes.data, offsets.ctypes.data, freq.ctypes.data, n,
+                                        float(all_freq), expected.ctypes.data, out.ctypes.data,
+                                        logz.ctypes.data if want_logz else None, SPM_CUDA_HOST, stream))
+        res = (expected, float(out[0]), int(round(out[1])))
+        return res + (logz[:n],) if want_logz else res
+
+    def run_device(self, words, offsets, freq, all_freq, expected, obj_ntokens, stream=None):
+        """Device-resident variant: torch CUDA tensors (uint8, int64, int64, float64[V], float64[2]);
+        expected / obj_ntokens are accumulated into."""
+        n = offsets.numel() - 1
+        _check(lib().spm_cuda_estep_run(self._h, words.data_ptr(), offsets.data_ptr(), freq.data_ptr(), n,
+                                        float(all_freq), expected.data_ptr(), obj_ntokens.data_ptr(), None,
+                                        SPM_CUDA_DEVICE, stream))

@@ -1,0 +1,103 @@
+// spm_estep.cuh -- the E-step of the unigram trainer for one word:
+// Lattice::PopulateMarginal (src/unigram_model.cc:272-328) + the Viterbi token
+// count of Trainer::RunEStep (src/unigram_model_trainer.cc:256-267), without
+// building a lattice.
+//
+// The reference keeps alpha / beta per NODE, but alpha[r] only depends on the
+// position r begins at and beta[l] on the position l ends at:
+//   A[e] = LSE over nodes (b -> e), in end_nodes_[e] order (ascending b), of score + A[b]
+//   B[b] = LSE over nodes (b -> e), in begin_nodes_[b] order (ascending length,
+//          the UNK node last), of score + B[e]
+//   Z = A[len];  expected[id] += freq * exp(A[b] + score + B[e] - Z)
+// with LogSumExp exactly as src/unigram_model.cc:51-63 ("init on the first element";
+// vmax when the gap exceeds 50; else vmax + log(exp(vmin - vmax) + 1.0) in double,
+// rounded to float).  An accumulator that starts at -inf reproduces "init on the first
+// element" (the gap test returns the first element unchanged).
+// Positions are BYTE offsets of character boundaries (pieces and text are valid UTF-8).
+// The lattice of a TrainerModel: every piece is NORMAL, unk_id_ = 0, UNK score =
+// min_score_ - 10 (src/unigram_model_trainer.cc:97-119).
+// `__host__ __device__`: tests/host_core.cc runs the same code against ref_estep.
+#pragma once
+#include <math.h>
+
+#include "spm_core.cuh"
+
+namespace spmb {
+
+struct EstepView {
+  const uint32_t *units;   // XDA of all pieces (spm_model.cc build_xda)
+  const uint2 *leaf;       // node -> (piece id, score bits)
+  float unk_score;         // min score - 10
+  int32_t unk_id;          // 0
+};
+
+SPM_HD float estep_lse(float x, float y) {
+  const float vmin = x < y ? x : y, vmax = x < y ? y : x;
+  if (vmax > vmin + 50.0f) return vmax;
+  return (float)((double)vmax + log(exp((double)(vmin - vmax)) + 1.0));
+}
+
+// Walks the pieces that start at byte b of w[0..n).  f(e, id, score) is called for every
+// node in begin_nodes_ order (ascending length; the one-character UNK node last when no
+// piece covers exactly the first character, src/unigram_model.cc:582-602).
+template <class F>
+SPM_HD void estep_nodes_from(const EstepView &ev, const uint8_t *w, int n, int b, F f) {
+  int cl = one_char_len(w[b]);
+  if (cl > n - b) cl = n - b;
+  uint32_t u = ev.units[0];
+  bool single = false;
+  for (int j = b; j < n; ++j) {
+    const uint32_t c = w[j];
+    if (!(u & 0x200u)) break;
+    const uint32_t child = (u >> 10) ^ c;
+    const uint32_t v = ev.units[child];
+    if ((v & 0xFFu) != c || (v & 0x300u) == 0) break;
+    u = v;
+    if (v & 0x100u) {
+      const uint2 lf = ev.leaf[child];
+      if (j + 1 - b == cl) single = true;
+      f(j + 1, (int32_t)(lf.x & 0x0FFFFFFFu), __uint_as_float_hd(lf.y));
+    }
+  }
+  if (!single) f(b + cl, ev.unk_id, ev.unk_score);
+}
+
+// One word.  A, B, V: float scratch of n + 1 entries each, C: int32 scratch of n + 1.
+// expected[id] receives freq * marginal through add(id, value).  Returns Z (log-likelihood
+// of the word, float as in the reference); *ntokens = length of the Viterbi path.
+template <class Add>
+SPM_HDN float estep_word(const EstepView &ev, const uint8_t *w, int n, float freq, float *A, float *B, float *V,
+                         int32_t *C, Add add, int32_t *ntokens) {
+  const float NINF = -INFINITY;
+  for (int k = 0; k <= n; ++k) { A[k] = NINF; B[k] = NINF; V[k] = NINF; C[k] = 0; }
+  A[0] = 0.0f; V[0] = 0.0f;
+  // forward: alpha and the Viterbi count (first strictly greater wins, src/unigram_model.cc:229-246)
+  for (int b = 0; b < n;) {
+    const float ab = A[b], vb = V[b];
+    const int32_t cb = C[b];
+    estep_nodes_from(ev, w, n, b, [&](int e, int32_t, float sc) {
+      A[e] = estep_lse(A[e], sc + ab);
+      const float cand = vb + sc;
+      if (cand > V[e]) { V[e] = cand; C[e] = cb + 1; }
+    });
+    int cl = one_char_len(w[b]);
+    b += cl > n - b ? n - b : cl;
+  }
+  const float Z = A[n];
+  *ntokens = C[n];
+  // backward: beta, and the expected counts of the nodes that begin at b
+  B[n] = 0.0f;
+  for (int b = n - 1; b >= 0; --b) {
+    if (b > 0 && (w[b] & 0xC0u) == 0x80u) continue;   // not a character boundary
+    float acc = NINF;
+    const float ab = A[b];
+    estep_nodes_from(ev, w, n, b, [&](int e, int32_t id, float sc) {
+      acc = estep_lse(acc, sc + B[e]);
+      add(id, (double)freq * exp((double)(ab + sc + B[e] - Z)));
+    });
+    B[b] = acc;
+  }
+  return Z;
+}
+
+}  // namespace spmb

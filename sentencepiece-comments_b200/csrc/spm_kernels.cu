@@ -2,28 +2,35 @@
 //
 // One spm_cuda_encode_batch call is cut into chunks of sentences; per chunk
 // (sentences are independent units; nothing here is GEMM-shaped, the work is
-// byte / trie / scan traffic):
+// byte / trie / hash / scan traffic).  A sentence is finished by the first tier
+// that can prove its result exact:
 //
-//   FAST TIER (unigram models)
-//   k_normalize_fast  charsmap leftmost-longest rewrite + whitespace policy into a
-//                     padded, aligned per-sentence slot; length histogram
+//   TIER 1, WORD MEMO (spm_memo.cuh; models without U+2581 inside pieces)
+//   k_memo_scan_plain  raw text staged through shared memory, printable-ASCII
+//                      words keyed with SWAR runs; other sentences are listed
+//   k_memo_scan        general normalizer writing word keys for the listed ones
 //                                                     (src/normalizer.cc:88-300)
-//   k_binscan/k_scatter  counting sort of the sentences by character count
-//                     (descending), so the 32 lanes of a warp walk sentences of
-//                     equal length in lock step
-//   k_encode_fast     persistent CTAs, one thread per sentence: trie walk + Viterbi
-//                     with the hot trie prefix, the DP ring and the text window in
-//                     shared memory / registers (spm_fast.cuh;
-//                     src/unigram_model.cc:535-604,222-261)
-//   GENERAL TIER (BPE models; unigram sentences the fast tier flags: near-tied
-//                 Viterbi candidates, heavy expansion, >= kFastMaxRaw bytes)
-//   k_gen_normalize / k_gen_encode  one thread per listed sentence, exact candidate
-//                     lists / BPE agenda in global scratch (spm_core.cuh;
-//                     src/bpe_model.cc:37-199)
-//   BOTH
-//   k_scan_*          exclusive scans (scratch offsets, CSR offsets)
-//   k_compact         one warp per sentence: extra options + CSR write
-//                     (src/sentencepiece_processor.cc:319-330,945-979)
+//   k_memo_words_*     every NEW word once: stand-alone Viterbi with margin
+//                      bookkeeping / BPE merges of the word
+//   k_memo_emit        tile per sentence, lane per word: copy the ids, carry the
+//                      bound of the backtrace score; leftovers are listed
+//   TIER 2, VITERBI / MERGE KERNELS over the leftovers (all sentences without memo)
+//   k_hist/k_binscan/k_scatter  counting sort by raw length (descending)
+//   k_normalize_fast   normalized text into a padded, aligned per-sentence slot
+//   k_encode_fast      persistent CTAs, one thread per sentence: trie walk + Viterbi
+//                      with the hot trie prefix, the DP ring and the text window in
+//                      shared memory / registers (spm_fast.cuh;
+//                      src/unigram_model.cc:535-604,222-261)
+//   k_encode_bpe_fast  word-wise exact merges (src/bpe_model.cc:37-199)
+//   TIER 3, GENERAL TIER (what tier 2 flags: near-tied Viterbi candidates, heavy
+//                 expansion, lines >= 64 KiB; every sentence of other models)
+//   k_gen_normalize / k_gen_encode(_block)  exact candidate lists / BPE agenda in
+//                      global or shared scratch (spm_core.cuh)
+//   ALL
+//   k_validate         offsets checked on the device
+//   k_scan_*           exclusive scans (scratch offsets, CSR offsets)
+//   k_compact          extra options + CSR write
+//                      (src/sentencepiece_processor.cc:319-330,945-979)
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -31,6 +38,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -39,6 +47,7 @@
 #include "spm_core.cuh"
 #include "spm_fast.cuh"
 #include "spm_memo.cuh"
+#include "spm_estep.cuh"
 #include "spm_model.h"
 
 using namespace spmb;
@@ -821,6 +830,52 @@ k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0
       for (int32_t q = lane; q < fc; q += 32)
         if (dst + q < capacity) ids[dst + q] = final_id_at(pl, src, core, q);
     }
+  }
+}
+
+// ---------------------------------------------------------------- unigram trainer E-step (spm_estep.cuh)
+// One thread per word.  Words of up to kEstepLocalBytes bytes keep their forward /
+// backward tables in local memory; longer ones (text without spaces) use a slice of a
+// global scratch buffer.  expected[] is accumulated in double with atomicAdd; the
+// log-likelihood and the token count are reduced per warp first.
+constexpr int kEstepLocalBytes = 47, kEstepThreads = 128;
+__global__ void __launch_bounds__(kEstepThreads)
+k_estep(EstepView ev, const uint8_t *words, const int64_t *off, const int64_t *freq, int64_t n, double inv_all_freq,
+        float *scratch, double *expected, double *obj_ntok, float *logz, uint32_t *bad) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double obj = 0.0, ntok = 0.0;
+  if (i < n) {
+    const int64_t o = off[i], len = off[i + 1] - o;
+    float z = 0.0f;
+    int32_t nt = 0;
+    if (len > 0 && len < (1 << 20)) {
+      const float f = (float)freq[i];       // PopulateMarginal takes float freq (src/unigram_model.cc:272)
+      auto add = [&](int32_t id, double v) { atomicAdd(&expected[id], v); };
+      if (len <= kEstepLocalBytes) {
+        float A[kEstepLocalBytes + 1], B[kEstepLocalBytes + 1], V[kEstepLocalBytes + 1];
+        int32_t C[kEstepLocalBytes + 1];
+        z = estep_word(ev, words + o, (int)len, f, A, B, V, C, add, &nt);
+      } else {
+        float *base = scratch + 4 * ((o - off[0]) + i);
+        z = estep_word(ev, words + o, (int)len, f, base, base + (len + 1), base + 2 * (len + 1),
+                       (int32_t *)(base + 3 * (len + 1)), add, &nt);
+      }
+      // objs[n] -= Z / all_sentence_freq with Z = freq * log-likelihood (:262-266)
+      obj = -(double)(f * z) * inv_all_freq;
+      ntok = (double)nt;
+    } else if (len != 0) {
+      atomicOr(bad, 1u);
+    }
+    if (logz) logz[i] = z;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    obj += __shfl_xor_sync(0xFFFFFFFFu, obj, d);
+    ntok += __shfl_xor_sync(0xFFFFFFFFu, ntok, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&obj_ntok[0], obj);
+    atomicAdd(&obj_ntok[1], ntok);
   }
 }
 
@@ -1614,6 +1669,125 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     g_err = "all normalized characters are not consumed.";  // src/sentencepiece_processor.cc:543
     return kInternal;
   }
+  return kOk;
+}
+
+// ---------------------------------------------------------------- E-step C ABI
+struct spm_cuda_estep {
+  int device = 0;
+  int V = 0;
+  EstepView ev;
+  DevBuf d_units, d_leaf;
+  mutable std::mutex mu;
+  mutable DevBuf w_words, w_off, w_freq, w_scratch, w_expected, w_out, w_logz;
+};
+
+int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int device, spm_cuda_estep **out) {
+  if (out == nullptr) { g_err = "output container is null"; return kInternal; }
+  *out = nullptr;
+  if (pieces == nullptr || scores == nullptr || V <= 0) { g_err = "no pieces are loaded."; return kInvalidArgument; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+    g_err = "no CUDA device available (this library has no CPU path)";
+    return kInternal;
+  }
+  if (device < 0 || device >= ndev) { g_err = "invalid device ordinal"; return kInvalidArgument; }
+  std::vector<std::string> ps;
+  std::vector<float> sc(scores, scores + V);
+  const char *q = pieces;
+  for (int i = 0; i < V; ++i) { ps.emplace_back(q); q += ps.back().size() + 1; }
+  HostTrie trie;
+  float min_score = 0;
+  int rc = build_estep_trie(ps, sc, &trie, &min_score, &g_err);
+  if (rc) return rc;
+  std::unique_ptr<spm_cuda_estep> E(new spm_cuda_estep);
+  E->device = device;
+  E->V = V;
+  CUDA_TRY(cudaSetDevice(device));
+  if ((rc = upload(&E->d_units, trie.units.data(), trie.units.size() * 4))) return rc;
+  if ((rc = upload(&E->d_leaf, trie.leaf.data(), trie.leaf.size() * 8))) return rc;
+  E->ev.units = (const uint32_t *)E->d_units.p;
+  E->ev.leaf = (const uint2 *)E->d_leaf.p;
+  E->ev.unk_score = min_score - 10.0f;   // kUnkPenalty, src/unigram_model.cc:550-551
+  E->ev.unk_id = 0;                      // TrainerModel never calls InitializePieces
+  *out = E.release();
+  return kOk;
+}
+
+void spm_cuda_estep_free(spm_cuda_estep *E) {
+  if (!E) return;
+  cudaSetDevice(E->device);
+  for (DevBuf *b : {&E->d_units, &E->d_leaf, &E->w_words, &E->w_off, &E->w_freq, &E->w_scratch, &E->w_expected,
+                    &E->w_out, &E->w_logz})
+    b->release();
+  delete E;
+}
+
+int spm_cuda_estep_vocab_size(const spm_cuda_estep *E) { return E ? E->V : 0; }
+
+int spm_cuda_estep_run(const spm_cuda_estep *E, const char *words, const int64_t *word_offsets, const int64_t *freq,
+                       int64_t n, double all_freq, double *expected, double *obj_ntokens, float *logz,
+                       int memory_space, void *cuda_stream) {
+  if (!E) { g_err = "E-step handle is null"; return kInvalidArgument; }
+  if (n < 0 || (n > 0 && (!words || !word_offsets || !freq)) || !expected || !obj_ntokens || !(all_freq > 0)) {
+    g_err = "invalid argument";
+    return kInvalidArgument;
+  }
+  std::lock_guard<std::mutex> lk(E->mu);
+  CUDA_TRY(cudaSetDevice(E->device));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  const bool host = memory_space == SPM_CUDA_HOST;
+  int rc;
+  const uint8_t *d_words = (const uint8_t *)words;
+  const int64_t *d_off = word_offsets, *d_freq = freq;
+  double *d_exp = expected, *d_out = obj_ntokens;
+  float *d_logz = logz;
+  int64_t lo = 0, hi = 0;
+  if (n > 0) {
+    if (host) { lo = word_offsets[0]; hi = word_offsets[n]; }
+    else {
+      CUDA_TRY(cudaMemcpyAsync(&lo, word_offsets, 8, cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaMemcpyAsync(&hi, word_offsets + n, 8, cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    if (hi < lo) { g_err = "word_offsets must be non-decreasing"; return kInvalidArgument; }
+  }
+  if ((rc = E->w_out.ensure(32))) return rc;
+  uint32_t *d_bad = (uint32_t *)((double *)E->w_out.p + 2);
+  if (host) {
+    if ((rc = E->w_words.ensure((size_t)(hi - lo) + 16))) return rc;
+    if ((rc = E->w_off.ensure((size_t)(n + 1) * 8))) return rc;
+    if ((rc = E->w_freq.ensure((size_t)(n + 1) * 8))) return rc;
+    if ((rc = E->w_expected.ensure((size_t)E->V * 8))) return rc;
+    if (logz && (rc = E->w_logz.ensure((size_t)(n + 1) * 4))) return rc;
+    if (n > 0) {
+      CUDA_TRY(cudaMemcpyAsync(E->w_words.p, words + lo, hi - lo, cudaMemcpyHostToDevice, st));
+      CUDA_TRY(cudaMemcpyAsync(E->w_off.p, word_offsets, (n + 1) * 8, cudaMemcpyHostToDevice, st));
+      CUDA_TRY(cudaMemcpyAsync(E->w_freq.p, freq, n * 8, cudaMemcpyHostToDevice, st));
+    }
+    CUDA_TRY(cudaMemcpyAsync(E->w_expected.p, expected, (size_t)E->V * 8, cudaMemcpyHostToDevice, st));
+    d_words = (const uint8_t *)E->w_words.p - lo;
+    d_off = (const int64_t *)E->w_off.p; d_freq = (const int64_t *)E->w_freq.p;
+    d_exp = (double *)E->w_expected.p; d_out = (double *)E->w_out.p;
+    d_logz = logz ? (float *)E->w_logz.p : nullptr;
+    CUDA_TRY(cudaMemcpyAsync(d_out, obj_ntokens, 16, cudaMemcpyHostToDevice, st));
+  }
+  CUDA_TRY(cudaMemsetAsync(d_bad, 0, 4, st));
+  if (n > 0) {
+    if ((rc = E->w_scratch.ensure((size_t)(4 * ((hi - lo) + n) + 16) * 4))) return rc;
+    k_estep<<<(unsigned)((n + kEstepThreads - 1) / kEstepThreads), kEstepThreads, 0, st>>>(
+        E->ev, d_words, d_off, d_freq, n, 1.0 / all_freq, (float *)E->w_scratch.p, d_exp, d_out, d_logz, d_bad);
+    CUDA_TRY(cudaGetLastError());
+  }
+  uint32_t bad = 0;
+  CUDA_TRY(cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, st));
+  if (host) {
+    CUDA_TRY(cudaMemcpyAsync(expected, d_exp, (size_t)E->V * 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(obj_ntokens, d_out, 16, cudaMemcpyDeviceToHost, st));
+    if (logz && n > 0) CUDA_TRY(cudaMemcpyAsync(logz, d_logz, n * 4, cudaMemcpyDeviceToHost, st));
+  }
+  CUDA_TRY(cudaStreamSynchronize(st));
+  if (bad) { g_err = "word longer than 1 MiB"; return kOutOfRange; }
   return kOk;
 }
 

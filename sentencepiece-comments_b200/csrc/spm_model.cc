@@ -262,6 +262,24 @@ void scan_charsmap(HostModel *m) {
 
 }  // namespace
 
+int build_estep_trie(const std::vector<std::string> &pieces, const std::vector<float> &scores, HostTrie *out,
+                     float *min_score, std::string *err) {
+  if (pieces.empty() || pieces.size() != scores.size()) { *err = "no pieces are loaded."; return kInternal; }
+  if (pieces.size() >= (1u << 28)) { *err = "vocabulary too large"; return kUnimplemented; }
+  std::vector<Key> keys;
+  std::map<std::string, int> seen;
+  float mn = FLT_MAX;
+  for (size_t i = 0; i < pieces.size(); ++i) {
+    if (pieces[i].empty()) { *err = "piece must not be empty."; return kInternal; }
+    if (!seen.emplace(pieces[i], (int)i).second) { *err = pieces[i] + " is already defined."; return kInternal; }
+    mn = std::min(mn, scores[i]);
+    keys.push_back(Key{pieces[i], (uint32_t)i | ((uint32_t)T_NORMAL << 28), f2u(scores[i]), exp((double)scores[i])});
+  }
+  *min_score = mn;
+  if (!build_xda(keys, out, err)) return kUnimplemented;
+  return kOk;
+}
+
 int piece_to_id(const HostModel &m, const std::string &piece) {
   // reserved_id_map_ and pieces_ are disjoint key sets over all pieces, so a
   // linear probe by string is the same lookup; only used at option-parse time.

@@ -68,6 +68,12 @@ int build_host_model(const void *data, size_t len, HostModel *m);
 // src/sentencepiece_processor.cc:203-231; min/max scores stay as loaded).
 void refresh_leaf_types(HostModel *m);
 
+// Piece trie of a TrainerModel for the E-step (src/unigram_model_trainer.cc:97-119: every
+// piece NORMAL, ids = positions, trie over all of them).  leaf = (id, score bits).
+// *min_score = min over the scores.  Returns a StatusCode and fills *err.
+int build_estep_trie(const std::vector<std::string> &pieces, const std::vector<float> &scores, HostTrie *out,
+                     float *min_score, std::string *err);
+
 // id of a piece by string as ModelInterface::PieceToId (model_interface.cc:87-97)
 int piece_to_id(const HostModel &m, const std::string &piece);
 

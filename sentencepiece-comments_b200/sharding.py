@@ -49,3 +49,32 @@ def global_id_offsets(local_id_offsets, group=None):
     counts = [int(c.item()) for c in allc]
     base = sum(counts[:rank])
     return np.asarray(local_id_offsets, dtype=np.int64) + base, sum(counts)
+
+
+def estep_shard_ranges(offsets, freq, world):
+    """Contiguous (word, freq) ranges balanced by BYTES: the E-step visits every word once
+    whatever its frequency, so the cost of a word is its length; cuts at
+    k * total_bytes / world."""
+    return shard_ranges(offsets, world)
+
+
+def allreduce_estep(expected, obj, ntokens, group=None):
+    """The only exchange step of the path: the serial merge of the per-thread
+    accumulators in Trainer::RunEStep (src/unigram_model_trainer.cc:274-280) becomes ONE
+    all-reduce(sum) of the packed vector [expected[V] | obj | ntokens] (float64).
+    expected: numpy float64[V] (host) or a torch tensor; returns (expected, obj, ntokens)
+    summed over the ranks, in the same container type."""
+    import torch
+    import torch.distributed as dist
+    is_np = isinstance(expected, np.ndarray)
+    e = torch.from_numpy(expected) if is_np else expected
+    backend = dist.get_backend(group)
+    dev = e.device if not is_np else torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else e.device
+    packed = torch.empty(e.numel() + 2, dtype=torch.float64, device=dev)
+    packed[:-2] = e.to(dev)
+    packed[-2] = float(obj)
+    packed[-1] = float(ntokens)
+    dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+    out = packed[:-2]
+    res = out.cpu().numpy() if is_np else out
+    return res, float(packed[-2].item()), int(round(float(packed[-1].item())))

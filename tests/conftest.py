@@ -68,7 +68,7 @@ def hostcore():
     """tests/host_core.cc: the kernels' __host__ __device__ core compiled for the CPU (test-only)."""
     csrc = os.path.join(ROOT, "sentencepiece-comments_b200", "csrc")
     srcs = [os.path.join(ROOT, "tests", "host_core.cc"), os.path.join(csrc, "spm_model.cc")]
-    deps = srcs + [os.path.join(csrc, "spm_core.cuh"), os.path.join(csrc, "spm_fast.cuh"), os.path.join(csrc, "spm_memo.cuh"),
+    deps = srcs + [os.path.join(csrc, "spm_core.cuh"), os.path.join(csrc, "spm_fast.cuh"), os.path.join(csrc, "spm_memo.cuh"), os.path.join(csrc, "spm_estep.cuh"),
                    os.path.join(csrc, "spm_model.h")]
     out = os.path.join(ROOT, "tests", "_build", "libspm_hostcore.so")
     _build_lib(deps, out, ["-I", csrc] + srcs)
@@ -87,6 +87,9 @@ def hostcore():
     L.hc_encode_batch.argtypes = [ctypes.c_void_p] * 3 + [ctypes.c_int64, ctypes.c_uint32, ctypes.c_int,
                                                          ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p,
                                                          ctypes.c_void_p]
+    L.hc_estep.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                           ctypes.c_void_p, ctypes.c_int64, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p,
+                           ctypes.c_void_p]
     return L
 
 

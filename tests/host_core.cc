@@ -8,11 +8,13 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <string>
 #include <vector>
 
 #include "spm_core.cuh"
 #include "spm_fast.cuh"
 #include "spm_memo.cuh"
+#include "spm_estep.cuh"
 #include "spm_model.h"
 
 using namespace spmb;
@@ -288,6 +290,37 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
     if (id_off[i] + fc > cap) return 8;
     for (int32_t j = 0; j < fc; ++j) ids[id_off[i] + j] = final_id_at(plan, core.data(), cnt, j);
     id_off[i + 1] = id_off[i] + fc;
+  }
+  return 0;
+}
+
+// E-step of the unigram trainer: the kernel's per-word function (spm_estep.cuh) on the CPU.
+int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *words, const int64_t *off,
+             const int64_t *freq, int64_t n, double all_freq, double *expected, double *obj_ntok, float *logz) {
+  std::vector<std::string> ps;
+  std::vector<float> sc(scores, scores + V);
+  const char *q = pieces;
+  for (int i = 0; i < V; ++i) { ps.emplace_back(q); q += ps.back().size() + 1; }
+  HostTrie trie;
+  float min_score = 0;
+  std::string err;
+  const int rc = build_estep_trie(ps, sc, &trie, &min_score, &err);
+  if (rc) return rc;
+  EstepView ev;
+  ev.units = trie.units.data(); ev.leaf = trie.leaf.data();
+  ev.unk_score = min_score - 10.0f; ev.unk_id = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const int len = (int)(off[i + 1] - off[i]);
+    if (len == 0) { if (logz) logz[i] = 0; continue; }
+    std::vector<float> A(len + 1), B(len + 1), Vt(len + 1);
+    std::vector<int32_t> C(len + 1);
+    int32_t nt = 0;
+    const float f = (float)freq[i];
+    const float z = estep_word(ev, words + off[i], len, f, A.data(), B.data(), Vt.data(), C.data(),
+                               [&](int32_t id, double v) { expected[id] += v; }, &nt);
+    obj_ntok[0] -= (double)(f * z) / all_freq;
+    obj_ntok[1] += nt;
+    if (logz) logz[i] = z;
   }
   return 0;
 }

@@ -112,3 +112,52 @@ def test_sharded_encode_world2_gloo():
     ids = np.concatenate([g[3] for g in got])
     offs = np.concatenate([got[0][4][:-1], got[1][4]])
     assert np.array_equal(ids, wi) and np.array_equal(offs, wo)
+
+
+def _estep_worker(rank, world, port_no, q):
+    import torch.distributed as dist
+    import spm_b200_pkg
+    from oracle import ref
+    spm_b200_pkg.load()
+    from spm_b200 import sharding
+    import test_estep as te
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port_no, rank=rank, world_size=world)
+    pieces, scores, words, freq = te.trainer_like_case(1500)
+    _, off = te.pack_words(words)
+    lo, hi = sharding.estep_shard_ranges(off, freq, world)[rank]
+    # the CPU stand-in for this rank's GPU E-step (the reference is only the checker here)
+    exp, _, obj, nt = ref.estep(pieces, scores, words[lo:hi], freq[lo:hi])
+    obj *= float(freq[lo:hi].sum()) / float(freq.sum())     # ref_estep divides by ITS sum of freq
+    exp, obj, nt = sharding.allreduce_estep(exp.astype(np.float64), obj, nt)
+    q.put((rank, exp, obj, nt))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_estep_allreduce_world2_gloo():
+    """The one exchange step of the path: expected[V] | obj | ntokens summed over the ranks."""
+    import torch.multiprocessing as mp
+    from oracle import ref
+    import test_estep as te
+    if not ref.available() or not hasattr(ref.lib(), "ref_estep"):
+        pytest.skip("reference library with the trainer is not built")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port_no = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    world = 2
+    procs = [ctx.Process(target=_estep_worker, args=(r, world, port_no, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = sorted([q.get(timeout=300) for _ in range(world)], key=lambda x: x[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    pieces, scores, words, freq = te.trainer_like_case(1500)
+    wexp, _, wobj, wnt = ref.estep(pieces, scores, words, freq)
+    for _, exp, obj, nt in got:
+        assert nt == wnt
+        assert np.allclose(exp, wexp, rtol=1e-4, atol=1e-5)
+        assert abs(obj - wobj) <= 1e-4 * abs(wobj)
+    assert np.array_equal(got[0][1], got[1][1])
