@@ -336,7 +336,7 @@ class UnigramEStep:
         logz = np.zeros(max(n, 1), dtype=np.float32) if want_logz else None
         _check(lib().spm_cuda_estep_run(self._h, words.ctypes.data, offsets.ctypes.data, freq.ctypes.data, n,
                                         float(all_freq), expected.ctypes.data, out.ctypes.data,
-                                        logz.ctypes.data if want_logz else None, SPM_CUDA_HOST, stream))
+                                        logz.ctypes.data if want_logz else None, HOST, stream))
         res = (expected, float(out[0]), int(round(out[1])))
         return res + (logz[:n],) if want_logz else res
 
@@ -346,4 +346,4 @@ class UnigramEStep:
         n = offsets.numel() - 1
         _check(lib().spm_cuda_estep_run(self._h, words.data_ptr(), offsets.data_ptr(), freq.data_ptr(), n,
                                         float(all_freq), expected.data_ptr(), obj_ntokens.data_ptr(), None,
-                                        SPM_CUDA_DEVICE, stream))
+                                        DEVICE, stream))
