@@ -209,6 +209,31 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def bind_to_gpu_numa_node(index):
+    """Run this rank (and first-touch its pinned buffers) on the NUMA node its GPU hangs off:
+    with one process per GPU the e2e leg is bound by host memory / PCIe root-complex traffic."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(index)
+        dom, bus, devn = getattr(p, "pci_domain_id", 0), p.pci_bus_id, p.pci_device_id
+        with open("/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, devn)) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 STAGE_KERNEL = {"encode": "k_encode_fast / k_encode_bpe_fast (general tier kernels for models without a fast tier)",
                 "normalize": "k_normalize_fast", "memo_collect": "k_memo_collect", "memo_words": "k_memo_words_*",
                 "memo_emit": "k_memo_emit", "compact": "k_scan_* + k_compact"}
@@ -227,7 +252,10 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
+    numa = bind_to_gpu_numa_node(local) if world > 1 else None
 
     def barrier():
         if world > 1:
@@ -323,7 +351,8 @@ def run_b200(args):
                 "dtype": "u8 text / int32 ids / f32 scores", "data": "synthetic",
                 "config": {"workload": workload_name(args), "sentences_per_gpu": n, "input_bytes_per_gpu": in_bytes,
                            "ids_per_gpu": n_ids, "l2": "inputs (%.2f GB) larger than L2; no flush" % (in_bytes / 1e9),
-                           "parallelism": "sentence-sharded x%d, no collective" % world},
+                           "parallelism": "sentence-sharded x%d, no collective" % world,
+                           "numa_node_rank0": numa},
                 "input_gb_per_s": bytes_all * args.steps / (ms_all * 1e-3) / 1e9,
                 "ids_per_s": ids_all * args.steps / (ms_all * 1e-3),
                 "general_tier_sentences_per_step": st["fallback_sentences"],
