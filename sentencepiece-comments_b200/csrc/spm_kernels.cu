@@ -511,7 +511,7 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       const uint8_t *p = src + i;
       uint4 v;
       if (p >= lo && p + 16 <= hi) {
-        v = *reinterpret_cast<const uint4 *>(p);
+        v = __ldcs(reinterpret_cast<const uint4 *>(p));      // streamed once: do not displace the memo table in L2
       } else {
         uint8_t tmp[16];
         for (int j = 0; j < 16; ++j) tmp[j] = (p + j >= lo && p + j < hi) ? p[j] : 0;
@@ -648,7 +648,7 @@ k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t c
         float bmax = 3.0e38f, sabs = 0.0f;
         int4 lo4 = make_int4(0, 0, 0, 0), hi4 = make_int4(0, 0, 0, 0);
         if (active) {
-          const int4 *r = reinterpret_cast<const int4 *>(tb.res + sl[w0 + lane]);
+          const int4 *r = reinterpret_cast<const int4 *>(tb.res + __ldcs(sl + w0 + lane));   // slots: streamed
           lo4 = __ldg(r); hi4 = __ldg(r + 1);
           meta = (uint32_t)lo4.x; bmax = __int_as_float(lo4.y); sabs = __int_as_float(lo4.z);
         }
@@ -682,13 +682,13 @@ k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t c
           if (k <= kMemoInlineIds) {
 #pragma unroll
             for (int j = 0; j < kMemoInlineIds; ++j)
-              if (j >= drop && j < k) out[pos + j - drop] = v[j];
+              if (j >= drop && j < k) __stcs(out + pos + j - drop, v[j]);
           } else {
             const int32_t *ov = tb.overflow + (size_t)v[kMemoInlineIds - 1] * kMemoOverflowIds;
 #pragma unroll
             for (int j = 0; j < kMemoInlineIds - 1; ++j)
-              if (j >= drop) out[pos + j - drop] = v[j];
-            for (int j = kMemoInlineIds - 1; j < k; ++j) out[pos + j - drop] = ov[j - (kMemoInlineIds - 1)];
+              if (j >= drop) __stcs(out + pos + j - drop, v[j]);
+            for (int j = kMemoInlineIds - 1; j < k; ++j) __stcs(out + pos + j - drop, ov[j - (kMemoInlineIds - 1)]);
           }
         }
         total += tile_ids;

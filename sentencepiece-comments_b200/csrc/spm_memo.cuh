@@ -70,6 +70,15 @@ struct MemoTable {
   int32_t *overflow;    // max_new rows of kMemoOverflowIds ids
 };
 
+// slot lists are written once and read once: keep them out of the way of the table in L2
+SPM_HD void memo_store_slot(uint32_t *p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
+
 SPM_HD uint32_t memo_hash(uint64_t k0, uint64_t k1) {
   uint64_t h = k0 * 0x9E3779B97F4A7C15ull ^ (k1 + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full;
   h ^= h >> 29;
@@ -291,7 +300,7 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
         slot = memo_find_or_insert(tb, mb | (c0 << 8), (c0 >> 56) | (c1 << 8) | (mb << 56));
       }
       if (slot == 0xFFFFFFFFu || nw >= cap) return -1;
-      slots[nw++] = slot;
+      memo_store_slot(slots + nw++, slot);
       if (p >= n) break;
       c0 = 0; c1 = 0; pos = 0; tail = false; prefix = 1;
     }
