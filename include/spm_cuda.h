@@ -101,6 +101,17 @@ int spm_cuda_last_stats(const spm_cuda_model *model, double *stats, int n);
 
 const char *spm_cuda_last_error(void);
 
+/* ---- Line splitting (the step before the path) ----------------
+ * A raw file buffer -> the CSR input of spm_cuda_encode_batch, with the lines
+ * std::getline hands to spm_encode (src/filesystem.cc:42-44,
+ * src/spm_encode_main.cc:183-193): a line ends at '\n' (dropped; a preceding '\r'
+ * stays), a last line without '\n' counts when it is not empty.
+ * text (>= len bytes) receives the bytes without the newlines, offsets[0..n] the CSR
+ * offsets into it, *n_lines = n.  RESOURCE_EXHAUSTED when n > capacity (*n_lines is set).
+ * The model handle only supplies the device and its workspace. */
+int spm_cuda_split_lines(const spm_cuda_model *model, const char *buf, int64_t len, char *text, int64_t *offsets,
+                         int64_t capacity, int64_t *n_lines, int memory_space, void *cuda_stream);
+
 /* ---- Unigram-trainer E-step (optional kernel) ----------------
  * Replaces the per-thread loop of unigram::Trainer::RunEStep
  * (src/unigram_model_trainer.cc:237-287): for every (word, freq) build the lattice of a

@@ -54,6 +54,7 @@ def lib():
         L.spm_cuda_estep_free.argtypes = [vp]
         L.spm_cuda_estep_vocab_size.argtypes = [vp]
         L.spm_cuda_estep_run.argtypes = [vp, vp, vp, vp, i64, ctypes.c_double, vp, vp, vp, i32, vp]
+        L.spm_cuda_split_lines.argtypes = [vp, vp, i64, vp, vp, i64, ctypes.POINTER(i64), i32, vp]
         _lib = L
     return _lib
 
@@ -212,6 +213,32 @@ class SentencePieceProcessor:
         rc = lib().spm_cuda_encode_batch(self._h, ptr(text), ptr(offsets), n, self._opts, ptr(ids), cap,
                                          ptr(id_offsets), HOST, stream)
         _check(rc)
+
+    def split_lines(self, buf, stream=None):
+        """A raw file buffer (bytes / uint8 array) -> (text uint8[], offsets int64[n+1]): the
+        lines std::getline hands to spm_encode (src/spm_encode_main.cc:183-193), split on the GPU."""
+        import numpy as np
+        self._need()
+        buf = np.frombuffer(buf, dtype=np.uint8) if isinstance(buf, (bytes, bytearray, memoryview)) else \
+            np.ascontiguousarray(buf, dtype=np.uint8)
+        n = ctypes.c_int64(0)
+        cap = max(16, len(buf) // 16)
+        while True:
+            text = np.empty(max(len(buf), 1), dtype=np.uint8)
+            off = np.empty(cap + 1, dtype=np.int64)
+            rc = lib().spm_cuda_split_lines(self._h, buf.ctypes.data, len(buf), text.ctypes.data, off.ctypes.data,
+                                            cap, ctypes.byref(n), HOST, stream)
+            if rc == 8 and n.value > cap:      # RESOURCE_EXHAUSTED: n_lines holds the needed capacity
+                cap = n.value
+                continue
+            _check(rc)
+            off = off[: n.value + 1]
+            return text[: int(off[-1])], off
+
+    def encode_file_buffer(self, buf):
+        """spm_encode --output_format=id on a raw file buffer: (ids int32[], id_offsets int64[n+1])."""
+        text, off = self.split_lines(buf)
+        return self.encode_packed(text, off)
 
     STAGES = ("encode", "normalize", "memo_collect", "memo_words", "memo_emit", "compact")
 

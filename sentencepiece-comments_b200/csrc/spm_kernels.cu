@@ -833,6 +833,50 @@ k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0
   }
 }
 
+// ---------------------------------------------------------------- line splitting (the step before the path)
+// A raw file buffer -> CSR (text without the '\n' bytes, offsets), lines as std::getline
+// yields them to spm_encode (src/filesystem.cc:42-44, src/spm_encode_main.cc:183-193): a
+// line ends at '\n' (dropped; a '\r' before it stays in the line), a last line without
+// '\n' counts when it is not empty.  Tiles of kNlTile bytes; pass 1 counts the newlines of
+// a tile, pass 2 (after the scan of the counts) ranks them and moves the bytes.
+constexpr int kNlThreads = 256, kNlPer = 16, kNlTile = kNlThreads * kNlPer;
+__global__ void __launch_bounds__(kNlThreads) k_nl_count(const uint8_t *buf, int64_t len, int32_t *tile_count) {
+  const int64_t p0 = (int64_t)blockIdx.x * kNlTile + (int64_t)threadIdx.x * kNlPer;
+  int c = 0;
+#pragma unroll
+  for (int k = 0; k < kNlPer; ++k)
+    if (p0 + k < len && buf[p0 + k] == '\n') ++c;
+  int64_t tot;
+  block_exclusive_scan((int64_t)c, &tot);
+  if (threadIdx.x == 0) tile_count[blockIdx.x] = (int32_t)tot;
+}
+__global__ void __launch_bounds__(kNlThreads)
+k_nl_scatter(const uint8_t *buf, int64_t len, const int64_t *tile_base, uint8_t *text, int64_t *offsets,
+             int64_t capacity) {
+  const int64_t p0 = (int64_t)blockIdx.x * kNlTile + (int64_t)threadIdx.x * kNlPer;
+  uint8_t b[kNlPer];
+  int c = 0;
+#pragma unroll
+  for (int k = 0; k < kNlPer; ++k) {
+    b[k] = p0 + k < len ? buf[p0 + k] : 0;
+    if (p0 + k < len && b[k] == '\n') ++c;
+  }
+  int64_t tot;
+  int64_t rank = block_exclusive_scan((int64_t)c, &tot) + tile_base[blockIdx.x];   // newlines before p0
+#pragma unroll
+  for (int k = 0; k < kNlPer; ++k) {
+    const int64_t p = p0 + k;
+    if (p >= len) break;
+    if (b[k] == '\n') {
+      ++rank;                                             // line `rank` starts after this byte
+      if (rank <= capacity) offsets[rank] = p + 1 - rank;
+    } else {
+      text[p - rank] = b[k];
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) offsets[0] = 0;
+}
+
 // ---------------------------------------------------------------- unigram trainer E-step (spm_estep.cuh)
 // One thread per word.  Words of up to kEstepLocalBytes bytes keep their forward /
 // backward tables in local memory; longer ones (text without spaces) use a slice of a
@@ -1669,6 +1713,69 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
     g_err = "all normalized characters are not consumed.";  // src/sentencepiece_processor.cc:543
     return kInternal;
   }
+  return kOk;
+}
+
+// ---------------------------------------------------------------- line splitting C ABI
+int spm_cuda_split_lines(const spm_cuda_model *M, const char *buf, int64_t len, char *text, int64_t *offsets,
+                         int64_t capacity, int64_t *n_lines, int memory_space, void *cuda_stream) {
+  if (!M) { g_err = "model is not loaded"; return kInvalidArgument; }
+  if (len < 0 || capacity < 0 || !offsets || !n_lines || (len > 0 && (!buf || !text))) {
+    g_err = "invalid argument";
+    return kInvalidArgument;
+  }
+  std::lock_guard<std::mutex> lk(M->mu);
+  CUDA_TRY(cudaSetDevice(M->device));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  const bool host = memory_space == SPM_CUDA_HOST;
+  int rc;
+  double launches = 0;
+  const int64_t ntiles = (len + kNlTile - 1) / kNlTile;
+  const uint8_t *d_buf = (const uint8_t *)buf;
+  uint8_t *d_text = (uint8_t *)text;
+  int64_t *d_off = offsets;
+  if (host) {
+    if ((rc = M->w_text.ensure((size_t)len + 16))) return rc;
+    if ((rc = M->w_norm.ensure((size_t)len + 16))) return rc;
+    if ((rc = M->w_off.ensure((size_t)(capacity + 1) * 8))) return rc;
+    if (len > 0) CUDA_TRY(cudaMemcpyAsync(M->w_text.p, buf, len, cudaMemcpyHostToDevice, st));
+    d_buf = (const uint8_t *)M->w_text.p; d_text = (uint8_t *)M->w_norm.p; d_off = (int64_t *)M->w_off.p;
+  }
+  if ((rc = M->w_cnt.ensure((size_t)(ntiles + 1) * 4))) return rc;
+  if ((rc = M->w_srcoff.ensure((size_t)(ntiles + 2) * 8))) return rc;
+  if ((rc = M->w_scalars.ensure(64))) return rc;
+  int64_t *d_total = (int64_t *)M->w_scalars.p;
+  int64_t total_nl = 0;
+  uint8_t last = '\n';
+  if (len > 0) {
+    k_nl_count<<<(unsigned)ntiles, kNlThreads, 0, st>>>(d_buf, len, (int32_t *)M->w_cnt.p);
+    if ((rc = run_scan(M, st, (const int32_t *)M->w_cnt.p, ntiles, IdentityOp(), (int64_t *)M->w_srcoff.p, d_total, 0,
+                       &launches)))
+      return rc;
+    k_nl_scatter<<<(unsigned)ntiles, kNlThreads, 0, st>>>(d_buf, len, (const int64_t *)M->w_srcoff.p, d_text, d_off,
+                                                          capacity);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(&total_nl, d_total, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(&last, d_buf + len - 1, 1, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+  }
+  const int64_t n = total_nl + ((len > 0 && last != '\n') ? 1 : 0);
+  *n_lines = n;
+  if (n > capacity) {
+    g_err = "offsets capacity too small: " + std::to_string(n) + " lines";
+    return kResourceExhausted;
+  }
+  const int64_t zero = 0, end = len - total_nl;
+  if (len == 0) {
+    if (host) offsets[0] = 0; else CUDA_TRY(cudaMemcpyAsync(d_off, &zero, 8, cudaMemcpyHostToDevice, st));
+  } else {
+    if (last != '\n') CUDA_TRY(cudaMemcpyAsync(d_off + n, &end, 8, cudaMemcpyHostToDevice, st));
+    if (host) {
+      CUDA_TRY(cudaMemcpyAsync(offsets, d_off, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, st));
+      if (end > 0) CUDA_TRY(cudaMemcpyAsync(text, d_text, (size_t)end, cudaMemcpyDeviceToHost, st));
+    }
+  }
+  CUDA_TRY(cudaStreamSynchronize(st));
   return kOk;
 }
 
