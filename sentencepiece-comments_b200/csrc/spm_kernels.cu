@@ -48,6 +48,7 @@
 #include "spm_fast.cuh"
 #include "spm_memo.cuh"
 #include "spm_estep.cuh"
+#include "spm_warp.cuh"
 #include "spm_model.h"
 
 using namespace spmb;
@@ -419,6 +420,68 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
       } else {
         cnt[t] = c;
       }
+    }
+    __syncwarp();
+  }
+}
+
+// The long lines in order of descending length (buckets of 256 bytes; one block): the persistent
+// warps of k_encode_warp then start with the longest lines, which bound its run time.
+__global__ void __launch_bounds__(1024)
+k_sort_long(const int64_t *off, int64_t c0, const int32_t *list, int count_idx, int32_t *sorted,
+            const uint32_t *counters) {
+  constexpr int kBuckets = kLongMaxRaw / 256;
+  __shared__ uint32_t hist[kBuckets];
+  const uint32_t n = counters[count_idx];
+  for (int k = threadIdx.x; k < kBuckets; k += 1024) hist[k] = 0;
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < n; i += 1024) {
+    const int64_t t = list[i];
+    atomicAdd(&hist[kBuckets - 1 - (int)((off[c0 + t + 1] - off[c0 + t]) >> 8)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int k = 0; k < kBuckets; ++k) { const uint32_t c = hist[k]; hist[k] = run; run += c; }
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < n; i += 1024) {
+    const int32_t t = list[i];
+    sorted[atomicAdd(&hist[kBuckets - 1 - (int)((off[c0 + t + 1] - off[c0 + t]) >> 8)], 1u)] = t;
+  }
+}
+
+// Long lines (kFastMaxRaw <= bytes < kLongMaxRaw) of unigram models: one WARP per line, exact
+// candidate lists in shared memory (spm_warp.cuh).  Persistent warps pull lines from the list.
+constexpr int kWarpWarps = 4;
+__global__ void __launch_bounds__(kWarpWarps * 32)
+k_encode_warp(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
+              const int32_t *list, int count_idx, int work_idx, uint32_t *back, int64_t stride, int32_t *stage,
+              int32_t *cnt, int32_t *gen_list, uint32_t *counters) {
+  __shared__ WarpScratch ws[kWarpWarps];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  FastView fv;
+  fv.units = fp.units; fv.score = fp.score; fv.leaf_id = fp.leaf_id;
+  fv.units_hot = fp.units; fv.score_hot = fp.score; fv.units_hot_saddr = 0; fv.score_hot_saddr = 0;
+  fv.k_units = 0; fv.k_scores = 0; fv.n_units = fp.n_units;
+  fv.ring = fp.ring; fv.unk_score = fp.unk_score; fv.smax = fp.smax; fv.unk_id = fp.unk_id;
+  const uint32_t count = counters[count_idx];
+  uint32_t *myback = back + ((int64_t)blockIdx.x * kWarpWarps + wid) * kWarpCapc * stride;
+  for (;;) {
+    uint32_t w = 0;
+    if (lane == 0) w = atomicAdd(&counters[work_idx], 1u);
+    w = __shfl_sync(0xFFFFFFFFu, w, 0);
+    if (w >= count) break;
+    const int32_t t = list[w];
+    const int32_t nl = nlen[t];
+    if (nl <= 0) continue;                 // empty, or routed to the general tier by the normalizer
+    int32_t c = -1;
+    if (nl + 2 <= stride)
+      c = warp_unigram(fv, ws[wid], norm + fast_norm_base(off, c0, t), nl, myback, stride,
+                       stage + fast_stage_base(off, c0, t));
+    if (lane == 0) {
+      if (c < 0) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
+      else cnt[t] = c;
     }
     __syncwarp();
   }
@@ -954,7 +1017,7 @@ struct spm_cuda_model {
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
-      w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
+      w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
   mutable std::vector<int64_t> h_woff;
   mutable double stats[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -974,7 +1037,7 @@ struct spm_cuda_model {
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
             &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
-            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf,
+            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status};
   }
@@ -1525,6 +1588,9 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       // long lines (kFastMaxRaw <= bytes < kLongMaxRaw): same kernels over long_list, on as
       // many warps per SM as a 2 GiB back-pointer budget allows
       const bool has_long = max_len >= kFastMaxRaw && max_long >= kFastMaxRaw;
+      static const bool no_warp = getenv("SPM_CUDA_NO_WARP") != nullptr;   // measurement of the older long-line path
+      const bool warp_ok = M->fast_kind == 1 && !no_warp && M->hm.ring <= kWarpRing &&
+                           M->hm.max_piece_chars + 1 <= kWarpHits && M->hm.piece.size() < (1u << 24);
       const int64_t back_rows_long = (max_long + kFastExtraChars + 8 + 3) & ~(int64_t)3;
       int long_warps = M->fast_kind == 1 ? kFastThreads / 32 : kBpeThreads / 32;
       if (M->fast_kind == 1)
@@ -1533,6 +1599,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       size_t back_bytes = (size_t)back_rows * M->sm_count * kFastThreads * 4;
       if (has_long) back_bytes = std::max(back_bytes, (size_t)back_rows_long * M->sm_count * long_warps * 32 * 4);
       if (M->fast_kind == 1 && (rc = M->w_back.ensure(back_bytes))) return rc;
+      if (has_long && (rc = M->w_vitl.ensure((size_t)std::min<int64_t>(cn, raw / kFastMaxRaw + 1) * 4))) return rc;
       if (has_long && (rc = M->w_longlist.ensure((size_t)std::min<int64_t>(cn, raw / kFastMaxRaw + 1) * 4))) return rc;
       const int64_t max_n_long = has_long ? std::min<int64_t>(cn, raw / kFastMaxRaw + 1) : 0;
       const unsigned gsort = (unsigned)((cn + kSortTile - 1) / kSortTile);
@@ -1603,11 +1670,25 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
             kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
             (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
-        if (has_long)
+        if (has_long && warp_ok) {
+          // one warp per long line, exact candidate lists (spm_warp.cuh); back records:
+          // kWarpCapc rows of `wstride` per resident warp, at most 4 GiB in all; longest lines first
+          const int64_t wstride = 3 * max_long + 136;
+          const int64_t wblocks = std::max<int64_t>(
+              1, std::min<int64_t>(5 * (int64_t)M->sm_count, (4096ll << 20) / (wstride * 4 * kWarpCapc * kWarpWarps)));
+          if ((rc = M->w_wback.ensure((size_t)(wblocks * kWarpWarps * kWarpCapc * wstride * 4)))) return rc;
+          k_sort_long<<<1, 1024, 0, st>>>(d_off, c0, (const int32_t *)M->w_longlist.p, C_NLONG,
+                                          (int32_t *)M->w_vitl.p, d_counters);
+          k_encode_warp<<<(unsigned)wblocks, kWarpWarps * 32, 0, st>>>(
+              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+              (const int32_t *)M->w_vitl.p, cnt_b, work_b, (uint32_t *)M->w_wback.p, wstride, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
+              (int32_t *)M->w_genlist.p, d_counters);
+        } else if (has_long) {
           k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
               long_warps, (uint32_t *)M->w_back.p, back_rows_long, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
               (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+        }
       } else {
         k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
