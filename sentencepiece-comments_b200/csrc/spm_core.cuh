@@ -66,6 +66,7 @@ struct ModelView {
   const uint32_t *cm_units;  // charsmap darts units (model data, uploaded verbatim)
   const uint8_t *cm_pool;    // NUL-delimited replacement strings
   const uint32_t *cm_first2; // 65536-bit filter: can a rule start with (b0,b1)?
+  const uint32_t *cm_cont2;  // 65536-bit filter: can a character starting (b0,b1) sit INSIDE a rule key / user symbol?
   uint32_t cm_n;             // 0: identity normalization
   uint32_t user_first[8];    // 256-bit filter on the first byte of user symbols
   int32_t model_type;

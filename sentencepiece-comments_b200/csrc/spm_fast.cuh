@@ -485,7 +485,8 @@ struct FastOut {
 template <class Sink>
 SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t n,
                                  const uint8_t *lo, const uint8_t *hi, Sink &o, int32_t *nchars_ub,
-                                 bool *content) {   // *content: something other than leading spaces was seen
+                                 bool *content,     // *content: something other than leading spaces was seen
+                                 bool mid = false) {  // in[] continues a line whose content has started (norm_find_cut)
   const bool esc = m.escape_ws, rws = m.remove_extra_ws;
   const uint32_t WS = esc ? 0x8196E2u : 0x20u;  // U+2581 little-endian, or ' '
   const int WSL = esc ? 3 : 1;
@@ -493,9 +494,9 @@ SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, con
   int r = (int)(in - q);
   uint64_t a0 = fast_load8_guard(q, lo, hi), a1 = fast_load8_guard(q + 8, lo, hi);
   int32_t nch = 0;
-  bool lead = rws;          // still stripping leading spaces (:103-112)
-  bool started = false;     // dummy prefix emitted
-  bool prev_space = rws;    // is_prev_space
+  bool lead = rws && !mid;        // still stripping leading spaces (:103-112)
+  bool started = mid;             // dummy prefix emitted
+  bool prev_space = rws && !mid;  // is_prev_space
   bool overflow = false;
   int64_t p = 0;
   while (p < n) {
@@ -594,6 +595,58 @@ SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, con
   *nchars_ub = nch;
   *content = started;
   return !overflow;
+}
+
+// Long lines are normalized in pieces (k_normalize_long).  A piece may start at `p` when the
+// scan is guaranteed to arrive there with a fresh match and a state that does not matter:
+//   * in[p] starts a character that never sits inside a rule key / user symbol (cm_cont2),
+//     so no match that began earlier can reach over p;
+//   * no rule / user symbol starts at it (first2, user_first) and it is not a space, so it
+//     is copied as it is whatever the whitespace state was, and leaves prev_space = false.
+// Returns the first such position >= from, or n.
+SPM_HD int64_t norm_find_cut(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t from, int64_t n) {
+  for (int64_t p = from; p < n; ++p) {
+    const uint32_t b0 = in[p];
+    if ((b0 & 0xC0u) == 0x80u || b0 == 0x20u) continue;
+    if (p + 1 >= n) continue;                       // the scan treats a last lone byte as "slow"
+    const uint32_t key = (b0 << 8) | in[p + 1];
+    if (m.cm_cont2 != nullptr && ((m.cm_cont2[key >> 5] >> (key & 31)) & 1)) continue;
+    if (m.cm_n != 0 && ((first2[key >> 5] >> (key & 31)) & 1)) continue;
+    if (m.user.n != 0 && ((m.user_first[b0 >> 5] >> (b0 & 31)) & 1)) continue;
+    return p;
+  }
+  return n;
+}
+
+// Piece `idx` = in[a..b) of a line cut by norm_find_cut: normalized into `slot` (8-byte
+// aligned, 3 * (b - a) + 72 + 8 bytes).  *content is only meaningful for piece 0.
+constexpr int kNormChunk = 512;   // raw bytes per piece (before the cut is moved to a safe position)
+SPM_HD int64_t norm_piece_slot(int64_t a, int idx) { return (3 * a + 88 * (int64_t)idx + 7) & ~(int64_t)7; }
+SPM_HDN bool norm_piece(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t a, int64_t b,
+                        const uint8_t *lo, const uint8_t *hi, uint8_t *slot, int idx, int32_t *out_len,
+                        int32_t *nchars, bool *content) {
+  FastOut o;
+  o.base = slot; o.acc = 0; o.len = 0; o.cap = (int32_t)(3 * (b - a) + 72);
+  const bool ok = fast_normalize_scan(m, first2, in + a, b - a, lo, hi, o, nchars, content, idx > 0);
+  o.flush();
+  *out_len = o.len;
+  return ok;
+}
+// After the pieces are concatenated in out[0..len): what fast_normalize() does behind its scan.
+// raw = raw bytes of the line (slot capacity 3 * raw + 72).  Returns the final length, -1 when
+// the line does not fit the fast tier's bounds.  The caller zeroes out[len .. align8(len) + kNormPad).
+SPM_HD int32_t norm_finish(const ModelView &m, uint8_t *out, int32_t len, int32_t nch, bool started, int64_t raw) {
+  if (len + 3 > 3 * raw + 72) return -1;
+  if (m.remove_extra_ws) {
+    if (m.escape_ws) { while (len >= 3 && out[len - 3] == 0xE2 && out[len - 2] == 0x96 && out[len - 1] == 0x81) { len -= 3; --nch; } }
+    else { while (len >= 1 && out[len - 1] == ' ') { len -= 1; --nch; } }
+  }
+  if (m.ws_suffix && m.add_dummy_prefix && started) {
+    if (m.escape_ws) { out[len] = 0xE2; out[len + 1] = 0x96; out[len + 2] = 0x81; len += 3; } else { out[len++] = ' '; }
+    ++nch;
+  }
+  if (nch > raw + kFastExtraChars) return -1;
+  return len;
 }
 
 SPM_HDN int32_t fast_normalize(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t n,

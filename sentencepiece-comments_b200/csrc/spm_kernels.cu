@@ -313,6 +313,83 @@ k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t 
   nlen[t] = nl;
 }
 
+// Long lines: one BLOCK per line, one thread per piece of ~kNormChunk raw bytes.  Pieces start
+// at positions norm_find_cut() proves safe, are normalized independently into a temporary
+// slot each (fast_normalize_scan with mid = true), then the block concatenates them into the
+// line's slot of `norm` and finishes the line as fast_normalize() does (trailing whitespace,
+// suffix, zero padding).  A 33 KB line takes the time of one 512-byte piece instead of 20 ms.
+constexpr int kNormLongThreads = kLongMaxRaw / kNormChunk;   // 128
+__device__ __forceinline__ int64_t norm_tmp_base(const int64_t *off, int64_t c0, int64_t t) {
+  const int64_t o = off[c0 + t] - off[c0];
+  return ((3 * o + 7) & ~(int64_t)7) + 88 * (o / kNormChunk) + 96 * t;
+}
+__global__ void __launch_bounds__(kNormLongThreads)
+k_normalize_long(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c0, const uint8_t *lo,
+                 const uint8_t *hi, const int32_t *list, int count_idx, uint8_t *tmp, uint8_t *norm, int32_t *nlen,
+                 int32_t *gen_list, uint32_t *counters) {
+  __shared__ uint32_t first2[2048];
+  __shared__ int64_t cuts[kNormLongThreads + 1];
+  __shared__ int32_t olen[kNormLongThreads], obase[kNormLongThreads + 1], onch[kNormLongThreads];
+  __shared__ int bad, started, total_len, total_nch;
+  if (blockIdx.x >= counters[count_idx]) return;
+  if (mv.cm_first2 != nullptr)
+    for (int k = threadIdx.x; k < 2048; k += kNormLongThreads) first2[k] = mv.cm_first2[k];
+  const int32_t t = list[blockIdx.x];
+  const int64_t o0 = off[c0 + t], len = off[c0 + t + 1] - o0;
+  const uint8_t *in = text + o0;
+  uint8_t *line_tmp = tmp + norm_tmp_base(off, c0, t);
+  const int i = threadIdx.x;
+  const int nchunks = (int)((len + kNormChunk - 1) / kNormChunk);
+  if (i == 0) { bad = 0; started = 0; }
+  __syncthreads();
+  if (i <= nchunks)
+    cuts[i] = i == 0 ? 0 : (i == nchunks ? len : norm_find_cut(mv, first2, in, (int64_t)i * kNormChunk, len));
+  __syncthreads();
+  olen[i] = 0; onch[i] = 0;
+  if (i < nchunks) {
+    const int64_t a = cuts[i], b = cuts[i + 1];
+    if (b > a) {
+      bool content = false;
+      const bool ok = norm_piece(mv, first2, in, a, b, lo, hi, line_tmp + norm_piece_slot(a, i), i, &olen[i], &onch[i],
+                                 &content);
+      if (i == 0 && content) started = 1;
+      // pieces after the first assume that the line's content has started
+      if (!ok || (i == 0 && !content && nchunks > 1)) bad = 1;
+    }
+  }
+  __syncthreads();
+  if (i == 0) {
+    int32_t run = 0, nc = 0;
+    for (int k = 0; k < nchunks; ++k) { obase[k] = run; run += olen[k]; nc += onch[k]; }
+    total_len = run; total_nch = nc;
+    if (run + 3 > 3 * len + 72) bad = 1;
+  }
+  __syncthreads();
+  uint8_t *out = norm + fast_norm_base(off, c0, t);
+  if (!bad) {
+    for (int k = 0; k < nchunks; ++k) {
+      const int32_t n_k = olen[k];
+      if (n_k == 0) continue;
+      const uint8_t *src = line_tmp + norm_piece_slot(cuts[k], k);
+      for (int32_t j = i; j < n_k; j += kNormLongThreads) out[obase[k] + j] = src[j];
+    }
+  }
+  __syncthreads();
+  if (i == 0) {
+    int32_t nl = bad ? -1 : norm_finish(mv, out, total_len, total_nch, started != 0, len);
+    if (nl < 0) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
+    nlen[t] = nl;
+    total_len = nl;
+  }
+  __syncthreads();
+  // zero padding: up to the next 8-byte boundary + kNormPad bytes
+  const int32_t nl = total_len;
+  if (nl >= 0) {
+    const int32_t z1 = ((nl + 7) & ~7) + kNormPad;
+    for (int32_t j = nl + i; j < z1; j += kNormLongThreads) out[j] = 0;
+  }
+}
+
 // Checks the offsets of the whole batch on the device (no O(n) work on the host):
 // scal[3] |= 1 when offsets decrease, scal[6] = longest sentence, scal[7] = longest
 // sentence shorter than kFastMaxRaw, scal[1] = longest sentence shorter than kLongMaxRaw
@@ -1013,11 +1090,11 @@ struct spm_cuda_model {
   int fast_kind = 0;       // 1: unigram (k_encode_fast), 2: BPE (k_encode_bpe_fast)
   int sm_count = 1;
   size_t fast_smem = 0;
-  DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2, d_funits, d_fscore, d_fleaf;
+  DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2, d_cont2, d_funits, d_fscore, d_fleaf;
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
-      w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
+      w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
   mutable std::vector<int64_t> h_woff;
   mutable double stats[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -1034,10 +1111,10 @@ struct spm_cuda_model {
   int bos_id = 0, eos_id = 0, pad_id = 0;
   std::vector<DevBuf *> all_bufs() const {
     spm_cuda_model *m = const_cast<spm_cuda_model *>(this);
-    return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2,
+    return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2, &m->d_cont2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
             &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
-            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback,
+            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status};
   }
@@ -1108,6 +1185,7 @@ int upload_model(spm_cuda_model *M) {
   if ((rc = upload(&M->d_cm_units, hm.cm_units, (size_t)hm.cm_n * 4))) return rc;
   if ((rc = upload(&M->d_cm_pool, hm.cm_pool, hm.cm_pool_size))) return rc;
   if ((rc = upload(&M->d_first2, hm.cm_first2.data(), hm.cm_first2.size() * 4))) return rc;
+  if ((rc = upload(&M->d_cont2, hm.cm_cont2.data(), hm.cm_cont2.size() * 4))) return rc;
   ModelView &v = M->mv;
   memset(&v, 0, sizeof(v));
   v.pieces.units = (const uint32_t *)M->d_units.p; v.pieces.leaf = (const uint2 *)M->d_leaf.p;
@@ -1116,6 +1194,7 @@ int upload_model(spm_cuda_model *M) {
   v.user.n = (uint32_t)hm.user.units.size();
   v.cm_units = (const uint32_t *)M->d_cm_units.p; v.cm_pool = (const uint8_t *)M->d_cm_pool.p;
   v.cm_first2 = hm.cm_first2.empty() ? nullptr : (const uint32_t *)M->d_first2.p;
+  v.cm_cont2 = hm.cm_cont2.empty() ? nullptr : (const uint32_t *)M->d_cont2.p;
   v.cm_n = hm.cm_n;
   memcpy(v.user_first, hm.user_first, sizeof(v.user_first));
   v.model_type = hm.model_type; v.unk_id = hm.unk_id;
@@ -1656,10 +1735,13 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       k_normalize_fast<<<gsent, kNormThreads, 0, st>>>(
           M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p, C_NFAST,
           (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
-      if (has_long)   // the grid covers the most long lines the chunk's bytes can hold
-        k_normalize_fast<<<glong, kNormThreads, 0, st>>>(
+      if (has_long) {   // one block per long line; the grid covers the most long lines the chunk's bytes can hold
+        if ((rc = M->w_ntmp.ensure((size_t)(3 * raw + 88 * (raw / kNormChunk + 1) + 96 * cn + 256)))) return rc;
+        k_normalize_long<<<(unsigned)max_n_long, kNormLongThreads, 0, st>>>(
             M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_longlist.p, C_NLONG,
-            (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
+            (uint8_t *)M->w_ntmp.p, (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p,
+            d_counters);
+      }
       if ((rc = kev_record(M, st, 1))) return rc;
       launches += has_long ? 5 : 4;
       const int32_t *list_a = (const int32_t *)M->w_perm.p, *list_b = (const int32_t *)M->w_longlist.p;

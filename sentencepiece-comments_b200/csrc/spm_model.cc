@@ -222,13 +222,28 @@ bool is_trie_type(uint32_t t) { return t == T_NORMAL || t == T_USER_DEFINED || t
 // charsmap statistics: first-two-bytes filter and worst-case expansion.
 void scan_charsmap(HostModel *m) {
   m->cm_first2.assign(65536 / 32, 0);
+  m->cm_cont2.assign(65536 / 32, 0);
+  // user-defined symbols are matched before the charsmap (src/normalizer.cc:240-249)
+  for (size_t i = 0; i < m->piece.size(); ++i) {
+    if (m->type[i] != T_USER_DEFINED) continue;
+    const std::string &pc = m->piece[i];
+    for (size_t k = one_char_len((uint8_t)pc[0]); k < pc.size(); k += one_char_len((uint8_t)pc[k])) {
+      const uint32_t b0 = (uint8_t)pc[k];
+      if (b0 < 0x80 || k + 1 >= pc.size()) { for (uint32_t x = 0; x < 256; ++x) m->cm_cont2[((b0 << 8) | x) >> 5] |= 1u << (((b0 << 8) | x) & 31); }
+      else { const uint32_t b1 = (uint8_t)pc[k + 1]; m->cm_cont2[((b0 << 8) | b1) >> 5] |= 1u << (((b0 << 8) | b1) & 31); }
+    }
+  }
   m->expansion = 3;  // ' ' -> U+2581 and a malformed byte -> U+FFFD are both 1 -> 3
-  if (m->cm_n == 0) { m->cm_first2.clear(); return; }
+  if (m->cm_n == 0) { m->cm_first2.clear(); return; }   // (cm_cont2 keeps the user-symbol marks)
   const uint32_t *a = m->cm_units;
   const uint32_t n = m->cm_n;
-  struct Item { uint32_t pos; int depth; uint32_t b0, b1; };
+  // cm_cont2: first two bytes of every character that sits at a NON-initial position of some
+  // key (prefixes of keys included: harmless over-marking).  A character outside this set can
+  // never be swallowed by a match that started earlier: a safe place to cut a long line.
+  auto mark_cont = [&](uint32_t b0, uint32_t b1) { m->cm_cont2[((b0 << 8) | b1) >> 5] |= 1u << (((b0 << 8) | b1) & 31); };
+  struct Item { uint32_t pos; int depth; uint32_t b0, b1; int lead; };
   std::vector<Item> stack;
-  stack.push_back(Item{du_offset(a[0]), 0, 0, 0});
+  stack.push_back(Item{du_offset(a[0]), 0, 0, 0, -1});
   while (!stack.empty()) {
     const Item it = stack.back();
     stack.pop_back();
@@ -240,6 +255,12 @@ void scan_charsmap(HostModel *m) {
       const uint32_t np = p ^ du_offset(u);
       const int depth = it.depth + 1;
       const uint32_t b0 = depth == 1 ? c : it.b0, b1 = depth == 2 ? c : it.b1;
+      int lead = -1;
+      if (depth > 1) {
+        if (c < 0x80) { for (uint32_t x = 0; x < 256; ++x) mark_cont(c, x); }
+        else if (c >= 0xC0) lead = (int)c;
+        else if (it.lead >= 0) mark_cont((uint32_t)it.lead, c);
+      }
       if (depth == 2) m->cm_first2[((b0 << 8) | b1) >> 5] |= 1u << (((b0 << 8) | b1) & 31);
       if ((u >> 8) & 1) {
         if (depth == 1)
@@ -255,7 +276,7 @@ void scan_charsmap(HostModel *m) {
           }
         }
       }
-      if (depth < 64 && np < n) stack.push_back(Item{np, depth, b0, b1});
+      if (depth < 64 && np < n) stack.push_back(Item{np, depth, b0, b1, lead});
     }
   }
 }

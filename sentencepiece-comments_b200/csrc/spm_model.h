@@ -37,6 +37,7 @@ struct HostModel {
   float min_score = 0, max_score = 0;
   HostTrie pieces, user;
   std::vector<uint32_t> cm_first2;
+  std::vector<uint32_t> cm_cont2;   // 64 Kbit: characters that occur inside (not at the start of) a rule key / user symbol
   uint32_t user_first[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const uint32_t *cm_units = nullptr;  // into charsmap
   uint32_t cm_n = 0;

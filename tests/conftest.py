@@ -84,6 +84,9 @@ def hostcore():
     L.hc_normalize_fast.restype = ctypes.c_int64
     L.hc_normalize_fast.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int64,
                                     ctypes.c_void_p]
+    L.hc_normalize_chunked.restype = ctypes.c_int64
+    L.hc_normalize_chunked.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p,
+                                       ctypes.c_int64]
     L.hc_encode_batch.argtypes = [ctypes.c_void_p] * 3 + [ctypes.c_int64, ctypes.c_uint32, ctypes.c_int,
                                                          ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p,
                                                          ctypes.c_void_p]
@@ -128,6 +131,14 @@ class HostCore:
         n = self.L.hc_normalize_fast(self.h, b, len(b), out, cap, ctypes.byref(nc))
         assert n >= -1, n
         return None if n < 0 else (out.raw[:n], nc.value)
+
+    def normalize_chunked(self, b, chunk):
+        """k_normalize_long's piecewise scheme; None when the line is routed to the general tier."""
+        cap = 3 * len(b) + 80
+        out = ctypes.create_string_buffer(cap)
+        n = self.L.hc_normalize_chunked(self.h, b, len(b), chunk, out, cap)
+        assert n >= -1, n
+        return None if n < 0 else out.raw[:n]
 
     def encode_batch(self, text, off, opts=0, capc=4):
         text = np.ascontiguousarray(text, dtype=np.uint8)

@@ -32,6 +32,7 @@ void make_view(Handle *h) {
   v.user.units = m.user.units.data(); v.user.leaf = m.user.leaf.data(); v.user.n = (uint32_t)m.user.units.size();
   v.cm_units = m.cm_units; v.cm_pool = m.cm_pool; v.cm_n = m.cm_n;
   v.cm_first2 = m.cm_first2.empty() ? nullptr : m.cm_first2.data();
+  v.cm_cont2 = m.cm_cont2.empty() ? nullptr : m.cm_cont2.data();
   memcpy(v.user_first, m.user_first, sizeof(v.user_first));
   v.model_type = m.model_type; v.unk_id = m.unk_id;
   v.unk_score = m.min_score - 10.0f; v.max_score = m.max_score; v.smax = m.smax; v.ring = m.ring;
@@ -88,6 +89,49 @@ int64_t hc_normalize_fast(void *p, const uint8_t *in, int64_t n, uint8_t *out, i
   for (int k = 0; k < kNormPad; ++k) if (o[nl + k] != 0) return -2;  // padding contract
   if (nl > cap) return -3;
   memcpy(out, o, nl);
+  return nl;
+}
+
+// k_normalize_long's scheme, sequentially: pieces of ~chunk raw bytes cut at norm_find_cut
+// positions, each normalized on its own, concatenated and finished.  Returns the length, -1
+// (general tier), or < -1 on a broken contract.
+int64_t hc_normalize_chunked(void *p, const uint8_t *in, int64_t n, int chunk, uint8_t *out, int64_t cap) {
+  Handle *h = (Handle *)p;
+  const ModelView &mv = h->mv;
+  if (n == 0) return 0;
+  std::vector<uint64_t> ibuf((n + 64) / 8 + 2, 0x5A5A5A5A5A5A5A5Aull);
+  uint8_t *src = (uint8_t *)ibuf.data() + 5;
+  memcpy(src, in, n);
+  const int nchunks = (int)((n + chunk - 1) / chunk);
+  std::vector<int64_t> cuts(nchunks + 1);
+  for (int i = 0; i <= nchunks; ++i)
+    cuts[i] = i == 0 ? 0 : (i == nchunks ? n : norm_find_cut(mv, mv.cm_first2, src, (int64_t)i * chunk, n));
+  std::vector<uint64_t> tmp((3 * n + 88 * (int64_t)nchunks + 96) / 8 + 2, 0x7777777777777777ull);
+  std::vector<int32_t> olen(nchunks, 0), onch(nchunks, 0);
+  bool bad = false, started = false;
+  for (int i = 0; i < nchunks; ++i) {
+    if (cuts[i + 1] < cuts[i]) return -4;
+    if (cuts[i + 1] == cuts[i]) continue;
+    bool content = false;
+    const bool ok = norm_piece(mv, mv.cm_first2, src, cuts[i], cuts[i + 1], src, src + n,
+                               (uint8_t *)tmp.data() + norm_piece_slot(cuts[i], i), i, &olen[i], &onch[i], &content);
+    if (i == 0 && content) started = true;
+    if (!ok || (i == 0 && !content && nchunks > 1)) bad = true;
+  }
+  if (bad) return -1;
+  int64_t total = 0, nch = 0;
+  for (int i = 0; i < nchunks; ++i) { total += olen[i]; nch += onch[i]; }
+  if (total + 3 > 3 * n + 72) return -1;
+  std::vector<uint8_t> o(3 * n + 72 + kNormPad + 16, 0x33);
+  int64_t at = 0;
+  for (int i = 0; i < nchunks; ++i) {
+    memcpy(o.data() + at, (const uint8_t *)tmp.data() + norm_piece_slot(cuts[i], i), olen[i]);
+    at += olen[i];
+  }
+  const int32_t nl = norm_finish(mv, o.data(), (int32_t)total, (int32_t)nch, started, n);
+  if (nl < 0) return -1;
+  if (nl > cap) return -3;
+  memcpy(out, o.data(), nl);
   return nl;
 }
 

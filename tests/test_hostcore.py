@@ -81,6 +81,30 @@ def test_normalizers_match_reference(make_hostcore, corpora, model):
         assert f is None or f[0] == want, s
 
 
+@pytest.mark.parametrize("model", ["botchan_uni8k", "botchan_uni2k_ud", "ref_ja_8k", "botchan_bpe2k_ud"])
+def test_piecewise_normalizer_matches(make_hostcore, corpora, model):
+    """k_normalize_long's scheme (pieces cut at norm_find_cut positions, normalized independently,
+    concatenated) gives the bytes of the sequential normalizer -- with tiny pieces so that cuts
+    fall next to rules, user symbols, whitespace runs and malformed bytes."""
+    hc = make_hostcore(model_bytes(model))
+    lines = [s for s in EDGE_SENTENCES if s]
+    for name, step, sep in (("wagahai", 40, b""), ("syn_dirty", 60, b"  "), ("botchan", 50, b" ")):
+        t, o = corpora[name]
+        for i in range(0, min(len(o) - 1, 1200), step):
+            lines.append(sep.join(bytes(t[o[k]:o[k + 1]]) for k in range(i, i + step)))
+    lines.append(b" ".join(EDGE_SENTENCES))
+    lines.append(b"".join(EDGE_SENTENCES))
+    served = 0
+    for s in lines:
+        want = hc.normalize(s)
+        for chunk in (3, 16, 512):
+            got = hc.normalize_chunked(s, chunk)
+            if got is not None:
+                served += 1
+                assert got == want, (model, chunk, s[:80])
+    assert served >= 2 * len(lines)
+
+
 @pytest.mark.parametrize("opts", ["bos", "eos:reverse", "reverse:bos:eos", "eos:reverse:bos:reverse:eos"])
 def test_extra_options(make_hostcore, corpora, opts):
     mb = model_bytes("botchan_uni8k")
