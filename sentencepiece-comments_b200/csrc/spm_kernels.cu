@@ -78,7 +78,7 @@ constexpr uint32_t ST_FWD = 1u << 17;   // fast-tier ids were staged in forward 
 
 // device-side counters of one chunk
 enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_WORK_LONG = 4, C_NLONG = 5,
-       C_NVIT = 6, C_WORK_VIT = 7, C_NVITL = 8, C_WORK_VITL = 9, C_NNEW = 10, C_NSLOW = 11, C_COUNT = 16 };
+       C_NVIT = 6, C_WORK_VIT = 7, C_NVITL = 8, C_WORK_VITL = 9, C_NNEW = 10, C_NSLOW = 11, C_NRETRY = 12, C_COUNT = 16 };
 // k_publish snapshot (int64 slots): counters | scalars | running id total of chunk k
 constexpr int kPubScal = C_COUNT, kPubTot = C_COUNT + 8;
 
@@ -456,7 +456,9 @@ __device__ __forceinline__ uint32_t fast_lanes_per_unit(uint32_t count, int warp
 __global__ void __launch_bounds__(kFastThreads, 1)
 k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
               const int32_t *perm, int count_idx, int work_idx, int max_warps, uint32_t *back, int64_t back_rows,
-              int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *gen_list, uint32_t *counters) {
+              int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *flag_list, int flag_idx, uint32_t *counters) {
+  // flag_list / flag_idx: where sentences with near-tied candidates go -- the list of k_encode_warp
+  // (keeps kWarpCapc candidates per position) when that kernel follows, else the general tier's
   extern __shared__ __align__(16) uint32_t smem[];
   uint32_t *units_hot = smem;
   float *score_hot = (float *)(smem + fp.k_units);
@@ -493,7 +495,8 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
                                      ring_bk + threadIdx.x, txt + threadIdx.x, kFastThreads, myback,
                                      stage + fast_stage_base(off, c0, t), &st);
       if (st) {
-        gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
+        flag_list[atomicAdd(&counters[flag_idx], 1u)] = t;
+        if (flag_idx != C_NGEN) atomicAdd(&counters[C_NRETRY], 1u);
       } else {
         cnt[t] = c;
       }
@@ -1678,8 +1681,10 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       size_t back_bytes = (size_t)back_rows * M->sm_count * kFastThreads * 4;
       if (has_long) back_bytes = std::max(back_bytes, (size_t)back_rows_long * M->sm_count * long_warps * 32 * 4);
       if (M->fast_kind == 1 && (rc = M->w_back.ensure(back_bytes))) return rc;
-      if (has_long && (rc = M->w_vitl.ensure((size_t)std::min<int64_t>(cn, raw / kFastMaxRaw + 1) * 4))) return rc;
-      if (has_long && (rc = M->w_longlist.ensure((size_t)std::min<int64_t>(cn, raw / kFastMaxRaw + 1) * 4))) return rc;
+      // (with k_encode_warp the long-line list also takes the sentences k_encode_fast flags)
+      const int64_t long_cap = warp_ok ? cn : std::min<int64_t>(cn, raw / kFastMaxRaw + 1);
+      if ((has_long || warp_ok) && (rc = M->w_vitl.ensure((size_t)long_cap * 4))) return rc;
+      if ((has_long || warp_ok) && (rc = M->w_longlist.ensure((size_t)long_cap * 4))) return rc;
       const int64_t max_n_long = has_long ? std::min<int64_t>(cn, raw / kFastMaxRaw + 1) : 0;
       const unsigned gsort = (unsigned)((cn + kSortTile - 1) / kSortTile);
       const unsigned gsent = (unsigned)((cn + 255) / 256), glong = (unsigned)((max_n_long + 255) / 256);
@@ -1748,13 +1753,16 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       const int cnt_a = C_NFAST, work_a = C_WORK, cnt_b = C_NLONG, work_b = C_WORK_LONG;
       if ((rc = kev_record(M, st, 0, T_ENCODE))) return rc;
       if (M->fast_kind == 1) {
+        // sentences the one-candidate kernel flags (near ties) are appended to the long-line list
+        // when k_encode_warp follows: it keeps kWarpCapc candidates per position itself
         k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
             kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
-            (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
-        if (has_long && warp_ok) {
-          // one warp per long line, exact candidate lists (spm_warp.cuh); back records:
-          // kWarpCapc rows of `wstride` per resident warp, at most 4 GiB in all; longest lines first
+            (uint32_t *)M->w_status.p, (int32_t *)(warp_ok ? M->w_longlist.p : M->w_genlist.p),
+            warp_ok ? C_NLONG : C_NGEN, d_counters);
+        if (warp_ok) {
+          // one warp per line, exact candidate lists (spm_warp.cuh); back records: kWarpCapc rows of
+          // `wstride` per resident warp, at most 4 GiB in all; longest lines first
           const int64_t wstride = 3 * max_long + 136;
           const int64_t wblocks = std::max<int64_t>(
               1, std::min<int64_t>(5 * (int64_t)M->sm_count, (4096ll << 20) / (wstride * 4 * kWarpCapc * kWarpWarps)));
@@ -1763,13 +1771,15 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
                                           (int32_t *)M->w_vitl.p, d_counters);
           k_encode_warp<<<(unsigned)wblocks, kWarpWarps * 32, 0, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-              (const int32_t *)M->w_vitl.p, cnt_b, work_b, (uint32_t *)M->w_wback.p, wstride, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
-              (int32_t *)M->w_genlist.p, d_counters);
+              (const int32_t *)M->w_vitl.p, cnt_b, work_b, (uint32_t *)M->w_wback.p, wstride, (int32_t *)M->w_stage.p,
+              (int32_t *)M->w_cnt.p, (int32_t *)M->w_genlist.p, d_counters);
+          launches += 2;
         } else if (has_long) {
           k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
               long_warps, (uint32_t *)M->w_back.p, back_rows_long, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
-              (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, d_counters);
+              (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, C_NGEN, d_counters);
+          launches += 1;
         }
       } else {
         k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
@@ -1781,9 +1791,10 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
               long_warps, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
               (int32_t *)M->w_genlist.p, d_counters);
+        launches += has_long ? 1 : 0;
       }
       if ((rc = kev_record(M, st, 1))) return rc;
-      launches += has_long ? 2 : 1;
+      launches += 1;
       CUDA_TRY(cudaGetLastError());
       k_publish<<<1, 32, 0, st>>>(d_counters, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
       CUDA_TRY(cudaStreamSynchronize(st));
@@ -1792,7 +1803,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       tr("fast kernel done, chunk", (long)kc);
       if (host && (rc = flush_outputs(kc))) return rc;   // earlier chunks are complete by now
       n_general += hc[C_NGEN];
-      n_viterbi += hc[C_NFAST] + hc[C_NLONG];
+      n_viterbi += hc[C_NFAST] + hc[C_NLONG] - hc[C_NRETRY];
       n_memo_words += hc[C_NNEW];
       if ((rc = run_general(M, st, d_text, d_off, c0, (const int32_t *)M->w_genlist.p, hc[C_NGEN], false,
                             &launches)))
