@@ -112,6 +112,56 @@ const char *spm_cuda_last_error(void);
 int spm_cuda_split_lines(const spm_cuda_model *model, const char *buf, int64_t len, char *text, int64_t *offsets,
                          int64_t capacity, int64_t *n_lines, int memory_space, void *cuda_stream);
 
+/* ---- Pieces / SentencePieceText (the step after the path) ------
+ * Replaces a loop of SentencePieceProcessor::Encode(input, SentencePieceText*)
+ * (src/sentencepiece_processor.h:258, .cc:560-573 -> PopulateSentencePieceText :488-551 ->
+ * ApplyExtraOptions :945-979), i.e. what EncodeAsPieces / EncodeAsSerializedProto return.
+ * Per final piece k of sentence i (k in [id_offsets[i], id_offsets[i+1])):
+ *   ids[k]                       SentencePiece.id
+ *   begin[k], end[k]             SentencePiece.begin / .end: byte span of the surface in the INPUT
+ *                                sentence (norm_to_orig at both ends, src/normalizer.cc:132-206)
+ *   nbegin[k], nend[k]           byte span of the piece in the NORMALIZED sentence; the piece string
+ *                                is norm_text[norm_offsets[i] + nbegin[k] .. + nend[k]) -- for an
+ *                                unknown piece that is the merged run of unknown characters
+ *                                (.cc:525-529), for every other piece it equals IdToPiece(id).
+ *   A bos / eos piece added by the extra options has nbegin = nend = -1 and begin = end = 0
+ *   (the reference leaves surface / begin / end unset); its string is IdToPiece(id).
+ * norm_text / norm_offsets[n+1]: the normalized sentences as CSR (Normalizer::Normalize).
+ * The five per-piece arrays share ids_capacity.  RESOURCE_EXHAUSTED when ids_capacity or
+ * norm_capacity is too small (id_offsets[n] / norm_offsets[n] hold the sizes to retry with);
+ * other errors as spm_cuda_encode_batch. */
+int spm_cuda_encode_batch_pieces(const spm_cuda_model *model, const char *text, const int64_t *text_offsets,
+                                 int64_t n, uint32_t extra_options, int32_t *ids, int32_t *begin, int32_t *end,
+                                 int32_t *nbegin, int32_t *nend, int64_t ids_capacity, int64_t *id_offsets,
+                                 char *norm_text, int64_t norm_capacity, int64_t *norm_offsets, int memory_space,
+                                 void *cuda_stream);
+
+/* ---- Batch Decode ----------------------------------------------
+ * Replaces a loop of SentencePieceProcessor::Decode(const std::vector<int>&, std::string*)
+ * (src/sentencepiece_processor.h:252, .cc:670-733): CONTROL pieces decode to "", the unknown
+ * id to TrainerSpec.unk_surface, every other piece to its string with U+2581 -> ' ', after
+ * dropping one leading U+2581 while the text is still empty.  CSR ids in, CSR text out
+ * (text_offsets[n+1]).  OUT_OF_RANGE for an id outside [0, GetPieceSize());
+ * RESOURCE_EXHAUSTED when text_capacity is too small (text_offsets[n] = bytes needed). */
+int spm_cuda_decode_batch(const spm_cuda_model *model, const int32_t *ids, const int64_t *id_offsets, int64_t n,
+                          char *text, int64_t text_capacity, int64_t *text_offsets, int memory_space,
+                          void *cuda_stream);
+
+/* ---- Dense / sparse layouts of a CSR result ---------------------
+ * The output shapes of the reference's only batch API, the TF ops
+ * (tensorflow/sentencepiece_processor_ops.cc:330-428), from the DEVICE-resident CSR that
+ * spm_cuda_encode_batch(SPM_CUDA_DEVICE) leaves behind (all pointers are device pointers,
+ * except max_len):
+ *   csr_max_len   *max_len (host) = longest row              (dense_shape[1], :339-343)
+ *   csr_to_dense  values[n, max_len] padded with `pad`, seq_len[n]      (:391-428)
+ *   csr_to_sparse indices[nnz, 2] = (row, column) of every id; values = ids (:345-378) */
+int spm_cuda_csr_max_len(const spm_cuda_model *model, const int64_t *id_offsets, int64_t n, int64_t *max_len,
+                         void *cuda_stream);
+int spm_cuda_csr_to_dense(const spm_cuda_model *model, const int32_t *ids, const int64_t *id_offsets, int64_t n,
+                          int32_t pad, int32_t *values, int64_t max_len, int32_t *seq_len, void *cuda_stream);
+int spm_cuda_csr_to_sparse(const spm_cuda_model *model, const int64_t *id_offsets, int64_t n, int64_t *indices,
+                           void *cuda_stream);
+
 /* ---- Unigram-trainer E-step (optional kernel) ----------------
  * Replaces the per-thread loop of unigram::Trainer::RunEStep
  * (src/unigram_model_trainer.cc:237-287): for every (word, freq) build the lattice of a

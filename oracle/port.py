@@ -56,6 +56,12 @@ def lib():
         L.oracle_encode_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                           ctypes.c_int64, ctypes.c_uint32, ctypes.c_void_p,
                                           ctypes.c_int64, ctypes.c_void_p]
+        L.oracle_encode_pieces_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                                 ctypes.c_uint32] + [ctypes.c_void_p] * 5 + [
+                                                 ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                                 ctypes.c_void_p]
+        L.oracle_decode_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                          ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -121,3 +127,39 @@ class OracleProcessor:
         if n < 0:
             raise RuntimeError("oracle_normalize capacity")
         return out.raw[:n], (n2o[: n + 1].copy() if n else n2o[:0])
+
+    def encode_pieces_batch(self, text, off):
+        """SentencePieceText view as CSR arrays (layout of spm_cuda_encode_batch_pieces):
+        dict(ids, begin, end, nbegin, nend, id_off, norm, norm_off)."""
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        n = len(off) - 1
+        cap = int(off[-1] - off[0]) + 34 * n + 64
+        ncap = 40 * int(off[-1] - off[0]) + 8 * n + 64
+        a = {k: np.empty(cap, dtype=np.int32) for k in ("ids", "begin", "end", "nbegin", "nend")}
+        id_off = np.zeros(n + 1, dtype=np.int64)
+        norm = np.empty(ncap, dtype=np.uint8)
+        norm_off = np.zeros(n + 1, dtype=np.int64)
+        rc = self.L.oracle_encode_pieces_batch(self.h, text.ctypes.data, off.ctypes.data, n, self.opts,
+                                               a["ids"].ctypes.data, a["begin"].ctypes.data, a["end"].ctypes.data,
+                                               a["nbegin"].ctypes.data, a["nend"].ctypes.data, cap,
+                                               id_off.ctypes.data, norm.ctypes.data, ncap, norm_off.ctypes.data)
+        if rc == 8:
+            raise RuntimeError("oracle capacity exceeded")
+        self.last_status = rc
+        out = {k: v[: id_off[n]].copy() for k, v in a.items()}
+        out.update(id_off=id_off, norm=norm[: norm_off[n]].copy(), norm_off=norm_off)
+        return out
+
+    def decode_batch(self, ids, id_off):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        id_off = np.ascontiguousarray(id_off, dtype=np.int64)
+        n = len(id_off) - 1
+        cap = 64 * len(ids) + 64
+        text = np.empty(cap, dtype=np.uint8)
+        toff = np.zeros(n + 1, dtype=np.int64)
+        rc = self.L.oracle_decode_batch(self.h, ids.ctypes.data, id_off.ctypes.data, n, text.ctypes.data, cap,
+                                        toff.ctypes.data)
+        if rc:
+            raise RuntimeError("oracle_decode_batch: code %d" % rc)
+        return text[: toff[n]].copy(), toff

@@ -39,6 +39,14 @@ def lib():
         L.ref_encode_count.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                        ctypes.c_int64, ctypes.c_int]
         L.ref_normalize.restype = ctypes.c_int64
+        L.ref_encode_proto_batch.restype = ctypes.c_int64
+        L.ref_encode_proto_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                             ctypes.c_int, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p,
+                                             ctypes.c_int]
+        L.ref_decode_batch.restype = ctypes.c_int64
+        L.ref_decode_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                       ctypes.c_int, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p,
+                                       ctypes.c_int]
         L.ref_normalize.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64,
                                     ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
         if hasattr(L, "ref_train"):
@@ -113,6 +121,44 @@ class RefProcessor:
         text = np.frombuffer(b, dtype=np.uint8)
         ids, _ = self.encode_batch(text, np.array([0, len(b)], dtype=np.int64))
         return ids.tolist()
+
+    def encode_proto_batch(self, text, off, threads=1):
+        """EncodeAsSerializedProto per sentence -> (proto bytes uint8[], proto_off int64[n+1])."""
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        n = len(off) - 1
+        poff = np.zeros(n + 1, dtype=np.int64)
+        tot = self.L.ref_encode_proto_batch(self.h, text.ctypes.data, off.ctypes.data, n, threads, None, 0,
+                                            poff.ctypes.data, 0)
+        out = np.empty(max(int(tot), 1), dtype=np.uint8)
+        self.L.ref_encode_proto_batch(self.h, text.ctypes.data, off.ctypes.data, n, threads, out.ctypes.data,
+                                      int(tot), poff.ctypes.data, 0)
+        return out[: int(tot)], poff
+
+    def encode_pieces_count(self, text, off, threads=1):
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        return self.L.ref_encode_proto_batch(self.h, text.ctypes.data, off.ctypes.data, len(off) - 1, threads,
+                                             None, 0, None, 1)
+
+    def decode_batch(self, ids, id_off, threads=1):
+        """Decode(ids) per sentence -> (text uint8[], text_off int64[n+1])."""
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        id_off = np.ascontiguousarray(id_off, dtype=np.int64)
+        n = len(id_off) - 1
+        toff = np.zeros(n + 1, dtype=np.int64)
+        tot = self.L.ref_decode_batch(self.h, ids.ctypes.data, id_off.ctypes.data, n, threads, None, 0,
+                                      toff.ctypes.data, 0)
+        out = np.empty(max(int(tot), 1), dtype=np.uint8)
+        self.L.ref_decode_batch(self.h, ids.ctypes.data, id_off.ctypes.data, n, threads, out.ctypes.data, int(tot),
+                                toff.ctypes.data, 0)
+        return out[: int(tot)], toff
+
+    def decode_count(self, ids, id_off, threads=1):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        id_off = np.ascontiguousarray(id_off, dtype=np.int64)
+        return self.L.ref_decode_batch(self.h, ids.ctypes.data, id_off.ctypes.data, len(id_off) - 1, threads,
+                                       None, 0, None, 1)
 
     def normalize(self, s):
         b = s.encode() if isinstance(s, str) else bytes(s)

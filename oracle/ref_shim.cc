@@ -11,6 +11,8 @@
 //   SentencePieceProcessor::Encode(ids)              src/sentencepiece_processor.h:244
 //   SentencePieceProcessor::SetEncodeExtraOptions    src/sentencepiece_processor.h:210
 //   SentencePieceProcessor::SetVocabulary            src/sentencepiece_processor.h:224
+//   SentencePieceProcessor::EncodeAsSerializedProto  src/sentencepiece_processor.h:381 (.cc:752-758)
+//   SentencePieceProcessor::Decode(ids, string*)     src/sentencepiece_processor.h:252 (.cc:670-733)
 //   normalizer::Normalizer::Normalize                src/normalizer.h
 //   SentencePieceTrainer::Train(args)                src/sentencepiece_trainer.h:59
 //   normalizer::Builder::CompileCharsMap             src/builder.h (fixture charsmaps for the golden tests)
@@ -22,6 +24,7 @@
 #include <vector>
 
 #include "normalizer.h"
+#include "sentencepiece.pb.h"
 #include "sentencepiece_model.pb.h"
 #include "sentencepiece_processor.h"
 #ifdef REF_WITH_TRAINER
@@ -145,6 +148,77 @@ int64_t ref_encode_count(void *p, const char *text, const int64_t *off, int64_t 
   int64_t s = 0;
   for (auto v : tot) s += v;
   return s;
+}
+
+// Encode(input, SentencePieceText*) per sentence, `threads` std::threads; the
+// serialized SentencePieceText protos go back to back into out (CSR out_off[n+1]).
+// Two-call protocol as above: out == nullptr => sizes only.  count_only: nothing is
+// kept (timed CPU baseline of the pieces path), returns the total proto bytes.
+int64_t ref_encode_proto_batch(void *p, const char *text, const int64_t *off, int64_t n, int threads,
+                               char *out, int64_t cap, int64_t *out_off, int count_only) {
+  auto *h = static_cast<RefHandle *>(p);
+  if (threads < 1) threads = 1;
+  std::vector<std::string> res(count_only ? 0 : n);
+  std::vector<int64_t> tot(threads, 0);
+  auto work = [&](int t) {
+    const int64_t lo = n * t / threads, hi = n * (t + 1) / threads;
+    for (int64_t i = lo; i < hi; ++i) {
+      sentencepiece::SentencePieceText spt;
+      auto st = h->sp.Encode(std::string(text + off[i], off[i + 1] - off[i]), &spt);
+      if (!st.ok()) spt.Clear();
+      if (count_only) tot[t] += (int64_t)spt.pieces_size();
+      else res[i] = spt.SerializeAsString();
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 0; t < threads; ++t) th.emplace_back(work, t);
+  for (auto &x : th) x.join();
+  if (count_only) {
+    int64_t s = 0;
+    for (auto v : tot) s += v;
+    return s;
+  }
+  out_off[0] = 0;
+  for (int64_t i = 0; i < n; ++i) out_off[i + 1] = out_off[i] + (int64_t)res[i].size();
+  if (out != nullptr) {
+    if (out_off[n] > cap) return -8;
+    for (int64_t i = 0; i < n; ++i) std::memcpy(out + out_off[i], res[i].data(), res[i].size());
+  }
+  return out_off[n];
+}
+
+// Decode(ids, std::string*) per sentence; CSR in, CSR out (same two-call protocol).
+int64_t ref_decode_batch(void *p, const int32_t *ids, const int64_t *id_off, int64_t n, int threads,
+                         char *out, int64_t cap, int64_t *out_off, int count_only) {
+  auto *h = static_cast<RefHandle *>(p);
+  if (threads < 1) threads = 1;
+  std::vector<std::string> res(count_only ? 0 : n);
+  std::vector<int64_t> tot(threads, 0);
+  auto work = [&](int t) {
+    const int64_t lo = n * t / threads, hi = n * (t + 1) / threads;
+    std::string text;
+    for (int64_t i = lo; i < hi; ++i) {
+      std::vector<int> v(ids + id_off[i], ids + id_off[i + 1]);
+      h->sp.Decode(v, &text).IgnoreError();
+      if (count_only) tot[t] += (int64_t)text.size();
+      else res[i] = text;
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 0; t < threads; ++t) th.emplace_back(work, t);
+  for (auto &x : th) x.join();
+  if (count_only) {
+    int64_t s = 0;
+    for (auto v : tot) s += v;
+    return s;
+  }
+  out_off[0] = 0;
+  for (int64_t i = 0; i < n; ++i) out_off[i + 1] = out_off[i] + (int64_t)res[i].size();
+  if (out != nullptr) {
+    if (out_off[n] > cap) return -8;
+    for (int64_t i = 0; i < n; ++i) std::memcpy(out + out_off[i], res[i].data(), res[i].size());
+  }
+  return out_off[n];
 }
 
 // Normalizer only.  out must hold cap bytes; n2o (may be null) cap+1 entries.

@@ -14,6 +14,7 @@ import os
 import numpy as np
 
 from . import build as _build
+from . import spt
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = _build.LIB
@@ -55,6 +56,12 @@ def lib():
         L.spm_cuda_estep_vocab_size.argtypes = [vp]
         L.spm_cuda_estep_run.argtypes = [vp, vp, vp, vp, i64, ctypes.c_double, vp, vp, vp, i32, vp]
         L.spm_cuda_split_lines.argtypes = [vp, vp, i64, vp, vp, i64, ctypes.POINTER(i64), i32, vp]
+        L.spm_cuda_encode_batch_pieces.argtypes = [vp, vp, vp, i64, ctypes.c_uint32, vp, vp, vp, vp, vp, i64, vp,
+                                                   vp, i64, vp, i32, vp]
+        L.spm_cuda_decode_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, i32, vp]
+        L.spm_cuda_csr_max_len.argtypes = [vp, vp, i64, ctypes.POINTER(i64), vp]
+        L.spm_cuda_csr_to_dense.argtypes = [vp, vp, vp, i64, i32, vp, i64, vp, vp]
+        L.spm_cuda_csr_to_sparse.argtypes = [vp, vp, i64, vp, vp]
         _lib = L
     return _lib
 
@@ -240,6 +247,155 @@ class SentencePieceProcessor:
         text, off = self.split_lines(buf)
         return self.encode_packed(text, off)
 
+    # ---- pieces / SentencePieceText (sentencepiece_processor.h:258, 338-381)
+    def encode_pieces_packed(self, text, offsets, stream=None):
+        """Host CSR in -> dict of host arrays: ids, begin, end (spans in the input), nbegin, nend
+        (spans in the normalized text), id_off, norm (normalized text), norm_off
+        (layout of spm_cuda_encode_batch_pieces, include/spm_cuda.h)."""
+        self._need()
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        n = len(offsets) - 1
+        raw = int(offsets[-1] - offsets[0])
+        cap, ncap = max(64, raw // 2 + 4 * n), max(64, raw + raw // 2 + 8 * n)
+        id_off = np.zeros(n + 1, dtype=np.int64)
+        norm_off = np.zeros(n + 1, dtype=np.int64)
+        while True:
+            a = {k: np.empty(cap, dtype=np.int32) for k in ("ids", "begin", "end", "nbegin", "nend")}
+            norm = np.empty(ncap, dtype=np.uint8)
+            rc = lib().spm_cuda_encode_batch_pieces(
+                self._h, text.ctypes.data, offsets.ctypes.data, n, self._opts, a["ids"].ctypes.data,
+                a["begin"].ctypes.data, a["end"].ctypes.data, a["nbegin"].ctypes.data, a["nend"].ctypes.data, cap,
+                id_off.ctypes.data, norm.ctypes.data, ncap, norm_off.ctypes.data, HOST, stream)
+            if rc == 8 and (int(id_off[n]) > cap or int(norm_off[n]) > ncap):
+                cap, ncap = max(cap, int(id_off[n])), max(ncap, int(norm_off[n]))
+                continue
+            _check(rc)
+            out = {k: v[: id_off[n]] for k, v in a.items()}
+            out.update(id_off=id_off, norm=norm[: norm_off[n]], norm_off=norm_off)
+            return out
+
+    def encode_pieces_device(self, text, offsets, ids, begin, end, nbegin, nend, id_offsets, norm_text, norm_offsets,
+                             stream=None):
+        """Device-resident variant on torch CUDA tensors (uint8, int64, 5 x int32 of equal size,
+        int64, uint8, int64)."""
+        import torch
+        self._need()
+        if stream is None:
+            stream = torch.cuda.current_stream(text.device).cuda_stream
+        n = offsets.numel() - 1
+        _check(lib().spm_cuda_encode_batch_pieces(
+            self._h, text.data_ptr(), offsets.data_ptr(), n, self._opts, ids.data_ptr(), begin.data_ptr(),
+            end.data_ptr(), nbegin.data_ptr(), nend.data_ptr(), ids.numel(), id_offsets.data_ptr(),
+            norm_text.data_ptr(), norm_text.numel(), norm_offsets.data_ptr(), DEVICE, stream))
+
+    def _one(self, input):
+        b = input.encode("utf-8") if isinstance(input, str) else bytes(input)
+        text = np.frombuffer(b, dtype=np.uint8)
+        off = np.array([0, len(b)], dtype=np.int64)
+        return b, text, off, self.encode_pieces_packed(text, off)
+
+    def EncodeAsPieces(self, input):
+        b, text, off, res = self._one(input)
+        return [p[0].decode("utf-8", "replace") for p in spt.sentence_pieces(0, text, off, res, self._piece_bytes)]
+
+    def EncodeAsSerializedProto(self, input):
+        b, text, off, res = self._one(input)
+        return spt.serialize(b, spt.sentence_pieces(0, text, off, res, self._piece_bytes))
+
+    def encode_as_serialized_protos(self, text, offsets):
+        """Batch EncodeAsSerializedProto: list of serialized SentencePieceText, one per sentence."""
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        res = self.encode_pieces_packed(text, offsets)
+        return [spt.serialize(text[offsets[i]:offsets[i + 1]].tobytes(),
+                              spt.sentence_pieces(i, text, offsets, res, self._piece_bytes))
+                for i in range(len(offsets) - 1)]
+
+    # ---- decode (sentencepiece_processor.h:252, .cc:670-733; SURVEY 8(f) rank 4)
+    def decode_packed(self, ids, id_offsets, stream=None):
+        """Host CSR ids -> (text uint8[], text_offsets int64[n+1])."""
+        self._need()
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        id_offsets = np.ascontiguousarray(id_offsets, dtype=np.int64)
+        n = len(id_offsets) - 1
+        toff = np.zeros(n + 1, dtype=np.int64)
+        cap = max(64, 6 * len(ids))
+        while True:
+            text = np.empty(cap, dtype=np.uint8)
+            rc = lib().spm_cuda_decode_batch(self._h, ids.ctypes.data, id_offsets.ctypes.data, n, text.ctypes.data,
+                                             cap, toff.ctypes.data, HOST, stream)
+            if rc == 8 and int(toff[n]) > cap:
+                cap = int(toff[n])
+                continue
+            _check(rc)
+            return text[: toff[n]], toff
+
+    def decode_device(self, ids, id_offsets, text, text_offsets, stream=None):
+        """Device CSR in/out on torch CUDA tensors (int32, int64, uint8, int64)."""
+        import torch
+        self._need()
+        if stream is None:
+            stream = torch.cuda.current_stream(ids.device).cuda_stream
+        n = id_offsets.numel() - 1
+        _check(lib().spm_cuda_decode_batch(self._h, ids.data_ptr(), id_offsets.data_ptr(), n, text.data_ptr(),
+                                           text.numel(), text_offsets.data_ptr(), DEVICE, stream))
+
+    def DecodeIds(self, ids):
+        text, _ = self.decode_packed(np.asarray(ids, dtype=np.int32), np.array([0, len(ids)], dtype=np.int64))
+        return text.tobytes().decode("utf-8", "replace")
+
+    Decode = DecodeIds
+
+    # ---- dense / sparse layouts of the TF ops (tensorflow/sentencepiece_processor_ops.cc:330-428;
+    # SURVEY 8(f) rank 3): torch CUDA tensors in and out
+    def csr_to_dense(self, ids, id_offsets, pad=0, stream=None):
+        """(ids int32[], id_offsets int64[n+1]) on the GPU -> (values int32[n, max_len], seq_len int32[n])."""
+        import torch
+        self._need()
+        if stream is None:
+            stream = torch.cuda.current_stream(ids.device).cuda_stream
+        n = id_offsets.numel() - 1
+        mx = ctypes.c_int64(0)
+        _check(lib().spm_cuda_csr_max_len(self._h, id_offsets.data_ptr(), n, ctypes.byref(mx), stream))
+        values = torch.empty((n, mx.value), dtype=torch.int32, device=ids.device)
+        seq_len = torch.empty(n, dtype=torch.int32, device=ids.device)
+        _check(lib().spm_cuda_csr_to_dense(self._h, ids.data_ptr(), id_offsets.data_ptr(), n, int(pad),
+                                           values.data_ptr(), mx.value, seq_len.data_ptr(), stream))
+        return values, seq_len
+
+    def csr_to_sparse(self, ids, id_offsets, stream=None):
+        """-> (indices int64[nnz, 2], values int32[nnz], dense_shape (n, max_len))."""
+        import torch
+        self._need()
+        if stream is None:
+            stream = torch.cuda.current_stream(ids.device).cuda_stream
+        n = id_offsets.numel() - 1
+        mx = ctypes.c_int64(0)
+        _check(lib().spm_cuda_csr_max_len(self._h, id_offsets.data_ptr(), n, ctypes.byref(mx), stream))
+        nnz = ids.numel()
+        indices = torch.empty((nnz, 2), dtype=torch.int64, device=ids.device)
+        _check(lib().spm_cuda_csr_to_sparse(self._h, id_offsets.data_ptr(), n, indices.data_ptr(), stream))
+        return indices, ids, (n, mx.value)
+
+    def encode_dense(self, sentences, pad=0):
+        """The TF op SentencepieceEncodeDense on the GPU: list of str/bytes ->
+        (values int32[n, max_len], seq_len int32[n]) as torch CUDA tensors."""
+        import torch
+        bs = [s.encode("utf-8") if isinstance(s, str) else bytes(s) for s in sentences]
+        off = np.zeros(len(bs) + 1, dtype=np.int64)
+        if bs:
+            np.cumsum([len(b) for b in bs], out=off[1:])
+        dev = torch.device("cuda", self._device)
+        text = torch.from_numpy(np.frombuffer(b"".join(bs) + b"\0", dtype=np.uint8).copy()).to(dev)
+        d_off = torch.from_numpy(off).to(dev)
+        cap = int(off[-1]) + 4 * len(bs) + 64
+        ids = torch.empty(cap, dtype=torch.int32, device=dev)
+        id_off = torch.empty(len(bs) + 1, dtype=torch.int64, device=dev)
+        self.encode_device(text, d_off, ids, id_off)
+        total = int(id_off[-1].item())
+        return self.csr_to_dense(ids[:total], id_off, pad)
+
     STAGES = ("encode", "normalize", "memo_collect", "memo_words", "memo_emit", "compact")
 
     def last_stats(self):
@@ -311,6 +467,9 @@ class SentencePieceProcessor:
     # snake_case aliases of the reference's python module
     load = Load
     encode_as_ids = EncodeAsIds
+    encode_as_pieces = EncodeAsPieces
+    encode_as_serialized_proto = EncodeAsSerializedProto
+    decode_ids = DecodeIds
     get_piece_size = GetPieceSize
     piece_to_id = PieceToId
     id_to_piece = IdToPiece

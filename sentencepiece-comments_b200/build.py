@@ -6,7 +6,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib", "libspm_cuda.so")
 SOURCES = ["spm_kernels.cu", "spm_model.cc"]
-HEADERS = ["spm_core.cuh", "spm_fast.cuh", "spm_memo.cuh", "spm_estep.cuh", "spm_warp.cuh", "spm_model.h", os.path.join("..", "..", "include", "spm_cuda.h")]
+HEADERS = ["spm_core.cuh", "spm_fast.cuh", "spm_memo.cuh", "spm_estep.cuh", "spm_warp.cuh", "spm_pieces.inc", "spm_model.h", os.path.join("..", "..", "include", "spm_cuda.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 

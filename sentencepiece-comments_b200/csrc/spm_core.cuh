@@ -227,31 +227,47 @@ SPM_HD int normalize_prefix(const ModelView &m, const uint8_t *in, int64_t n, co
 
 // Whole-sentence normalisation (src/normalizer.cc:88-211) into out[0..cap).
 // Returns the normalized length, or -1 when it does not fit (tier overflow).
-// norm_to_orig is not produced (ids do not need it).
-SPM_HDN int32_t normalize_sentence(const ModelView &m, const uint8_t *in, int64_t n, uint8_t *out,
-                                   int64_t cap) {
+// ALIGN: also writes norm_to_orig (n2o[0..len], one entry per normalized byte
+// plus the final one; :132-153,:166-176,:191-206) -- ids do not need it, the
+// pieces / SentencePieceText output does.
+template <bool ALIGN>
+SPM_HDN int32_t normalize_sentence_t(const ModelView &m, const uint8_t *in, int64_t n, uint8_t *out,
+                                     int64_t cap, int32_t *n2o) {
   if (n == 0) return 0;
   const uint8_t *rep; int rl;
+  int32_t consumed = 0;
   if (m.remove_extra_ws) {  // strip leading spaces (:103-112)
     while (n > 0) {
       const int c = normalize_prefix(m, in, n, &rep, &rl);
       if (!(rl == 1 && rep != nullptr && rep[0] == ' ')) break;
-      in += c; n -= c;
+      in += c; n -= c; consumed += c;
     }
   }
   if (n == 0) return 0;
   int64_t o = 0;
   const bool esc = m.escape_ws;
-  if (!m.ws_suffix && m.add_dummy_prefix) {  // add_ws (:132-153)
-    if (esc) { if (o + 3 > cap) return -1; out[o] = 0xE2; out[o + 1] = 0x96; out[o + 2] = 0x81; o += 3; }
-    else { if (o + 1 > cap) return -1; out[o++] = ' '; }
-  }
+  auto put_ws = [&]() -> bool {   // add_ws (:132-153) and the escaped space (:166-172)
+    if (esc) {
+      if (o + 3 > cap) return false;
+      out[o] = 0xE2; out[o + 1] = 0x96; out[o + 2] = 0x81;
+      if (ALIGN) { n2o[o] = consumed; n2o[o + 1] = consumed; n2o[o + 2] = consumed; }
+      o += 3;
+    } else {
+      if (o + 1 > cap) return false;
+      if (ALIGN) n2o[o] = consumed;
+      out[o++] = ' ';
+    }
+    return true;
+  };
+  if (!m.ws_suffix && m.add_dummy_prefix && !put_ws()) return -1;
   bool is_prev_space = m.remove_extra_ws;
   while (n > 0) {
     const int c = normalize_prefix(m, in, n, &rep, &rl);
     if (rep == nullptr) {  // malformed byte -> U+FFFD
       if (o + 3 > cap) return -1;
-      out[o] = 0xEF; out[o + 1] = 0xBF; out[o + 2] = 0xBD; o += 3;
+      out[o] = 0xEF; out[o + 1] = 0xBF; out[o + 2] = 0xBD;
+      if (ALIGN) { n2o[o] = consumed; n2o[o + 1] = consumed; n2o[o + 2] = consumed; }
+      o += 3;
       is_prev_space = false;
     } else {
       int k = 0;
@@ -260,28 +276,39 @@ SPM_HDN int32_t normalize_sentence(const ModelView &m, const uint8_t *in, int64_
         for (; k < rl; ++k) {
           const uint8_t b = rep[k];
           if (esc && b == ' ') {
-            if (o + 3 > cap) return -1;
-            out[o] = 0xE2; out[o + 1] = 0x96; out[o + 2] = 0x81; o += 3;
+            if (!put_ws()) return -1;
           } else {
             if (o + 1 > cap) return -1;
+            if (ALIGN) n2o[o] = consumed;
             out[o++] = b;
           }
         }
         is_prev_space = rep[rl - 1] == ' ';
       }
     }
-    in += c; n -= c;
+    in += c; n -= c; consumed += c;
     if (!m.remove_extra_ws) is_prev_space = false;
   }
-  if (m.remove_extra_ws) {  // strip trailing whitespace symbols (:191-201)
-    if (esc) { while (o >= 3 && out[o - 3] == 0xE2 && out[o - 2] == 0x96 && out[o - 1] == 0x81) o -= 3; }
-    else { while (o >= 1 && out[o - 1] == ' ') o -= 1; }
+  if (m.remove_extra_ws) {  // strip trailing whitespace symbols (:191-201); consumed = n2o[new length]
+    if (esc) {
+      while (o >= 3 && out[o - 3] == 0xE2 && out[o - 2] == 0x96 && out[o - 1] == 0x81) {
+        o -= 3;
+        if (ALIGN) consumed = n2o[o];
+      }
+    } else {
+      while (o >= 1 && out[o - 1] == ' ') {
+        o -= 1;
+        if (ALIGN) consumed = n2o[o];
+      }
+    }
   }
-  if (m.ws_suffix && m.add_dummy_prefix) {
-    if (esc) { if (o + 3 > cap) return -1; out[o] = 0xE2; out[o + 1] = 0x96; out[o + 2] = 0x81; o += 3; }
-    else { if (o + 1 > cap) return -1; out[o++] = ' '; }
-  }
+  if (m.ws_suffix && m.add_dummy_prefix && !put_ws()) return -1;
+  if (ALIGN) n2o[o] = consumed;   // :204
   return (int32_t)o;
+}
+SPM_HDN int32_t normalize_sentence(const ModelView &m, const uint8_t *in, int64_t n, uint8_t *out,
+                                   int64_t cap) {
+  return normalize_sentence_t<false>(m, in, n, out, cap, nullptr);
 }
 
 // ------------------------------------------------------------------ unigram
@@ -324,10 +351,12 @@ SPM_HD uint64_t pack_rec(uint32_t id, uint32_t len, uint32_t prevslot) {
 // caller reruns the sentence with a larger CAPC).
 //
 // Writes ids (forward order) to out[0..cap) and returns their count; when they
-// do not fit, sets ST_IDS_OVERFLOW and still returns the count.
+// do not fit, sets ST_IDS_OVERFLOW and still returns the count.  out_end (may be
+// null): the byte offset in s where each emitted piece ends (a merged unk run
+// ends where its last character ends) -- piece k is s[out_end[k-1], out_end[k]).
 template <int CAPC>
 SPM_HDN int32_t unigram_encode(const ModelView &m, const uint8_t *s, int32_t n, const UniScratch &sc,
-                               int32_t *out, int32_t cap, uint32_t *status) {
+                               int32_t *out, int32_t cap, uint32_t *status, int32_t *out_end = nullptr) {
   if (n <= 0) return 0;
   const uint32_t mask = (uint32_t)m.ring - 1;
   for (int i = 0; i < m.ring; ++i) sc.ringCnt[i] = 0;
@@ -432,17 +461,24 @@ SPM_HDN int32_t unigram_encode(const ModelView &m, const uint8_t *s, int32_t n, 
     int32_t pos = n, idx = total;
     uint32_t slot = eos_slot;
     int64_t pending = -1;
+    int32_t pend_end = n;
     while (pos > 0) {
       const uint64_t rec = sc.back[(int64_t)slot * sc.stride + pos];
       const int32_t id = (int32_t)(uint32_t)rec;
-      if (pending >= 0 && !(id == m.unk_id && (int32_t)pending == m.unk_id)) {
-        if (pass == 0) ++total; else out[--idx] = (int32_t)pending;
+      const bool merge = pending >= 0 && id == m.unk_id && (int32_t)pending == m.unk_id;
+      if (pending >= 0 && !merge) {
+        if (pass == 0) ++total;
+        else { out[--idx] = (int32_t)pending; if (out_end) out_end[idx] = pend_end; }
       }
+      if (!merge) pend_end = pos;
       pending = id;
       pos -= (int32_t)((rec >> 32) & 0xFFFF);
       slot = (uint32_t)(rec >> 48) & 0xFF;
     }
-    if (pending >= 0) { if (pass == 0) ++total; else out[--idx] = (int32_t)pending; }
+    if (pending >= 0) {
+      if (pass == 0) ++total;
+      else { out[--idx] = (int32_t)pending; if (out_end) out_end[idx] = pend_end; }
+    }
     if (pass == 0 && total > cap) { st |= ST_IDS_OVERFLOW; break; }
   }
   *status |= st;
@@ -458,8 +494,9 @@ SPM_HD int64_t bpe_scratch_words(int64_t n) { return 5 * n + 7 * (3 * n + 4) + 2
 // src/sentencepiece_processor.cc:488-551 (unk-run merge; a CONTROL id leaves
 // normalized bytes unconsumed => INTERNAL error, no ids).
 // Returns the id count (ids forward in out), or -1 for the INTERNAL case.
+// out_end (may be null): as in unigram_encode.
 SPM_HDN int32_t bpe_encode(const ModelView &m, const uint8_t *s, int32_t n, int32_t *w, int32_t *out,
-                           int32_t cap, uint32_t *status) {
+                           int32_t cap, uint32_t *status, int32_t *out_end = nullptr) {
   if (n <= 0) return 0;
   int32_t *begin = w, *size = w + n, *prev = w + 2 * n, *next = w + 3 * n, *freeze = w + 4 * n;
   const int32_t hcap = 3 * n + 4;
@@ -534,13 +571,15 @@ SPM_HDN int32_t bpe_encode(const ModelView &m, const uint8_t *s, int32_t n, int3
   // the last-recorded merge of the same string (rev_merge, :171-189)
   int32_t total = 0;
   bool is_prev_unk = false, control_seen = false;
-  auto emit = [&](int32_t id, uint32_t type) {
+  auto emit = [&](int32_t id, uint32_t type, int32_t end) {
     const bool is_unk = type == T_UNKNOWN;
     if (type == T_CONTROL) {
       control_seen = true;
     } else if (!(is_prev_unk && is_unk)) {
-      if (total < cap) out[total] = id;
+      if (total < cap) { out[total] = id; if (out_end) out_end[total] = end; }
       ++total;
+    } else if (out_end && total - 1 < cap) {
+      out_end[total - 1] = end;   // the unk run grows (sentencepiece_processor.cc:525-529)
     }
     is_prev_unk = is_unk;
   };
@@ -564,7 +603,7 @@ SPM_HDN int32_t bpe_encode(const ModelView &m, const uint8_t *s, int32_t n, int3
           if (eq) split = lleft[j];
         }
       }
-      if (split < 0) { emit(id, type); continue; }
+      if (split < 0) { emit(id, type, b + z); continue; }
       if (sp + 2 > hcap) { *status |= ST_INTERNAL; break; }
       stb[sp] = b + split; sts[sp] = z - split; ++sp;   // right first, left on top
       stb[sp] = b; sts[sp] = split; ++sp;
@@ -611,6 +650,29 @@ SPM_HD int32_t final_id_at(const ExtraPlan &p, const int32_t *core_ids, int32_t 
   j -= p.npre;
   if (j < core) return core_ids[p.flip ? core - 1 - j : j];
   return p.suf[j - core];
+}
+
+
+// SentencePieceText view of final piece j (PopulateSentencePieceText + ApplyExtraOptions,
+// src/sentencepiece_processor.cc:488-551,945-979): the id, its span [nbegin, nend) in the
+// normalized text and the span [begin, end) of its surface in the input (norm_to_orig
+// at both ends).  The bos / eos pieces of the extra options carry no span: nbegin = nend
+// = -1, begin = end = 0 (unset proto fields).
+struct PieceSpan { int32_t id, begin, end, nbegin, nend; };
+SPM_HD PieceSpan final_piece_at(const ExtraPlan &p, const int32_t *core_ids, const int32_t *core_end,
+                                const int32_t *n2o, int32_t core, int32_t j) {
+  PieceSpan r;
+  r.begin = r.end = 0; r.nbegin = r.nend = -1;
+  if (j < p.npre) { r.id = p.pre[j]; return r; }
+  j -= p.npre;
+  if (j >= core) { r.id = p.suf[j - core]; return r; }
+  const int32_t k = p.flip ? core - 1 - j : j;
+  r.id = core_ids[k];
+  r.nbegin = k > 0 ? core_end[k - 1] : 0;
+  r.nend = core_end[k];
+  r.begin = n2o[r.nbegin];
+  r.end = n2o[r.nend];
+  return r;
 }
 
 }  // namespace spmb

@@ -119,7 +119,8 @@ k_gen_normalize(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c
 
 __device__ __forceinline__ void gen_encode_one(const ModelView &mv, int64_t i, int64_t nb, int32_t nl, uint32_t st,
                                                int32_t *w, const uint8_t *norm, int32_t *gstage, int32_t *cnt,
-                                               uint32_t *status, int64_t *srcoff, uint32_t *status_or) {
+                                               uint32_t *status, int64_t *srcoff, uint32_t *status_or,
+                                               int32_t *gends = nullptr) {
   int32_t c = 0;
   if (st == 0) {
     if (mv.model_type == M_UNIGRAM) {
@@ -130,9 +131,9 @@ __device__ __forceinline__ void gen_encode_one(const ModelView &mv, int64_t i, i
       sc.candRec = (uint64_t *)w; w += 2 * mv.ring * kCapc;
       sc.back = (uint64_t *)w;
       sc.stride = nl + 1;
-      c = unigram_encode<kCapc>(mv, norm + nb, nl, sc, gstage + nb, nl, &st);
+      c = unigram_encode<kCapc>(mv, norm + nb, nl, sc, gstage + nb, nl, &st, gends ? gends + nb : nullptr);
     } else {
-      c = bpe_encode(mv, norm + nb, nl, w, gstage + nb, nl, &st);
+      c = bpe_encode(mv, norm + nb, nl, w, gstage + nb, nl, &st, gends ? gends + nb : nullptr);
     }
   }
   cnt[i] = c;
@@ -146,13 +147,13 @@ __global__ void __launch_bounds__(kThreads)
 k_gen_encode(ModelView mv, const int32_t *list, const uint32_t *count, int64_t t0, int64_t tn,
              const int64_t *noff, const uint8_t *norm, const int32_t *nlen, const int64_t *woff, int64_t wbase,
              int32_t *scratch, int32_t *gstage, const uint32_t *gstatus, int32_t *cnt, uint32_t *status, int64_t *srcoff,
-             uint32_t *status_or) {
+             uint32_t *status_or, int32_t *gends) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= tn) return;
   if (count != nullptr && t0 + t >= (int64_t)*count) return;
   const int64_t i = list ? list[t0 + t] : t0 + t;  // chunk-relative sentence index
   gen_encode_one(mv, i, noff[t], nlen[t], gstatus[t], scratch + (woff[t] - wbase), norm, gstage, cnt, status, srcoff,
-                 status_or);
+                 status_or, gends);
 }
 
 // latency variant for short lists (the sentences the fast tier flags): one block per
@@ -1099,6 +1100,9 @@ struct spm_cuda_model {
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
       w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
+  mutable DevBuf px[20];   // workspace of the pieces / decode / dense calls (spm_pieces.inc)
+  mutable bool dec_ready = false;   // decode tables uploaded (px[PX_DECREC], px[PX_DECPOOL])
+  mutable int dec_maxlen = 1;       // longest decoded piece in bytes
   mutable std::vector<int64_t> h_woff;
   mutable double stats[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   mutable cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -1119,7 +1123,10 @@ struct spm_cuda_model {
             &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
             &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
-            &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status};
+            &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status,
+            &m->px[0], &m->px[1], &m->px[2], &m->px[3], &m->px[4], &m->px[5], &m->px[6], &m->px[7], &m->px[8], &m->px[9],
+            &m->px[10], &m->px[11], &m->px[12], &m->px[13], &m->px[14], &m->px[15], &m->px[16], &m->px[17], &m->px[18],
+            &m->px[19]};
   }
 };
 
@@ -1289,7 +1296,7 @@ int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text,
                                          (const int64_t *)M->g_woff.p + a, wbase, (int32_t *)M->g_scratch.p,
                                          (int32_t *)M->g_stage.p, (const uint32_t *)M->g_status.p + a,
                                          (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
-                                         (int64_t *)M->w_srcoff.p, d_stor);
+                                         (int64_t *)M->w_srcoff.p, d_stor, nullptr);
     *launches += 1;
     if (timed && (rc = kev_record(M, st, 1))) return rc;
     CUDA_TRY(cudaGetLastError());
@@ -2073,3 +2080,6 @@ int spm_cuda_estep_run(const spm_cuda_estep *E, const char *words, const int64_t
 }
 
 }  // extern "C"
+
+// pieces / SentencePieceText spans, batch Decode, dense / sparse layouts
+#include "spm_pieces.inc"

@@ -80,6 +80,7 @@ bool parse_proto(const void *data, size_t len, HostModel *m) {
         if (!q.ok) return false;
         if (g.num == 3 && g.wt == 0) m->model_type = (int)g.v;
         else if (g.num == 24 && g.wt == 0) m->ws_suffix = g.v != 0;
+        else if (g.num == 44 && g.wt == 2) m->unk_surface = std::string((const char *)g.s, g.n).c_str();  // .c_str(): sentencepiece_processor.cc:676
         else if (g.num == 45 && g.wt == 2) m->unk_piece.assign((const char *)g.s, g.n);
         else if (g.num == 46 && g.wt == 2) m->bos_piece.assign((const char *)g.s, g.n);
         else if (g.num == 47 && g.wt == 2) m->eos_piece.assign((const char *)g.s, g.n);

@@ -32,6 +32,7 @@ struct HostModel {
   bool ws_suffix = false, add_dummy_prefix = true, remove_extra_ws = true, escape_ws = true;
   std::string charsmap;  // precompiled_charsmap blob
   std::string unk_piece = "<unk>", bos_piece = "<s>", eos_piece = "</s>", pad_piece = "<pad>";
+  std::string unk_surface = " \xE2\x81\x87 ";  // TrainerSpec.unk_surface (sentencepiece_model.proto:184), used by Decode
   // ---- derived
   int unk_id = -1;
   float min_score = 0, max_score = 0;

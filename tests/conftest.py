@@ -153,6 +153,27 @@ class HostCore:
         assert rc == 0, rc
         return ids[: io[n]].copy(), io, st[:n]
 
+    def encode_pieces_batch(self, text, off, opts=0):
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        n = len(off) - 1
+        cap = int(off[-1] - off[0]) * 4 + 40 * n + 64
+        ncap = self.L.hc_expansion(self.h) * int(off[-1] - off[0]) + 16 * n + 64
+        a = {k: np.empty(cap, dtype=np.int32) for k in ("ids", "begin", "end", "nbegin", "nend")}
+        io = np.zeros(n + 1, dtype=np.int64)
+        norm = np.empty(ncap, dtype=np.uint8)
+        no = np.zeros(n + 1, dtype=np.int64)
+        rc = self.L.hc_encode_pieces_batch(
+            ctypes.c_void_p(self.h), ctypes.c_void_p(text.ctypes.data), ctypes.c_void_p(off.ctypes.data),
+            ctypes.c_int64(n), ctypes.c_uint32(opts), *[ctypes.c_void_p(a[k].ctypes.data) for k in
+                                                        ("ids", "begin", "end", "nbegin", "nend")],
+            ctypes.c_int64(cap), ctypes.c_void_p(io.ctypes.data), ctypes.c_void_p(norm.ctypes.data),
+            ctypes.c_int64(ncap), ctypes.c_void_p(no.ctypes.data))
+        assert rc == 0, rc
+        out = {k: v[: io[n]].copy() for k, v in a.items()}
+        out.update(id_off=io, norm=norm[: no[n]].copy(), norm_off=no)
+        return out
+
 
 @pytest.fixture(scope="session")
 def make_hostcore(hostcore):

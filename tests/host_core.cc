@@ -338,6 +338,61 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
   return 0;
 }
 
+// The pieces path (spm_pieces.inc: k_pc_normalize -> k_gen_encode with piece ends -> k_pc_emit)
+// on the CPU: aligned normalizer, exact tier with out_end, final_piece_at.  Same CSR layout
+// as spm_cuda_encode_batch_pieces.
+int hc_encode_pieces_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n, uint32_t opts, int32_t *ids,
+                           int32_t *begin, int32_t *end, int32_t *nbegin, int32_t *nend, int64_t cap, int64_t *id_off,
+                           uint8_t *norm_out, int64_t norm_cap, int64_t *norm_off) {
+  Handle *h = (Handle *)p;
+  const ModelView &mv = h->mv;
+  const ExtraPlan plan = make_extra_plan(opts, piece_to_id(h->hm, h->hm.bos_piece), piece_to_id(h->hm, h->hm.eos_piece));
+  std::vector<uint8_t> norm;
+  std::vector<int32_t> words, core, ends, n2o;
+  id_off[0] = 0;
+  norm_off[0] = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const int64_t len = off[i + 1] - off[i];
+    const int64_t need = ((int64_t)h->hm.expansion * len + 8 + 7) & ~(int64_t)7;
+    norm.assign(need, 0);
+    n2o.assign(need, -1);
+    uint32_t st = 0;
+    int32_t nl = normalize_sentence_t<true>(mv, text + off[i], len, norm.data(), need - 1, n2o.data());
+    if (nl < 0) return 90;
+    core.assign(nl + 1, 0);
+    ends.assign(nl + 1, 0);
+    int32_t cnt = 0;
+    if (mv.model_type == M_UNIGRAM) {
+      words.assign(uni_scratch_words(mv.ring, 8, nl), 0);
+      UniScratch sc;
+      int32_t *w = words.data();
+      sc.ringM = (float *)w; w += mv.ring;
+      sc.ringCnt = (uint32_t *)w; w += mv.ring;
+      sc.candBt = (float *)w; w += mv.ring * 8;
+      w += ((w - words.data()) & 1);
+      sc.candRec = (uint64_t *)w; w += 2 * mv.ring * 8;
+      sc.back = (uint64_t *)w;
+      sc.stride = nl + 1;
+      cnt = unigram_encode<8>(mv, norm.data(), nl, sc, core.data(), nl, &st, ends.data());
+    } else {
+      words.assign(bpe_scratch_words(nl), 0);
+      cnt = bpe_encode(mv, norm.data(), nl, words.data(), core.data(), nl, &st, ends.data());
+    }
+    if (st & (ST_CAND_OVERFLOW | ST_IDS_OVERFLOW)) return 91;
+    const int32_t fc = final_count(plan, cnt);
+    if (id_off[i] + fc > cap || norm_off[i] + nl > norm_cap) return 8;
+    for (int32_t j = 0; j < fc; ++j) {
+      const PieceSpan ps = final_piece_at(plan, core.data(), ends.data(), n2o.data(), cnt, j);
+      const int64_t q = id_off[i] + j;
+      ids[q] = ps.id; begin[q] = ps.begin; end[q] = ps.end; nbegin[q] = ps.nbegin; nend[q] = ps.nend;
+    }
+    memcpy(norm_out + norm_off[i], norm.data(), nl);
+    id_off[i + 1] = id_off[i] + fc;
+    norm_off[i + 1] = norm_off[i] + nl;
+  }
+  return 0;
+}
+
 // E-step of the unigram trainer: the kernel's per-word function (spm_estep.cuh) on the CPU.
 int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *words, const int64_t *off,
              const int64_t *freq, int64_t n, double all_freq, double *expected, double *obj_ntok, float *logz) {
