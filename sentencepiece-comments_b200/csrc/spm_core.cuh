@@ -675,4 +675,84 @@ SPM_HD PieceSpan final_piece_at(const ExtraPlan &p, const int32_t *core_ids, con
   return r;
 }
 
+
+// ---- spans from ids: the fast half of the pieces path --------------------------------
+// The id path (word memo / Viterbi / merge kernels) yields the final ids of a sentence but
+// not where each piece lies.  Every piece other than the unknown one has a fixed string, so
+// walking the ids over the normalized text recovers the boundaries; only a run of unknown
+// characters has no fixed length.  Its end e* is found by elimination: every character of
+// the run has no usable one-character piece (unigram: PopulateNodes adds the UNK node only
+// then, src/unigram_model.cc:596-602; BPE: PieceToId of the symbol misses,
+// src/model_interface.cc:87-97) and the next piece's string starts at e*.  e* itself always
+// satisfies both, so when exactly ONE position does, it is e*; with two or more (or any
+// inconsistency: a piece that does not fit, text left over) the function returns false and
+// the sentence is redone by the exact tier, which records the piece ends.
+struct PieceTable {
+  const int32_t *plen;    // bytes of piece id
+  const uint32_t *poff;   // offset of its string in pool
+  const uint8_t *pool;
+};
+SPM_HD bool unk_eligible(const ModelView &m, const uint8_t *c, int cl) {
+  const uint2 lf = xda_exact(m.pieces, c, cl);
+  if (lf.x == 0xFFFFFFFFu) return true;
+  const uint32_t type = lf.x >> 28;
+  return m.model_type == M_UNIGRAM ? !(type == T_NORMAL || type == T_USER_DEFINED) : type == T_UNKNOWN;
+}
+// s[0..nl): normalized sentence, n2o its norm_to_orig; fids[0..fc): the FINAL ids of the
+// sentence (extra options applied).  Writes the four span arrays at the same final positions
+// (entries >= room are skipped).
+SPM_HDN bool spans_from_ids(const ModelView &m, const PieceTable &pt, const ExtraPlan &plan, const uint8_t *s,
+                            int32_t nl, const int32_t *n2o, const int32_t *fids, int32_t fc, int32_t *begin,
+                            int32_t *end, int32_t *nbegin, int32_t *nend, int64_t room) {
+  if (fc == 0) return true;   // nothing to place (empty input without extra options, or the reference's error)
+  const int32_t core = fc - plan.npre - plan.nsuf;
+  if (core < 0) return false;
+  for (int32_t j = 0; j < fc; ++j) {
+    if (j >= plan.npre && j < plan.npre + core) continue;
+    if (j < room) { begin[j] = 0; end[j] = 0; nbegin[j] = -1; nend[j] = -1; }
+  }
+  int32_t pos = 0;
+  for (int32_t k = 0; k < core; ++k) {
+    const int32_t j = plan.npre + (plan.flip ? core - 1 - k : k);
+    const int32_t id = fids[j];
+    int32_t e;
+    if (id != m.unk_id) {
+      e = pos + SPM_LDG(pt.plen + id);
+      if (e > nl) return false;
+    } else {
+      const uint8_t *np = nullptr;
+      int32_t npl = 0;
+      if (k + 1 < core) {
+        const int32_t nid = fids[plan.npre + (plan.flip ? core - 2 - k : k + 1)];
+        if (nid == m.unk_id) return false;   // unknown runs are merged: cannot follow each other
+        np = pt.pool + SPM_LDG(pt.poff + nid);
+        npl = SPM_LDG(pt.plen + nid);
+      }
+      int32_t found = -1, q = pos;
+      while (q < nl) {
+        int cl = one_char_len(s[q]);
+        if (cl > nl - q) cl = nl - q;
+        if (!unk_eligible(m, s + q, cl)) break;
+        q += cl;
+        bool match;
+        if (np == nullptr) {
+          match = q == nl;
+        } else {
+          match = q + npl <= nl;
+          for (int32_t b = 0; match && b < npl; ++b) match = s[q + b] == SPM_LDG(np + b);
+        }
+        if (match) {
+          if (found >= 0) return false;   // two candidate ends: only the Viterbi tie-break knows
+          found = q;
+        }
+      }
+      if (found < 0) return false;
+      e = found;
+    }
+    if (j < room) { nbegin[j] = pos; nend[j] = e; begin[j] = n2o[pos]; end[j] = n2o[e]; }
+    pos = e;
+  }
+  return pos == nl;
+}
+
 }  // namespace spmb

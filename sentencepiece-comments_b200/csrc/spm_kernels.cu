@@ -343,8 +343,10 @@ k_normalize_long(ModelView mv, const uint8_t *text, const int64_t *off, int64_t 
   const int nchunks = (int)((len + kNormChunk - 1) / kNormChunk);
   if (i == 0) { bad = 0; started = 0; }
   __syncthreads();
-  if (i <= nchunks)
-    cuts[i] = i == 0 ? 0 : (i == nchunks ? len : norm_find_cut(mv, first2, in, (int64_t)i * kNormChunk, len));
+  // (nchunks can equal the thread count -- lines of 65,025..65,535 bytes -- so the end cut is
+  // thread 0's job, not thread nchunks')
+  if (i == 0) { cuts[0] = 0; cuts[nchunks] = len; }
+  else if (i < nchunks) cuts[i] = norm_find_cut(mv, first2, in, (int64_t)i * kNormChunk, len);
   __syncthreads();
   olen[i] = 0; onch[i] = 0;
   if (i < nchunks) {
@@ -457,10 +459,21 @@ __device__ __forceinline__ uint32_t fast_lanes_per_unit(uint32_t count, int warp
 __global__ void __launch_bounds__(kFastThreads, 1)
 k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
               const int32_t *perm, int count_idx, int work_idx, int max_warps, uint32_t *back, int64_t back_rows,
-              int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *flag_list, int flag_idx, uint32_t *counters) {
+              int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *flag_list, int flag_idx, uint32_t *counters,
+              uint32_t warp_route) {
   // flag_list / flag_idx: where sentences with near-tied candidates go -- the list of k_encode_warp
   // (keeps kWarpCapc candidates per position) when that kernel follows, else the general tier's
   extern __shared__ __align__(16) uint32_t smem[];
+  // A short list (what the word memo leaves over: a few thousand sentences with rare words) is
+  // latency-bound here -- one thread walks a whole sentence through cold trie paths -- so it is
+  // handed to k_encode_warp as a whole: 32 lanes per sentence, 6 x shorter on 6 k sentences.
+  if (warp_route != 0 && counters[count_idx] <= warp_route) {
+    const uint32_t nf = counters[count_idx];
+    for (uint32_t i = blockIdx.x * kFastThreads + threadIdx.x; i < nf; i += gridDim.x * kFastThreads)
+      flag_list[atomicAdd(&counters[flag_idx], 1u)] = perm[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&counters[C_NRETRY], nf);
+    return;
+  }
   uint32_t *units_hot = smem;
   float *score_hot = (float *)(smem + fp.k_units);
   float *ring_bt = (float *)(smem + fp.k_units + fp.k_scores);
@@ -555,7 +568,10 @@ k_encode_warp(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
     if (w >= count) break;
     const int32_t t = list[w];
     const int32_t nl = nlen[t];
-    if (nl <= 0) continue;                 // empty, or routed to the general tier by the normalizer
+    if (nl <= 0) {                         // empty, or routed to the general tier by the normalizer (which sets cnt later)
+      if (lane == 0) cnt[t] = 0;
+      continue;
+    }
     int32_t c = -1;
     if (nl + 2 <= stride)
       c = warp_unigram(fv, ws[wid], norm + fast_norm_base(off, c0, t), nl, myback, stride,
@@ -1455,6 +1471,16 @@ int spm_cuda_last_stats(const spm_cuda_model *M, double *stats, int n) {
   return kOk;
 }
 
+}  // extern "C"
+
+// The body of spm_cuda_encode_batch; the caller holds M->mu (the pieces path runs it first
+// for the ids and then adds the spans, spm_pieces.inc).
+static int encode_batch_locked(const spm_cuda_model *M, const char *text, const int64_t *text_offsets, int64_t n,
+                               uint32_t extra_options, int32_t *ids, int64_t ids_capacity, int64_t *id_offsets,
+                               int memory_space, void *cuda_stream);
+
+extern "C" {
+
 int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64_t *text_offsets, int64_t n,
                           uint32_t extra_options, int32_t *ids, int64_t ids_capacity, int64_t *id_offsets,
                           int memory_space, void *cuda_stream) {
@@ -1465,6 +1491,15 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   }
   if (memory_space != SPM_CUDA_HOST && memory_space != SPM_CUDA_DEVICE) { g_err = "bad memory_space"; return kInvalidArgument; }
   std::lock_guard<std::mutex> lk(M->mu);
+  return encode_batch_locked(M, text, text_offsets, n, extra_options, ids, ids_capacity, id_offsets, memory_space,
+                             cuda_stream);
+}
+
+}  // extern "C"
+
+static int encode_batch_locked(const spm_cuda_model *M, const char *text, const int64_t *text_offsets, int64_t n,
+                               uint32_t extra_options, int32_t *ids, int64_t ids_capacity, int64_t *id_offsets,
+                               int memory_space, void *cuda_stream) {
   CUDA_TRY(cudaSetDevice(M->device));
   cudaStream_t st = (cudaStream_t)cuda_stream;
   static const bool trace = getenv("SPM_CUDA_TRACE") != nullptr;   // host-side timeline on stderr
@@ -1756,6 +1791,8 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
       }
       if ((rc = kev_record(M, st, 1))) return rc;
       launches += has_long ? 5 : 4;
+      static const char *env_route = getenv("SPM_CUDA_WARP_ROUTE");   // tuning experiments only
+      const uint32_t warp_route = env_route ? (uint32_t)atoll(env_route) : 262144u;
       const int32_t *list_a = (const int32_t *)M->w_perm.p, *list_b = (const int32_t *)M->w_longlist.p;
       const int cnt_a = C_NFAST, work_a = C_WORK, cnt_b = C_NLONG, work_b = C_WORK_LONG;
       if ((rc = kev_record(M, st, 0, T_ENCODE))) return rc;
@@ -1766,7 +1803,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
             kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
             (uint32_t *)M->w_status.p, (int32_t *)(warp_ok ? M->w_longlist.p : M->w_genlist.p),
-            warp_ok ? C_NLONG : C_NGEN, d_counters);
+            warp_ok ? C_NLONG : C_NGEN, d_counters, warp_ok ? warp_route : 0u);
         if (warp_ok) {
           // one warp per line, exact candidate lists (spm_warp.cuh); back records: kWarpCapc rows of
           // `wstride` per resident warp, at most 4 GiB in all; longest lines first
@@ -1785,7 +1822,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
           k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
               long_warps, (uint32_t *)M->w_back.p, back_rows_long, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
-              (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, C_NGEN, d_counters);
+              (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, C_NGEN, d_counters, 0u);
           launches += 1;
         }
       } else {
@@ -1896,6 +1933,8 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
   }
   return kOk;
 }
+
+extern "C" {
 
 // ---------------------------------------------------------------- line splitting C ABI
 int spm_cuda_split_lines(const spm_cuda_model *M, const char *buf, int64_t len, char *text, int64_t *offsets,

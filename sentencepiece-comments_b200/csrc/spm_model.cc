@@ -487,6 +487,16 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
   m->fast_ok = m->model_type == M_UNIGRAM && text_valid && m->pieces.units.size() < 0x00FFFFFFu &&
                m->max_piece_chars < 200;
   refresh_leaf_types(m);  // (re)derives bpe_fast_ok as well
+  // piece strings by id (spans_from_ids of the pieces path, spm_core.cuh)
+  m->plen.resize(V);
+  m->poff.resize(V);
+  m->ppool.clear();
+  for (size_t i = 0; i < V; ++i) {
+    m->plen[i] = (int32_t)m->piece[i].size();
+    m->poff[i] = (uint32_t)m->ppool.size();
+    m->ppool += m->piece[i];
+  }
+  m->ppool += '\0';
   return kOk;
 }
 

@@ -60,6 +60,10 @@ struct HostModel {
   bool ascii_plain = false;       // see build_host_model
   bool memo_ok = false;           // no lattice node / merge crosses a U+2581: words can be memoised (spm_memo.cuh)
   bool neg_only = false;          // every node score of the fast view (and the UNK score) is <= 0
+  // ---- piece strings by id (pieces path)
+  std::vector<int32_t> plen;
+  std::vector<uint32_t> poff;
+  std::string ppool;
   std::string error;
 };
 

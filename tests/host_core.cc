@@ -23,6 +23,7 @@ namespace {
 struct Handle {
   HostModel hm;
   ModelView mv;
+  PieceTable pt;
 };
 void make_view(Handle *h) {
   HostModel &m = h->hm;
@@ -39,6 +40,7 @@ void make_view(Handle *h) {
   v.add_dummy_prefix = m.add_dummy_prefix; v.remove_extra_ws = m.remove_extra_ws;
   v.escape_ws = m.escape_ws; v.ws_suffix = m.ws_suffix; v.has_unused = m.has_unused;
   v.ascii_plain = m.ascii_plain;
+  h->pt.plen = m.plen.data(); h->pt.poff = m.poff.data(); h->pt.pool = (const uint8_t *)m.ppool.data();
 }
 }  // namespace
 
@@ -343,7 +345,7 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
 // as spm_cuda_encode_batch_pieces.
 int hc_encode_pieces_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n, uint32_t opts, int32_t *ids,
                            int32_t *begin, int32_t *end, int32_t *nbegin, int32_t *nend, int64_t cap, int64_t *id_off,
-                           uint8_t *norm_out, int64_t norm_cap, int64_t *norm_off) {
+                           uint8_t *norm_out, int64_t norm_cap, int64_t *norm_off, int64_t *n_flagged) {
   Handle *h = (Handle *)p;
   const ModelView &mv = h->mv;
   const ExtraPlan plan = make_extra_plan(opts, piece_to_id(h->hm, h->hm.bos_piece), piece_to_id(h->hm, h->hm.eos_piece));
@@ -385,6 +387,21 @@ int hc_encode_pieces_batch(void *p, const uint8_t *text, const int64_t *off, int
       const PieceSpan ps = final_piece_at(plan, core.data(), ends.data(), n2o.data(), cnt, j);
       const int64_t q = id_off[i] + j;
       ids[q] = ps.id; begin[q] = ps.begin; end[q] = ps.end; nbegin[q] = ps.nbegin; nend[q] = ps.nend;
+    }
+    if (n_flagged != nullptr) {
+      // the fast half (k_pc_spans): spans recovered from the final ids alone; where it claims
+      // success it must agree with the exact tier's piece ends
+      std::vector<int32_t> fb(fc + 1), fe(fc + 1), fnb(fc + 1), fne(fc + 1);
+      const bool ok = spans_from_ids(mv, h->pt, plan, norm.data(), nl, n2o.data(), ids + id_off[i], fc, fb.data(),
+                                     fe.data(), fnb.data(), fne.data(), fc);
+      if (!ok) {
+        ++*n_flagged;
+      } else {
+        for (int32_t j = 0; j < fc; ++j) {
+          const int64_t q = id_off[i] + j;
+          if (fb[j] != begin[q] || fe[j] != end[q] || fnb[j] != nbegin[q] || fne[j] != nend[q]) return 95;
+        }
+      }
     }
     memcpy(norm_out + norm_off[i], norm.data(), nl);
     id_off[i + 1] = id_off[i] + fc;

@@ -81,6 +81,10 @@ def test_core_pieces_match_reference(make_hostcore, ref_pieces, small_corpora, s
     mb = model_bytes(model)
     hc = make_hostcore(mb)
     res = hc.encode_pieces_batch(text, off, opts=port.pack_options(opts))
+    # (inside: spans_from_ids, the fast half, must agree with the exact tier wherever it claims success)
+    n_unknown_runs = 0 if corpus == "edge" or "wagahai" in (corpus, model.split("_")[0]) or model == "ref_ja_8k" else 1
+    assert res["flagged"] <= (len(off) - 1) * (0.02 if n_unknown_runs else 1.0), res["flagged"]
+    print(model, corpus, "flagged", res["flagged"], "of", len(off) - 1)
     assert_protos(protos_of(spt_mod, text, off, res, model_pieces(mb)), ref_pieces, mpf.case_name(model, corpus, opts),
                   text, off)
 
