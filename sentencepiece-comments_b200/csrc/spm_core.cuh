@@ -712,9 +712,38 @@ SPM_HDN bool spans_from_ids(const ModelView &m, const PieceTable &pt, const Extr
     if (j < room) { begin[j] = 0; end[j] = 0; nbegin[j] = -1; nend[j] = -1; }
   }
   int32_t pos = 0;
-  for (int32_t k = 0; k < core; ++k) {
+  int32_t ob = core > 0 ? n2o[0] : 0;   // norm_to_orig[pos]
+  for (int32_t k = 0; k < core;) {
+    // Known pieces go eight at a time: their ids, lengths and norm_to_orig entries are
+    // independent loads (one thread serves a whole sentence, so this is where the
+    // memory-level parallelism comes from); an unknown piece is settled on its own.
+    constexpr int G = 8;
+    const int32_t g = core - k < G ? core - k : G;
+    int32_t idv[G], ev[G];
+    bool has_unk = false;
+    for (int u = 0; u < G; ++u)
+      if (u < g) { idv[u] = fids[plan.npre + (plan.flip ? core - 1 - (k + u) : k + u)]; has_unk |= idv[u] == m.unk_id; }
+    if (!has_unk) {
+      const int32_t start = pos;
+      for (int u = 0; u < G; ++u) if (u < g) ev[u] = SPM_LDG(pt.plen + idv[u]);
+      for (int u = 0; u < G; ++u) if (u < g) { pos += ev[u]; ev[u] = pos; }   // piece ends
+      if (pos > nl) return false;
+      int32_t ov[G];
+      for (int u = 0; u < G; ++u) if (u < g) ov[u] = n2o[ev[u]];
+      for (int u = 0; u < G; ++u) {
+        if (u >= g) break;
+        const int32_t j = plan.npre + (plan.flip ? core - 1 - (k + u) : k + u);
+        if (j < room) {
+          nbegin[j] = u ? ev[u - 1] : start; nend[j] = ev[u];
+          begin[j] = u ? ov[u - 1] : ob; end[j] = ov[u];
+        }
+      }
+      ob = ov[g - 1];
+      k += g;
+      continue;
+    }
     const int32_t j = plan.npre + (plan.flip ? core - 1 - k : k);
-    const int32_t id = fids[j];
+    const int32_t id = idv[0];
     int32_t e;
     if (id != m.unk_id) {
       e = pos + SPM_LDG(pt.plen + id);
@@ -749,8 +778,11 @@ SPM_HDN bool spans_from_ids(const ModelView &m, const PieceTable &pt, const Extr
       if (found < 0) return false;
       e = found;
     }
-    if (j < room) { nbegin[j] = pos; nend[j] = e; begin[j] = n2o[pos]; end[j] = n2o[e]; }
+    const int32_t oe = n2o[e];
+    if (j < room) { nbegin[j] = pos; nend[j] = e; begin[j] = ob; end[j] = oe; }
     pos = e;
+    ob = oe;
+    ++k;
   }
   return pos == nl;
 }

@@ -456,6 +456,7 @@ struct FastOut {
   SPM_HD bool done() const { return false; }
   static constexpr bool kRuns = false;           // no bulk path for runs of plain bytes
   SPM_HD int take(uint64_t, int) { return 0; }
+  SPM_HD void at(int32_t) {}                     // (input position of the step: only AlignedOut records it)
   SPM_HD void put(uint32_t v, int k) {  // k in 1..4 bytes, little-endian in v
     const int f = len & 7;
     acc |= (uint64_t)v << (8 * f);
@@ -467,6 +468,18 @@ struct FastOut {
   }
   SPM_HD void flush() {
     if (len & 7) *reinterpret_cast<uint64_t *>(base + (len & ~7)) = acc;
+  }
+};
+
+// FastOut that also records norm_to_orig (src/normalizer.cc:132-176: every normalized byte
+// maps to `consumed`, the input offset at which its NormalizePrefix step started).
+struct AlignedOut : FastOut {
+  int32_t *n2o;
+  int32_t cur;
+  SPM_HD void at(int32_t p) { cur = p; }
+  SPM_HD void put(uint32_t v, int k) {
+    for (int j = 0; j < k; ++j) n2o[len + j] = cur;
+    FastOut::put(v, k);
   }
 };
 
@@ -545,6 +558,7 @@ SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, con
       const bool is_space = b0 == 0x20;
       if (lead && is_space) { p += 1; r += 1; goto advance; }   // np == " ": keep stripping
       lead = false;
+      o.at((int32_t)p);
       if (!started) {  // first real content: dummy prefix (:132-153)
         started = true;
         if (!m.ws_suffix && m.add_dummy_prefix) { o.put(WS, WSL); ++nch; }
@@ -564,6 +578,7 @@ SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, con
       const bool one_space = rep != nullptr && rl == 1 && rep[0] == ' ';
       if (lead && one_space) { p += consumed; r += consumed; goto advance; }
       lead = false;
+      o.at((int32_t)p);
       if (!started) {
         started = true;
         if (!m.ws_suffix && m.add_dummy_prefix) { o.put(WS, WSL); ++nch; }
@@ -687,6 +702,40 @@ SPM_HDN int32_t fast_normalize(const ModelView &m, const uint32_t *first2, const
     for (int32_t k = 0; k < kNormPad; k += 8) *reinterpret_cast<uint64_t *>(out + z + k) = 0;
   }
   *nchars_ub = nch;
+  return len;
+}
+
+
+// fast_normalize() that also fills norm_to_orig: n2o[0..len] (one entry per normalized byte and
+// the final one, src/normalizer.cc:191-206).  Same contract otherwise; -1: caller falls back to
+// normalize_sentence_t<true>.
+SPM_HDN int32_t fast_normalize_aligned(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t n,
+                                       const uint8_t *lo, const uint8_t *hi, uint8_t *out, int32_t cap, int32_t *n2o) {
+  if (n == 0) return 0;
+  const bool esc = m.escape_ws, rws = m.remove_extra_ws;
+  const uint32_t WS = esc ? 0x8196E2u : 0x20u;
+  const int WSL = esc ? 3 : 1;
+  AlignedOut o;
+  o.base = out; o.acc = 0; o.len = 0; o.cap = cap; o.n2o = n2o; o.cur = 0;
+  int32_t nch = 0;
+  bool started = false;
+  if (!fast_normalize_scan(m, first2, in, n, lo, hi, o, &nch, &started)) return -1;
+  o.flush();
+  int32_t len = o.len;
+  int32_t consumed = (int32_t)n;
+  if (rws) {  // strip trailing whitespace symbols; consumed = norm_to_orig[new length] (:191-201)
+    if (esc) { while (len >= 3 && out[len - 3] == 0xE2 && out[len - 2] == 0x96 && out[len - 1] == 0x81) { len -= 3; consumed = n2o[len]; } }
+    else { while (len >= 1 && out[len - 1] == ' ') { len -= 1; consumed = n2o[len]; } }
+  }
+  if (m.ws_suffix && m.add_dummy_prefix && started) {
+    o.len = len;
+    o.acc = (len & 7) ? *reinterpret_cast<uint64_t *>(out + (len & ~7)) & ((1ull << (8 * (len & 7))) - 1) : 0;
+    o.at(consumed);
+    o.put(WS, WSL);
+    o.flush();
+    len = o.len;
+  }
+  if (started || len > 0) n2o[len] = consumed;
   return len;
 }
 

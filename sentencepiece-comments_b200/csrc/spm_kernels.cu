@@ -1117,6 +1117,8 @@ struct spm_cuda_model {
       w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
   mutable DevBuf px[20];   // workspace of the pieces / decode / dense calls (spm_pieces.inc)
+  mutable uint32_t last_stor = 0;   // OR of the status words of the last encode_batch_locked call
+  mutable bool pt_ready = false;    // piece strings uploaded (px[PX_PLEN..PX_PPOOL])
   mutable bool dec_ready = false;   // decode tables uploaded (px[PX_DECREC], px[PX_DECPOOL])
   mutable int dec_maxlen = 1;       // longest decoded piece in bytes
   mutable std::vector<int64_t> h_woff;
@@ -1594,7 +1596,9 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
   if (memo) {
     const uint64_t want = 2 * (uint64_t)n + (uint64_t)(text_hi - text_lo) / 16;
     uint64_t entries = 1 << 12;
-    while (entries < want && entries < (1ull << 23)) entries <<= 1;
+    static const char *env_bits = getenv("SPM_CUDA_MEMO_BITS");   // tuning experiments only
+    const int max_bits = env_bits ? std::max(12, std::min(26, atoi(env_bits))) : 23;
+    while (entries < want && entries < (1ull << max_bits)) entries <<= 1;
     if ((rc = M->w_memo.ensure(entries * sizeof(MemoKey)))) return rc;
     if ((rc = M->w_mres.ensure(entries * sizeof(MemoRes)))) return rc;
     if ((rc = M->w_newlist.ensure(entries / 2 * 4))) return rc;
@@ -1880,6 +1884,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
   const int64_t hsc[3] = {M->h_pin[kPubScal], M->h_pin[kPubScal + 1], M->h_pin[kPubScal + 2]};
   const int64_t total = hsc[0];
   stor = (uint32_t)hsc[2];
+  M->last_stor = stor;
   if (n == 0) {
     const int64_t z = 0;
     if (host) id_offsets[0] = 0;

@@ -156,6 +156,7 @@ struct MemoSink {
     tail = false; started = false; fail = false; pending = 0;
   }
   SPM_HD bool room(int64_t) const { return true; }
+  SPM_HD void at(int32_t) {}
   SPM_HD bool done() const { return fail; }
   SPM_HD uint32_t lookup(uint64_t mb) {
     if (tail) return memo_find_or_insert(tb, c0 | mb, c1 | (mb << 56));

@@ -361,6 +361,21 @@ int hc_encode_pieces_batch(void *p, const uint8_t *text, const int64_t *off, int
     uint32_t st = 0;
     int32_t nl = normalize_sentence_t<true>(mv, text + off[i], len, norm.data(), need - 1, n2o.data());
     if (nl < 0) return 90;
+    if (len > 0) {
+      // the fast tier's aligned scan (k_pc_normalize tries it first) must give the same text and map
+      std::vector<uint64_t> ibuf((len + 64) / 8 + 2, 0x5A5A5A5A5A5A5A5Aull);
+      uint8_t *src = (uint8_t *)ibuf.data() + 3 + (i % 8);
+      memcpy(src, text + off[i], len);
+      const int32_t fcap = (int32_t)(3 * len + 72);
+      std::vector<uint64_t> obuf((fcap + kNormPad + 16) / 8 + 2, 0x7777777777777777ull);
+      std::vector<int32_t> fmap(fcap + kNormPad + 16, -7);
+      const int32_t fl = fast_normalize_aligned(mv, mv.cm_first2, src, len, src, src + len, (uint8_t *)obuf.data(), fcap,
+                                                fmap.data());
+      if (fl >= 0) {
+        if (fl != nl || memcmp(obuf.data(), norm.data(), nl) != 0) return 96;
+        for (int32_t k = 0; nl > 0 && k <= nl; ++k) if (fmap[k] != n2o[k]) return 97;
+      }
+    }
     core.assign(nl + 1, 0);
     ends.assign(nl + 1, 0);
     int32_t cnt = 0;

@@ -106,6 +106,32 @@ def test_oracle_decode_matches_reference(ref_pieces, small_corpora, model, corpu
 WS = "▁"
 
 
+def ambiguous_model(model_type):
+    """"QQ" and "QQQ" are pieces, "Q" alone is not: in "QQQQQ..." a run of unknown characters can
+    end in several places, which only the Viterbi tie-break / the merge order settles -- the
+    sentences spans_from_ids must hand back to the exact tier."""
+    return pw.model(pw.base_pieces() + [(WS, -2.0), ("QQ", -1.5), ("QQQ", -3.5), ("a", -2.5), ("b", -2.5),
+                                        ("ab", -3.0)], model_type=model_type)
+
+
+AMBIGUOUS = [b"QQQQQ", b"QQQ", b"Q", b"QQ", b"aQQQQQb", b"QQQQQQQ ab QQQ", b"xQQQyQQQQz", b"QxQ", b"abQQQQQQQQQQQab",
+             "日QQQ本QQQQQ".encode(), b"Q Q Q QQ QQQ QQQQ QQQQQ"]
+
+
+@pytest.mark.parametrize("model_type", [pw.UNIGRAM, pw.BPE])
+def test_core_pieces_ambiguous_unknown_runs(make_hostcore, model_type):
+    from tools import synth
+    mb = ambiguous_model(model_type)
+    text, off = synth.pack_lines(AMBIGUOUS)
+    hc = make_hostcore(mb)
+    res = hc.encode_pieces_batch(text, off)          # (inside: fast spans == exact tier wherever they claim success)
+    want = port.OracleProcessor(mb).encode_pieces_batch(text, off)
+    for k in ("id_off", "norm_off", "ids", "begin", "end", "nbegin", "nend", "norm"):
+        assert np.array_equal(res[k], want[k]), k
+    if model_type == pw.UNIGRAM:
+        assert res["flagged"] >= 1      # "QQQQQ": unk(Q) QQ QQ / QQ unk(Q) QQ / ... all fit the ids' shape
+
+
 def decode_test_model():
     """DecodeMockModel of src/sentencepiece_processor_test.cc:467-494 as a real ModelProto."""
     return pw.model(pw.base_pieces() + [(WS + "ABC", -1.0), (WS + "DE", -1.0), ("F", -1.0), ("G" + WS + "H", -1.0)])
@@ -170,6 +196,19 @@ def test_gpu_pieces_match_oracle_arrays(spm_b200, corpora, model, corpus):
     ids, io = sp.encode_packed(text, off)
     res = sp.encode_pieces_packed(text, off)
     assert np.array_equal(ids, res["ids"]) and np.array_equal(io, res["id_off"])
+
+
+@gpu
+@pytest.mark.parametrize("model_type", [pw.UNIGRAM, pw.BPE])
+def test_gpu_pieces_ambiguous_unknown_runs(spm_b200, model_type):
+    from tools import synth
+    mb = ambiguous_model(model_type)
+    text, off = synth.pack_lines(AMBIGUOUS * 40)
+    sp = spm_b200.SentencePieceProcessor()
+    sp.LoadFromSerializedProto(mb)
+    assert_same_arrays(sp.encode_pieces_packed(text, off), port.OracleProcessor(mb).encode_pieces_batch(text, off))
+    if model_type == pw.UNIGRAM:
+        assert sp.last_stats()["fallback_sentences"] >= 40     # the exact tier settled the ambiguous ones
 
 
 @gpu
