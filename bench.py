@@ -235,7 +235,7 @@ def bind_to_gpu_numa_node(index):
 
 
 STAGE_KERNEL = {"encode": "k_encode_fast / k_encode_bpe_fast (general tier kernels for models without a fast tier)",
-                "normalize": "k_normalize_fast", "memo_collect": "k_memo_collect", "memo_words": "k_memo_words_*",
+                "normalize": "k_normalize_fast", "memo_collect": "k_memo_scan_plain (+ k_memo_scan for the listed sentences)", "memo_words": "k_memo_words_*",
                 "memo_emit": "k_memo_emit", "compact": "k_scan_* + k_compact"}
 
 
@@ -337,11 +337,11 @@ def run_b200(args):
     if rank == 0:
         peak, peak_src = measured_peak()
         # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, one launch, from the
-        # ncu --set full capture of this very workload (profiles/r1_v5_summary.md); null otherwise
+        # ncu --set full capture of this very workload (profiles/r1_v11_summary.md); null otherwise
         traffic = None
         if (dom == "memo_collect" and args.model == "syn_uni32k" and args.corpus == "syn_en"
                 and n == 10_000_000):
-            traffic = 4.14e9
+            traffic = 3.97e9
         k_avg_ms = kern_ms / max(kern_launches, 1)
         alg_per_launch = alg_bytes * args.steps / max(kern_launches, 1)
         achieved = alg_per_launch / (k_avg_ms * 1e-3) / 1e9 if k_avg_ms > 0 else 0.0
