@@ -206,7 +206,7 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT, flush=True)
 
 
 def bind_to_gpu_numa_node(index):
@@ -376,13 +376,22 @@ def run_b200(args):
             line["cpu_baseline"] = {"value": m / dt, "unit": UNIT, "cores": threads, "kind": kind,
                                     "sample": "first %d sentences of the workload (%d B, %d ids), %.1f s wall, "
                                               "in-process Encode(ids) loop" % (m, int(off[m]), cids, dt)}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=RESULT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
+RESULT = sys.stdout
+
+
 def main():
+    global RESULT
     args = parse_args()
+    # stdout carries exactly one JSON line: whatever else writes to fd 1 (NCCL prints its version
+    # banner there with printf) goes to stderr instead
+    sys.stdout.flush()
+    RESULT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

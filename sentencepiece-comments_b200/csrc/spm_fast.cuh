@@ -476,10 +476,25 @@ struct FastOut {
 struct AlignedOut : FastOut {
   int32_t *n2o;
   int32_t cur;
+  static constexpr bool kRuns = true;   // runs of plain bytes are taken from the window in one piece
   SPM_HD void at(int32_t p) { cur = p; }
   SPM_HD void put(uint32_t v, int k) {
     for (int j = 0; j < k; ++j) n2o[len + j] = cur;
     FastOut::put(v, k);
+  }
+  // `run` (1..8) printable-ASCII bytes from the low end of w: each is a NormalizePrefix step of
+  // its own (one byte in, the same byte out), so byte j maps to input offset cur + j.
+  SPM_HD int take(uint64_t w, int run) {
+    for (int j = 0; j < run; ++j) n2o[len + j] = cur + j;
+    const int f = len & 7;
+    const uint64_t v = run == 8 ? w : (w & ((1ull << (8 * run)) - 1));
+    acc |= v << (8 * f);
+    if (f + run >= 8) {
+      *reinterpret_cast<uint64_t *>(base + (len & ~7)) = acc;
+      acc = f ? v >> (8 * (8 - f)) : 0;
+    }
+    len += run;
+    return run;
   }
 };
 
@@ -525,6 +540,7 @@ SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, con
       // the successor of the last byte must be known to be ASCII (or the end of the sentence)
       if (run == 8 || (run < n - p && ((w >> (8 * run)) & 0x80u))) --run;
       if (run > 0) {
+        o.at((int32_t)p);
         run = o.take(w, run);
         if (run > 0) {
           lead = false; prev_space = false;

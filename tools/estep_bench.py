@@ -44,7 +44,14 @@ def word_counts(n_sentences):
     return np.frombuffer(b"".join(ws), dtype=np.uint8).copy(), offs, freq, ws
 
 
+RESULT_FD = 1
+
+
 def main():
+    global RESULT_FD
+    sys.stdout.flush()
+    RESULT_FD = os.dup(1)     # stdout carries the JSON line only; NCCL's banner (printf to fd 1) goes to stderr
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--sentences", type=int, default=2_000_000)
@@ -142,7 +149,8 @@ def main():
         big = rexp > 1e-2
         line["parity"] = {"ntokens_equal": bool(nt == rnt),
                           "max_rel_err_expected": float(np.max(np.abs(e[big] - rexp[big]) / rexp[big]))}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.write(RESULT_FD, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 
