@@ -1117,6 +1117,7 @@ struct spm_cuda_model {
       w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
   mutable DevBuf px[20];   // workspace of the pieces / decode / dense calls (spm_pieces.inc)
+  mutable int emit_blocks = 0;      // resident CTAs of k_memo_emit per SM (occupancy query, first use)
   mutable uint32_t last_stor = 0;   // OR of the status words of the last encode_batch_locked call
   mutable bool pt_ready = false;    // piece strings uploaded (px[PX_PLEN..PX_PPOOL])
   mutable bool dec_ready = false;   // decode tables uploaded (px[PX_DECREC], px[PX_DECPOOL])
@@ -1767,7 +1768,17 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         }
         if ((rc = kev_record(M, st, 1))) return rc;
         if ((rc = kev_record(M, st, 0, T_MEMO_EMIT))) return rc;
-        const unsigned gemit = (unsigned)std::min<int64_t>((cn + 15) / 16, 8 * (int64_t)M->sm_count);
+        // grid-stride kernel: exactly as many CTAs as are resident at once (6 per SM at 40 registers), so
+        // that the sentences are dealt out in ONE wave -- with 8 per SM the last quarter of the CTAs ran
+        // alone at a third of the machine
+        static const char *env_emit = getenv("SPM_CUDA_EMIT_BLOCKS");   // tuning experiments only
+        if (M->emit_blocks == 0) {
+          int occ = 0;
+          CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_memo_emit, kMemoThreads, 0));
+          M->emit_blocks = std::max(1, occ);
+        }
+        const int64_t emit_per_sm = env_emit ? std::max(1, atoi(env_emit)) : M->emit_blocks;
+        const unsigned gemit = (unsigned)std::min<int64_t>((cn + 15) / 16, emit_per_sm * (int64_t)M->sm_count);
         k_memo_emit<<<gemit, kMemoThreads, 0, st>>>(
             tb, M->fast_kind == 1, d_off, c0, cn, (const uint32_t *)M->w_wslots.p, (const int32_t *)M->w_nwords.p,
             (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
