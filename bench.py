@@ -235,7 +235,7 @@ def bind_to_gpu_numa_node(index):
 
 
 STAGE_KERNEL = {"encode": "k_encode_fast / k_encode_bpe_fast (general tier kernels for models without a fast tier)",
-                "normalize": "k_normalize_fast", "memo_collect": "k_memo_scan_plain (+ k_memo_scan for the listed sentences)", "memo_words": "k_memo_words_*",
+                "normalize": "k_normalize_fast", "memo_collect": "k_memo_scan_words (+ k_memo_scan for the listed sentences)", "memo_words": "k_memo_words_*",
                 "memo_emit": "k_memo_emit", "compact": "k_scan_* + k_compact"}
 
 

@@ -695,6 +695,146 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
   status[t] = 0;
 }
 
+// k_memo_scan_words: the same scan with the lanes of a warp working on BYTES and on WORDS instead
+// of on sentences (one thread per sentence runs at the pace of the longest of 32 sentences and
+// diverges at every word end: 14 active threads per warp instruction).  The warp stages the
+// contiguous text of its 32 sentences as before, marks the sentence starts in a bitmap, then
+//   sweep: 8 bytes per lane and step (sw_chunk_masks): word starts / word ends / unfit bytes as
+//          bit masks, placed in two shared lists by a warp prefix sum (k-th start pairs with
+//          the k-th end);
+//   words: one lane per word: sentence of the word (binary search over the 32 starts), key from
+//          the staged bytes (sw_word_slot), 16-byte probe / 128-bit CAS, slot stored at
+//          (sentence's slot list)[word index] -- the layout k_memo_emit reads.
+// A warp whose text holds more than kSwCap words runs memo_scan_plain per lane instead.
+constexpr int kSwWarps = 4, kSwCap = 640, kSwMapWords = kScanWarpBytes / 32 + 4;
+struct SwWarp {
+  __align__(16) uint8_t stage[kScanWarpBytes];
+  uint32_t bmap[kSwMapWords];        // bit i: a sentence starts at stage byte i (or the warp's text ends there)
+  uint16_t wpos[kSwCap], wend[kSwCap];   // first / last byte of word k
+  uint16_t sstart[32];               // first byte of the sentence of lane l
+  uint16_t fw[32];                   // words before it
+  int32_t wdelta[32];                // its slot list, relative to the one of the warp's first sentence
+  uint32_t flags[32];                // 1: a word cannot be keyed (-1), 2: not a plain sentence (-2)
+};
+__device__ __forceinline__ int sw_owner(const uint16_t *sstart, int pos) {   // last sentence starting at or before pos
+  int t = 0;
+#pragma unroll
+  for (int step = 16; step; step >>= 1)
+    if ((int)sstart[t + step] <= pos) t += step;
+  return t;
+}
+__global__ void __launch_bounds__(kSwWarps * 32)
+k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn,
+                  const uint8_t *lo, const uint8_t *hi, uint32_t *wslots, int32_t *nwords, int32_t *cnt,
+                  uint32_t *status, int32_t *slow_list, uint32_t *counters) {
+  __shared__ SwWarp shw[kSwWarps];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  SwWarp &sh = shw[wid];
+  const int64_t tw = ((int64_t)blockIdx.x * kSwWarps + wid) * 32;
+  if (tw >= cn) return;
+  const int64_t t = tw + lane;
+  const bool live = t < cn;
+  const int64_t a = off[c0 + tw], b = off[c0 + min(tw + 32, cn)];
+  const int64_t o0 = live ? off[c0 + t] : b, o1 = live ? off[c0 + t + 1] : b, len = o1 - o0;
+  const uint8_t *src = (const uint8_t *)((uintptr_t)(text + a) & ~(uintptr_t)15);
+  const int64_t span = (text + b) - src;
+  const bool staged = span <= kScanWarpBytes - 48 && mv.ascii_plain && mv.escape_ws;   // sw_word_slot reads 32 + 7 bytes
+  int32_t nw = 0;
+  if (!staged) {
+    if (len >= kLongMaxRaw) nw = -1;
+    else if (len > 0) nw = -2;
+  } else {
+    for (int64_t i = lane * 16; i < span + 16; i += 512) {   // + 16: the sweep looks one byte past the text
+      const uint8_t *p = src + i;
+      uint4 v;
+      if (p >= lo && p + 16 <= hi) {
+        v = __ldcs(reinterpret_cast<const uint4 *>(p));      // streamed once: do not displace the memo table in L2
+      } else {
+        uint8_t tmp[16];
+        for (int j = 0; j < 16; ++j) tmp[j] = (p + j >= lo && p + j < hi) ? p[j] : 0;
+        memcpy(&v, tmp, 16);
+      }
+      *reinterpret_cast<uint4 *>(&sh.stage[i]) = v;
+    }
+    const int a_rel = (int)((text + a) - src), b_rel = (int)span, s_rel = (int)((text + o0) - src);
+    for (int j = lane; j < (b_rel >> 5) + 2; j += 32) sh.bmap[j] = 0;
+    sh.sstart[lane] = (uint16_t)s_rel;
+    sh.flags[lane] = 0;
+    sh.wdelta[lane] = live ? (int32_t)(memo_wslot_base(off, c0, t) - memo_wslot_base(off, c0, tw)) : 0;
+    __syncwarp();
+    atomicOr(&sh.bmap[s_rel >> 5], 1u << (s_rel & 31));
+    if (lane == 31) atomicOr(&sh.bmap[b_rel >> 5], 1u << (b_rel & 31));
+    __syncwarp();
+    // ---- sweep
+    const uint8_t *bm8 = reinterpret_cast<const uint8_t *>(sh.bmap);
+    int total = 0, total_e = 0;
+    bool over = false;
+    for (int g0 = a_rel & ~7; g0 < b_rel; g0 += 256) {
+      const int g = g0 + lane * 8;
+      SwMasks m;
+      m.ws = 0; m.we = 0; m.bad = 0;
+      if (g < b_rel) {
+        const uint64_t w = *reinterpret_cast<const uint64_t *>(&sh.stage[g]);
+        const uint32_t pb = g > 0 ? sh.stage[g - 1] : 0u, nb = sh.stage[g + 8];
+        const uint32_t b9 = (uint32_t)bm8[g >> 3] | ((uint32_t)bm8[(g >> 3) + 1] << 8);
+        m = sw_chunk_masks(w, pb, nb, b9, a_rel - g, b_rel - g);
+      }
+      const uint32_t mine = (uint32_t)__popc(m.ws) | ((uint32_t)__popc(m.we) << 16);
+      uint32_t inc = mine;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= d) inc += y;
+      }
+      const uint32_t all = __shfl_sync(0xFFFFFFFFu, inc, 31);
+      if (total + (int)(all & 0xFFFFu) > kSwCap) { over = true; break; }
+      int ks = total + (int)((inc - mine) & 0xFFFFu), ke = total_e + (int)((inc - mine) >> 16);
+      for (uint32_t x = m.ws; x; x &= x - 1) sh.wpos[ks++] = (uint16_t)(g + __ffs(x) - 1);
+      for (uint32_t x = m.we; x; x &= x - 1) sh.wend[ke++] = (uint16_t)(g + __ffs(x) - 1);
+      for (uint32_t x = m.bad; x; x &= x - 1) atomicOr(&sh.flags[sw_owner(sh.sstart, g + __ffs(x) - 1)], 2u);
+      total += (int)(all & 0xFFFFu);
+      total_e += (int)(all >> 16);
+    }
+    __syncwarp();
+    if (over) {
+      if (len > 0)
+        nw = memo_scan_plain(tb, &sh.stage[s_rel], (int32_t)len, mv.add_dummy_prefix ? 1 : 0,
+                             wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4);
+    } else {
+      // words before my sentence = starts listed below my first byte
+      int first = 0;
+      for (int n = total; n > 0;) {
+        const int half = n >> 1;
+        if ((int)sh.wpos[first + half] < s_rel) { first += half + 1; n -= half + 1; }
+        else n = half;
+      }
+      sh.fw[lane] = (uint16_t)first;
+      const int next = __shfl_down_sync(0xFFFFFFFFu, first, 1);
+      nw = (lane == 31 ? total : next) - first;
+      __syncwarp();
+      // ---- words
+      uint32_t *wl = wslots + memo_wslot_base(off, c0, tw);
+      const uint64_t prefix0 = mv.add_dummy_prefix ? 1ull : 0ull;
+      for (int k = lane; k < total; k += 32) {
+        const int s = sh.wpos[k], n = (int)sh.wend[k] - s + 1;
+        const int u = sw_owner(sh.sstart, s);
+        const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, s == (int)sh.sstart[u] ? prefix0 : 1ull);
+        if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[u], 1u);
+        else memo_store_slot(wl + sh.wdelta[u] + (k - (int)sh.fw[u]), slot);
+      }
+      __syncwarp();
+      const uint32_t f = sh.flags[lane];
+      if (f & 2u) nw = -2;
+      else if (f & 1u) nw = -1;
+    }
+  }
+  if (!live) return;
+  if (nw == -2) slow_list[atomicAdd(&counters[C_NSLOW], 1u)] = (int32_t)t;
+  nwords[t] = nw;
+  cnt[t] = 0;
+  status[t] = 0;
+}
+
 // k_memo_scan: the general scan (fast_normalize_scan + MemoSink: every normalizer rule,
 // user symbols, whitespace policy, long words) over the sentences k_memo_scan_plain listed.
 __global__ void __launch_bounds__(kMemoThreads)
@@ -1747,10 +1887,17 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         tb.n_new = d_counters + C_NNEW;
         const unsigned gnew = (tb.max_new + 255) / 256;
         if ((rc = kev_record(M, st, 0, T_MEMO_COLLECT))) return rc;
-        k_memo_scan_plain<<<gsent, kScanWarps * 32, 0, st>>>(
-            M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
-            (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
-            d_counters);
+        static const bool scan_lanes = getenv("SPM_CUDA_SCAN_PER_SENTENCE") != nullptr;   // measurement of the older scan
+        if (scan_lanes)
+          k_memo_scan_plain<<<gsent, kScanWarps * 32, 0, st>>>(
+              M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
+              (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
+              d_counters);
+        else
+          k_memo_scan_words<<<(unsigned)((cn + kSwWarps * 32 - 1) / (kSwWarps * 32)), kSwWarps * 32, 0, st>>>(
+              M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
+              (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
+              d_counters);
         k_memo_scan<<<gsent, kMemoThreads, 0, st>>>(
             M->mv, tb, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_vit.p,
             (uint32_t *)M->w_wslots.p, (int32_t *)M->w_nwords.p, d_counters);

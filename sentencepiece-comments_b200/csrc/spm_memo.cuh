@@ -310,6 +310,71 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
   return nw;
 }
 
+// ---- the same scan, byte-parallel (k_memo_scan_words): the text of 32 consecutive sentences is
+// swept 8 bytes per lane; every lane reports, as 8-bit masks over its bytes, where words start,
+// where they end and which bytes make a sentence unfit for this scan.  A word is a maximal
+// run of bytes 0x21..0x7E inside one sentence; `b9` bit j says that a sentence starts at byte
+// j of the chunk (bit 8: at the first byte after it; the end of the warp's text counts as a
+// start), `lo`/`hi` clip the chunk to the warp's text ([lo, hi) of 0..8), `pb`/`nb` are the
+// bytes before and after the chunk.  A sentence is unfit (memo_scan_plain's -2) when it holds
+// a byte outside 0x20..0x7E, or a space that is leading, trailing or follows a space.
+struct SwMasks {
+  uint32_t ws, we, bad;
+};
+SPM_HD uint32_t sw_gather(uint64_t f) {   // bit 7 of byte j -> bit j
+  return (uint32_t)(((f >> 7) * 0x0102040810204080ull) >> 56);
+}
+SPM_HD SwMasks sw_chunk_masks(uint64_t w, uint32_t pb, uint32_t nb, uint32_t b9, int lo, int hi) {
+  const uint64_t H = 0x8080808080808080ull, L7 = 0x7F7F7F7F7F7F7F7Full;
+  const uint64_t lw = w & L7;
+  const uint64_t ge21 = (lw | H) - 0x2121212121212121ull;   // bit 7: low seven bits >= 0x21 (no borrow leaves a byte)
+  const uint64_t le7e = ~(lw + 0x0101010101010101ull);      // bit 7: low seven bits <= 0x7E (no carry leaves a byte)
+  const uint64_t x = w ^ 0x2020202020202020ull;
+  const uint64_t spf = ~(((x & L7) + L7) | x) & H;          // byte == 0x20
+  lo = lo < 0 ? 0 : (lo > 8 ? 8 : lo);
+  hi = hi < 0 ? 0 : (hi > 8 ? 8 : hi);
+  const uint32_t valid = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+  const uint32_t good = sw_gather(ge21 & le7e & ~w & H) & valid;
+  const uint32_t sp = sw_gather(spf);
+  const uint32_t pgood = (pb >= 0x21u && pb <= 0x7Eu) ? 1u : 0u, psp = pb == 0x20u ? 1u : 0u;
+  const uint32_t ngood = (nb >= 0x21u && nb <= 0x7Eu) ? 0x80u : 0u;
+  const uint32_t bcur = b9 & 0xFFu, bnext = (b9 >> 1) & 0xFFu;
+  const uint32_t gprev = (good << 1) | pgood, gnext = (good >> 1) | ngood;
+  SwMasks m;
+  m.ws = good & (bcur | ~gprev) & 0xFFu;
+  m.we = good & (bnext | ~gnext) & 0xFFu;
+  m.bad = ((valid & ~good & ~sp) | (sp & valid & (bcur | bnext | (sp << 1) | psp))) & 0xFFu;
+  return m;
+}
+
+// Slot of the word s[0..n) (n >= 1 bytes of 0x21..0x7E, s readable in aligned 8-byte words up to
+// 32 + 7 bytes past its start): exactly the keys memo_scan_plain() builds -- one head key up to
+// 14 bytes, head + tail key up to 24.  0xFFFFFFFF: the word cannot be keyed (too long, table full).
+SPM_HD uint32_t sw_word_slot(const MemoTable &tb, const uint8_t *s, int n, uint64_t prefix) {
+  if (n > kMemoMaxBytes) return 0xFFFFFFFFu;
+  const uint8_t *q = (const uint8_t *)((uintptr_t)s & ~(uintptr_t)7);
+  const int r = (int)(s - q);
+  const uint64_t a0 = fast_load8(q), a1 = fast_load8(q + 8), a2 = fast_load8(q + 16), a3 = fast_load8(q + 24);
+  uint64_t w0 = fast_window(a0, a1, r), w1 = fast_window(a1, a2, r);
+  if (n <= kMemoKeyBytes) {
+    if (n < 8) { w0 &= ~0ull >> (8 * (8 - n)); w1 = 0; }
+    else if (n < 16) w1 &= n == 8 ? 0ull : ~0ull >> (8 * (16 - n));
+    const uint64_t mb = ((uint64_t)n << 1) | prefix;
+    return memo_find_or_insert(tb, mb | (w0 << 8), (w0 >> 56) | (w1 << 8) | (mb << 56));
+  }
+  const uint64_t w2 = fast_window(a2, a3, r);
+  const uint64_t hb = 0x40ull | prefix;
+  const uint64_t h1 = w1 & 0x0000FFFFFFFFFFFFull;
+  const uint32_t hs = memo_find_or_insert(tb, hb | (w0 << 8), (w0 >> 56) | (h1 << 8) | (hb << 56));
+  if (hs == 0xFFFFFFFFu) return hs;
+  const int nt = n - kMemoKeyBytes;                        // 1..10 bytes go into the tail key
+  uint64_t t0 = (w1 >> 48) | (w2 << 16), t1 = w2 >> 48;    // word bytes 14..21, 22..23
+  if (nt < 8) { t0 &= ~0ull >> (8 * (8 - nt)); t1 = 0; }
+  else t1 &= nt == 8 ? 0ull : (nt == 9 ? 0xFFull : 0xFFFFull);
+  const uint64_t mb = 0x80ull | (uint64_t)nt;
+  return memo_find_or_insert(tb, ((uint64_t)hs << 8) | (t0 << 32) | mb, (t0 >> 32) | (t1 << 32) | (mb << 56));
+}
+
 // Bytes of the word in slot `slot`: U+2581 prefix (when keyed with one) + content, zero
 // padded to `cap` (>= 40) bytes.  Returns the byte count; 0 for a head entry (not a word).
 SPM_HD int memo_word_bytes(const MemoKey *keys, uint32_t slot, uint8_t *out, int cap) {

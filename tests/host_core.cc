@@ -8,6 +8,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -452,6 +453,101 @@ int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *word
     obj_ntok[0] -= (double)(f * z) / all_freq;
     obj_ntok[1] += nt;
     if (logz) logz[i] = z;
+  }
+  return 0;
+}
+
+
+// The byte-parallel word scan (k_memo_scan_words: sw_chunk_masks + sw_word_slot, lanes replayed
+// one after another) against memo_scan_plain() on the same table: same word count, same
+// slots, no key that the per-sentence scan did not make.  text/off: n sentences; groups of 32
+// are laid out like a warp's staging buffer at every alignment.  Returns 0, or 100000000 * kind +
+// sentence index of the first difference.
+int64_t hc_scan_words_check(const uint8_t *text, const int64_t *off, int64_t n, int prefix0, int64_t *n_plain) {
+  const size_t slots_n = 1 << 18;
+  std::vector<MemoKey> mkeys(slots_n);
+  std::vector<MemoRes> mres(1);
+  std::vector<uint32_t> mnew(slots_n / 2);
+  memset((void *)mkeys.data(), 0, slots_n * sizeof(MemoKey));
+  uint32_t n_new = 0;
+  MemoTable tb;
+  memset(&tb, 0, sizeof(tb));
+  tb.keys = mkeys.data(); tb.res = mres.data(); tb.mask = (uint32_t)slots_n - 1; tb.new_list = mnew.data();
+  tb.n_new = &n_new; tb.max_new = (uint32_t)mnew.size();
+  *n_plain = 0;
+  for (int64_t tw = 0; tw < n; tw += 32) {
+    const int64_t te = std::min<int64_t>(tw + 32, n);
+    const int64_t a = off[tw], b = off[te];
+    const int a_rel = (int)(tw / 32 % 16);
+    const int b_rel = a_rel + (int)(b - a);
+    if (b_rel > 5120 - 48) continue;
+    std::vector<uint64_t> sbuf(5120 / 8 + 8, 0xA5A5A5A5A5A5A5A5ull);      // what lies around the text must not matter
+    uint8_t *stage = (uint8_t *)sbuf.data();
+    memcpy(stage + a_rel, text + a, b - a);
+    // reference: one sentence at a time
+    std::vector<std::vector<uint32_t>> want(32);
+    int32_t want_nw[32];
+    bool all_ok = true;
+    for (int64_t t = tw; t < te; ++t) {
+      const int64_t len = off[t + 1] - off[t];
+      want[t - tw].assign(len / 2 + 4, 0);
+      want_nw[t - tw] = len > 0 ? memo_scan_plain(tb, stage + a_rel + (off[t] - a), (int32_t)len, prefix0,
+                                                  want[t - tw].data(), (int32_t)(len / 2 + 4)) : 0;
+      if (want_nw[t - tw] < 0) all_ok = false; else ++*n_plain;
+    }
+    const uint32_t new_before = n_new;
+    // the warp
+    int sstart[32];
+    std::vector<uint8_t> bmap((5120 / 32 + 4) * 4, 0);
+    for (int l = 0; l < 32; ++l) {
+      sstart[l] = tw + l < te ? a_rel + (int)(off[tw + l] - a) : b_rel;
+      bmap[sstart[l] >> 3] |= (uint8_t)(1u << (sstart[l] & 7));
+    }
+    bmap[b_rel >> 3] |= (uint8_t)(1u << (b_rel & 7));
+    auto owner = [&](int pos) { int t = 0; for (int st = 16; st; st >>= 1) if (sstart[t + st] <= pos) t += st; return t; };
+    std::vector<int> wpos, wend;
+    uint32_t flags[32] = {0};
+    for (int g0 = a_rel & ~7; g0 < b_rel; g0 += 256)
+      for (int l = 0; l < 32; ++l) {
+        const int g = g0 + l * 8;
+        if (g >= b_rel) continue;
+        uint64_t w;
+        memcpy(&w, stage + g, 8);
+        const uint32_t pb = g > 0 ? stage[g - 1] : 0u, nb = stage[g + 8];
+        const uint32_t b9 = (uint32_t)bmap[g >> 3] | ((uint32_t)bmap[(g >> 3) + 1] << 8);
+        const SwMasks m = sw_chunk_masks(w, pb, nb, b9, a_rel - g, b_rel - g);
+        for (uint32_t x = m.ws; x; x &= x - 1) wpos.push_back(g + __builtin_ctz(x));
+        for (uint32_t x = m.we; x; x &= x - 1) wend.push_back(g + __builtin_ctz(x));
+        for (uint32_t x = m.bad; x; x &= x - 1) flags[owner(g + __builtin_ctz(x))] |= 2u;
+      }
+    if (wpos.size() != wend.size()) return 100000000ll + tw;
+    std::vector<std::vector<uint32_t>> got(32);
+    int first[33];
+    for (int l = 0; l < 32; ++l) first[l] = (int)(std::lower_bound(wpos.begin(), wpos.end(), sstart[l]) - wpos.begin());
+    first[32] = (int)wpos.size();
+    for (size_t k = 0; k < wpos.size(); ++k) {
+      const int s = wpos[k], len = wend[k] - s + 1;
+      if (len < 1) return 200000000ll + tw;
+      const int u = owner(s);
+      const uint32_t slot = sw_word_slot(tb, stage + s, len, s == sstart[u] ? (uint64_t)prefix0 : 1ull);
+      if (slot == 0xFFFFFFFFu) flags[u] |= 1u;
+      if ((int)got[u].size() != (int)k - first[u]) return 300000000ll + tw + u;
+      got[u].push_back(slot);
+    }
+    for (int64_t t = tw; t < te; ++t) {
+      const int l = (int)(t - tw);
+      int32_t nw = first[l + 1] - first[l];
+      if (flags[l] & 2u) nw = -2; else if (flags[l] & 1u) nw = -1;
+      const int32_t w = want_nw[l];
+      if (w == -2 && nw != -2) return 400000000ll + t;
+      if (w == -1 && nw >= 0) return 500000000ll + t;
+      if (w >= 0) {
+        if (nw != w) return 600000000ll + t;
+        for (int k = 0; k < w; ++k)
+          if (got[l][k] != want[l][k]) return 700000000ll + t;
+      }
+    }
+    if (all_ok && n_new != new_before) return 800000000ll + tw;
   }
   return 0;
 }

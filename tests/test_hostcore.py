@@ -3,6 +3,7 @@ spm_fast.cuh fast tier, host model loader) compiled for the CPU by
 tests/host_core.cc and compared with the reference fixtures / the oracle.
 This is how every kernel change is parity-checked in the GPU-less container
 before it runs on a B200; the shipped library has no host encode path."""
+import ctypes
 import os
 
 import numpy as np
@@ -162,6 +163,36 @@ def test_word_memo_serves_and_matches(make_hostcore, corpora):
         plain = float(((st >> 23) & 1).mean())     # sentences keyed by memo_scan_plain
         if corpus == "syn_en":
             assert plain >= 0.9, (model, plain)
+
+
+def test_word_scan_matches_sentence_scan(hostcore, corpora):
+    """k_memo_scan_words' arithmetic (sw_chunk_masks, sw_word_slot; lanes replayed on the CPU)
+    keys every word exactly as memo_scan_plain does: same word counts, same slots, no extra
+    keys -- on clean text, on text with NFKC / control / malformed bytes, and on edge shapes."""
+    rng = np.random.default_rng(7)
+    edge = [b"", b"a", b" ", b"a b", b" a", b"a ", b"a  b", b"abcdefghijklmn", b"abcdefghijklmno", b"x" * 24, b"y" * 25,
+            b"abcdefghijklmn abcdefghijklmnopqrstuvwx z", b"a\tb", b"caf\xc3\xa9 au lait", b"~ ! ~", b"\x7f", b"a \x1f",
+            b"", b"", b"z", b"ab cd ef gh ij kl mn op qr st uv wx yz" * 3, b"q" * 60 + b" r"]
+    for _ in range(300):    # random shapes around the 8-byte chunk borders
+        k = int(rng.integers(0, 40))
+        edge.append(bytes(rng.choice(np.frombuffer(b"ab  c.Z~", dtype=np.uint8), size=k).tolist()))
+    etext = np.frombuffer(b"".join(edge), dtype=np.uint8)
+    eoff = np.concatenate([[0], np.cumsum([len(e) for e in edge])]).astype(np.int64)
+    cases = [(etext, eoff)]
+    for name in ("syn_en", "syn_dirty", "botchan"):
+        text, off = corpora[name]
+        m = min(4000, len(off) - 1)
+        cases.append((np.ascontiguousarray(text[: off[m]]), np.ascontiguousarray(off[: m + 1])))
+    hostcore.hc_scan_words_check.restype = ctypes.c_int64
+    hostcore.hc_scan_words_check.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p]
+    plain = []
+    for text, off in cases:
+        for prefix in (1, 0):
+            n_plain = ctypes.c_int64(0)
+            rc = hostcore.hc_scan_words_check(text.ctypes.data, off.ctypes.data, len(off) - 1, prefix, ctypes.byref(n_plain))
+            assert rc == 0, rc
+        plain.append(n_plain.value)
+    assert plain[1] >= 3900 and 2000 < plain[2] < 3900, plain   # clean text: all plain; "dirty": most (botchan lines end in \r: none)
 
 
 def test_loader_rejects_bad_models(hostcore):

@@ -19,7 +19,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${V}_launches_pieces.csv python tools/pieces_bench.py --op pieces --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > $O/${V}_ncu_launches_pieces.log 2>&1
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/${V}_launches_decode.csv python tools/pieces_bench.py --op decode --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > $O/${V}_ncu_launches_decode.log 2>&1
 # full captures: the top kernels of the id path, the pieces path and decode (one launch each)
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_memo_scan_plain|k_memo_emit|k_compact|k_encode_warp' -c 4 -f -o $O/${V}_full_ids python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > $O/${V}_ncu_full_ids.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_memo_scan_words|k_memo_emit|k_compact|k_encode_warp' -c 4 -f -o $O/${V}_full_ids python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > $O/${V}_ncu_full_ids.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_pc_normalize|k_pc_spans|k_pc_copy_norm' -c 3 -f -o $O/${V}_full_pieces python tools/pieces_bench.py --op pieces --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > $O/${V}_ncu_full_pieces.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_decode' -c 2 -f -o $O/${V}_full_decode python tools/pieces_bench.py --op decode --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > $O/${V}_ncu_full_decode.log 2>&1
 ls -la $O | tail -40
