@@ -655,8 +655,8 @@ constexpr int kScanWarps = 8, kScanWarpBytes = 5120;
 constexpr int kMemoThreads = 256;
 __global__ void __launch_bounds__(kScanWarps * 32)
 k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn,
-                  const uint8_t *lo, const uint8_t *hi, uint32_t *wslots, int32_t *nwords, int32_t *cnt,
-                  uint32_t *status, int32_t *slow_list, uint32_t *counters) {
+                  const uint8_t *lo, const uint8_t *hi, uint32_t *wslots, uint32_t *wbase, uint32_t half,
+                  int32_t *nwords, int32_t *cnt, uint32_t *status, int32_t *slow_list, uint32_t *counters) {
   __shared__ __align__(16) uint8_t stage[kScanWarps][kScanWarpBytes];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t tw = ((int64_t)blockIdx.x * kScanWarps + wid) * 32;
@@ -690,6 +690,7 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
     nw = memo_scan_plain(tb, &stage[wid][0] + ((text + o0) - src), (int32_t)len, mv.add_dummy_prefix ? 1 : 0,
                          wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4);
   if (nw == -2) slow_list[atomicAdd(&counters[C_NSLOW], 1u)] = (int32_t)t;
+  wbase[t] = (uint32_t)memo_wslot_base(off, c0, t) + (nw == -2 ? half : 0u);
   nwords[t] = nw;
   cnt[t] = 0;
   status[t] = 0;
@@ -704,7 +705,8 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
 //          the k-th end);
 //   words: one lane per word: sentence of the word (binary search over the 32 starts), key from
 //          the staged bytes (sw_word_slot), 16-byte probe / 128-bit CAS, slot stored at
-//          (sentence's slot list)[word index] -- the layout k_memo_emit reads.
+//          (warp's slot list)[k]: coalesced, dense; wbase[t] tells k_memo_emit where the words
+//          of sentence t begin.
 // A warp whose text holds more than kSwCap words runs memo_scan_plain per lane instead.
 constexpr int kSwWarps = 4, kSwCap = 640, kSwMapWords = kScanWarpBytes / 32 + 4;
 struct SwWarp {
@@ -713,7 +715,6 @@ struct SwWarp {
   uint16_t wpos[kSwCap], wend[kSwCap];   // first / last byte of word k
   uint16_t sstart[32];               // first byte of the sentence of lane l
   uint16_t fw[32];                   // words before it
-  int32_t wdelta[32];                // its slot list, relative to the one of the warp's first sentence
   uint32_t flags[32];                // 1: a word cannot be keyed (-1), 2: not a plain sentence (-2)
 };
 __device__ __forceinline__ int sw_owner(const uint16_t *sstart, int pos) {   // last sentence starting at or before pos
@@ -725,8 +726,8 @@ __device__ __forceinline__ int sw_owner(const uint16_t *sstart, int pos) {   // 
 }
 __global__ void __launch_bounds__(kSwWarps * 32)
 k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off, int64_t c0, int64_t cn,
-                  const uint8_t *lo, const uint8_t *hi, uint32_t *wslots, int32_t *nwords, int32_t *cnt,
-                  uint32_t *status, int32_t *slow_list, uint32_t *counters) {
+                  const uint8_t *lo, const uint8_t *hi, uint32_t *wslots, uint32_t *wbase, uint32_t half,
+                  int32_t *nwords, int32_t *cnt, uint32_t *status, int32_t *slow_list, uint32_t *counters) {
   __shared__ SwWarp shw[kSwWarps];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   SwWarp &sh = shw[wid];
@@ -740,6 +741,9 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
   const int64_t span = (text + b) - src;
   const bool staged = span <= kScanWarpBytes - 48 && mv.ascii_plain && mv.escape_ws;   // sw_word_slot reads 32 + 7 bytes
   int32_t nw = 0;
+  // where k_memo_emit finds the slots of my sentence: the general scan and the per-lane scan keep one
+  // list per sentence in the upper half of wslots, the words of a swept warp lie side by side
+  uint32_t wb = live ? half + (uint32_t)memo_wslot_base(off, c0, t) : 0u;
   if (!staged) {
     if (len >= kLongMaxRaw) nw = -1;
     else if (len > 0) nw = -2;
@@ -760,7 +764,6 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
     for (int j = lane; j < (b_rel >> 5) + 2; j += 32) sh.bmap[j] = 0;
     sh.sstart[lane] = (uint16_t)s_rel;
     sh.flags[lane] = 0;
-    sh.wdelta[lane] = live ? (int32_t)(memo_wslot_base(off, c0, t) - memo_wslot_base(off, c0, tw)) : 0;
     __syncwarp();
     atomicOr(&sh.bmap[s_rel >> 5], 1u << (s_rel & 31));
     if (lane == 31) atomicOr(&sh.bmap[b_rel >> 5], 1u << (b_rel & 31));
@@ -798,8 +801,8 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
     __syncwarp();
     if (over) {
       if (len > 0)
-        nw = memo_scan_plain(tb, &sh.stage[s_rel], (int32_t)len, mv.add_dummy_prefix ? 1 : 0,
-                             wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4);
+        nw = memo_scan_plain(tb, &sh.stage[s_rel], (int32_t)len, mv.add_dummy_prefix ? 1 : 0, wslots + wb,
+                             (int32_t)(len >> 1) + 4);
     } else {
       // words before my sentence = starts listed below my first byte
       int first = 0;
@@ -813,23 +816,26 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       nw = (lane == 31 ? total : next) - first;
       __syncwarp();
       // ---- words
-      uint32_t *wl = wslots + memo_wslot_base(off, c0, tw);
+      const uint32_t wbw = (uint32_t)memo_wslot_base(off, c0, tw);   // the warp's words: wl[0 .. total)
+      uint32_t *wl = wslots + wbw;
       const uint64_t prefix0 = mv.add_dummy_prefix ? 1ull : 0ull;
       for (int k = lane; k < total; k += 32) {
         const int s = sh.wpos[k], n = (int)sh.wend[k] - s + 1;
         const int u = sw_owner(sh.sstart, s);
         const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, s == (int)sh.sstart[u] ? prefix0 : 1ull);
         if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[u], 1u);
-        else memo_store_slot(wl + sh.wdelta[u] + (k - (int)sh.fw[u]), slot);
+        else memo_store_slot(wl + k, slot);
       }
       __syncwarp();
       const uint32_t f = sh.flags[lane];
       if (f & 2u) nw = -2;
       else if (f & 1u) nw = -1;
+      else wb = wbw + (uint32_t)first;
     }
   }
   if (!live) return;
   if (nw == -2) slow_list[atomicAdd(&counters[C_NSLOW], 1u)] = (int32_t)t;
+  wbase[t] = wb;
   nwords[t] = nw;
   cnt[t] = 0;
   status[t] = 0;
@@ -922,7 +928,7 @@ k_memo_words_bpe(FastParams fp, MemoTable tb, const uint8_t *wtext, const int32_
 constexpr int kEmitTile = 16;
 __global__ void __launch_bounds__(kMemoThreads)
 k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t cn, const uint32_t *wslots,
-            const int32_t *nwords, int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *vit_list,
+            const uint32_t *wbase, const int32_t *nwords, int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *vit_list,
             uint32_t *counters, int list_idx) {
   const int lane = threadIdx.x & (kEmitTile - 1);
   const unsigned tmask = 0xFFFFu << (threadIdx.x & 16);     // the lanes of this tile inside the warp
@@ -938,7 +944,7 @@ k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t c
     if (!bad) {
       const int64_t o0 = off[c0 + t];
       const int32_t cap = (int32_t)(off[c0 + t + 1] - o0) + kFastExtraChars;
-      const uint32_t *sl = wslots + memo_wslot_base(off, c0, t);
+      const uint32_t *sl = wslots + wbase[t];
       int32_t *out = stage + fast_stage_base(off, c0, t);
       float bub = 0.0f;
       bool carry_unk = false;
@@ -1254,7 +1260,7 @@ struct spm_cuda_model {
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
-      w_perm, w_genlist, w_longlist, w_wslots, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
+      w_perm, w_genlist, w_longlist, w_wslots, w_wbase, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status;
   mutable DevBuf px[20];   // workspace of the pieces / decode / dense calls (spm_pieces.inc)
   mutable int emit_blocks = 0;      // resident CTAs of k_memo_emit per SM (occupancy query, first use)
@@ -1280,7 +1286,7 @@ struct spm_cuda_model {
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2, &m->d_cont2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
             &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
-            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
+            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_wbase, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status,
             &m->px[0], &m->px[1], &m->px[2], &m->px[3], &m->px[4], &m->px[5], &m->px[6], &m->px[7], &m->px[8], &m->px[9],
@@ -1880,7 +1886,10 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       // sort -> normalize -> Viterbi / merge path below, like every sentence does without the memo.
       const int32_t *todo = nullptr;     // nullptr: all sentences of the chunk
       if (memo) {
-        if ((rc = M->w_wslots.ensure((size_t)(raw / 2 + 4 * cn + 64) * 4))) return rc;
+        // lower half: the words of 32 sentences side by side (k_memo_scan_words); upper half: one list per sentence
+        const uint32_t wslot_half = (uint32_t)(raw / 2 + 4 * cn + 64);
+        if ((rc = M->w_wslots.ensure((size_t)wslot_half * 2 * 4))) return rc;
+        if ((rc = M->w_wbase.ensure(cn * 4))) return rc;
         if ((rc = M->w_nwords.ensure(cn * 4))) return rc;
         if ((rc = M->w_vit.ensure(cn * 4))) return rc;
         MemoTable tb = memo_tb;
@@ -1891,16 +1900,16 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         if (scan_lanes)
           k_memo_scan_plain<<<gsent, kScanWarps * 32, 0, st>>>(
               M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
-              (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
+              (uint32_t *)M->w_wbase.p, wslot_half, (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
               d_counters);
         else
           k_memo_scan_words<<<(unsigned)((cn + kSwWarps * 32 - 1) / (kSwWarps * 32)), kSwWarps * 32, 0, st>>>(
               M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
-              (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
+              (uint32_t *)M->w_wbase.p, wslot_half, (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
               d_counters);
         k_memo_scan<<<gsent, kMemoThreads, 0, st>>>(
             M->mv, tb, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_vit.p,
-            (uint32_t *)M->w_wslots.p, (int32_t *)M->w_nwords.p, d_counters);
+            (uint32_t *)M->w_wslots.p + wslot_half, (int32_t *)M->w_nwords.p, d_counters);
         launches += 1;
         if ((rc = kev_record(M, st, 1))) return rc;
         if ((rc = kev_record(M, st, 0, T_MEMO_WORDS))) return rc;
@@ -1927,7 +1936,8 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         const int64_t emit_per_sm = env_emit ? std::max(1, atoi(env_emit)) : M->emit_blocks;
         const unsigned gemit = (unsigned)std::min<int64_t>((cn + 15) / 16, emit_per_sm * (int64_t)M->sm_count);
         k_memo_emit<<<gemit, kMemoThreads, 0, st>>>(
-            tb, M->fast_kind == 1, d_off, c0, cn, (const uint32_t *)M->w_wslots.p, (const int32_t *)M->w_nwords.p,
+            tb, M->fast_kind == 1, d_off, c0, cn, (const uint32_t *)M->w_wslots.p, (const uint32_t *)M->w_wbase.p,
+            (const int32_t *)M->w_nwords.p,
             (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
             d_counters, C_NVIT);
         if ((rc = kev_record(M, st, 1))) return rc;
