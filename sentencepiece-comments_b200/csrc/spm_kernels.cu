@@ -1119,6 +1119,35 @@ k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0
   }
   const bool simple = plan.npre == 0 && plan.nsuf == 0;
   const int m = (int)min((int64_t)32, cn - t0);
+  if (simple) {
+    // four sentences per step: their loads are in flight together (one sentence at a time is one
+    // dependent DRAM round trip per sentence and warp)
+    for (int j = 0; j < m; j += 4) {
+      int32_t v[4], core[4];
+      int64_t dst[4];
+      const int32_t *src[4];
+      bool rev[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int jj = min(j + u, 31);
+        core[u] = __shfl_sync(0xFFFFFFFFu, my_core, jj);
+        const int gen = __shfl_sync(0xFFFFFFFFu, my_gen, jj);
+        const int64_t so = __shfl_sync(0xFFFFFFFFu, my_src, jj);
+        dst[u] = __shfl_sync(0xFFFFFFFFu, my_dst, jj);
+        if (j + u >= m) core[u] = 0;
+        src[u] = (gen == 1 ? gstage : stage) + so;
+        rev[u] = (plan.flip != 0) == (gen != 0);   // unigram fast-tier staging is already reversed
+        v[u] = lane < core[u] ? __ldcs(src[u] + (rev[u] ? core[u] - 1 - lane : lane)) : 0;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (lane < core[u] && dst[u] + lane < capacity) __stcs(ids + dst[u] + lane, v[u]);
+        for (int32_t q = lane + 32; q < core[u]; q += 32)
+          if (dst[u] + q < capacity) ids[dst[u] + q] = src[u][rev[u] ? core[u] - 1 - q : q];
+      }
+    }
+    return;
+  }
   for (int j = 0; j < m; ++j) {
     const int32_t core = __shfl_sync(0xFFFFFFFFu, my_core, j);
     const int gen = __shfl_sync(0xFFFFFFFFu, my_gen, j);
@@ -1779,13 +1808,19 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     // fixed latency of the leftover tiers -- a few hundred rare-word sentences walk cold trie
     // paths -- and 16 chunks measured slower than 8: profiles/r1_v5_summary.md.)
     int64_t want = kMaxChunk;
+    // The last chunks are small: what cannot overlap is the last chunk's kernels and its copy-out
+    // (1/32 of the batch instead of 1/8).  SPM_CUDA_HOST_CHUNKS=k: k equal chunks (measurements).
+    static const int kTaper[8] = {5, 5, 5, 5, 5, 4, 2, 1};   // 32nds of the batch
+    bool taper = false;
     if (host && n >= (1 << 20)) {
       static const char *env_chunks = getenv("SPM_CUDA_HOST_CHUNKS");   // tuning experiments only
       const int64_t parts = std::max<int64_t>(1, std::min<int64_t>(64, env_chunks ? atoll(env_chunks) : 8));
       want = std::min(kMaxChunk, (n + parts - 1) / parts);
+      taper = env_chunks == nullptr && n / 32 * 5 < kMaxChunk;
     }
     int64_t c0 = 0, off_c0 = text_lo;
     while (c0 < n) {
+      if (taper) want = chunks.size() < 7 ? std::max<int64_t>(1, n / 32 * kTaper[chunks.size()]) : kMaxChunk;
       int64_t c1 = std::min(n, c0 + want), off_c1 = 0;
       if ((rc = read_off(c1, &off_c1))) return rc;
       while (off_c1 - off_c0 > kRawBudget && c1 - c0 > 1) {
