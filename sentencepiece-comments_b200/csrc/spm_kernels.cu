@@ -6,8 +6,10 @@
 // that can prove its result exact:
 //
 //   TIER 1, WORD MEMO (spm_memo.cuh; models without U+2581 inside pieces)
-//   k_memo_scan_plain  raw text staged through shared memory, printable-ASCII
-//                      words keyed with SWAR runs; other sentences are listed
+//   k_memo_scan_words  raw text of 32 sentences staged through shared memory; lanes
+//                      sweep it 8 bytes each (word starts / ends as bit masks), then
+//                      one lane per word keys and probes; other sentences are listed
+//                      (k_memo_scan_plain: the older thread-per-sentence form)
 //   k_memo_scan        general normalizer writing word keys for the listed ones
 //                                                     (src/normalizer.cc:88-300)
 //   k_memo_words_*     every NEW word once: stand-alone Viterbi with margin
@@ -708,11 +710,12 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
 //          (warp's slot list)[k]: coalesced, dense; wbase[t] tells k_memo_emit where the words
 //          of sentence t begin.
 // A warp whose text holds more than kSwCap words runs memo_scan_plain per lane instead.
-constexpr int kSwWarps = 4, kSwCap = 640, kSwMapWords = kScanWarpBytes / 32 + 4;
+constexpr int kSwWarps = 4, kSwBytes = 4608, kSwCap = 512, kSwLong = 64, kSwMapWords = kSwBytes / 32 + 4;
 struct SwWarp {
-  __align__(16) uint8_t stage[kScanWarpBytes];
+  __align__(16) uint8_t stage[kSwBytes];
   uint32_t bmap[kSwMapWords];        // bit i: a sentence starts at stage byte i (or the warp's text ends there)
   uint16_t wpos[kSwCap], wend[kSwCap];   // first / last byte of word k
+  uint16_t wlong[kSwLong];           // words of 15..24 bytes (two dependent probes): keyed after the others
   uint16_t sstart[32];               // first byte of the sentence of lane l
   uint16_t fw[32];                   // words before it
   uint32_t flags[32];                // 1: a word cannot be keyed (-1), 2: not a plain sentence (-2)
@@ -739,7 +742,7 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
   const int64_t o0 = live ? off[c0 + t] : b, o1 = live ? off[c0 + t + 1] : b, len = o1 - o0;
   const uint8_t *src = (const uint8_t *)((uintptr_t)(text + a) & ~(uintptr_t)15);
   const int64_t span = (text + b) - src;
-  const bool staged = span <= kScanWarpBytes - 48 && mv.ascii_plain && mv.escape_ws;   // sw_word_slot reads 32 + 7 bytes
+  const bool staged = span <= kSwBytes - 48 && mv.ascii_plain && mv.escape_ws;   // sw_word_slot reads 32 + 7 bytes
   int32_t nw = 0;
   // where k_memo_emit finds the slots of my sentence: the general scan and the per-lane scan keep one
   // list per sentence in the upper half of wslots, the words of a swept warp lie side by side
@@ -819,7 +822,42 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       const uint32_t wbw = (uint32_t)memo_wslot_base(off, c0, tw);   // the warp's words: wl[0 .. total)
       uint32_t *wl = wslots + wbw;
       const uint64_t prefix0 = mv.add_dummy_prefix ? 1ull : 0ull;
-      for (int k = lane; k < total; k += 32) {
+      // A word of more than 14 bytes takes two dependent probes (head key, tail key): one such word
+      // among 32 would hold the whole warp for two more round trips, so these wait in a list.
+      int nlong = 0;
+      for (int k0 = 0; k0 < total; k0 += 32) {
+        const int k = k0 + lane;
+        bool later = false;
+        if (k < total) {
+          const int s = sh.wpos[k], n = (int)sh.wend[k] - s + 1;
+          const int u = sw_owner(sh.sstart, s);
+          later = n > kMemoKeyBytes && n <= kMemoMaxBytes;
+          if (!later) {
+            const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, s == (int)sh.sstart[u] ? prefix0 : 1ull);
+            if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[u], 1u);
+            else memo_store_slot(wl + k, slot);
+          }
+        }
+        const uint32_t bl = __ballot_sync(0xFFFFFFFFu, later);
+        if (bl) {
+          const int at = nlong + __popc(bl & ((1u << lane) - 1u));
+          if (later && at < kSwLong) sh.wlong[at] = (uint16_t)k;
+          nlong += __popc(bl);
+          if (nlong > kSwLong) {   // no room: key it now
+            if (later && at >= kSwLong) {
+              const int s = sh.wpos[k], n = (int)sh.wend[k] - s + 1;
+              const int u = sw_owner(sh.sstart, s);
+              const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, s == (int)sh.sstart[u] ? prefix0 : 1ull);
+              if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[u], 1u);
+              else memo_store_slot(wl + k, slot);
+            }
+            nlong = kSwLong;
+          }
+        }
+      }
+      __syncwarp();
+      for (int j = lane; j < nlong; j += 32) {
+        const int k = sh.wlong[j];
         const int s = sh.wpos[k], n = (int)sh.wend[k] - s + 1;
         const int u = sw_owner(sh.sstart, s);
         const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, s == (int)sh.sstart[u] ? prefix0 : 1ull);
