@@ -17,7 +17,8 @@ from . import build as _build
 from . import spt
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = _build.LIB
+# SPM_B200_LIB_VARIANT: a differently compiled libspm_cuda.so (same sources, other build-time knobs) for A/B measurements
+LIB_PATH = os.environ.get("SPM_B200_LIB_VARIANT") or _build.LIB
 
 HOST, DEVICE = 0, 1
 _OPT_CODES = {"bos": 1, "eos": 2, "reverse": 3}
