@@ -180,11 +180,9 @@ k_gen_encode_block(ModelView mv, const int32_t *list, int64_t tn, const int64_t 
 __device__ __forceinline__ int64_t fast_norm_base(const int64_t *off, int64_t c0, int64_t t) {
   return ((3 * (off[c0 + t] - off[c0]) + 15) & ~(int64_t)15) + 160 * t;
 }
-// Slot in the id staging buffer: len + kFastExtraChars ids (ids <= characters), starting on a
-// 32-byte sector, with room to round the stored count up to whole sectors (k_memo_emit).
-constexpr int kStageRowExtra = kFastExtraChars + 16;
+// Slot in the id staging buffer: len + kFastExtraChars ids (ids <= characters).
 __device__ __forceinline__ int64_t fast_stage_base(const int64_t *off, int64_t c0, int64_t t) {
-  return ((off[c0 + t] - off[c0]) + kStageRowExtra * t) & ~(int64_t)7;
+  return (off[c0 + t] - off[c0]) + kFastExtraChars * t;
 }
 
 // Sort key = raw length.  Empty sentences produce nothing; sentences of kFastMaxRaw bytes
@@ -712,16 +710,14 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
 //          (warp's slot list)[k]: coalesced, dense; wbase[t] tells k_memo_emit where the words
 //          of sentence t begin.
 // A warp whose text holds more than kSwCap words runs memo_scan_plain per lane instead.
-#ifndef SPM_SW_BYTES          // build-time knobs of measurements (profiles/r1_v21_summary.md)
+#ifndef SPM_SW_BYTES          // build-time knobs of the measurements in profiles/r1_v21_summary.md
 #define SPM_SW_BYTES 4096
 #endif
 #ifndef SPM_SW_DEFER
 #define SPM_SW_DEFER 1
 #endif
-#ifndef SPM_EMIT_STAGED
-#define SPM_EMIT_STAGED 1
-#endif
-// 32 sentences of the bench corpus: 3.2 KB of text, 512 words on average
+// 32 sentences of the bench corpus: 3.2 KB of text and 512 words on average; 7.3 KB of shared
+// memory per warp -> 7 CTAs = 28 warps per SM
 constexpr int kSwWarps = 4, kSwBytes = SPM_SW_BYTES, kSwCap = 640, kSwLong = 64, kSwMapWords = kSwBytes / 32 + 4;
 struct SwWarp {
   __align__(16) uint8_t stage[kSwBytes];
@@ -975,16 +971,11 @@ k_memo_words_bpe(FastParams fp, MemoTable tb, const uint8_t *wtext, const int32_
 // restated with tile scans): lanes fetch the 32-byte result records of their words, a
 // prefix sum places the ids (forward order) in the staging area.  A sentence with a word
 // that is not memoised / not context-free here joins the list of the Viterbi tier.
-constexpr int kEmitTile = 16, kEmitBuf = 64;
+constexpr int kEmitTile = 16;
 __global__ void __launch_bounds__(kMemoThreads)
 k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t cn, const uint32_t *wslots,
             const uint32_t *wbase, const int32_t *nwords, int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *vit_list,
             uint32_t *counters, int list_idx) {
-  // The ids of a sentence are put together in shared memory and leave as whole 32-byte sectors
-  // (the row starts on a sector, the last sector is padded with zeros): a store that covers a
-  // sector only partly makes the L2 fetch it from DRAM first.
-  __shared__ int32_t ebuf[kMemoThreads / kEmitTile][kEmitBuf];
-  int32_t *buf = ebuf[threadIdx.x / kEmitTile];
   const int lane = threadIdx.x & (kEmitTile - 1);
   const unsigned tmask = 0xFFFFu << (threadIdx.x & 16);     // the lanes of this tile inside the warp
   const int64_t tiles = (int64_t)gridDim.x * (kMemoThreads / kEmitTile);
@@ -1003,7 +994,6 @@ k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t c
       int32_t *out = stage + fast_stage_base(off, c0, t);
       float bub = 0.0f;
       bool carry_unk = false;
-      bool direct = !SPM_EMIT_STAGED;                    // more than kEmitBuf ids: stored one by one
       for (int32_t w0 = 0; w0 < nw && !bad; w0 += kEmitTile) {
         const bool active = w0 + lane < nw;
         uint32_t meta = kMemoReady;
@@ -1039,24 +1029,18 @@ k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t c
         pos += total - (k - drop);                       // exclusive, sentence-wide
         if (total + tile_ids > cap) ok = false;
         if (__any_sync(tmask, !ok)) { bad = true; break; }
-        if (!direct && total + tile_ids > kEmitBuf) {
-          __syncwarp(tmask);
-          for (int32_t q = lane; q < total; q += kEmitTile) out[q] = buf[q];
-          direct = true;
-        }
         if (k > 0) {
           const int32_t v[kMemoInlineIds] = {lo4.w, hi4.x, hi4.y, hi4.z, hi4.w};
-          int32_t *wp = direct ? out + pos - drop : buf + pos - drop;
           if (k <= kMemoInlineIds) {
 #pragma unroll
             for (int j = 0; j < kMemoInlineIds; ++j)
-              if (j >= drop && j < k) wp[j] = v[j];
+              if (j >= drop && j < k) __stcs(out + pos + j - drop, v[j]);
           } else {
             const int32_t *ov = tb.overflow + (size_t)v[kMemoInlineIds - 1] * kMemoOverflowIds;
 #pragma unroll
             for (int j = 0; j < kMemoInlineIds - 1; ++j)
-              if (j >= drop) wp[j] = v[j];
-            for (int j = kMemoInlineIds - 1; j < k; ++j) wp[j] = ov[j - (kMemoInlineIds - 1)];
+              if (j >= drop) __stcs(out + pos + j - drop, v[j]);
+            for (int j = kMemoInlineIds - 1; j < k; ++j) __stcs(out + pos + j - drop, ov[j - (kMemoInlineIds - 1)]);
           }
         }
         total += tile_ids;
@@ -1064,12 +1048,7 @@ k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t c
         const int last_active = min(nw - w0, kEmitTile) - 1;
         carry_unk = __shfl_sync(tmask, last_unk, last_active, kEmitTile);
       }
-      if (!bad && !direct) {
-        __syncwarp(tmask);
-        for (int32_t q = lane; q < ((total + 7) & ~7); q += kEmitTile) __stcs(out + q, q < total ? buf[q] : 0);
-      }
     }
-    __syncwarp(tmask);      // the next sentence of this tile reuses buf
     if (lane == 0) {
       if (bad) {
         vit_list[atomicAdd(&counters[list_idx], 1u)] = (int32_t)t;
@@ -1167,7 +1146,6 @@ k_scan_final(const int32_t *in, int64_t n, Op op, const int64_t *partial, const 
 // Final layout (extra options) into the CSR values.  Each lane reads the header of one
 // sentence (coalesced), then the warp copies the 32 sentences one after another.
 // Fast-tier sentences were staged in reverse order, general-tier ones forward.
-constexpr int kCompactCap = 1024;   // ids of 32 sentences staged by one warp (more: stored directly)
 __global__ void __launch_bounds__(256)
 k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0, int64_t cn, const int32_t *stage,
           const int32_t *gstage, const int64_t *srcoff, const uint32_t *status, const int32_t *cnt,
@@ -1187,54 +1165,6 @@ k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0
   }
   const bool simple = plan.npre == 0 && plan.nsuf == 0;
   const int m = (int)min((int64_t)32, cn - t0);
-  if (simple) {
-    // The ids of the warp's 32 sentences are one contiguous piece of the CSR values.  They are
-    // gathered in shared memory (four sentences per step: their loads are in flight together) and
-    // leave in whole, aligned 128-byte lines: a store that covers a 32-byte sector only partly
-    // makes the L2 fetch the sector from DRAM first (ncu: 1 GB of reads per 0.9 GB written when
-    // every sentence was stored on its own).
-    __shared__ int32_t cbuf[8][kCompactCap];
-    int32_t *buf = cbuf[threadIdx.x >> 5];
-    const int64_t d0 = __shfl_sync(0xFFFFFFFFu, my_dst, 0);
-    const int64_t d1 = __shfl_sync(0xFFFFFFFFu, my_dst + max(my_core, 0), m - 1);
-    const bool staged = d1 - d0 <= kCompactCap;
-    for (int j = 0; j < m; j += 4) {
-      int32_t v[4], core[4];
-      int64_t dst[4];
-      const int32_t *src[4];
-      bool rev[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int jj = min(j + u, 31);
-        core[u] = __shfl_sync(0xFFFFFFFFu, my_core, jj);
-        const int gen = __shfl_sync(0xFFFFFFFFu, my_gen, jj);
-        const int64_t so = __shfl_sync(0xFFFFFFFFu, my_src, jj);
-        dst[u] = __shfl_sync(0xFFFFFFFFu, my_dst, jj);
-        if (j + u >= m) core[u] = 0;
-        src[u] = (gen == 1 ? gstage : stage) + so;
-        rev[u] = (plan.flip != 0) == (gen != 0);   // unigram fast-tier staging is already reversed
-        v[u] = lane < core[u] ? __ldcs(src[u] + (rev[u] ? core[u] - 1 - lane : lane)) : 0;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (staged) {
-          if (lane < core[u]) buf[dst[u] - d0 + lane] = v[u];
-          for (int32_t q = lane + 32; q < core[u]; q += 32) buf[dst[u] - d0 + q] = src[u][rev[u] ? core[u] - 1 - q : q];
-        } else {
-          if (lane < core[u] && dst[u] + lane < capacity) ids[dst[u] + lane] = v[u];
-          for (int32_t q = lane + 32; q < core[u]; q += 32)
-            if (dst[u] + q < capacity) ids[dst[u] + q] = src[u][rev[u] ? core[u] - 1 - q : q];
-        }
-      }
-    }
-    if (staged) {
-      __syncwarp();
-      const int64_t hi = min(d1, capacity);
-      for (int64_t q = (d0 & ~(int64_t)31) + lane; q < hi; q += 32)
-        if (q >= d0) __stcs(ids + q, buf[q - d0]);
-    }
-    return;
-  }
   for (int j = 0; j < m; ++j) {
     const int32_t core = __shfl_sync(0xFFFFFFFFu, my_core, j);
     const int gen = __shfl_sync(0xFFFFFFFFu, my_gen, j);
@@ -1895,19 +1825,13 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     // fixed latency of the leftover tiers -- a few hundred rare-word sentences walk cold trie
     // paths -- and 16 chunks measured slower than 8: profiles/r1_v5_summary.md.)
     int64_t want = kMaxChunk;
-    // The last chunks are small: what cannot overlap is the last chunk's kernels and its copy-out
-    // (1/32 of the batch instead of 1/8).  SPM_CUDA_HOST_CHUNKS=k: k equal chunks (measurements).
-    static const int kTaper[8] = {5, 5, 5, 5, 5, 4, 2, 1};   // 32nds of the batch
-    bool taper = false;
     if (host && n >= (1 << 20)) {
       static const char *env_chunks = getenv("SPM_CUDA_HOST_CHUNKS");   // tuning experiments only
       const int64_t parts = std::max<int64_t>(1, std::min<int64_t>(64, env_chunks ? atoll(env_chunks) : 8));
       want = std::min(kMaxChunk, (n + parts - 1) / parts);
-      taper = env_chunks == nullptr && n / 32 * 5 < kMaxChunk;
     }
     int64_t c0 = 0, off_c0 = text_lo;
     while (c0 < n) {
-      if (taper) want = chunks.size() < 7 ? std::max<int64_t>(1, n / 32 * kTaper[chunks.size()]) : kMaxChunk;
       int64_t c1 = std::min(n, c0 + want), off_c1 = 0;
       if ((rc = read_off(c1, &off_c1))) return rc;
       while (off_c1 - off_c0 > kRawBudget && c1 - c0 > 1) {
@@ -1976,7 +1900,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     CUDA_TRY(cudaMemsetAsync(d_counters, 0, C_COUNT * 4, st));
     if (M->fast) {
       if ((rc = M->w_norm.ensure((size_t)(3 * raw + 160 * cn + 256)))) return rc;
-      if ((rc = M->w_stage.ensure((size_t)(raw + kStageRowExtra * cn + 64) * 4))) return rc;
+      if ((rc = M->w_stage.ensure((size_t)(raw + kFastExtraChars * cn + 64) * 4))) return rc;
       if ((rc = M->w_nlen.ensure(cn * 4))) return rc;
       if ((rc = M->w_perm.ensure(cn * 4))) return rc;
       if ((rc = M->w_genlist.ensure(cn * 4))) return rc;
