@@ -1323,7 +1323,7 @@ struct spm_cuda_model {
   // host-memory calls: copy-in / copy-out streams so that PCIe traffic overlaps the kernels
   mutable cudaStream_t s_in = nullptr, s_out = nullptr;
   mutable std::vector<cudaEvent_t> ev_in, ev_done;
-  mutable cudaEvent_t ev_start = nullptr, ev_out = nullptr;
+  mutable cudaEvent_t ev_start = nullptr, ev_out = nullptr, ev_mid = nullptr;
   mutable int64_t *h_pin = nullptr;   // mapped pinned memory: snapshots written by k_publish
   mutable int64_t *d_pin = nullptr;   // its device address
   int bos_id = 0, eos_id = 0, pad_id = 0;
@@ -1591,6 +1591,7 @@ void spm_cuda_model_free(spm_cuda_model *M) {
   for (cudaEvent_t e : M->ev_done) cudaEventDestroy(e);
   if (M->ev_start) cudaEventDestroy(M->ev_start);
   if (M->ev_out) cudaEventDestroy(M->ev_out);
+  if (M->ev_mid) cudaEventDestroy(M->ev_mid);
   if (M->h_pin) cudaFreeHost(M->h_pin);
   if (M->ev0) cudaEventDestroy(M->ev0);
   if (M->ev1) cudaEventDestroy(M->ev1);
@@ -1820,18 +1821,24 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
   struct Chunk { int64_t c0, c1, o0, o1; };
   std::vector<Chunk> chunks;
   {
-    // host-memory calls of some size are cut into 8 chunks so that copy-in, kernels and
-    // copy-out pipeline.  (More chunks shorten the un-overlapped tail but every chunk pays the
-    // fixed latency of the leftover tiers -- a few hundred rare-word sentences walk cold trie
-    // paths -- and 16 chunks measured slower than 8: profiles/r1_v5_summary.md.)
+    // host-memory calls of some size are cut into chunks so that copy-in, kernels and copy-out
+    // pipeline.  The call is bound by PCIe (profiles/r1_v23_summary.md: the kernels are done 7 ms
+    // before the last ids have left), so what counts is how early the copy-out can start and how
+    // little is left when the copy-in ends: small chunks at both ends, large ones in between
+    // (every chunk pays the fixed latency of the leftover tiers).  SPM_CUDA_HOST_CHUNKS=k: k
+    // equal chunks (measurements).
+    static const int kTaper[10] = {1, 2, 4, 5, 5, 5, 4, 3, 2, 1};   // 32nds of the batch
     int64_t want = kMaxChunk;
+    bool taper = false;
     if (host && n >= (1 << 20)) {
       static const char *env_chunks = getenv("SPM_CUDA_HOST_CHUNKS");   // tuning experiments only
       const int64_t parts = std::max<int64_t>(1, std::min<int64_t>(64, env_chunks ? atoll(env_chunks) : 8));
       want = std::min(kMaxChunk, (n + parts - 1) / parts);
+      taper = env_chunks == nullptr && n / 32 * 5 < kMaxChunk;
     }
     int64_t c0 = 0, off_c0 = text_lo;
     while (c0 < n) {
+      if (taper) want = chunks.size() < 9 ? std::max<int64_t>(1, n / 32 * kTaper[chunks.size()]) : kMaxChunk;
       int64_t c1 = std::min(n, c0 + want), off_c1 = 0;
       if ((rc = read_off(c1, &off_c1))) return rc;
       while (off_c1 - off_c0 > kRawBudget && c1 - c0 > 1) {
@@ -1850,6 +1857,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       CUDA_TRY(cudaStreamCreateWithFlags(&M->s_out, cudaStreamNonBlocking));
       CUDA_TRY(cudaEventCreateWithFlags(&M->ev_start, cudaEventDisableTiming));
       CUDA_TRY(cudaEventCreateWithFlags(&M->ev_out, cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&M->ev_mid, cudaEventDisableTiming));
     }
     if (nch + 1 > 4096) { g_err = "too many chunks"; return kOutOfRange; }
     while (M->ev_in.size() < nch) {
@@ -1875,6 +1883,8 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
   // soon as its running total has reached the host, while later chunks compute
   size_t flushed = 0;
   int64_t ids_done = 0;
+  if (host)
+    for (size_t k = 0; k < nch; ++k) M->h_pin[kPubTot + k] = -1;   // "total of chunk k not published yet"
   auto flush_outputs = [&](size_t upto) -> int {   // chunks [flushed, upto) have their totals in h_pin
     for (; flushed < upto; ++flushed) {
       const Chunk &ch = chunks[flushed];
@@ -2059,7 +2069,20 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       launches += 1;
       CUDA_TRY(cudaGetLastError());
       k_publish<<<1, 32, 0, st>>>(d_counters, (const int64_t *)M->w_scalars.p, M->d_pin, -1);
-      CUDA_TRY(cudaStreamSynchronize(st));
+      if (host) {
+        // While this chunk waits for its text, the chunk before it finishes: its ids leave the
+        // moment its total shows up in the mapped snapshot, not when this chunk is half done.
+        CUDA_TRY(cudaEventRecord(M->ev_mid, st));
+        for (;;) {
+          const cudaError_t q = cudaEventQuery(M->ev_mid);
+          if (q == cudaSuccess) break;
+          if (q != cudaErrorNotReady) CUDA_TRY(q);
+          if (flushed < kc && ((volatile int64_t *)M->h_pin)[kPubTot + flushed] >= 0 && (rc = flush_outputs(flushed + 1)))
+            return rc;
+        }
+      } else {
+        CUDA_TRY(cudaStreamSynchronize(st));
+      }
       int64_t hc[C_COUNT];
       for (int k = 0; k < C_COUNT; ++k) hc[k] = M->h_pin[k];
       tr("fast kernel done, chunk", (long)kc);
