@@ -337,11 +337,12 @@ def run_b200(args):
     if rank == 0:
         peak, peak_src = measured_peak()
         # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, one launch, from the
-        # ncu --set full capture of this very workload (profiles/r1_v11_summary.md); null otherwise
+        # ncu --set full capture of this very workload (k_memo_scan_words: 1.44 + 0.80 GB,
+        # profiles/r1_v23_summary.md / r1_v21_ncu_full_keys.txt); null otherwise
         traffic = None
         if (dom == "memo_collect" and args.model == "syn_uni32k" and args.corpus == "syn_en"
                 and n == 10_000_000):
-            traffic = 3.97e9
+            traffic = 2.233e9
         k_avg_ms = kern_ms / max(kern_launches, 1)
         alg_per_launch = alg_bytes * args.steps / max(kern_launches, 1)
         achieved = alg_per_launch / (k_avg_ms * 1e-3) / 1e9 if k_avg_ms > 0 else 0.0
