@@ -196,3 +196,59 @@ def test_long_lines(spm_b200, corpora, model, corpus):
     # only the >= 64 KiB lines (and the rare flagged ones) may take the general tier
     if corpus != "syn_dirty":   # (dirty text: an over-long word sends the whole line to the general tier)
         assert st["fallback_sentences"] < (lens >= 4096).sum()
+
+
+@pytest.mark.parametrize("model", ["syn_uni32k", "syn_bpe32k", "botchan_uni8k"])
+def test_word_scan_shapes(spm_b200, corpora, model):
+    """k_memo_scan_words on the shapes its CPU replay covers, end to end against the reference:
+    words of 1 / 14 / 15 / 24 / 25 bytes, empty and one-byte sentences, leading / trailing /
+    double spaces, control and non-ASCII bytes, warps with more words than the shared word list
+    holds (per-lane fallback), warps whose text does not fit the staging buffer, sentences
+    at every alignment of the 8-byte sweep."""
+    mb = model_bytes(model)
+    sp = spm_b200.SentencePieceProcessor()
+    sp.LoadFromSerializedProto(mb)
+    chk, _ = checker(mb)
+    rng = np.random.default_rng(11)
+    text, off = corpora["syn_en"]
+    words = bytes(text[: off[400]]).split()
+    words += [b"a", b"I", b"x" * 14, b"y" * 15, b"internationalisations", b"z" * 24, b"w" * 25, b"q" * 60,
+              b"counter-revolutionary.", b"Mr.", b"(sic)", b"~", b"caf\xc3\xa9", b"na\xc3\xafve", b"\xef\xbd\x81"]
+    lines = []
+    for i in range(6000):
+        r = rng.random()
+        if r < 0.05:
+            lines.append(b"")
+        elif r < 0.08:
+            lines.append(bytes([int(rng.integers(0x20, 0x7F))]))
+        elif r < 0.11:     # many one-letter words: more than 640 words in a warp
+            lines.append(b" ".join([b"a", b"b", b"I", b"o"][int(k)] for k in rng.integers(0, 4, size=int(rng.integers(30, 70)))))
+        elif r < 0.12:     # a long line: the warp's text does not fit its staging buffer
+            lines.append(b" ".join(words[int(k)] for k in rng.integers(0, 400, size=int(rng.integers(700, 1200)))))
+        else:
+            k = int(rng.integers(1, 24))
+            ws = [words[int(j)] for j in rng.integers(0, len(words), size=k)]
+            s = b" ".join(ws)
+            q = rng.random()
+            if q < 0.03:
+                s = b" " + s
+            elif q < 0.06:
+                s = s + b" "
+            elif q < 0.09:
+                s = s.replace(b" ", b"  ", 1)
+            elif q < 0.11:
+                s = s.replace(b" ", b"\t", 1)
+            elif q < 0.12:
+                s = s + b"\r"
+            lines.append(s)
+    from tools import synth
+    t2, o2 = synth.pack_lines(lines)
+    want = ref_encode(chk, t2, o2)
+    assert_same(sp.encode_packed(t2, o2), want, t2, o2)
+    import torch
+    dt, do = torch.from_numpy(t2).cuda(), torch.from_numpy(o2).cuda()
+    ids = torch.empty(int(want[1][-1]) + 8, dtype=torch.int32, device="cuda")
+    ido = torch.empty(len(o2), dtype=torch.int64, device="cuda")
+    sp.encode_device(dt, do, ids, ido)
+    torch.cuda.synchronize()
+    assert_same((ids[: int(want[1][-1])].cpu().numpy(), ido.cpu().numpy()), want, t2, o2)
