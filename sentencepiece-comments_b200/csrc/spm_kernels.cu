@@ -722,7 +722,7 @@ constexpr int kSwWarps = 4, kSwBytes = SPM_SW_BYTES, kSwCap = 640, kSwLong = 64,
 struct SwWarp {
   __align__(16) uint8_t stage[kSwBytes];
   uint32_t bmap[kSwMapWords];        // bit i: a sentence starts at stage byte i (or the warp's text ends there)
-  uint16_t wpos[kSwCap], wend[kSwCap];   // first / last byte of word k
+  uint16_t wpos[kSwCap], wend[kSwCap];   // first (| 0x8000: it begins its sentence) / last byte of word k
   uint16_t wlong[kSwLong];           // words of 15..24 bytes (two dependent probes): keyed after the others
   uint16_t sstart[32];               // first byte of the sentence of lane l
   uint16_t fw[32];                   // words before it
@@ -786,7 +786,7 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
     for (int g0 = a_rel & ~7; g0 < b_rel; g0 += 256) {
       const int g = g0 + lane * 8;
       SwMasks m;
-      m.ws = 0; m.we = 0; m.bad = 0;
+      m.ws = 0; m.we = 0; m.bad = 0; m.b = 0;
       if (g < b_rel) {
         const uint64_t w = *reinterpret_cast<const uint64_t *>(&sh.stage[g]);
         const uint32_t pb = g > 0 ? sh.stage[g - 1] : 0u, nb = sh.stage[g + 8];
@@ -803,7 +803,11 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       const uint32_t all = __shfl_sync(0xFFFFFFFFu, inc, 31);
       if (total + (int)(all & 0xFFFFu) > kSwCap) { over = true; break; }
       int ks = total + (int)((inc - mine) & 0xFFFFu), ke = total_e + (int)((inc - mine) >> 16);
-      for (uint32_t x = m.ws; x; x &= x - 1) sh.wpos[ks++] = (uint16_t)(g + __ffs(x) - 1);
+      // bit 15: the word begins its sentence (the dummy prefix decides its first key bit)
+      for (uint32_t x = m.ws; x; x &= x - 1) {
+        const int at = __ffs(x) - 1;
+        sh.wpos[ks++] = (uint16_t)((g + at) | (((m.b >> at) & 1u) << 15));
+      }
       for (uint32_t x = m.we; x; x &= x - 1) sh.wend[ke++] = (uint16_t)(g + __ffs(x) - 1);
       for (uint32_t x = m.bad; x; x &= x - 1) atomicOr(&sh.flags[sw_owner(sh.sstart, g + __ffs(x) - 1)], 2u);
       total += (int)(all & 0xFFFFu);
@@ -819,7 +823,7 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       int first = 0;
       for (int n = total; n > 0;) {
         const int half = n >> 1;
-        if ((int)sh.wpos[first + half] < s_rel) { first += half + 1; n -= half + 1; }
+        if ((int)(sh.wpos[first + half] & 0x7FFFu) < s_rel) { first += half + 1; n -= half + 1; }
         else n = half;
       }
       sh.fw[lane] = (uint16_t)first;
@@ -837,12 +841,12 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
         const int k = k0 + lane;
         bool later = false;
         if (k < total) {
-          const int s = sh.wpos[k], n = (int)sh.wend[k] - s + 1;
-          const int u = sw_owner(sh.sstart, s);
+          const uint32_t e = sh.wpos[k];
+          const int s = (int)(e & 0x7FFFu), n = (int)sh.wend[k] - s + 1;
           later = SPM_SW_DEFER && n > kMemoKeyBytes && n <= kMemoMaxBytes;
           if (!later) {
-            const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, s == (int)sh.sstart[u] ? prefix0 : 1ull);
-            if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[u], 1u);
+            const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, (e >> 15) ? prefix0 : 1ull);
+            if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[sw_owner(sh.sstart, s)], 1u);   // rare: the owner is only looked up here
             else memo_store_slot(wl + k, slot);
           }
         }
@@ -853,10 +857,10 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
           nlong += __popc(bl);
           if (nlong > kSwLong) {   // no room: key it now
             if (later && at >= kSwLong) {
-              const int s = sh.wpos[k], n = (int)sh.wend[k] - s + 1;
-              const int u = sw_owner(sh.sstart, s);
-              const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, s == (int)sh.sstart[u] ? prefix0 : 1ull);
-              if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[u], 1u);
+              const uint32_t e = sh.wpos[k];
+              const int s = (int)(e & 0x7FFFu), n = (int)sh.wend[k] - s + 1;
+              const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, (e >> 15) ? prefix0 : 1ull);
+              if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[sw_owner(sh.sstart, s)], 1u);
               else memo_store_slot(wl + k, slot);
             }
             nlong = kSwLong;
@@ -866,10 +870,10 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       __syncwarp();
       for (int j = lane; j < nlong; j += 32) {
         const int k = sh.wlong[j];
-        const int s = sh.wpos[k], n = (int)sh.wend[k] - s + 1;
-        const int u = sw_owner(sh.sstart, s);
-        const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, s == (int)sh.sstart[u] ? prefix0 : 1ull);
-        if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[u], 1u);
+        const uint32_t e = sh.wpos[k];
+        const int s = (int)(e & 0x7FFFu), n = (int)sh.wend[k] - s + 1;
+        const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, (e >> 15) ? prefix0 : 1ull);
+        if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[sw_owner(sh.sstart, s)], 1u);
         else memo_store_slot(wl + k, slot);
       }
       __syncwarp();

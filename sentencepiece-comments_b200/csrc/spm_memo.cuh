@@ -319,7 +319,7 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
 // bytes before and after the chunk.  A sentence is unfit (memo_scan_plain's -2) when it holds
 // a byte outside 0x20..0x7E, or a space that is leading, trailing or follows a space.
 struct SwMasks {
-  uint32_t ws, we, bad;
+  uint32_t ws, we, bad, b;   // b: the sentence starts among the chunk's 8 bytes
 };
 SPM_HD uint32_t sw_gather(uint64_t f) {   // bit 7 of byte j -> bit j
   return (uint32_t)(((f >> 7) * 0x0102040810204080ull) >> 56);
@@ -341,6 +341,7 @@ SPM_HD SwMasks sw_chunk_masks(uint64_t w, uint32_t pb, uint32_t nb, uint32_t b9,
   const uint32_t bcur = b9 & 0xFFu, bnext = (b9 >> 1) & 0xFFu;
   const uint32_t gprev = (good << 1) | pgood, gnext = (good >> 1) | ngood;
   SwMasks m;
+  m.b = bcur;
   m.ws = good & (bcur | ~gprev) & 0xFFu;
   m.we = good & (bnext | ~gnext) & 0xFFu;
   m.bad = ((valid & ~good & ~sp) | (sp & valid & (bcur | bnext | (sp << 1) | psp))) & 0xFFu;
