@@ -1825,26 +1825,24 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
   struct Chunk { int64_t c0, c1, o0, o1; };
   std::vector<Chunk> chunks;
   {
-    // host-memory calls of some size are cut into chunks so that copy-in, kernels and copy-out
-    // pipeline.  The call is bound by PCIe (profiles/r1_v23_summary.md: the kernels are done 7 ms
+    // host-memory calls of some size are cut into equal chunks so that copy-in, kernels and copy-out
+    // pipeline.  The call is bound by PCIe (profiles/r1_v23_summary.md: the kernels are done long
     // before the last ids have left), so what counts is how early the copy-out can start and how
-    // little is left when the copy-in ends: small chunks at both ends, large ones in between
-    // (every chunk pays the fixed latency of the leftover tiers).  SPM_CUDA_HOST_CHUNKS=k: k
-    // equal chunks (measurements).
-    static const int kTaper[10] = {1, 2, 4, 5, 5, 5, 4, 3, 2, 1};   // 32nds of the batch
+    // little is left when the copy-in ends -- against the fixed cost of a chunk (the leftover
+    // tiers' latency, ~30 launches and a host round trip: ~0.8 ms; BPE, whose merge kernel takes
+    // ~1.7 ms over a chunk's leftover sentences whatever the chunk holds: ~2.5 ms).  Measured per
+    // 10 M sentences: unigram 8 / 12 / 16 / 24 chunks 28.0 / 26.9 / 26.7 / 29.1 ms (text with many
+    // rule hits: 12: 27.7, 16: 31.0), chunks tapered at both ends 27.2; BPE 4 / 5 / 6 / 7: 33.2 /
+    // 33.0 / 34.4 / 36.4.  SPM_CUDA_HOST_CHUNKS=k overrides the count (measurements).
     int64_t want = kMaxChunk;
-    bool taper = false;
     if (host && n >= (1 << 20)) {
       static const char *env_chunks = getenv("SPM_CUDA_HOST_CHUNKS");   // tuning experiments only
-      // BPE: the merge kernel over a chunk's leftover sentences costs ~1.7 ms whatever the chunk's size,
-      // so few, equal chunks (4 / 5 / 6 / 7 / tapered 10: 33.2 / 33.0 / 34.4 / 36.4 / 40.6 ms per 10 M sentences)
-      const int64_t parts = std::max<int64_t>(1, std::min<int64_t>(64, env_chunks ? atoll(env_chunks) : 5));
+      const int64_t parts = std::max<int64_t>(
+          1, std::min<int64_t>(64, env_chunks ? atoll(env_chunks) : (M->fast_kind == 2 ? 5 : 12)));
       want = std::min(kMaxChunk, (n + parts - 1) / parts);
-      taper = env_chunks == nullptr && M->fast_kind != 2 && n / 32 * 5 < kMaxChunk;
     }
     int64_t c0 = 0, off_c0 = text_lo;
     while (c0 < n) {
-      if (taper) want = chunks.size() < 9 ? std::max<int64_t>(1, n / 32 * kTaper[chunks.size()]) : kMaxChunk;
       int64_t c1 = std::min(n, c0 + want), off_c1 = 0;
       if ((rc = read_off(c1, &off_c1))) return rc;
       while (off_c1 - off_c0 > kRawBudget && c1 - c0 > 1) {
