@@ -9,6 +9,7 @@ timeout 900 python -m pytest tests -m gpu -x -q > $O/${V}_pytest_gpu.log 2>&1; e
 timeout 300 python bench.py --no-cpu-baseline > $O/${V}_bench_config2.json 2> $O/${V}_bench_config2.err; echo "bench rc=$?"
 timeout 300 python bench.py --corpus syn_dirty --no-cpu-baseline --no-e2e > $O/${V}_bench_config2_dirty.json 2>/dev/null
 timeout 300 python bench.py --model syn_bpe32k --no-cpu-baseline --no-e2e > $O/${V}_bench_config3.json 2>/dev/null
+shopt -s nullglob
 for f in sentencepiece-comments_b200/lib/variants/*.so; do
   n=$(basename $f .so)
   SPM_B200_LIB_VARIANT=$PWD/$f timeout 300 python bench.py --no-cpu-baseline --no-e2e > $O/${V}_bench_config2_var_$n.json 2>/dev/null
