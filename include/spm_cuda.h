@@ -4,8 +4,8 @@
  * (SentencePiece 0.1.82) has no C ABI or batch entry point of its own; each
  * function below names the C++ interface it stands in for, so that a
  * `sentencepiece::SentencePieceProcessor`-shaped facade (see
- * sentencepiece-comments_b200/csrc/spm_processor.h and INTEGRATION.md) can be
- * built on top with unchanged signatures.
+ * include/spm_cuda_processor.h and INTEGRATION.md) can be built on top with
+ * unchanged signatures.
  *
  * Error convention: every int-returning function returns a
  * sentencepiece::util::error::Code value (src/sentencepiece_processor.h:101-119;
@@ -51,6 +51,27 @@ void spm_cuda_model_free(spm_cuda_model *model);
  * types (ModelProto::SentencePiece::Type values, one byte per piece).  Must
  * not run concurrently with encode calls on the same model. */
 int spm_cuda_model_set_piece_types(spm_cuda_model *model, const uint8_t *types, int n);
+
+/* Per-handle knobs.  The reference has no counterpart (its processor has no tiers); they exist
+ * so that tests and measurements can reach, on small batches, the code paths a real batch only
+ * takes at scale, and switch single tiers off.  Results never depend on them.
+ *   "memo"              1   word-memo tier on / off
+ *   "memo_bits"         23  log2 of the most memo-table slots one call may use (12..26)
+ *   "host_chunks"       0   SPM_CUDA_HOST calls: number of pipelined chunks (0: 12 unigram / 5 BPE)
+ *   "host_chunk_min"    2^20  ... for calls of at least this many sentences
+ *   "max_chunk"         0   most sentences per chunk (0: 2^24 with a fast tier, 2^20 without)
+ *   "warp"              1   warp-per-line kernel for long / near-tied lines on / off
+ *   "warp_route"        262144  leftover lists up to this size go to the warp kernel as a whole (0: never)
+ *   "scan_per_sentence" 0   thread-per-sentence word scan instead of the byte-parallel one
+ *   "emit_blocks"       0   CTAs of the memo emit kernel per SM (0: occupancy query)
+ *   "pieces_exact"      0   encode_batch_pieces: every sentence through the exact tier
+ * NOT_FOUND for an unknown name.  Must not run concurrently with calls on the same model. */
+int spm_cuda_model_set_option(spm_cuda_model *model, const char *name, int64_t value);
+int spm_cuda_model_get_option(const spm_cuda_model *model, const char *name, int64_t *value);
+
+/* Frees the device workspace kept from earlier calls (it grows to the largest batch seen and is
+ * otherwise reused); model tables stay loaded.  No counterpart in the reference (host heap). */
+int spm_cuda_model_release_workspace(spm_cuda_model *model);
 
 /* Replaces a loop of SentencePieceProcessor::Encode(input, std::vector<int>*)
  * (src/sentencepiece_processor.h:244, .cc:319-330) over n sentences.

@@ -55,6 +55,10 @@ def lib():
             L.ref_estep.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p,
                                     ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p,
                                     ctypes.c_void_p, ctypes.c_void_p]
+        if hasattr(L, "ref_estep64"):
+            L.ref_estep64.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p,
+                                      ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p,
+                                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -197,3 +201,26 @@ def estep(pieces, scores, words, freq):
     if rc:
         raise RuntimeError("ref_estep failed")
     return expected, logz, obj.value, nt.value
+
+
+def estep64(pieces, scores, words, freq):
+    """estep() plus expected64 = the float64 re-accumulation of the reference's own per-word
+    posteriors: (expected f32[V], logz f32[n], obj, ntokens, expected64 f64[V])."""
+    L = lib()
+    if not hasattr(L, "ref_estep64"):
+        raise RuntimeError("reference library was built without ref_estep64")
+    scores = np.ascontiguousarray(scores, dtype=np.float32)
+    freq = np.ascontiguousarray(freq, dtype=np.int64)
+    pb = b"".join(p + b"\0" for p in pieces)
+    wb = b"".join(w + b"\0" for w in words)
+    expected = np.zeros(len(pieces), dtype=np.float32)
+    expected64 = np.zeros(len(pieces), dtype=np.float64)
+    logz = np.zeros(len(words), dtype=np.float32)
+    obj = ctypes.c_double(0)
+    nt = ctypes.c_int64(0)
+    rc = L.ref_estep64(pb, scores.ctypes.data, len(pieces), wb, freq.ctypes.data, len(words),
+                       expected.ctypes.data, logz.ctypes.data, ctypes.byref(obj), ctypes.byref(nt),
+                       expected64.ctypes.data)
+    if rc:
+        raise RuntimeError("ref_estep64 failed")
+    return expected, logz, obj.value, nt.value, expected64

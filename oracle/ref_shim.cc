@@ -311,6 +311,59 @@ int ref_estep(const char *pieces, const float *scores, int V, const char *words,
   *ntokens = nt;
   return 0;
 }
+
+// ref_estep plus expected64[V]: the float64 re-accumulation of the reference's OWN posteriors
+// (SURVEY.md H9).  The reference sums freq * posterior of every node into a float vector over
+// the whole corpus (:321), whose rounding error on large counts exceeds 1e-5; here each word's
+// PopulateMarginal runs a second time into a zeroed float scratch, and the word's contribution
+// per piece id (a handful of node posteriors) is added to a double.  expected[] stays exactly
+// what the reference accumulates.
+int ref_estep64(const char *pieces, const float *scores, int V, const char *words,
+                const int64_t *freq, int64_t n, float *expected, float *logz,
+                double *obj, int64_t *ntokens, double *expected64) {
+  using namespace sentencepiece;
+  TrainerSpec ts;
+  NormalizerSpec ns;
+  unigram::TrainerModel model(ts, ns);
+  unigram::TrainerModel::SentencePieces sps;
+  const char *q = pieces;
+  for (int i = 0; i < V; ++i) {
+    sps.emplace_back(std::string(q), scores[i]);
+    q += sps.back().first.size() + 1;
+  }
+  model.SetSentencePieces(std::move(sps));
+  std::vector<float> exp(V, 0.0f), tmp(V, 0.0f);
+  for (int i = 0; i < V; ++i) expected64[i] = 0.0;
+  int64_t all_freq = 0;
+  for (int64_t i = 0; i < n; ++i) all_freq += freq[i];
+  float o = 0.0f;
+  int64_t nt = 0;
+  unigram::Lattice lattice;
+  const char *w = words;
+  for (int64_t i = 0; i < n; ++i) {
+    const size_t wl = std::strlen(w);
+    lattice.SetSentence(absl::string_view(w, wl));
+    model.PopulateNodes(&lattice);
+    const float Z = lattice.PopulateMarginal(freq[i], &exp);
+    lattice.PopulateMarginal(freq[i], &tmp);
+    for (int pos = 0; pos < lattice.size(); ++pos) {
+      for (const auto *node : lattice.begin_nodes(pos)) {
+        if (node->id >= 0 && tmp[node->id] != 0.0f) {
+          expected64[node->id] += (double)tmp[node->id];
+          tmp[node->id] = 0.0f;
+        }
+      }
+    }
+    nt += lattice.Viterbi().size();
+    if (logz) logz[i] = Z;
+    o -= Z / all_freq;
+    w += wl + 1;
+  }
+  std::memcpy(expected, exp.data(), V * sizeof(float));
+  *obj = o;
+  *ntokens = nt;
+  return 0;
+}
 #endif
 
 }  // extern "C"

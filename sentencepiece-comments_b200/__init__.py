@@ -39,6 +39,9 @@ def lib():
         L.spm_cuda_model_load.argtypes = [ctypes.c_char_p, ctypes.c_size_t, i32, ctypes.POINTER(vp)]
         L.spm_cuda_model_free.argtypes = [vp]
         L.spm_cuda_model_set_piece_types.argtypes = [vp, vp, i32]
+        L.spm_cuda_model_set_option.argtypes = [vp, ctypes.c_char_p, i64]
+        L.spm_cuda_model_get_option.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(i64)]
+        L.spm_cuda_model_release_workspace.argtypes = [vp]
         L.spm_cuda_encode_batch.argtypes = [vp, vp, vp, i64, ctypes.c_uint32, vp, i64, vp, i32, vp]
         L.spm_cuda_model_piece_size.argtypes = [vp]
         L.spm_cuda_model_piece.argtypes = [vp, i32, ctypes.POINTER(i32)]
@@ -163,6 +166,21 @@ class SentencePieceProcessor:
         types[types == UNUSED] = NORMAL
         _check(lib().spm_cuda_model_set_piece_types(self._h, types.ctypes.data, len(types)))
         return True
+
+    # ---- per-handle knobs (include/spm_cuda.h: spm_cuda_model_set_option; tests / measurements)
+    def set_option(self, name, value):
+        self._need()
+        _check(lib().spm_cuda_model_set_option(self._h, name.encode(), int(value)))
+
+    def get_option(self, name):
+        self._need()
+        v = ctypes.c_int64(0)
+        _check(lib().spm_cuda_model_get_option(self._h, name.encode(), ctypes.byref(v)))
+        return v.value
+
+    def release_workspace(self):
+        self._need()
+        _check(lib().spm_cuda_model_release_workspace(self._h))
 
     # ---- encode (sentencepiece_processor.h:244, 333-335)
     def Encode(self, input):

@@ -354,9 +354,11 @@ SPM_HD uint64_t pack_rec(uint32_t id, uint32_t len, uint32_t prevslot) {
 // do not fit, sets ST_IDS_OVERFLOW and still returns the count.  out_end (may be
 // null): the byte offset in s where each emitted piece ends (a merged unk run
 // ends where its last character ends) -- piece k is s[out_end[k-1], out_end[k]).
-template <int CAPC>
-SPM_HDN int32_t unigram_encode(const ModelView &m, const uint8_t *s, int32_t n, const UniScratch &sc,
-                               int32_t *out, int32_t cap, uint32_t *status, int32_t *out_end = nullptr) {
+// (CAPC is a run-time value here; the wrappers below fix it at compile time for the common
+// tier and pass the model's ring size -- which no candidate list can exceed -- for the retry.)
+SPM_HD int32_t unigram_encode_impl(const ModelView &m, const uint8_t *s, int32_t n, const UniScratch &sc,
+                                   const uint32_t CAPC, int32_t *out, int32_t cap, uint32_t *status,
+                                   int32_t *out_end) {
   if (n <= 0) return 0;
   const uint32_t mask = (uint32_t)m.ring - 1;
   for (int i = 0; i < m.ring; ++i) sc.ringCnt[i] = 0;
@@ -483,6 +485,19 @@ SPM_HDN int32_t unigram_encode(const ModelView &m, const uint8_t *s, int32_t n, 
   }
   *status |= st;
   return total;
+}
+template <int CAPC>
+SPM_HDN int32_t unigram_encode(const ModelView &m, const uint8_t *s, int32_t n, const UniScratch &sc,
+                               int32_t *out, int32_t cap, uint32_t *status, int32_t *out_end = nullptr) {
+  return unigram_encode_impl(m, s, n, sc, (uint32_t)CAPC, out, cap, status, out_end);
+}
+// Any capacity up to 255 (the back records keep the predecessor's slot in 8 bits).  With
+// capc >= ring no sentence can overflow: the candidates pending at one end position begin at
+// distinct earlier positions of the ring.
+SPM_HDN int32_t unigram_encode_capc(const ModelView &m, const uint8_t *s, int32_t n, const UniScratch &sc,
+                                    int capc, int32_t *out, int32_t cap, uint32_t *status,
+                                    int32_t *out_end = nullptr) {
+  return unigram_encode_impl(m, s, n, sc, (uint32_t)capc, out, cap, status, out_end);
 }
 
 // ------------------------------------------------------------------ BPE

@@ -68,6 +68,23 @@ thread_local std::string g_err;
     }                                                                                     \
   } while (0)
 
+// Every ABI entry runs on the model's device and hands the caller's current device back on
+// every exit path (a host framework with several GPUs in one process keeps its own).
+struct DeviceGuard {
+  int prev = -1, dev = -1;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int device) : dev(device) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0 && prev != dev) cudaSetDevice(prev);
+  }
+};
+#define DEVICE_GUARD(device)       \
+  DeviceGuard device_guard_(device); \
+  CUDA_TRY(device_guard_.err)
+
 constexpr int kCapc = 8;          // near-tie candidates kept per position by the exact tier
 constexpr int kThreads = 128;     // general-tier block size
 #ifndef SPM_FAST_THREADS
@@ -119,21 +136,26 @@ k_gen_normalize(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c
   gstatus[t] = st;
 }
 
+// status_or[0]: OR of the status words; status_or[1]: some sentence met more than kCapc near-tied
+// candidates and waits for the retry with room for every candidate (run_capc_retry).
 __device__ __forceinline__ void gen_encode_one(const ModelView &mv, int64_t i, int64_t nb, int32_t nl, uint32_t st,
                                                int32_t *w, const uint8_t *norm, int32_t *gstage, int32_t *cnt,
                                                uint32_t *status, int64_t *srcoff, uint32_t *status_or,
-                                               int32_t *gends = nullptr) {
+                                               int32_t *gends = nullptr, int capc = kCapc) {
   int32_t c = 0;
   if (st == 0) {
     if (mv.model_type == M_UNIGRAM) {
       UniScratch sc;
       sc.ringM = (float *)w; w += mv.ring;
       sc.ringCnt = (uint32_t *)w; w += mv.ring;
-      sc.candBt = (float *)w; w += mv.ring * kCapc;
-      sc.candRec = (uint64_t *)w; w += 2 * mv.ring * kCapc;
+      sc.candBt = (float *)w; w += mv.ring * capc;
+      sc.candRec = (uint64_t *)w; w += 2 * mv.ring * capc;
       sc.back = (uint64_t *)w;
       sc.stride = nl + 1;
-      c = unigram_encode<kCapc>(mv, norm + nb, nl, sc, gstage + nb, nl, &st, gends ? gends + nb : nullptr);
+      if (capc == kCapc)
+        c = unigram_encode<kCapc>(mv, norm + nb, nl, sc, gstage + nb, nl, &st, gends ? gends + nb : nullptr);
+      else
+        c = unigram_encode_capc(mv, norm + nb, nl, sc, capc, gstage + nb, nl, &st, gends ? gends + nb : nullptr);
     } else {
       c = bpe_encode(mv, norm + nb, nl, w, gstage + nb, nl, &st, gends ? gends + nb : nullptr);
     }
@@ -141,7 +163,37 @@ __device__ __forceinline__ void gen_encode_one(const ModelView &mv, int64_t i, i
   cnt[i] = c;
   status[i] = st | ST_GEN;
   srcoff[i] = nb;
+  if (capc == kCapc && (st & ST_CAND_OVERFLOW)) {
+    atomicOr(status_or + 1, 1u);
+    st &= ~ST_CAND_OVERFLOW;
+  }
   if (st) atomicOr(status_or, st);
+}
+
+// The retry: listed sentence t takes a scratch slice for `capc` candidates per position from
+// a bump counter (plan), then runs the exact tier again (retry).  rbase[t] < 0: not flagged.
+__device__ __forceinline__ int64_t retry_words(const ModelView &mv, int capc, int32_t nl) {
+  return (uni_scratch_words(mv.ring, capc, nl) + 1) & ~(int64_t)1;   // 8-byte aligned slices
+}
+__global__ void __launch_bounds__(kThreads)
+k_gen_retry_plan(ModelView mv, const int32_t *list, int64_t tn, const int32_t *nlen, const uint32_t *status,
+                 int capc, int64_t *rbase, unsigned long long *total) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= tn) return;
+  const int64_t i = list ? list[t] : t;
+  int64_t b = -1;
+  if (status[i] & ST_CAND_OVERFLOW) b = (int64_t)atomicAdd(total, (unsigned long long)retry_words(mv, capc, nlen[t]));
+  rbase[t] = b;
+}
+__global__ void __launch_bounds__(kThreads)
+k_gen_retry(ModelView mv, const int32_t *list, int64_t tn, const int64_t *noff, const uint8_t *norm,
+            const int32_t *nlen, const int64_t *rbase, int capc, int32_t *scratch, int32_t *gstage, int32_t *cnt,
+            uint32_t *status, int64_t *srcoff, uint32_t *status_or, int32_t *gends) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= tn || rbase[t] < 0) return;
+  const int64_t i = list ? list[t] : t;
+  gen_encode_one(mv, i, noff[t], nlen[t], 0u, scratch + rbase[t], norm, gstage, cnt, status, srcoff, status_or, gends,
+                 capc);
 }
 
 // throughput variant: one thread per listed sentence, scratch in global memory
@@ -1297,9 +1349,27 @@ struct DevBuf {
 
 }  // namespace
 
+// Per-handle knobs (spm_cuda_model_set_option).  The defaults are what ships; tests and
+// measurements switch tiers off / shrink tables through the setter to reach paths that real
+// batches only take at scale.  The SPM_CUDA_* environment variables of round 1 are read ONCE
+// PER LOAD as initial values (tools/gpu_variants.sh style A/B runs), never latched process-wide.
+struct Options {
+  int64_t memo = 1;               // word-memo tier
+  int64_t memo_bits = 23;         // log2 of the most table slots a call may use (12..26)
+  int64_t host_chunks = 0;        // host-memory calls: chunk count (0: 12 unigram / 5 BPE)
+  int64_t host_chunk_min = 1 << 20;   // ... for calls of at least this many sentences
+  int64_t max_chunk = 0;          // most sentences per chunk (0: 2^24 fast models, 2^20 others)
+  int64_t warp = 1;               // k_encode_warp for long / flagged lines
+  int64_t scan_per_sentence = 0;  // k_memo_scan_plain instead of k_memo_scan_words
+  int64_t warp_route = 262144;    // leftover lists up to this size go to k_encode_warp as a whole (0: never)
+  int64_t emit_blocks = 0;        // CTAs of k_memo_emit per SM (0: occupancy query)
+  int64_t pieces_exact = 0;       // pieces path: every sentence through the exact tier
+};
+
 struct spm_cuda_model {
   HostModel hm;
   int device = 0;
+  Options opt;
   ModelView mv;
   FastParams fp;
   bool fast = false;       // a fast tier is usable
@@ -1311,7 +1381,7 @@ struct spm_cuda_model {
   mutable std::mutex mu;
   mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
       w_perm, w_genlist, w_longlist, w_wslots, w_wbase, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
-      g_nlen, g_words, g_woff, g_scratch, g_status;
+      g_nlen, g_words, g_woff, g_scratch, g_status, g_rbase, g_rscratch;
   mutable DevBuf px[20];   // workspace of the pieces / decode / dense calls (spm_pieces.inc)
   mutable int emit_blocks = 0;      // resident CTAs of k_memo_emit per SM (occupancy query, first use)
   mutable uint32_t last_stor = 0;   // OR of the status words of the last encode_batch_locked call
@@ -1331,6 +1401,11 @@ struct spm_cuda_model {
   mutable int64_t *h_pin = nullptr;   // mapped pinned memory: snapshots written by k_publish
   mutable int64_t *d_pin = nullptr;   // its device address
   int bos_id = 0, eos_id = 0, pad_id = 0;
+  std::vector<DevBuf *> workspace_bufs() const {   // all_bufs() without the model tables (d_*)
+    std::vector<DevBuf *> v = all_bufs();
+    v.erase(v.begin(), v.begin() + 11);
+    return v;
+  }
   std::vector<DevBuf *> all_bufs() const {
     spm_cuda_model *m = const_cast<spm_cuda_model *>(this);
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2, &m->d_cont2,
@@ -1338,7 +1413,7 @@ struct spm_cuda_model {
             &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
             &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_wbase, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
-            &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status,
+            &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status, &m->g_rbase, &m->g_rscratch,
             &m->px[0], &m->px[1], &m->px[2], &m->px[3], &m->px[4], &m->px[5], &m->px[6], &m->px[7], &m->px[8], &m->px[9],
             &m->px[10], &m->px[11], &m->px[12], &m->px[13], &m->px[14], &m->px[15], &m->px[16], &m->px[17], &m->px[18],
             &m->px[19]};
@@ -1463,11 +1538,44 @@ int kev_record(const spm_cuda_model *M, cudaStream_t st, int which, int tag = T_
   return kOk;
 }
 
+// After an exact-tier pass over `tn` listed sentences: when some met more than kCapc near-tied
+// candidates at one position (status_or[1], published with the scalars), those run again with
+// room for every candidate a position can hold (min(ring, 255)), so one pathological sentence
+// neither fails the batch nor changes its ids.  d_scal[2] = status_or[0] | status_or[1] << 32.
+int run_capc_retry(const spm_cuda_model *M, cudaStream_t st, const int32_t *list, int64_t tn, int64_t *d_scal,
+                   int32_t *gends, double *launches) {
+  if (M->hm.model_type != M_UNIGRAM || tn <= 0) return kOk;
+  int rc;
+  k_publish<<<1, 32, 0, st>>>(nullptr, d_scal, M->d_pin, -1);
+  CUDA_TRY(cudaStreamSynchronize(st));
+  if ((M->h_pin[kPubScal + 2] >> 32) == 0) return kOk;
+  const int capc = std::min(M->hm.ring, 255);
+  if ((rc = M->g_rbase.ensure((size_t)tn * 8 + 8))) return rc;
+  unsigned long long *d_total = (unsigned long long *)M->g_rbase.p + tn;
+  CUDA_TRY(cudaMemsetAsync(d_total, 0, 8, st));
+  const unsigned grid = (unsigned)((tn + kThreads - 1) / kThreads);
+  k_gen_retry_plan<<<grid, kThreads, 0, st>>>(M->mv, list, tn, (const int32_t *)M->g_nlen.p,
+                                              (const uint32_t *)M->w_status.p, capc, (int64_t *)M->g_rbase.p, d_total);
+  unsigned long long total = 0;
+  CUDA_TRY(cudaMemcpyAsync(&total, d_total, 8, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  if ((rc = M->g_rscratch.ensure((size_t)total * 4 + 64))) return rc;
+  uint32_t *d_stor = (uint32_t *)(d_scal + 2);
+  CUDA_TRY(cudaMemsetAsync(d_stor + 1, 0, 4, st));
+  k_gen_retry<<<grid, kThreads, 0, st>>>(M->mv, list, tn, (const int64_t *)M->g_noff.p, (const uint8_t *)M->g_norm.p,
+                                         (const int32_t *)M->g_nlen.p, (const int64_t *)M->g_rbase.p, capc,
+                                         (int32_t *)M->g_rscratch.p, (int32_t *)M->g_stage.p, (int32_t *)M->w_cnt.p,
+                                         (uint32_t *)M->w_status.p, (int64_t *)M->w_srcoff.p, d_stor, gends);
+  *launches += 2;
+  CUDA_TRY(cudaGetLastError());
+  return kOk;
+}
+
 // General tier over `gcount` sentences of the chunk (list: device array of
 // chunk-relative indices, or nullptr for "all sentences 0..gcount-1").
 // `timed`: this is the dominant kernel of a non-fast model (event pair recorded).
-int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text, const int64_t *d_off, int64_t c0,
-                const int32_t *list, int64_t gcount, bool timed, double *launches) {
+int run_general_pass(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text, const int64_t *d_off, int64_t c0,
+                     const int32_t *list, int64_t gcount, bool timed, double *launches) {
   if (gcount <= 0) return kOk;
   int rc;
   const int exp_ = M->hm.expansion;
@@ -1547,6 +1655,14 @@ int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text,
   return kOk;
 }
 
+int run_general(const spm_cuda_model *M, cudaStream_t st, const uint8_t *d_text, const int64_t *d_off, int64_t c0,
+                const int32_t *list, int64_t gcount, bool timed, double *launches) {
+  if (gcount <= 0) return kOk;
+  int rc = run_general_pass(M, st, d_text, d_off, c0, list, gcount, timed, launches);
+  if (rc) return rc;
+  return run_capc_retry(M, st, list, gcount, (int64_t *)M->w_scalars.p, nullptr, launches);
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------- C ABI
@@ -1567,10 +1683,22 @@ int spm_cuda_model_load(const void *serialized_model, size_t len, int device, sp
   int rc = build_host_model(serialized_model, len, &M->hm);
   if (rc) { g_err = M->hm.error; delete M; return rc; }
   M->device = device;
+  {  // initial option values from the environment (A/B measurement scripts); read per load
+    auto env = [](const char *k, int64_t *v) { const char *e = getenv(k); if (e && *e) *v = atoll(e); };
+    if (getenv("SPM_CUDA_NO_MEMO")) M->opt.memo = 0;
+    if (getenv("SPM_CUDA_NO_WARP")) M->opt.warp = 0;
+    if (getenv("SPM_CUDA_SCAN_PER_SENTENCE")) M->opt.scan_per_sentence = 1;
+    if (getenv("SPM_CUDA_PIECES_EXACT")) M->opt.pieces_exact = 1;
+    env("SPM_CUDA_MEMO_BITS", &M->opt.memo_bits);
+    env("SPM_CUDA_HOST_CHUNKS", &M->opt.host_chunks);
+    env("SPM_CUDA_EMIT_BLOCKS", &M->opt.emit_blocks);
+    env("SPM_CUDA_WARP_ROUTE", &M->opt.warp_route);
+  }
   M->bos_id = piece_to_id(M->hm, M->hm.bos_piece);
   M->eos_id = piece_to_id(M->hm, M->hm.eos_piece);
   M->pad_id = piece_to_id(M->hm, M->hm.pad_piece);
-  if (cudaSetDevice(device) != cudaSuccess) { g_err = "cudaSetDevice failed"; delete M; return kInternal; }
+  DeviceGuard guard(device);
+  if (guard.err != cudaSuccess) { g_err = "cudaSetDevice failed"; delete M; return kInternal; }
   rc = upload_model(M);
   if (rc) { spm_cuda_model_free(M); return rc; }
   if (cudaHostAlloc((void **)&M->h_pin, (kPubTot + 4096) * 8, cudaHostAllocMapped) != cudaSuccess ||
@@ -1587,7 +1715,7 @@ int spm_cuda_model_load(const void *serialized_model, size_t len, int device, sp
 
 void spm_cuda_model_free(spm_cuda_model *M) {
   if (!M) return;
-  cudaSetDevice(M->device);
+  DeviceGuard guard(M->device);
   for (DevBuf *b : M->all_bufs()) b->release();
   if (M->s_in) cudaStreamDestroy(M->s_in);
   if (M->s_out) cudaStreamDestroy(M->s_out);
@@ -1615,10 +1743,53 @@ int spm_cuda_model_set_piece_types(spm_cuda_model *M, const uint8_t *types, int 
   }
   for (int i = 0; i < n; ++i) M->hm.type[i] = types[i];
   refresh_leaf_types(&M->hm);
-  CUDA_TRY(cudaSetDevice(M->device));
+  DEVICE_GUARD(M->device);
   CUDA_TRY(cudaMemcpy(M->d_leaf.p, M->hm.pieces.leaf.data(), M->hm.pieces.leaf.size() * 8, cudaMemcpyHostToDevice));
   M->mv.has_unused = M->hm.has_unused;
   return configure_fast(M);
+}
+
+static int64_t *option_slot(Options *o, const char *name) {
+  const struct { const char *name; int64_t *p; } table[] = {
+      {"memo", &o->memo}, {"memo_bits", &o->memo_bits}, {"host_chunks", &o->host_chunks},
+      {"host_chunk_min", &o->host_chunk_min}, {"max_chunk", &o->max_chunk}, {"warp", &o->warp},
+      {"scan_per_sentence", &o->scan_per_sentence}, {"warp_route", &o->warp_route},
+      {"emit_blocks", &o->emit_blocks}, {"pieces_exact", &o->pieces_exact}};
+  for (const auto &e : table)
+    if (strcmp(e.name, name) == 0) return e.p;
+  return nullptr;
+}
+
+int spm_cuda_model_set_option(spm_cuda_model *M, const char *name, int64_t value) {
+  if (!M || !name) { g_err = "null argument"; return kInvalidArgument; }
+  std::lock_guard<std::mutex> lk(M->mu);
+  int64_t *slot = option_slot(&M->opt, name);
+  if (!slot) { g_err = std::string("unknown option: ") + name; return kNotFound; }
+  if (value < 0) { g_err = std::string("option value must be >= 0: ") + name; return kInvalidArgument; }
+  *slot = value;
+  return kOk;
+}
+
+int spm_cuda_model_get_option(const spm_cuda_model *M, const char *name, int64_t *value) {
+  if (!M || !name || !value) { g_err = "null argument"; return kInvalidArgument; }
+  std::lock_guard<std::mutex> lk(M->mu);
+  const int64_t *slot = option_slot(const_cast<Options *>(&M->opt), name);
+  if (!slot) { g_err = std::string("unknown option: ") + name; return kNotFound; }
+  *value = *slot;
+  return kOk;
+}
+
+// Frees the workspace of past calls (it grows to the largest batch seen and is otherwise kept
+// for the next call); the model tables stay.
+int spm_cuda_model_release_workspace(spm_cuda_model *M) {
+  if (!M) { g_err = "model is null"; return kInvalidArgument; }
+  std::lock_guard<std::mutex> lk(M->mu);
+  DEVICE_GUARD(M->device);
+  CUDA_TRY(cudaDeviceSynchronize());
+  for (DevBuf *b : M->workspace_bufs()) b->release();
+  M->pt_ready = false;
+  M->dec_ready = false;
+  return kOk;
 }
 
 int spm_cuda_model_piece_size(const spm_cuda_model *M) { return (int)M->hm.piece.size(); }
@@ -1700,7 +1871,7 @@ int spm_cuda_encode_batch(const spm_cuda_model *M, const char *text, const int64
 static int encode_batch_locked(const spm_cuda_model *M, const char *text, const int64_t *text_offsets, int64_t n,
                                uint32_t extra_options, int32_t *ids, int64_t ids_capacity, int64_t *id_offsets,
                                int memory_space, void *cuda_stream) {
-  CUDA_TRY(cudaSetDevice(M->device));
+  DEVICE_GUARD(M->device);
   cudaStream_t st = (cudaStream_t)cuda_stream;
   static const bool trace = getenv("SPM_CUDA_TRACE") != nullptr;   // host-side timeline on stderr
   const auto t_begin = std::chrono::steady_clock::now();
@@ -1786,16 +1957,14 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
   const ExtraPlan plan = make_extra_plan(extra_options, M->bos_id, M->eos_id);
   const int exp_ = M->hm.expansion;
   // word memo (spm_memo.cuh): one table per call, zeroed here -- nothing survives the call.
-  // SPM_CUDA_NO_MEMO=1 switches the tier off (measurement of the Viterbi / merge kernels alone).
-  static const bool no_memo = getenv("SPM_CUDA_NO_MEMO") != nullptr;
-  const bool memo = M->fast && M->hm.memo_ok && !no_memo && n > 0;
+  // Option "memo" = 0 switches the tier off (the Viterbi / merge kernels alone).
+  const bool memo = M->fast && M->hm.memo_ok && M->opt.memo != 0 && n > 0;
   MemoTable memo_tb;
   memset(&memo_tb, 0, sizeof(memo_tb));
   if (memo) {
     const uint64_t want = 2 * (uint64_t)n + (uint64_t)(text_hi - text_lo) / 16;
     uint64_t entries = 1 << 12;
-    static const char *env_bits = getenv("SPM_CUDA_MEMO_BITS");   // tuning experiments only
-    const int max_bits = env_bits ? std::max(12, std::min(26, atoi(env_bits))) : 23;
+    const int max_bits = (int)std::max<int64_t>(12, std::min<int64_t>(26, M->opt.memo_bits));
     while (entries < want && entries < (1ull << max_bits)) entries <<= 1;
     if ((rc = M->w_memo.ensure(entries * sizeof(MemoKey)))) return rc;
     if ((rc = M->w_mres.ensure(entries * sizeof(MemoRes)))) return rc;
@@ -1819,7 +1988,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
   // chunk = as many sentences as fit the byte budget (fast tier: the raw text; general
   // tier: the worst-case normalized text) -- one chunk for all but huge batches
   const int64_t kRawBudget = M->fast ? (2048ll << 20) : (256ll << 20) / exp_;
-  const int64_t kMaxChunk = M->fast ? (1 << 24) : (1 << 20);
+  const int64_t kMaxChunk = M->opt.max_chunk > 0 ? M->opt.max_chunk : (M->fast ? (1 << 24) : (1 << 20));
   uint32_t stor = 0;
   int64_t n_general = 0, n_viterbi = 0, n_memo_words = 0;
   struct Chunk { int64_t c0, c1, o0, o1; };
@@ -1833,13 +2002,12 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     // ~1.7 ms over a chunk's leftover sentences whatever the chunk holds: ~2.5 ms).  Measured per
     // 10 M sentences: unigram 8 / 12 / 16 / 24 chunks 28.0 / 26.9 / 26.7 / 29.1 ms (text with many
     // rule hits: 12: 27.7, 16: 31.0), chunks tapered at both ends 27.2; BPE 4 / 5 / 6 / 7: 33.2 /
-    // 33.0 / 34.4 / 36.4.  SPM_CUDA_HOST_CHUNKS=k overrides the count (measurements).
+    // 33.0 / 34.4 / 36.4.  Options "host_chunks" / "host_chunk_min" override count and threshold.
     int64_t want = kMaxChunk;
-    if (host && n >= (1 << 20)) {
-      static const char *env_chunks = getenv("SPM_CUDA_HOST_CHUNKS");   // tuning experiments only
+    if (host && n >= std::max<int64_t>(1, M->opt.host_chunk_min)) {
       const int64_t parts = std::max<int64_t>(
-          1, std::min<int64_t>(64, env_chunks ? atoll(env_chunks) : (M->fast_kind == 2 ? 5 : 12)));
-      want = std::min(kMaxChunk, (n + parts - 1) / parts);
+          1, std::min<int64_t>(64, M->opt.host_chunks > 0 ? M->opt.host_chunks : (M->fast_kind == 2 ? 5 : 12)));
+      want = std::max<int64_t>(1, std::min(kMaxChunk, (n + parts - 1) / parts));
     }
     int64_t c0 = 0, off_c0 = text_lo;
     while (c0 < n) {
@@ -1923,17 +2091,21 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       // long lines (kFastMaxRaw <= bytes < kLongMaxRaw): same kernels over long_list, on as
       // many warps per SM as a 2 GiB back-pointer budget allows
       const bool has_long = max_len >= kFastMaxRaw && max_long >= kFastMaxRaw;
-      static const bool no_warp = getenv("SPM_CUDA_NO_WARP") != nullptr;   // measurement of the older long-line path
-      const bool warp_ok = M->fast_kind == 1 && !no_warp && M->hm.ring <= kWarpRing &&
+      const bool warp_ok = M->fast_kind == 1 && M->opt.warp != 0 && M->hm.ring <= kWarpRing &&
                            M->hm.max_piece_chars + 1 <= kWarpHits && M->hm.piece.size() < (1u << 24);
       const int64_t back_rows_long = (max_long + kFastExtraChars + 8 + 3) & ~(int64_t)3;
       int long_warps = M->fast_kind == 1 ? kFastThreads / 32 : kBpeThreads / 32;
       if (M->fast_kind == 1)
         long_warps = (int)std::max<int64_t>(
             1, std::min<int64_t>(long_warps, (2048ll << 20) / (back_rows_long * 4 * 32 * M->sm_count)));
-      size_t back_bytes = (size_t)back_rows * M->sm_count * kFastThreads * 4;
-      if (has_long) back_bytes = std::max(back_bytes, (size_t)back_rows_long * M->sm_count * long_warps * 32 * 4);
-      if (M->fast_kind == 1 && (rc = M->w_back.ensure(back_bytes))) return rc;
+      // k_encode_fast hands a list of up to warp_route sentences to k_encode_warp as a whole: a chunk
+      // that small never needs the per-thread back-pointer rows (2.4 GB for one 4 KB line otherwise)
+      const uint32_t warp_route = (uint32_t)std::max<int64_t>(0, std::min<int64_t>(M->opt.warp_route, 0x7FFFFFFF));
+      const bool fast_may_run = !(warp_ok && warp_route != 0 && (uint64_t)cn <= warp_route);
+      size_t back_bytes = fast_may_run ? (size_t)back_rows * M->sm_count * kFastThreads * 4 : 0;
+      if (has_long && !warp_ok)
+        back_bytes = std::max(back_bytes, (size_t)back_rows_long * M->sm_count * long_warps * 32 * 4);
+      if (M->fast_kind == 1 && back_bytes > 0 && (rc = M->w_back.ensure(back_bytes))) return rc;
       // (with k_encode_warp the long-line list also takes the sentences k_encode_fast flags)
       const int64_t long_cap = warp_ok ? cn : std::min<int64_t>(cn, raw / kFastMaxRaw + 1);
       if ((has_long || warp_ok) && (rc = M->w_vitl.ensure((size_t)long_cap * 4))) return rc;
@@ -1956,8 +2128,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         tb.n_new = d_counters + C_NNEW;
         const unsigned gnew = (tb.max_new + 255) / 256;
         if ((rc = kev_record(M, st, 0, T_MEMO_COLLECT))) return rc;
-        static const bool scan_lanes = getenv("SPM_CUDA_SCAN_PER_SENTENCE") != nullptr;   // measurement of the older scan
-        if (scan_lanes)
+        if (M->opt.scan_per_sentence != 0)   // the older thread-per-sentence scan
           k_memo_scan_plain<<<gsent, kScanWarps * 32, 0, st>>>(
               M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
               (uint32_t *)M->w_wbase.p, wslot_half, (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
@@ -1987,13 +2158,12 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         // grid-stride kernel: exactly as many CTAs as are resident at once (6 per SM at 40 registers), so
         // that the sentences are dealt out in ONE wave -- with 8 per SM the last quarter of the CTAs ran
         // alone at a third of the machine
-        static const char *env_emit = getenv("SPM_CUDA_EMIT_BLOCKS");   // tuning experiments only
         if (M->emit_blocks == 0) {
           int occ = 0;
           CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_memo_emit, kMemoThreads, 0));
           M->emit_blocks = std::max(1, occ);
         }
-        const int64_t emit_per_sm = env_emit ? std::max(1, atoi(env_emit)) : M->emit_blocks;
+        const int64_t emit_per_sm = M->opt.emit_blocks > 0 ? M->opt.emit_blocks : M->emit_blocks;
         const unsigned gemit = (unsigned)std::min<int64_t>((cn + 15) / 16, emit_per_sm * (int64_t)M->sm_count);
         k_memo_emit<<<gemit, kMemoThreads, 0, st>>>(
             tb, M->fast_kind == 1, d_off, c0, cn, (const uint32_t *)M->w_wslots.p, (const uint32_t *)M->w_wbase.p,
@@ -2023,8 +2193,6 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       }
       if ((rc = kev_record(M, st, 1))) return rc;
       launches += has_long ? 5 : 4;
-      static const char *env_route = getenv("SPM_CUDA_WARP_ROUTE");   // tuning experiments only
-      const uint32_t warp_route = env_route ? (uint32_t)atoll(env_route) : 262144u;
       const int32_t *list_a = (const int32_t *)M->w_perm.p, *list_b = (const int32_t *)M->w_longlist.p;
       const int cnt_a = C_NFAST, work_a = C_WORK, cnt_b = C_NLONG, work_b = C_WORK_LONG;
       if ((rc = kev_record(M, st, 0, T_ENCODE))) return rc;
@@ -2040,8 +2208,9 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
           // one warp per line, exact candidate lists (spm_warp.cuh); back records: kWarpCapc rows of
           // `wstride` per resident warp, at most 4 GiB in all; longest lines first
           const int64_t wstride = 3 * max_long + 136;
-          const int64_t wblocks = std::max<int64_t>(
+          int64_t wblocks = std::max<int64_t>(
               1, std::min<int64_t>(5 * (int64_t)M->sm_count, (4096ll << 20) / (wstride * 4 * kWarpCapc * kWarpWarps)));
+          wblocks = std::min<int64_t>(wblocks, (cn + kWarpWarps - 1) / kWarpWarps);   // a warp per listed line at most
           if ((rc = M->w_wback.ensure((size_t)(wblocks * kWarpWarps * kWarpCapc * wstride * 4)))) return rc;
           k_sort_long<<<1, 1024, 0, st>>>(d_off, c0, (const int32_t *)M->w_longlist.p, C_NLONG,
                                           (int32_t *)M->w_vitl.p, d_counters);
@@ -2191,7 +2360,7 @@ int spm_cuda_split_lines(const spm_cuda_model *M, const char *buf, int64_t len, 
     return kInvalidArgument;
   }
   std::lock_guard<std::mutex> lk(M->mu);
-  CUDA_TRY(cudaSetDevice(M->device));
+  DEVICE_GUARD(M->device);
   cudaStream_t st = (cudaStream_t)cuda_stream;
   const bool host = memory_space == SPM_CUDA_HOST;
   int rc;
@@ -2276,7 +2445,7 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
   std::unique_ptr<spm_cuda_estep> E(new spm_cuda_estep);
   E->device = device;
   E->V = V;
-  CUDA_TRY(cudaSetDevice(device));
+  DEVICE_GUARD(device);
   if ((rc = upload(&E->d_units, trie.units.data(), trie.units.size() * 4))) return rc;
   if ((rc = upload(&E->d_leaf, trie.leaf.data(), trie.leaf.size() * 8))) return rc;
   E->ev.units = (const uint32_t *)E->d_units.p;
@@ -2289,7 +2458,7 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
 
 void spm_cuda_estep_free(spm_cuda_estep *E) {
   if (!E) return;
-  cudaSetDevice(E->device);
+  DeviceGuard guard(E->device);
   for (DevBuf *b : {&E->d_units, &E->d_leaf, &E->w_words, &E->w_off, &E->w_freq, &E->w_scratch, &E->w_expected,
                     &E->w_out, &E->w_logz})
     b->release();
@@ -2307,7 +2476,7 @@ int spm_cuda_estep_run(const spm_cuda_estep *E, const char *words, const int64_t
     return kInvalidArgument;
   }
   std::lock_guard<std::mutex> lk(E->mu);
-  CUDA_TRY(cudaSetDevice(E->device));
+  DEVICE_GUARD(E->device);
   cudaStream_t st = (cudaStream_t)cuda_stream;
   const bool host = memory_space == SPM_CUDA_HOST;
   int rc;

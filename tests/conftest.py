@@ -55,6 +55,21 @@ EDGE_SENTENCES = [
 ]
 
 
+def near_tie_model(kmax=20, eps=3e-7):
+    """A unigram model whose pieces a, aa, ... a^kmax have near-additive scores: in a long run of
+    'a' more than 8 (the exact tier's first capacity) DISTINCT near-tied candidates end at one
+    position, so the sentence must take the retry with room for every candidate."""
+    import protowire as pw
+    ps = pw.base_pieces() + [("\u2581", -2.0)]
+    ps += [("a" * k, -float(k) - eps * k * k) for k in range(1, kmax + 1)]
+    ps += [("b", -3.0), ("\u2581b", -3.5)]
+    return pw.model(ps)
+
+
+NEAR_TIE_SENTENCES = [b"a" * n for n in (1, 5, 13, 40, 100, 300, 1000, 5000)] + \
+    [b"aaaa b " + b"a" * 77 + b" ab" * 5, b"b" + b"a" * 30 + b"b", b"", b"b b b"]
+
+
 def _build_lib(src_files, out, extra):
     os.makedirs(os.path.dirname(out), exist_ok=True)
     newest = max(os.path.getmtime(s) for s in src_files)

@@ -138,7 +138,8 @@ int64_t hc_normalize_chunked(void *p, const uint8_t *in, int64_t n, int chunk, u
   return nl;
 }
 
-// capc: candidate capacity of the unigram tier to emulate (1, 4 or 16); 0: the fast tiers
+// capc: candidate capacity of the unigram tier to emulate (1, 4 or 16; other values: with the
+// library's retry at min(ring, 255) on overflow); 0: the fast tiers
 // with the library's routing; -1: the word memo in front of them (sentences it served carry
 // status bit 20).  status[n] receives the per-sentence status bits.
 int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n, uint32_t opts, int capc_arg,
@@ -273,19 +274,26 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
       std::vector<int32_t> rev(nl + 1);
       cnt = fast_unigram(fv, (const uint8_t *)tbuf.data(), nl, rbt.data(), rbk.data(), txt.data(), 1, (uint32_t *)(((uintptr_t)back.data() + 15) & ~(uintptr_t)15), rev.data(), &st);
       if (st & ST_CAND_OVERFLOW) {
-        st = ST_CAND_OVERFLOW;  // reported; result comes from the exact tier
-        words.assign(uni_scratch_words(mv.ring, 16, nl), 0);
-        UniScratch sc;
-        int32_t *w = words.data();
-        sc.ringM = (float *)w; w += mv.ring;
-        sc.ringCnt = (uint32_t *)w; w += mv.ring;
-        sc.candBt = (float *)w; w += mv.ring * 16;
-        w += ((w - words.data()) & 1);
-        sc.candRec = (uint64_t *)w; w += 2 * mv.ring * 16;
-        sc.back = (uint64_t *)w;
-        sc.stride = nl + 1;
-        uint32_t st2 = 0;
-        cnt = unigram_encode<16>(mv, norm.data(), nl, sc, core.data(), nl, &st2);
+        // reported; the result comes from the exact tier as in the library: 8 candidates per
+        // position, then the retry with room for every candidate
+        st = ST_CAND_OVERFLOW;
+        for (int pass = 0; pass < 2; ++pass) {
+          const int cc = pass == 0 ? 8 : (mv.ring < 255 ? mv.ring : 255);
+          words.assign(uni_scratch_words(mv.ring, cc, nl) + 2, 0);
+          UniScratch sc;
+          int32_t *w = words.data();
+          sc.ringM = (float *)w; w += mv.ring;
+          sc.ringCnt = (uint32_t *)w; w += mv.ring;
+          sc.candBt = (float *)w; w += mv.ring * cc;
+          w += ((w - words.data()) & 1);
+          sc.candRec = (uint64_t *)w; w += 2 * mv.ring * cc;
+          sc.back = (uint64_t *)w;
+          sc.stride = nl + 1;
+          uint32_t st2 = 0;
+          cnt = unigram_encode_capc(mv, norm.data(), nl, sc, cc, core.data(), nl, &st2);
+          if (!(st2 & ST_CAND_OVERFLOW)) break;
+          if (pass == 0) st |= 1u << 23;
+        }
       } else {
         for (int32_t j = 0; j < cnt; ++j) core[j] = rev[cnt - 1 - j];
       }
@@ -327,7 +335,26 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
       sc.stride = nl + 1;
       if (capc == 1) cnt = unigram_encode<1>(mv, norm.data(), nl, sc, core.data(), nl, &st);
       else if (capc == 4) cnt = unigram_encode<4>(mv, norm.data(), nl, sc, core.data(), nl, &st);
-      else cnt = unigram_encode<16>(mv, norm.data(), nl, sc, core.data(), nl, &st);
+      else if (capc == 16) cnt = unigram_encode<16>(mv, norm.data(), nl, sc, core.data(), nl, &st);
+      else {
+        // any other capacity: the library's flow (gen_encode_one + run_capc_retry) -- a sentence that
+        // meets more near-tied candidates than `capc` runs again with room for every candidate
+        cnt = unigram_encode_capc(mv, norm.data(), nl, sc, capc, core.data(), nl, &st);
+        if (st & ST_CAND_OVERFLOW) {
+          const int big = mv.ring < 255 ? mv.ring : 255;
+          words.assign(uni_scratch_words(mv.ring, big, nl) + 2, 0);
+          w = words.data();
+          sc.ringM = (float *)w; w += mv.ring;
+          sc.ringCnt = (uint32_t *)w; w += mv.ring;
+          sc.candBt = (float *)w; w += mv.ring * big;
+          w += ((w - words.data()) & 1);
+          sc.candRec = (uint64_t *)w; w += 2 * mv.ring * big;
+          sc.back = (uint64_t *)w;
+          st = 0;
+          cnt = unigram_encode_capc(mv, norm.data(), nl, sc, big, core.data(), nl, &st);
+          st |= 1u << 23;   // reported: the retry ran
+        }
+      }
     } else {
       words.assign(bpe_scratch_words(nl), 0);
       cnt = bpe_encode(mv, norm.data(), nl, words.data(), core.data(), nl, &st);

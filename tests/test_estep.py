@@ -54,6 +54,31 @@ def trainer_like_case(n_words=4000):
     return pieces, scores, [w for w, _ in items], np.array([c for _, c in items], dtype=np.int64)
 
 
+def check_against_reference(exp, logz, obj, nt, freq, rexp, rlogz, robj, rnt, rexp64):
+    """North-star tolerance, SURVEY.md H9: per-word logZ and the expected counts against the
+    float64 re-accumulation of the reference's OWN posteriors (oracle/ref_shim.cc ref_estep64)
+    at 1e-5 relative; the Viterbi token count exactly.  The reference's float accumulator
+    (expected[id] += ... in float over the whole corpus, src/unigram_model.cc:321) is itself
+    further from that re-accumulation than 1e-5 on large counts: its delta is bounded loosely
+    and printed, not held to the tolerance."""
+    assert nt == rnt
+    # the shim records what PopulateMarginal returns: freq * logZ (src/unigram_model.cc:327)
+    f32 = freq.astype(np.float32)
+    assert np.allclose(logz * f32, rlogz, rtol=REL, atol=0)
+    floor = 1e-6                      # counts below this are sums of posteriors < 1e-6: absolute bound
+    big = rexp64 > floor
+    assert big.sum() > 1000
+    rel = np.abs(exp[big] - rexp64[big]) / rexp64[big]
+    assert rel.max() <= REL, "expected counts: max relative error %.3g vs the f64 re-accumulation" % rel.max()
+    assert np.abs(exp[~big] - rexp64[~big]).max() <= floor * REL * 10 if (~big).any() else True
+    # obj: the reference adds -Z / all_freq in float word by word; ours in double
+    assert abs(obj - robj) <= 5e-5 * abs(robj)
+    ref_rel = np.abs(rexp[big].astype(np.float64) - rexp64[big]) / rexp64[big]
+    print("reference float accumulator vs its own f64 re-accumulation: max rel %.3g; ours: %.3g" % (
+        ref_rel.max(), rel.max()))
+    assert np.allclose(exp, rexp, rtol=1e-3, atol=1e-5)
+
+
 def test_closed_form_of_the_reference_test(hostcore):
     """src/unigram_model_test.cc:271-313 (LatticeTest.PopulateMarginalTest), tolerance 1e-3 there."""
     pieces = [b"A", b"B", b"C", b"AB", b"BC", b"ABC"]
@@ -73,16 +98,9 @@ def test_hostcore_matches_reference_estep(hostcore):
     if not ref.available() or not hasattr(ref.lib(), "ref_estep"):
         pytest.skip("reference library with the trainer is not built")
     pieces, scores, words, freq = trainer_like_case()
-    rexp, rlogz, robj, rnt = ref.estep(pieces, scores, words, freq)
+    rexp, rlogz, robj, rnt, rexp64 = ref.estep64(pieces, scores, words, freq)
     exp, logz, obj, nt = hc_estep(hostcore, pieces, scores, words, freq)
-    assert nt == rnt
-    # the shim records what PopulateMarginal returns: freq * logZ (src/unigram_model.cc:327)
-    assert np.allclose(logz * freq.astype(np.float32), rlogz, rtol=REL, atol=1e-6)
-    big = rexp > 1e-3
-    assert big.sum() > 1000
-    assert np.allclose(exp[big], rexp[big], rtol=REL * 5)      # the reference accumulates in float
-    assert np.allclose(exp, rexp, rtol=1e-3, atol=1e-5)
-    assert abs(obj - robj) <= REL * 5 * abs(robj)
+    check_against_reference(exp, logz, obj, nt, freq, rexp, rlogz, robj, rnt, rexp64)
 
 
 @pytest.mark.gpu
@@ -91,17 +109,11 @@ def test_gpu_estep_matches_reference(spm_b200):
     if not hasattr(ref.lib(), "ref_estep"):
         pytest.skip("reference library was built without the trainer")
     pieces, scores, words, freq = trainer_like_case()
-    rexp, rlogz, robj, rnt = ref.estep(pieces, scores, words, freq)
+    rexp, rlogz, robj, rnt, rexp64 = ref.estep64(pieces, scores, words, freq)
     es = spm_b200.UnigramEStep(pieces, scores)
     text, off = pack_words(words)
     exp, obj, nt, logz = es.run(text, off, freq, want_logz=True)
-    assert nt == rnt
-    # the shim records what PopulateMarginal returns: freq * logZ (src/unigram_model.cc:327)
-    assert np.allclose(logz * freq.astype(np.float32), rlogz, rtol=REL, atol=1e-6)
-    big = rexp > 1e-3
-    assert np.allclose(exp[big], rexp[big], rtol=REL * 5)
-    assert np.allclose(exp, rexp, rtol=1e-3, atol=1e-5)
-    assert abs(obj - robj) <= REL * 5 * abs(robj)
+    check_against_reference(exp, logz, obj, nt, freq, rexp, rlogz, robj, rnt, rexp64)
     # two shards summed = the whole (what the all-reduce does across GPUs)
     from importlib import import_module
     sh = import_module("sentencepiece-comments_b200.sharding")

@@ -44,6 +44,25 @@ def test_core_matches_reference_fixture(make_hostcore, corpora, ref_ids, model, 
             assert not (st & 4).any(), "exact tier overflowed its candidate list"
 
 
+def test_core_near_tie_retry(make_hostcore):
+    """More than 8 near-tied candidates at one position: the exact tier's first pass overflows
+    (capacity 8 as in the library), the retry at min(ring, 255) reproduces the reference."""
+    from conftest import NEAR_TIE_SENTENCES, near_tie_model
+    from tools import synth
+    mb = near_tie_model()
+    text, off = synth.pack_lines(NEAR_TIE_SENTENCES)
+    chk, _ = checker(mb)
+    wi, wo = chk.encode_batch(text, off)
+    hc = make_hostcore(mb)
+    gi, go, st = hc.encode_batch(text, off, capc=8)
+    assert np.array_equal(go, wo) and np.array_equal(gi, wi)
+    assert (st & (1 << 23)).sum() >= 4, "the crafted sentences did not overflow the 8-candidate lists"
+    assert not (st & 4).any()
+    for capc in (0, -1):      # fast tier / word memo in front: flagged, served by the exact tier
+        gi, go, _ = hc.encode_batch(text, off, capc=capc)
+        assert np.array_equal(go, wo) and np.array_equal(gi, wi), capc
+
+
 @pytest.mark.parametrize("model", mf.EDGE_MODELS)
 def test_core_edge_sentences(make_hostcore, corpora, ref_ids, model):
     text, off = corpora["edge"]

@@ -115,6 +115,29 @@ class EnglishCorpus:
         return text, off
 
 
+    def word_counts(self, n, first=0):
+        """The (word, freq) list of sentences [first, first + n) of the CLEAN corpus, without
+        generating it: (list of word bytes, int64 freq), by descending frequency.  Exactly the
+        whitespace-split tokens of generate(n, first) with their counts."""
+        assert not self.cfg.dirty
+        nw = self.cfg.nwords
+        hist = np.zeros(3 * nw, dtype=np.int64)
+        self.lib.synth_word_hist(ctypes.byref(self.cfg), ctypes.c_uint64(self.seed), ctypes.c_int64(first),
+                                 ctypes.c_int64(n), ctypes.c_void_p(hist.ctypes.data))
+        idx = np.flatnonzero(hist)
+        order = idx[np.argsort(-hist[idx], kind="stable")]
+        words = []
+        for k in order:
+            wi, v = divmod(int(k), 3)
+            w = self._bytes[self._woff[wi]:self._woff[wi + 1]]
+            if v == 1:
+                w = w[:1].upper() + w[1:]
+            elif v == 2:
+                w = w + b"."
+            words.append(w)
+        return words, hist[order]
+
+
 class ResampledCorpus:
     """Config 4: lines of a base text re-sampled with replacement."""
 

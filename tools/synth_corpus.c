@@ -123,6 +123,32 @@ void synth_fill(const synth_cfg *c, uint64_t seed, int64_t first, int64_t n, con
   for (int64_t i = 0; i < n; ++i) gen_sentence(c, seed, first + i, out + off[i]);
 }
 
+/* The (word, freq) list of the clean corpus without materialising it: hist[3 * wi + v] counts
+ * word type wi in variant v (0 as is, 1 first letter upper-cased = first word of a sentence,
+ * 2 with the sentence's trailing '.').  What SplitSentencesByWhitespace would hand the unigram
+ * trainer's E-step for sentences [first, first + n) (src/trainer_interface.cc:465-477). */
+void synth_word_hist(const synth_cfg *c, uint64_t seed, int64_t first, int64_t n, int64_t *hist) {
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < n; ++i) {
+    uint64_t rng = seed * 0xD1342543DE82EF95ull + (uint64_t)(first + i) * 0x2545F4914F6CDD1Dull + 1;
+    splitmix(&rng);
+    double L = exp(-c->lambda), p = 1.0;
+    int k = 0;
+    do { ++k; p *= u01(&rng); } while (p > L);
+    int nw = k - 1;
+    if (nw < 3) nw = 3;
+    if (nw > 60) nw = 60;
+    for (int w = 0; w < nw; ++w) {
+      const int wi = pick_word(c, &rng);
+      int v = 0;
+      if (w == 0 && c->words[c->woff[wi]] >= 'a' && c->words[c->woff[wi]] <= 'z') v = 1;
+      if (w == nw - 1) v = 2;
+#pragma omp atomic
+      hist[3 * (int64_t)wi + v] += 1;
+    }
+  }
+}
+
 /* CJK-style corpus: re-sample whole lines of a base text (config 4). */
 int64_t synth_resample_lengths(const int64_t *loff, int64_t nlines, uint64_t seed, int64_t first,
                                int64_t n, int64_t *off) {
