@@ -1929,10 +1929,11 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
   }
 
   if ((rc = M->w_scalars.ensure(64))) return rc;
-  if ((rc = M->w_counters.ensure(C_COUNT * 4))) return rc;
+  if ((rc = M->w_counters.ensure((C_COUNT + 4) * 4))) return rc;   // + per-call counters (not reset per chunk)
   int64_t *d_carry = (int64_t *)M->w_scalars.p;        // [0] running CSR total
   uint32_t *d_counters = (uint32_t *)M->w_counters.p;
   CUDA_TRY(cudaMemsetAsync(M->w_scalars.p, 0, 64, st));
+  CUDA_TRY(cudaMemsetAsync(d_counters + C_COUNT, 0, 16, st));
   int64_t max_len = 0, max_raw = 0, max_long = 0;
   if (n > 0) {
     const unsigned vgrid = (unsigned)std::min<int64_t>((n + 255) / 256, 4 * (int64_t)M->sm_count);
@@ -1979,6 +1980,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     memo_tb.max_new = (uint32_t)(entries / 2);
     if ((rc = M->w_movf.ensure((size_t)memo_tb.max_new * kMemoOverflowIds * 4))) return rc;
     memo_tb.overflow = (int32_t *)M->w_movf.p;
+    memo_tb.n_ovf = d_counters + C_COUNT;
     if (M->fast_kind == 2) {
       if ((rc = M->w_wtext.ensure((size_t)memo_tb.max_new * 64))) return rc;
       if ((rc = M->w_wlen.ensure((size_t)memo_tb.max_new * 4))) return rc;

@@ -68,6 +68,7 @@ struct MemoTable {
   uint32_t *n_new;      // their count (may exceed max_new: the excess is never encoded)
   uint32_t max_new;
   int32_t *overflow;    // max_new rows of kMemoOverflowIds ids
+  uint32_t *n_ovf;      // rows handed out so far -- per CALL, not per pass: results outlive the pass (chunk) that made them
 };
 
 // slot lists are written once and read once: keep them out of the way of the table in L2
@@ -404,19 +405,27 @@ SPM_HD int memo_word_bytes(const MemoKey *keys, uint32_t slot, uint8_t *out, int
   return nb;
 }
 
-// Stores ids (forward order), flags and bounds of an encoded word; `row` = its list index.
+// Stores ids (forward order), flags and bounds of an encoded word; `row` = its index in new_list.
 SPM_HD void memo_store(const MemoTable &tb, uint32_t row, const int32_t *ids, int32_t cnt, bool bad,
                        int32_t unk_id, float bmax, float sabs) {
   MemoRes *e = tb.res + tb.new_list[row];
   uint32_t meta = kMemoReady;
   if (bad || cnt <= 0 || cnt > kMemoMaxIds) { meta |= kMemoBad; cnt = 0; }
-  if (cnt <= kMemoInlineIds) {
-    for (int j = 0; j < cnt; ++j) e->ids[j] = ids[j];
+  if (cnt > kMemoInlineIds) {       // an overflow row of its own, kept until the end of the call
+#if defined(__CUDA_ARCH__)
+    const uint32_t orow = atomicAdd(tb.n_ovf, 1u);
+#else
+    const uint32_t orow = (*tb.n_ovf)++;
+#endif
+    if (orow >= tb.max_new) { meta |= kMemoBad; cnt = 0; }
+    else {
+      for (int j = 0; j < kMemoInlineIds - 1; ++j) e->ids[j] = ids[j];
+      e->ids[kMemoInlineIds - 1] = (int32_t)orow;
+      for (int j = kMemoInlineIds - 1; j < cnt; ++j)
+        tb.overflow[(size_t)orow * kMemoOverflowIds + (j - (kMemoInlineIds - 1))] = ids[j];
+    }
   } else {
-    for (int j = 0; j < kMemoInlineIds - 1; ++j) e->ids[j] = ids[j];
-    e->ids[kMemoInlineIds - 1] = (int32_t)row;
-    for (int j = kMemoInlineIds - 1; j < cnt; ++j)
-      tb.overflow[(size_t)row * kMemoOverflowIds + (j - (kMemoInlineIds - 1))] = ids[j];
+    for (int j = 0; j < cnt; ++j) e->ids[j] = ids[j];
   }
   if (cnt > 0 && ids[0] == unk_id) meta |= kMemoFirstUnk;
   if (cnt > 0 && ids[cnt - 1] == unk_id) meta |= kMemoLastUnk;

@@ -153,7 +153,7 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
   std::vector<MemoRes> mres;
   std::vector<uint32_t> mnew;
   std::vector<int32_t> movf;
-  uint32_t m_n_new = 0, m_done = 0;
+  uint32_t m_n_new = 0, m_done = 0, m_n_ovf = 0;
   MemoTable tb;
   memset(&tb, 0, sizeof(tb));
   FastView mfv;
@@ -167,7 +167,7 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
     mnew.resize(slots / 2);
     movf.resize(mnew.size() * kMemoOverflowIds);
     tb.keys = mkeys.data(); tb.res = mres.data(); tb.mask = (uint32_t)slots - 1; tb.new_list = mnew.data();
-    tb.n_new = &m_n_new; tb.max_new = (uint32_t)mnew.size(); tb.overflow = movf.data();
+    tb.n_new = &m_n_new; tb.max_new = (uint32_t)mnew.size(); tb.overflow = movf.data(); tb.n_ovf = &m_n_ovf;
     mfv.units = mfv.units_hot = h->hm.funits.data();
     mfv.score = mfv.score_hot = h->hm.fscore.data();
     mfv.leaf_id = h->hm.fleaf.data();
