@@ -133,6 +133,19 @@ const char *spm_cuda_last_error(void);
 int spm_cuda_split_lines(const spm_cuda_model *model, const char *buf, int64_t len, char *text, int64_t *offsets,
                          int64_t capacity, int64_t *n_lines, int memory_space, void *cuda_stream);
 
+/* The same line splitting for callers that cannot allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE
+ * REFERENCE.  Device pointers only (the
+ * SPM_CUDA_DEVICE form of spm_cuda_split_lines, same outputs, same errors); the scratch of the
+ * two kernels -- per-tile newline counts and their scan -- lives in a file-scope __device__ array
+ * of 786,448 bytes that every GPU loading the library holds until exit, so the call makes no
+ * cudaMalloc / cudaFree / allocating library call.  Limit: len <= 268,435,456 bytes (256 MiB);
+ * a longer buffer is refused with OUT_OF_RANGE and a message naming the limit.  All calls on one
+ * GPU share the array: calls that overlap in time on the same GPU (different streams or threads)
+ * race; serialise them.  model may be NULL (the current device is used). */
+int spm_cuda_split_lines_noalloc(const spm_cuda_model *model, const char *buf, int64_t len, char *text,
+                                 int64_t *offsets, int64_t capacity, int64_t *n_lines, void *cuda_stream);
+
 /* ---- Pieces / SentencePieceText (the step after the path) ------
  * Replaces a loop of SentencePieceProcessor::Encode(input, SentencePieceText*)
  * (src/sentencepiece_processor.h:258, .cc:560-573 -> PopulateSentencePieceText :488-551 ->

@@ -60,6 +60,7 @@ def lib():
         L.spm_cuda_estep_vocab_size.argtypes = [vp]
         L.spm_cuda_estep_run.argtypes = [vp, vp, vp, vp, i64, ctypes.c_double, vp, vp, vp, i32, vp]
         L.spm_cuda_split_lines.argtypes = [vp, vp, i64, vp, vp, i64, ctypes.POINTER(i64), i32, vp]
+        L.spm_cuda_split_lines_noalloc.argtypes = [vp, vp, i64, vp, vp, i64, ctypes.POINTER(i64), vp]
         L.spm_cuda_encode_batch_pieces.argtypes = [vp, vp, vp, i64, ctypes.c_uint32, vp, vp, vp, vp, vp, i64, vp,
                                                    vp, i64, vp, i32, vp]
         L.spm_cuda_decode_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, i32, vp]
@@ -260,6 +261,25 @@ class SentencePieceProcessor:
             _check(rc)
             off = off[: n.value + 1]
             return text[: int(off[-1])], off
+
+    def split_lines_device(self, buf, text, offsets, noalloc=False, stream=None):
+        """Device-resident line splitting on torch CUDA tensors (uint8 buf, uint8 text of >= buf's
+        size, int64 offsets of capacity + 1); returns the line count.  noalloc=True takes
+        spm_cuda_split_lines_noalloc: static device scratch, no allocation, buffers <= 256 MiB."""
+        import torch
+        self._need()
+        if stream is None:
+            stream = torch.cuda.current_stream(buf.device).cuda_stream
+        n = ctypes.c_int64(0)
+        cap = offsets.numel() - 1
+        if noalloc:
+            rc = lib().spm_cuda_split_lines_noalloc(self._h, buf.data_ptr(), buf.numel(), text.data_ptr(),
+                                                    offsets.data_ptr(), cap, ctypes.byref(n), stream)
+        else:
+            rc = lib().spm_cuda_split_lines(self._h, buf.data_ptr(), buf.numel(), text.data_ptr(),
+                                            offsets.data_ptr(), cap, ctypes.byref(n), DEVICE, stream)
+        _check(rc)
+        return n.value
 
     def encode_file_buffer(self, buf):
         """spm_encode --output_format=id on a raw file buffer: (ids int32[], id_offsets int64[n+1])."""

@@ -2416,6 +2416,101 @@ int spm_cuda_split_lines(const spm_cuda_model *M, const char *buf, int64_t len, 
   return kOk;
 }
 
+// ---------------------------------------------------------------- line splitting without any allocation
+// spm_cuda_split_lines_noalloc: the same two kernels (k_nl_count, k_nl_scatter) with their scratch --
+// the newline count of every 4 KB tile, its exclusive scan, the total -- in a file-scope device
+// array instead of the handle's cudaMalloc'ed workspace, for callers that cannot allocate (code
+// under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that
+// loads the library holds the array until exit; every call shares it (calls that overlap on one
+// GPU race).  Nothing in it has to start at zero: each call overwrites the entries it reads.
+constexpr int64_t kNoAllocMaxLen = 256ll << 20;                     // largest buffer the entry point takes
+constexpr int kNoAllocMaxTiles = (int)(kNoAllocMaxLen / kNlTile);   // 65,536 tiles of 4 KB
+struct NlScratch {
+  int64_t base[kNoAllocMaxTiles + 1];   // newlines before tile k
+  int32_t count[kNoAllocMaxTiles];      // newlines inside tile k
+  int64_t result[2];                    // [0] newlines in the buffer, [1] its last byte
+};
+static __device__ __align__(256) unsigned char g_nl_scratch[sizeof(NlScratch)];   // 786,448 bytes
+
+// One block: exclusive scan of count[0..ntiles) into base[], the totals, and the end offset of an
+// unterminated last line (the scatter kernel writes offsets[k] at the k-th newline only).
+__global__ void __launch_bounds__(kScanThreads)
+k_nl_scan_static(NlScratch *sc, int64_t ntiles, const uint8_t *buf, int64_t len, int64_t *offsets, int64_t capacity) {
+  const int64_t per = (ntiles + kScanThreads - 1) / kScanThreads;
+  const int64_t a = (int64_t)threadIdx.x * per, b = a + per < ntiles ? a + per : ntiles;
+  int64_t s = 0;
+  for (int64_t k = a; k < b; ++k) s += sc->count[k];
+  int64_t tot;
+  int64_t run = block_exclusive_scan(s, &tot);
+  for (int64_t k = a; k < b; ++k) { sc->base[k] = run; run += sc->count[k]; }
+  if (threadIdx.x == 0) {
+    const uint8_t last = buf[len - 1];
+    sc->result[0] = tot;
+    sc->result[1] = last;
+    if (last != '\n' && tot + 1 <= capacity) offsets[tot + 1] = len - tot;
+  }
+}
+
+namespace {
+std::mutex g_nl_mu;
+NlScratch *g_nl_addr[64] = {};   // per device: the array's DEVICE address (the symbol itself is a host-side stand-in)
+int nl_scratch_of_current_device(NlScratch **out) {
+  int dev = -1;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { g_err = "device ordinal out of range"; return kOutOfRange; }
+  std::lock_guard<std::mutex> lk(g_nl_mu);
+  if (!g_nl_addr[dev]) {   // once per device, with that device current
+    void *p = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&p, g_nl_scratch));
+    g_nl_addr[dev] = (NlScratch *)p;
+  }
+  *out = g_nl_addr[dev];
+  return kOk;
+}
+}  // namespace
+
+int spm_cuda_split_lines_noalloc(const spm_cuda_model *M, const char *buf, int64_t len, char *text, int64_t *offsets,
+                                 int64_t capacity, int64_t *n_lines, void *cuda_stream) {
+  if (len < 0 || capacity < 0 || !offsets || !n_lines || (len > 0 && (!buf || !text))) {
+    g_err = "invalid argument";
+    return kInvalidArgument;
+  }
+  if (len > kNoAllocMaxLen) {
+    g_err = "spm_cuda_split_lines_noalloc: buffer of " + std::to_string(len) + " bytes exceeds the static scratch (" +
+            std::to_string(kNoAllocMaxLen) + " bytes at most; use spm_cuda_split_lines)";
+    return kOutOfRange;
+  }
+  int dev = -1;
+  if (M) dev = M->device; else CUDA_TRY(cudaGetDevice(&dev));
+  DEVICE_GUARD(dev);
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  if (len == 0) {
+    CUDA_TRY(cudaMemsetAsync(offsets, 0, 8, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    *n_lines = 0;
+    return kOk;
+  }
+  NlScratch *sc = nullptr;
+  int rc = nl_scratch_of_current_device(&sc);
+  if (rc) return rc;
+  const int64_t ntiles = (len + kNlTile - 1) / kNlTile;
+  k_nl_count<<<(unsigned)ntiles, kNlThreads, 0, st>>>((const uint8_t *)buf, len, sc->count);
+  k_nl_scan_static<<<1, kScanThreads, 0, st>>>(sc, ntiles, (const uint8_t *)buf, len, offsets, capacity);
+  k_nl_scatter<<<(unsigned)ntiles, kNlThreads, 0, st>>>((const uint8_t *)buf, len, sc->base, (uint8_t *)text, offsets,
+                                                        capacity);
+  CUDA_TRY(cudaGetLastError());
+  int64_t res[2] = {0, '\n'};
+  CUDA_TRY(cudaMemcpyAsync(res, sc->result, 16, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  const int64_t n = res[0] + (res[1] != '\n' ? 1 : 0);
+  *n_lines = n;
+  if (n > capacity) {
+    g_err = "offsets capacity too small: " + std::to_string(n) + " lines";
+    return kResourceExhausted;
+  }
+  return kOk;
+}
+
 // ---------------------------------------------------------------- E-step C ABI
 struct spm_cuda_estep {
   int device = 0;
