@@ -1670,6 +1670,10 @@ extern "C" {
 
 const char *spm_cuda_last_error(void) { return g_err.c_str(); }
 
+}  // extern "C"
+static int run_self_test(spm_cuda_model *M);   // spm_pieces.inc
+extern "C" {
+
 int spm_cuda_model_load(const void *serialized_model, size_t len, int device, spm_cuda_model **out) {
   if (out == nullptr) { g_err = "output container is null"; return kInternal; }
   *out = nullptr;
@@ -1709,6 +1713,9 @@ int spm_cuda_model_load(const void *serialized_model, size_t len, int device, sp
   }
   cudaEventCreate(&M->ev0);
   cudaEventCreate(&M->ev1);
+  // self-test samples carried by the model (src/sentencepiece_processor.cc:134-154)
+  rc = run_self_test(M);
+  if (rc) { spm_cuda_model_free(M); return rc; }
   *out = M;
   return kOk;
 }

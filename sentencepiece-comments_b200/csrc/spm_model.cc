@@ -86,6 +86,22 @@ bool parse_proto(const void *data, size_t len, HostModel *m) {
         else if (g.num == 47 && g.wt == 2) m->eos_piece.assign((const char *)g.s, g.n);
         else if (g.num == 48 && g.wt == 2) m->pad_piece.assign((const char *)g.s, g.n);
       }
+    } else if (f.num == 4) {  // SelfTestData { repeated Sample samples = 1 { input = 1, expected = 2 } }
+      while (q.more()) {
+        const Reader::Field g = q.next();
+        if (!q.ok) return false;
+        if (g.num != 1 || g.wt != 2) continue;
+        Reader u(g.s, g.n);
+        std::string in, ex;
+        while (u.more()) {
+          const Reader::Field h = u.next();
+          if (!u.ok) return false;
+          if (h.num == 1 && h.wt == 2) in.assign((const char *)h.s, h.n);
+          else if (h.num == 2 && h.wt == 2) ex.assign((const char *)h.s, h.n);
+        }
+        m->self_test_input.push_back(in);
+        m->self_test_expected.push_back(ex);
+      }
     } else if (f.num == 3) {  // NormalizerSpec
       while (q.more()) {
         const Reader::Field g = q.next();

@@ -32,6 +32,9 @@ struct HostModel {
   bool ws_suffix = false, add_dummy_prefix = true, remove_extra_ws = true, escape_ws = true;
   std::string charsmap;  // precompiled_charsmap blob
   std::string unk_piece = "<unk>", bos_piece = "<s>", eos_piece = "</s>", pad_piece = "<pad>";
+  // ModelProto.self_test_data: Load refuses a model whose samples do not reproduce
+  // (src/sentencepiece_processor.cc:134-154)
+  std::vector<std::string> self_test_input, self_test_expected;
   std::string unk_surface = " \xE2\x81\x87 ";  // TrainerSpec.unk_surface (sentencepiece_model.proto:184), used by Decode
   // ---- derived
   int unk_id = -1;
