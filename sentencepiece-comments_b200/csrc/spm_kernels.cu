@@ -94,6 +94,7 @@ constexpr int kFastThreads = SPM_FAST_THREADS; // fast-tier block size (one pers
 constexpr int kBpeThreads = 512;  // BPE fast-tier block size
 constexpr uint32_t ST_GEN = 1u << 16;   // sentence was encoded by the general tier (ids in gstage, forward order)
 constexpr uint32_t ST_FWD = 1u << 17;   // fast-tier ids were staged in forward order (BPE)
+constexpr uint32_t ST_PACKED = 1u << 18;  // word memo: ids forward, packed with the group's (k_memo_emit)
 
 // device-side counters of one chunk
 enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_WORK_LONG = 4, C_NLONG = 5,
@@ -1023,96 +1024,152 @@ k_memo_words_bpe(FastParams fp, MemoTable tb, const uint8_t *wtext, const int32_
   memo_store_ids(tb, idx, ids, c, st != 0 || nb == 0, fv.unk_id);
 }
 
-// k_memo_emit: one 16-lane tile per sentence, one lane per word (memo_emit() of spm_memo.cuh
-// restated with tile scans): lanes fetch the 32-byte result records of their words, a
-// prefix sum places the ids (forward order) in the staging area.  A sentence with a word
-// that is not memoised / not context-free here joins the list of the Viterbi tier.
-constexpr int kEmitTile = 16;
-__global__ void __launch_bounds__(kMemoThreads)
+// k_memo_emit: one WARP per group of 32 consecutive sentences, one lane per WORD of the group's flat word
+// list (memo_emit() of spm_memo.cuh restated with warp scans).  k_memo_scan_words lays the slots of a
+// group's words side by side, so 32 lanes fetch 32 slots with one coalesced load and gather the 32-byte
+// result records of their words; what a sentence needs in order -- the bound of the backtrace score
+// (exclusive sum of sabs), the unknown run that continues across a word boundary -- is a SEGMENTED warp
+// scan over the flat list, and the id positions are one plain prefix sum over the whole group: the ids
+// of the group's sentences land back to back ("packed") from the staging slot of its first sentence, so
+// that k_compact streams whole groups.  A sentence with a word that is not memoised / not context-free
+// here joins the list of the Viterbi tier (its ids in the packed area are never read).
+// spos[t]: where the ids of sentence t start, relative to the group's first staging slot.
+constexpr int kEmitWarps = 8;
+#ifndef SPM_EMIT_MINB          // resident CTAs per SM the register allocation aims at (A/B builds)
+#define SPM_EMIT_MINB 5
+#endif
+__global__ void __launch_bounds__(kEmitWarps * 32, SPM_EMIT_MINB)
 k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t cn, const uint32_t *wslots,
-            const uint32_t *wbase, const int32_t *nwords, int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *vit_list,
-            uint32_t *counters, int list_idx) {
-  const int lane = threadIdx.x & (kEmitTile - 1);
-  const unsigned tmask = 0xFFFFu << (threadIdx.x & 16);     // the lanes of this tile inside the warp
-  const int64_t tiles = (int64_t)gridDim.x * (kMemoThreads / kEmitTile);
-  for (int64_t t = (int64_t)blockIdx.x * (kMemoThreads / kEmitTile) + threadIdx.x / kEmitTile; t < cn; t += tiles) {
-    const int32_t nw = nwords[t];
-    if (nw == 0) {
-      if (lane == 0) status[t] = ST_FWD;
-      continue;
+            const uint32_t *wbase, const int32_t *nwords, int32_t *stage, int32_t *cnt, uint32_t *status,
+            int32_t *spos, int32_t *vit_list, uint32_t *counters, int list_idx) {
+  __shared__ int32_t s_pos[kEmitWarps][32];
+  __shared__ uint32_t s_bad[kEmitWarps];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const unsigned FULL = 0xFFFFFFFFu;
+  const int64_t groups = (cn + 31) >> 5;
+  for (int64_t g = (int64_t)blockIdx.x * kEmitWarps + wid; g < groups; g += (int64_t)gridDim.x * kEmitWarps) {
+    const int64_t tw = g << 5, t = tw + lane;
+    const bool live = t < cn;
+    const int32_t nw_raw = live ? nwords[t] : 0;
+    const int32_t nw = nw_raw > 0 ? nw_raw : 0;
+    const uint32_t wb = nw > 0 ? wbase[t] : 0u;
+    int32_t cap = 0;
+    if (live) cap = (int32_t)(off[c0 + t + 1] - off[c0 + t]) + kFastExtraChars;
+    // exclusive prefix of the word counts: flat word f of the group belongs to the last sentence s with pre[s] <= f
+    int32_t pinc = nw;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int32_t y = __shfl_up_sync(FULL, pinc, d);
+      if (lane >= d) pinc += y;
     }
-    bool bad = nw < 0;
-    int32_t total = 0;
-    if (!bad) {
-      const int64_t o0 = off[c0 + t];
-      const int32_t cap = (int32_t)(off[c0 + t + 1] - o0) + kFastExtraChars;
-      const uint32_t *sl = wslots + wbase[t];
-      int32_t *out = stage + fast_stage_base(off, c0, t);
-      float bub = 0.0f;
-      bool carry_unk = false;
-      for (int32_t w0 = 0; w0 < nw && !bad; w0 += kEmitTile) {
-        const bool active = w0 + lane < nw;
-        uint32_t meta = kMemoReady;
-        float bmax = 3.0e38f, sabs = 0.0f;
-        int4 lo4 = make_int4(0, 0, 0, 0), hi4 = make_int4(0, 0, 0, 0);
-        if (active) {
-          const int4 *r = reinterpret_cast<const int4 *>(tb.res + __ldcs(sl + w0 + lane));   // slots: streamed
-          lo4 = __ldg(r); hi4 = __ldg(r + 1);
-          meta = (uint32_t)lo4.x; bmax = __int_as_float(lo4.y); sabs = __int_as_float(lo4.z);
-        }
-        bool ok = (meta & (kMemoReady | kMemoBad)) == kMemoReady;
-        // exclusive prefix of sabs inside the tile (+ what came before)
-        float inc = sabs;
+    const int32_t pre = pinc - nw, total = __shfl_sync(FULL, pinc, 31);
+    const int64_t gbase = fast_stage_base(off, c0, tw);
+    const int32_t lim = (int32_t)min((int64_t)0x7FFFFFFF, fast_stage_base(off, c0, min(tw + 32, cn)) - gbase);
+    int32_t *out = stage + gbase;
+    if (lane == 0) s_bad[wid] = 0;
+    s_pos[wid][lane] = 0;
+    __syncwarp();
+    int32_t run_ids = 0;           // ids placed by the words before this step (uniform)
+    float carry_bub = 0.0f;        // of the sentence that continues from the step before
+    bool carry_unk = false;
+    for (int32_t f0 = 0; f0 < total; f0 += 32) {
+      const int32_t f = f0 + lane;
+      const bool active = f < total;
+      int s = 0;
 #pragma unroll
-        for (int d = 1; d < kEmitTile; d <<= 1) {
-          const float y = __shfl_up_sync(tmask, inc, d, kEmitTile);
-          if (lane >= d) inc += y;
-        }
-        if (unigram && active && !(bub + (inc - sabs) < bmax)) ok = false;
-        // an unknown run continues across a word boundary: drop the repeated id
-        const bool last_unk = (meta & kMemoLastUnk) != 0;
-        bool prev_unk = __shfl_up_sync(tmask, last_unk, 1, kEmitTile);
-        if (lane == 0) prev_unk = carry_unk;
-        const int k = active ? (int)(meta & 0xFFu) : 0;
-        const int drop = (active && prev_unk && (meta & kMemoFirstUnk)) ? 1 : 0;
-        int pos = k - drop;
-#pragma unroll
-        for (int d = 1; d < kEmitTile; d <<= 1) {
-          const int y = __shfl_up_sync(tmask, pos, d, kEmitTile);
-          if (lane >= d) pos += y;
-        }
-        const int tile_ids = __shfl_sync(tmask, pos, kEmitTile - 1, kEmitTile);
-        pos += total - (k - drop);                       // exclusive, sentence-wide
-        if (total + tile_ids > cap) ok = false;
-        if (__any_sync(tmask, !ok)) { bad = true; break; }
-        if (k > 0) {
-          const int32_t v[kMemoInlineIds] = {lo4.w, hi4.x, hi4.y, hi4.z, hi4.w};
-          if (k <= kMemoInlineIds) {
-#pragma unroll
-            for (int j = 0; j < kMemoInlineIds; ++j)
-              if (j >= drop && j < k) __stcs(out + pos + j - drop, v[j]);
-          } else {
-            const int32_t *ov = tb.overflow + (size_t)v[kMemoInlineIds - 1] * kMemoOverflowIds;
-#pragma unroll
-            for (int j = 0; j < kMemoInlineIds - 1; ++j)
-              if (j >= drop) __stcs(out + pos + j - drop, v[j]);
-            for (int j = kMemoInlineIds - 1; j < k; ++j) __stcs(out + pos + j - drop, ov[j - (kMemoInlineIds - 1)]);
-          }
-        }
-        total += tile_ids;
-        bub += __shfl_sync(tmask, inc, kEmitTile - 1, kEmitTile);
-        const int last_active = min(nw - w0, kEmitTile) - 1;
-        carry_unk = __shfl_sync(tmask, last_unk, last_active, kEmitTile);
+      for (int step = 16; step; step >>= 1) {
+        const int32_t v = __shfl_sync(FULL, pre, (s + step) & 31);
+        if (s + step < 32 && v <= f) s += step;
       }
-    }
-    if (lane == 0) {
-      if (bad) {
-        vit_list[atomicAdd(&counters[list_idx], 1u)] = (int32_t)t;
-      } else {
-        cnt[t] = total;
-        status[t] = ST_FWD;
+      const int32_t my_pre = __shfl_sync(FULL, pre, s);
+      const uint32_t my_wb = __shfl_sync(FULL, wb, s);
+      const bool head = active && f == my_pre;
+      uint32_t meta = kMemoReady;
+      float bmax = 3.0e38f, sabs = 0.0f;
+      int4 lo4 = make_int4(0, 0, 0, 0), hi4 = make_int4(0, 0, 0, 0);
+      if (active) {
+        const int4 *r = reinterpret_cast<const int4 *>(tb.res + __ldcs(wslots + my_wb + (uint32_t)(f - my_pre)));   // slots: streamed
+        lo4 = __ldg(r); hi4 = __ldg(r + 1);
+        meta = (uint32_t)lo4.x; bmax = __int_as_float(lo4.y); sabs = __int_as_float(lo4.z);
       }
+      bool ok = (meta & (kMemoReady | kMemoBad)) == kMemoReady;
+      // inclusive scan of sabs inside my sentence: lanes from the head of my sentence (or lane 0 when
+      // it began in an earlier step) up to me
+      const uint32_t heads = __ballot_sync(FULL, head);
+      const uint32_t below = heads & (0xFFFFFFFFu >> (31 - lane));
+      const int seg0 = below ? 31 - __clz(below) : 0;
+      const bool continued = below == 0;                    // my sentence began before this step
+      float inc = sabs;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const float y = __shfl_up_sync(FULL, inc, d);
+        if (lane - d >= seg0) inc += y;
+      }
+      if (continued) inc += carry_bub;
+      if (unigram && active && !(inc - sabs < bmax)) ok = false;
+      // an unknown run continues across a word boundary: drop the repeated id
+      const bool last_unk = active && (meta & kMemoLastUnk) != 0;
+      bool prev_unk = __shfl_up_sync(FULL, last_unk, 1);
+      if (lane == 0) prev_unk = carry_unk;
+      if (head) prev_unk = false;
+      const int k = active ? (int)(meta & 0xFFu) : 0;
+      const int drop = (active && prev_unk && (meta & kMemoFirstUnk)) ? 1 : 0;
+      int pos = k - drop;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int y = __shfl_up_sync(FULL, pos, d);
+        if (lane >= d) pos += y;
+      }
+      const int step_ids = __shfl_sync(FULL, pos, 31);
+      pos += run_ids - (k - drop);                           // exclusive, group-wide
+      if (head) s_pos[wid][s] = pos;
+      if (!ok) atomicOr(&s_bad[wid], 1u << s);
+      if (k > 0 && pos + k - drop <= lim) {
+        const int32_t v[kMemoInlineIds] = {lo4.w, hi4.x, hi4.y, hi4.z, hi4.w};
+        if (k <= kMemoInlineIds) {
+#pragma unroll
+          for (int j = 0; j < kMemoInlineIds; ++j)
+            if (j >= drop && j < k) __stcs(out + pos + j - drop, v[j]);
+        } else {
+          const int32_t *ov = tb.overflow + (size_t)v[kMemoInlineIds - 1] * kMemoOverflowIds;
+#pragma unroll
+          for (int j = 0; j < kMemoInlineIds - 1; ++j)
+            if (j >= drop) __stcs(out + pos + j - drop, v[j]);
+          for (int j = kMemoInlineIds - 1; j < k; ++j) __stcs(out + pos + j - drop, ov[j - (kMemoInlineIds - 1)]);
+        }
+      }
+      run_ids += step_ids;
+      carry_bub = __shfl_sync(FULL, inc, 31);
+      carry_unk = __shfl_sync(FULL, last_unk, 31);
     }
+    __syncwarp();
+    // per sentence: its ids are [my_pos, start of the next sentence with words) of the packed area
+    const uint32_t badmask = s_bad[wid];
+    const int32_t my_pos = nw > 0 ? s_pos[wid][lane] : 0;
+    int32_t nxt = nw > 0 ? my_pos : 0x7FFFFFFF;            // inclusive suffix minimum
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int32_t y = __shfl_down_sync(FULL, nxt, d);
+      if (lane + d < 32) nxt = min(nxt, y);
+    }
+    int32_t end = __shfl_down_sync(FULL, nxt, 1);
+    if (lane == 31) end = 0x7FFFFFFF;
+    end = min(end, run_ids);
+    const int32_t count = nw > 0 ? end - my_pos : 0;
+    const bool bad = live && (nw_raw < 0 || ((badmask >> lane) & 1u) || count > cap || my_pos + count > lim);
+    if (live && !bad) {
+      cnt[t] = count;
+      status[t] = ST_FWD | ST_PACKED;
+      spos[t] = my_pos;
+    }
+    const uint32_t bm = __ballot_sync(FULL, bad);
+    if (bm) {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(&counters[list_idx], (uint32_t)__popc(bm));
+      base = __shfl_sync(FULL, base, 0);
+      if (bad) vit_list[base + __popc(bm & ((1u << lane) - 1u))] = (int32_t)t;
+    }
+    __syncwarp();
   }
 }
 
@@ -1199,34 +1256,68 @@ k_scan_final(const int32_t *in, int64_t n, Op op, const int64_t *partial, const 
   if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = *carry;
 }
 
-// Final layout (extra options) into the CSR values.  Each lane reads the header of one
-// sentence (coalesced), then the warp copies the 32 sentences one after another.
-// Fast-tier sentences were staged in reverse order, general-tier ones forward.
+// Final layout (extra options) into the CSR values, one warp per group of 32 sentences.  Each lane
+// reads the header of one sentence (coalesced).  A group the word memo served as a whole lies
+// packed in `stage` from the group's first slot, in CSR order: one streaming copy.  Otherwise
+// the warp copies the 32 sentences one after another: memo-served ones from the packed area
+// (forward), Viterbi / merge tier ones from their own slot in `vstage` (unigram: reversed),
+// general-tier ones from `gstage` (forward).
 __global__ void __launch_bounds__(256)
 k_compact(const __grid_constant__ ExtraPlan plan, const int64_t *off, int64_t c0, int64_t cn, const int32_t *stage,
-          const int32_t *gstage, const int64_t *srcoff, const uint32_t *status, const int32_t *cnt,
-          const int64_t *id_off, int32_t *ids, int64_t capacity) {
+          const int32_t *vstage, const int32_t *gstage, const int64_t *srcoff, const uint32_t *status,
+          const int32_t *cnt, const int32_t *spos, const int64_t *id_off, int32_t *ids, int64_t capacity) {
   const int lane = threadIdx.x & 31;
+  const unsigned FULL = 0xFFFFFFFFu;
   const int64_t t0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32;
   if (t0 >= cn) return;
   const int64_t t = t0 + lane;
   int32_t my_core = -1;
   int64_t my_src = 0, my_dst = 0;
-  int my_gen = 0;
+  int my_gen = 0;      // 0: tier 2, reversed; 1: general tier; 2: tier 2, forward; 3: word memo, packed
+  bool packed = true;
+  const int64_t gbase = fast_stage_base(off, c0, t0);
   if (t < cn) {
+    const uint32_t st = status[t];
     my_core = cnt[t];
-    my_gen = (status[t] & ST_GEN) != 0 ? 1 : ((status[t] & ST_FWD) ? 2 : 0);   // 2: fast tier, forward
-    my_src = my_gen == 1 ? srcoff[t] : fast_stage_base(off, c0, t);
+    packed = (st & ST_PACKED) != 0;
+    my_gen = (st & ST_GEN) != 0 ? 1 : (packed ? 3 : ((st & ST_FWD) ? 2 : 0));
+    my_src = my_gen == 1 ? srcoff[t] : (packed ? gbase + spos[t] : fast_stage_base(off, c0, t));
     my_dst = id_off[c0 + t];
   }
   const bool simple = plan.npre == 0 && plan.nsuf == 0;
   const int m = (int)min((int64_t)32, cn - t0);
+  if (simple && plan.flip == 0 && __all_sync(FULL, packed)) {
+    // the whole group: ids [gbase, gbase + total) -> [id_off[t0], id_off[t0 + m])
+    const int64_t dst = __shfl_sync(FULL, my_dst, 0);
+    const int64_t total = id_off[c0 + t0 + m] - dst;
+    const int32_t *src = stage + gbase;
+    if (dst + total <= capacity) {
+      // 16-byte stores: peel to the alignment of the destination, then every lane moves 4 ids per
+      // step (four independent loads in flight; the source is aligned to 4 bytes only)
+      const int64_t head = min(total, (int64_t)((4 - (((uintptr_t)(ids + dst) >> 2) & 3)) & 3));
+      if (lane < head) __stcs(ids + dst + lane, __ldcs(src + lane));
+      const int64_t body = (total - head) >> 2;
+      const int32_t *s4 = src + head;
+      int4 *d4 = reinterpret_cast<int4 *>(ids + dst + head);
+      for (int64_t q = lane; q < body; q += 32) {
+        int4 v;
+        v.x = __ldcs(s4 + 4 * q); v.y = __ldcs(s4 + 4 * q + 1); v.z = __ldcs(s4 + 4 * q + 2); v.w = __ldcs(s4 + 4 * q + 3);
+        __stcs(d4 + q, v);
+      }
+      const int64_t done = head + 4 * body;
+      if (done + lane < total) __stcs(ids + dst + done + lane, __ldcs(src + done + lane));
+    } else {
+      for (int64_t q = lane; q < total; q += 32)
+        if (dst + q < capacity) ids[dst + q] = src[q];
+    }
+    return;
+  }
   for (int j = 0; j < m; ++j) {
-    const int32_t core = __shfl_sync(0xFFFFFFFFu, my_core, j);
-    const int gen = __shfl_sync(0xFFFFFFFFu, my_gen, j);
-    const int64_t so = __shfl_sync(0xFFFFFFFFu, my_src, j);
-    const int64_t dst = __shfl_sync(0xFFFFFFFFu, my_dst, j);
-    const int32_t *src = (gen == 1 ? gstage : stage) + so;
+    const int32_t core = __shfl_sync(FULL, my_core, j);
+    const int gen = __shfl_sync(FULL, my_gen, j);
+    const int64_t so = __shfl_sync(FULL, my_src, j);
+    const int64_t dst = __shfl_sync(FULL, my_dst, j);
+    const int32_t *src = (gen == 1 ? gstage : (gen == 3 ? stage : vstage)) + so;
     if (simple) {
       const bool rev = (plan.flip != 0) == (gen != 0);   // unigram fast-tier staging is already reversed
       for (int32_t q = lane; q < core; q += 32)
@@ -1379,7 +1470,7 @@ struct spm_cuda_model {
   DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2, d_cont2, d_funits, d_fscore, d_fleaf;
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
-  mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
+  mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_vstage, w_spos, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
       w_perm, w_genlist, w_longlist, w_wslots, w_wbase, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status, g_rbase, g_rscratch;
   mutable DevBuf px[20];   // workspace of the pieces / decode / dense calls (spm_pieces.inc)
@@ -1410,7 +1501,7 @@ struct spm_cuda_model {
     spm_cuda_model *m = const_cast<spm_cuda_model *>(this);
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2, &m->d_cont2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
-            &m->w_stage, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
+            &m->w_stage, &m->w_vstage, &m->w_spos, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
             &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_wbase, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status, &m->g_rbase, &m->g_rscratch,
@@ -2089,9 +2180,15 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     if ((rc = M->w_status.ensure(cn * 4))) return rc;
     if ((rc = M->w_srcoff.ensure(cn * 8))) return rc;
     CUDA_TRY(cudaMemsetAsync(d_counters, 0, C_COUNT * 4, st));
+    int32_t *d_vstage = nullptr;
     if (M->fast) {
       if ((rc = M->w_norm.ensure((size_t)(3 * raw + 160 * cn + 256)))) return rc;
       if ((rc = M->w_stage.ensure((size_t)(raw + kFastExtraChars * cn + 64) * 4))) return rc;
+      // with the word memo in front, `stage` holds the packed ids of whole groups (k_memo_emit); the
+      // sentences it leaves to the Viterbi / merge kernels stage into their own slots of a second buffer
+      if (memo && (rc = M->w_vstage.ensure((size_t)(raw + kFastExtraChars * cn + 64) * 4))) return rc;
+      if (memo && (rc = M->w_spos.ensure(cn * 4))) return rc;
+      d_vstage = (int32_t *)(memo ? M->w_vstage.p : M->w_stage.p);
       if ((rc = M->w_nlen.ensure(cn * 4))) return rc;
       if ((rc = M->w_perm.ensure(cn * 4))) return rc;
       if ((rc = M->w_genlist.ensure(cn * 4))) return rc;
@@ -2169,16 +2266,17 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         // alone at a third of the machine
         if (M->emit_blocks == 0) {
           int occ = 0;
-          CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_memo_emit, kMemoThreads, 0));
+          CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_memo_emit, kEmitWarps * 32, 0));
           M->emit_blocks = std::max(1, occ);
         }
         const int64_t emit_per_sm = M->opt.emit_blocks > 0 ? M->opt.emit_blocks : M->emit_blocks;
-        const unsigned gemit = (unsigned)std::min<int64_t>((cn + 15) / 16, emit_per_sm * (int64_t)M->sm_count);
-        k_memo_emit<<<gemit, kMemoThreads, 0, st>>>(
+        const unsigned gemit = (unsigned)std::min<int64_t>((cn + 32 * kEmitWarps - 1) / (32 * kEmitWarps),
+                                                           emit_per_sm * (int64_t)M->sm_count);
+        k_memo_emit<<<gemit, kEmitWarps * 32, 0, st>>>(
             tb, M->fast_kind == 1, d_off, c0, cn, (const uint32_t *)M->w_wslots.p, (const uint32_t *)M->w_wbase.p,
             (const int32_t *)M->w_nwords.p,
-            (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
-            d_counters, C_NVIT);
+            (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_spos.p,
+            (int32_t *)M->w_vit.p, d_counters, C_NVIT);
         if ((rc = kev_record(M, st, 1))) return rc;
         launches += 2;
         todo = (const int32_t *)M->w_vit.p;
@@ -2210,7 +2308,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         // when k_encode_warp follows: it keeps kWarpCapc candidates per position itself
         k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
-            kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
+            kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows, d_vstage, (int32_t *)M->w_cnt.p,
             (uint32_t *)M->w_status.p, (int32_t *)(warp_ok ? M->w_longlist.p : M->w_genlist.p),
             warp_ok ? C_NLONG : C_NGEN, d_counters, warp_ok ? warp_route : 0u);
         if (warp_ok) {
@@ -2225,25 +2323,25 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
                                           (int32_t *)M->w_vitl.p, d_counters);
           k_encode_warp<<<(unsigned)wblocks, kWarpWarps * 32, 0, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-              (const int32_t *)M->w_vitl.p, cnt_b, work_b, (uint32_t *)M->w_wback.p, wstride, (int32_t *)M->w_stage.p,
+              (const int32_t *)M->w_vitl.p, cnt_b, work_b, (uint32_t *)M->w_wback.p, wstride, d_vstage,
               (int32_t *)M->w_cnt.p, (int32_t *)M->w_genlist.p, d_counters);
           launches += 2;
         } else if (has_long) {
           k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
-              long_warps, (uint32_t *)M->w_back.p, back_rows_long, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p,
+              long_warps, (uint32_t *)M->w_back.p, back_rows_long, d_vstage, (int32_t *)M->w_cnt.p,
               (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, C_NGEN, d_counters, 0u);
           launches += 1;
         }
       } else {
         k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
-            kBpeThreads / 32, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
+            kBpeThreads / 32, d_vstage, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
             (int32_t *)M->w_genlist.p, d_counters);
         if (has_long)
           k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
-              long_warps, (int32_t *)M->w_stage.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
+              long_warps, d_vstage, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
               (int32_t *)M->w_genlist.p, d_counters);
         launches += has_long ? 1 : 0;
       }
@@ -2284,10 +2382,10 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     fop.extra = plan.npre + plan.nsuf;
     if ((rc = run_scan(M, st, (const int32_t *)M->w_cnt.p, cn, fop, d_idoff + c0, d_carry, 1, &launches))) return rc;
     const unsigned cgrid = (unsigned)((cn + 255) / 256);  // 8 warps x 32 sentences per block
-    k_compact<<<cgrid, 256, 0, st>>>(plan, d_off, c0, cn, (const int32_t *)M->w_stage.p,
+    k_compact<<<cgrid, 256, 0, st>>>(plan, d_off, c0, cn, (const int32_t *)M->w_stage.p, d_vstage,
                                      (const int32_t *)M->g_stage.p, (const int64_t *)M->w_srcoff.p,
-                                     (const uint32_t *)M->w_status.p, (const int32_t *)M->w_cnt.p, d_idoff, d_ids,
-                                     d_cap);
+                                     (const uint32_t *)M->w_status.p, (const int32_t *)M->w_cnt.p,
+                                     (const int32_t *)M->w_spos.p, d_idoff, d_ids, d_cap);
     if ((rc = kev_record(M, st, 1))) return rc;
     launches += 1;
     CUDA_TRY(cudaGetLastError());
