@@ -65,6 +65,7 @@ int spm_cuda_model_set_piece_types(spm_cuda_model *model, const uint8_t *types, 
  *   "scan_per_sentence" 0   thread-per-sentence word scan instead of the byte-parallel one
  *   "emit_blocks"       0   CTAs of the memo emit kernel per SM (0: occupancy query)
  *   "pieces_exact"      0   encode_batch_pieces: every sentence through the exact tier
+ *   "bpe_route"         8192  BPE: leftover lists up to this size go to the general tier as a whole (0: never)
  * NOT_FOUND for an unknown name.  Must not run concurrently with calls on the same model. */
 int spm_cuda_model_set_option(spm_cuda_model *model, const char *name, int64_t value);
 int spm_cuda_model_get_option(const spm_cuda_model *model, const char *name, int64_t *value);

@@ -644,8 +644,18 @@ k_encode_warp(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
 __global__ void __launch_bounds__(kBpeThreads, 1)
 k_encode_bpe_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
                   const int32_t *perm, int count_idx, int work_idx, int max_warps, int32_t *stage, int32_t *cnt,
-                  uint32_t *status, int32_t *gen_list, uint32_t *counters) {
+                  uint32_t *status, int32_t *gen_list, uint32_t *counters, uint32_t gen_route) {
   extern __shared__ __align__(16) uint32_t smem[];
+  // A short list (what the word memo leaves over: a few hundred sentences with words it cannot key) is
+  // pure latency here -- one thread merges a whole sentence word by word, 1.7 ms whatever the count --
+  // so it goes to the general tier as a whole: one block per sentence, agenda in shared memory.
+  if (gen_route != 0 && counters[count_idx] <= gen_route) {
+    const uint32_t nf = counters[count_idx];
+    for (uint32_t i = blockIdx.x * kBpeThreads + threadIdx.x; i < nf; i += gridDim.x * kBpeThreads)
+      gen_list[atomicAdd(&counters[C_NGEN], 1u)] = perm[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&counters[C_NRETRY], nf);
+    return;
+  }
   uint32_t *units_hot = smem;
   float *score_hot = (float *)(smem + fp.k_units);
   uint32_t *scr = smem + fp.k_units + fp.k_scores;
@@ -942,6 +952,54 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
   nwords[t] = nw;
   cnt[t] = 0;
   status[t] = 0;
+}
+
+// The sentences listed for the general scan, in order of descending raw length (bins of 8 bytes): the 32
+// threads of a warp of k_memo_scan then walk sentences of one length instead of running at the pace
+// of the longest of 32 random ones.  Counting sort: block-private histograms, one block scans the bins.
+constexpr int kLsBins = 512, kLsThreads = 256;
+__device__ __forceinline__ int ls_bin(const int64_t *off, int64_t c0, int32_t t) {
+  const int64_t len = off[c0 + t + 1] - off[c0 + t];
+  const int b = (int)(len >> 3);
+  return kLsBins - 1 - (b < kLsBins ? b : kLsBins - 1);      // bin 0 = longest
+}
+__global__ void __launch_bounds__(kLsThreads)
+k_ls_hist(const int64_t *off, int64_t c0, const int32_t *list, const uint32_t *counters, int count_idx, uint32_t *hist) {
+  __shared__ uint32_t sh[kLsBins];
+  for (int k = threadIdx.x; k < kLsBins; k += kLsThreads) sh[k] = 0;
+  __syncthreads();
+  const uint32_t n = counters[count_idx];
+  for (uint32_t i = blockIdx.x * kLsThreads + threadIdx.x; i < n; i += gridDim.x * kLsThreads)
+    atomicAdd(&sh[ls_bin(off, c0, list[i])], 1u);
+  __syncthreads();
+  for (int k = threadIdx.x; k < kLsBins; k += kLsThreads)
+    if (sh[k]) atomicAdd(&hist[k], sh[k]);
+}
+__global__ void __launch_bounds__(kLsBins) k_ls_scan(uint32_t *hist, uint32_t *cursor) {
+  __shared__ uint32_t wsum[kLsBins / 32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const uint32_t v = hist[tid];
+  uint32_t inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+    if (lane >= d) inc += y;
+  }
+  if (lane == 31) wsum[wid] = inc;
+  __syncthreads();
+  uint32_t base = 0;
+  for (int k = 0; k < wid; ++k) base += wsum[k];
+  cursor[tid] = base + inc - v;
+  hist[tid] = 0;                      // ready for the next chunk
+}
+__global__ void __launch_bounds__(kLsThreads)
+k_ls_scatter(const int64_t *off, int64_t c0, const int32_t *list, const uint32_t *counters, int count_idx,
+             uint32_t *cursor, int32_t *sorted) {
+  const uint32_t n = counters[count_idx];
+  for (uint32_t i = blockIdx.x * kLsThreads + threadIdx.x; i < n; i += gridDim.x * kLsThreads) {
+    const int32_t t = list[i];
+    sorted[atomicAdd(&cursor[ls_bin(off, c0, t)], 1u)] = t;
+  }
 }
 
 // k_memo_scan: the general scan (fast_normalize_scan + MemoSink: every normalizer rule,
@@ -1455,6 +1513,7 @@ struct Options {
   int64_t warp_route = 262144;    // leftover lists up to this size go to k_encode_warp as a whole (0: never)
   int64_t emit_blocks = 0;        // CTAs of k_memo_emit per SM (0: occupancy query)
   int64_t pieces_exact = 0;       // pieces path: every sentence through the exact tier
+  int64_t bpe_route = 8192;       // BPE leftover lists up to this size go to the general tier as a whole (0: never)
 };
 
 struct spm_cuda_model {
@@ -1470,7 +1529,8 @@ struct spm_cuda_model {
   DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2, d_cont2, d_funits, d_fscore, d_fleaf;
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
-  mutable DevBuf w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_vstage, w_spos, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
+  mutable bool lshist_zeroed = false;
+  mutable DevBuf w_lshist, w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_vstage, w_spos, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
       w_perm, w_genlist, w_longlist, w_wslots, w_wbase, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status, g_rbase, g_rscratch;
   mutable DevBuf px[20];   // workspace of the pieces / decode / dense calls (spm_pieces.inc)
@@ -1501,7 +1561,7 @@ struct spm_cuda_model {
     spm_cuda_model *m = const_cast<spm_cuda_model *>(this);
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2, &m->d_cont2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
-            &m->w_stage, &m->w_vstage, &m->w_spos, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
+            &m->w_stage, &m->w_vstage, &m->w_spos, &m->w_lshist, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
             &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_wbase, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status, &m->g_rbase, &m->g_rscratch,
@@ -1852,7 +1912,7 @@ static int64_t *option_slot(Options *o, const char *name) {
       {"memo", &o->memo}, {"memo_bits", &o->memo_bits}, {"host_chunks", &o->host_chunks},
       {"host_chunk_min", &o->host_chunk_min}, {"max_chunk", &o->max_chunk}, {"warp", &o->warp},
       {"scan_per_sentence", &o->scan_per_sentence}, {"warp_route", &o->warp_route},
-      {"emit_blocks", &o->emit_blocks}, {"pieces_exact", &o->pieces_exact}};
+      {"emit_blocks", &o->emit_blocks}, {"pieces_exact", &o->pieces_exact}, {"bpe_route", &o->bpe_route}};
   for (const auto &e : table)
     if (strcmp(e.name, name) == 0) return e.p;
   return nullptr;
@@ -1885,6 +1945,7 @@ int spm_cuda_model_release_workspace(spm_cuda_model *M) {
   DEVICE_GUARD(M->device);
   CUDA_TRY(cudaDeviceSynchronize());
   for (DevBuf *b : M->workspace_bufs()) b->release();
+  M->lshist_zeroed = false;
   M->pt_ready = false;
   M->dec_ready = false;
   return kOk;
@@ -2244,8 +2305,18 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
               M->mv, tb, d_text, d_off, c0, cn, d_text + text_lo, d_text + text_hi, (uint32_t *)M->w_wslots.p,
               (uint32_t *)M->w_wbase.p, wslot_half, (int32_t *)M->w_nwords.p, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_vit.p,
               d_counters);
+        // the listed sentences by descending length (w_perm is free until the leftover tier sorts into it)
+        if ((rc = M->w_lshist.ensure(2 * kLsBins * 4))) return rc;
+        if (!M->lshist_zeroed) { CUDA_TRY(cudaMemsetAsync(M->w_lshist.p, 0, 2 * kLsBins * 4, st)); M->lshist_zeroed = true; }
+        const unsigned gls = (unsigned)std::min<int64_t>((cn + kLsThreads - 1) / kLsThreads, 2 * (int64_t)M->sm_count);
+        k_ls_hist<<<gls, kLsThreads, 0, st>>>(d_off, c0, (const int32_t *)M->w_vit.p, d_counters, C_NSLOW,
+                                             (uint32_t *)M->w_lshist.p);
+        k_ls_scan<<<1, kLsBins, 0, st>>>((uint32_t *)M->w_lshist.p, (uint32_t *)M->w_lshist.p + kLsBins);
+        k_ls_scatter<<<gls, kLsThreads, 0, st>>>(d_off, c0, (const int32_t *)M->w_vit.p, d_counters, C_NSLOW,
+                                                (uint32_t *)M->w_lshist.p + kLsBins, (int32_t *)M->w_perm.p);
+        launches += 3;
         k_memo_scan<<<gsent, kMemoThreads, 0, st>>>(
-            M->mv, tb, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_vit.p,
+            M->mv, tb, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p,
             (uint32_t *)M->w_wslots.p + wslot_half, (int32_t *)M->w_nwords.p, d_counters);
         launches += 1;
         if ((rc = kev_record(M, st, 1))) return rc;
@@ -2337,12 +2408,13 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
             kBpeThreads / 32, d_vstage, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
-            (int32_t *)M->w_genlist.p, d_counters);
+            (int32_t *)M->w_genlist.p, d_counters,
+            (uint32_t)std::max<int64_t>(0, std::min<int64_t>(M->opt.bpe_route, 0x7FFFFFFF)));
         if (has_long)
           k_encode_bpe_fast<<<M->sm_count, kBpeThreads, M->fast_smem, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
               long_warps, d_vstage, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p,
-              (int32_t *)M->w_genlist.p, d_counters);
+              (int32_t *)M->w_genlist.p, d_counters, 0u);
         launches += has_long ? 1 : 0;
       }
       if ((rc = kev_record(M, st, 1))) return rc;
