@@ -1146,7 +1146,8 @@ k_memo_emit(MemoTable tb, int unigram, const int64_t *off, int64_t c0, int64_t c
       float bmax = 3.0e38f, sabs = 0.0f;
       int4 lo4 = make_int4(0, 0, 0, 0), hi4 = make_int4(0, 0, 0, 0);
       if (active) {
-        const int4 *r = reinterpret_cast<const int4 *>(tb.res + __ldcs(wslots + my_wb + (uint32_t)(f - my_pre)));   // slots: streamed
+        const uint32_t slot = __ldcs(wslots + my_wb + (uint32_t)(f - my_pre));   // slots: streamed
+        const int4 *r = reinterpret_cast<const int4 *>(tb.res + slot);
         lo4 = __ldg(r); hi4 = __ldg(r + 1);
         meta = (uint32_t)lo4.x; bmax = __int_as_float(lo4.y); sabs = __int_as_float(lo4.z);
       }
@@ -1435,37 +1436,85 @@ k_nl_scatter(const uint8_t *buf, int64_t len, const int64_t *tile_base, uint8_t 
 }
 
 // ---------------------------------------------------------------- unigram trainer E-step (spm_estep.cuh)
-// One thread per word.  Words of up to kEstepLocalBytes bytes keep their forward /
-// backward tables in local memory; longer ones (text without spaces) use a slice of a
-// global scratch buffer.  expected[] is accumulated in double with atomicAdd; the
-// log-likelihood and the token count are reduced per warp first.
-constexpr int kEstepLocalBytes = 47, kEstepThreads = 128;
+// One thread per word, words taken in order of descending length (counting sort, so the 32 words
+// of a warp run equally long).  Words of up to kEstepSmemBytes bytes keep their forward / backward
+// / Viterbi tables in shared memory ([position][thread]: no local-memory traffic); longer ones
+// (text without spaces) use a slice of a global scratch buffer.  expected[] is accumulated in
+// double: pieces with a hot slot (the kEstepHot - 1 highest scores, which collect most of the mass)
+// in a per-CTA shared table flushed once at the end, the rest with one global atomicAdd per node;
+// the log-likelihood and the token count are reduced per warp first.
+constexpr int kEstepSmemBytes = 31, kEstepThreads = 128, kEstepBins = 64;
+constexpr int kEstepSmem = kEstepHot * 8 + (kEstepSmemBytes + 1) * kEstepThreads * 13;   // 69,632 bytes
+__global__ void __launch_bounds__(256)
+k_estep_hist(const int64_t *off, int64_t n, uint32_t *hist) {
+  __shared__ uint32_t sh[kEstepBins];
+  if (threadIdx.x < kEstepBins) sh[threadIdx.x] = 0;
+  __syncthreads();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t len = off[i + 1] - off[i];
+    atomicAdd(&sh[kEstepBins - 1 - (int)min(len < 0 ? (int64_t)0 : len, (int64_t)(kEstepBins - 1))], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < kEstepBins && sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], sh[threadIdx.x]);
+}
+__global__ void k_estep_binscan(uint32_t *hist, uint32_t *cursor) {   // one warp, 2 bins per lane
+  const int lane = threadIdx.x;
+  const uint32_t a = hist[2 * lane], b = hist[2 * lane + 1];
+  uint32_t inc = a + b;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+    if (lane >= d) inc += y;
+  }
+  cursor[2 * lane] = inc - a - b;
+  cursor[2 * lane + 1] = inc - b;
+}
+__global__ void __launch_bounds__(256)
+k_estep_scatter(const int64_t *off, int64_t n, uint32_t *cursor, uint32_t *perm) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t len = off[i + 1] - off[i];
+    const int bin = kEstepBins - 1 - (int)min(len < 0 ? (int64_t)0 : len, (int64_t)(kEstepBins - 1));
+    perm[atomicAdd(&cursor[bin], 1u)] = (uint32_t)i;
+  }
+}
+
 __global__ void __launch_bounds__(kEstepThreads)
-k_estep(EstepView ev, const uint8_t *words, const int64_t *off, const int64_t *freq, int64_t n, double inv_all_freq,
-        float *scratch, double *expected, double *obj_ntok, float *logz, uint32_t *bad) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+k_estep(EstepView ev, const int32_t *hot_ids, const uint8_t *words, const int64_t *off, const int64_t *freq, int64_t n,
+        const uint32_t *perm, double inv_all_freq, float *scratch, double *expected, double *obj_ntok, float *logz) {
+  extern __shared__ __align__(16) uint8_t estep_smem[];     // kEstepSmem bytes: hot table | A | B | V | C
+  constexpr int kTab = (kEstepSmemBytes + 1) * kEstepThreads;
+  double *s_hot = reinterpret_cast<double *>(estep_smem);
+  float *sA = reinterpret_cast<float *>(s_hot + kEstepHot), *sB = sA + kTab, *sV = sB + kTab;
+  uint8_t *sC = reinterpret_cast<uint8_t *>(sV + kTab);
+  for (int k = threadIdx.x; k < kEstepHot; k += kEstepThreads) s_hot[k] = 0.0;
+  __syncthreads();
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   double obj = 0.0, ntok = 0.0;
-  if (i < n) {
+  if (idx < n) {
+    const int64_t i = perm[idx];
     const int64_t o = off[i], len = off[i + 1] - o;
     float z = 0.0f;
     int32_t nt = 0;
     if (len > 0 && len < (1 << 20)) {
       const float f = (float)freq[i];       // PopulateMarginal takes float freq (src/unigram_model.cc:272)
-      auto add = [&](int32_t id, double v) { atomicAdd(&expected[id], v); };
-      if (len <= kEstepLocalBytes) {
-        float A[kEstepLocalBytes + 1], B[kEstepLocalBytes + 1], V[kEstepLocalBytes + 1];
-        int32_t C[kEstepLocalBytes + 1];
-        z = estep_word(ev, words + o, (int)len, f, A, B, V, C, add, &nt);
+      auto add = [&](uint32_t x, double v) {
+        const uint32_t slot = ev.id_mask == 0xFFFFFu ? x >> 20 : 0u;
+        if (slot) atomicAdd(&s_hot[slot], v);
+        else atomicAdd(&expected[x & ev.id_mask], v);
+      };
+      if (len <= kEstepSmemBytes) {
+        z = estep_word(ev, words + o, (int)len, f, sA + threadIdx.x, sB + threadIdx.x, sV + threadIdx.x,
+                       sC + threadIdx.x, kEstepThreads, add, &nt);
       } else {
         float *base = scratch + 4 * ((o - off[0]) + i);
         z = estep_word(ev, words + o, (int)len, f, base, base + (len + 1), base + 2 * (len + 1),
-                       (int32_t *)(base + 3 * (len + 1)), add, &nt);
+                       (int32_t *)(base + 3 * (len + 1)), 1, add, &nt);
       }
       // objs[n] -= Z / all_sentence_freq with Z = freq * log-likelihood (:262-266)
       obj = -(double)(f * z) * inv_all_freq;
       ntok = (double)nt;
     } else if (len != 0) {
-      atomicOr(bad, 1u);
+      obj = __longlong_as_double(0x7FF8000000000000ll);   // a word of 1 MiB or more: the objective comes back NaN
     }
     if (logz) logz[i] = z;
   }
@@ -1477,6 +1526,11 @@ k_estep(EstepView ev, const uint8_t *words, const int64_t *off, const int64_t *f
   if ((threadIdx.x & 31) == 0) {
     atomicAdd(&obj_ntok[0], obj);
     atomicAdd(&obj_ntok[1], ntok);
+  }
+  __syncthreads();
+  for (int k = threadIdx.x + 1; k < kEstepHot; k += kEstepThreads) {
+    const double v = s_hot[k];
+    if (v != 0.0) atomicAdd(&expected[hot_ids[k]], v);
   }
 }
 
@@ -2693,9 +2747,9 @@ struct spm_cuda_estep {
   int device = 0;
   int V = 0;
   EstepView ev;
-  DevBuf d_units, d_leaf;
+  DevBuf d_units, d_leaf, d_hot;
   mutable std::mutex mu;
-  mutable DevBuf w_words, w_off, w_freq, w_scratch, w_expected, w_out, w_logz;
+  mutable DevBuf w_words, w_off, w_freq, w_scratch, w_expected, w_out, w_logz, w_perm, w_hist;
 };
 
 int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int device, spm_cuda_estep **out) {
@@ -2714,7 +2768,8 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
   for (int i = 0; i < V; ++i) { ps.emplace_back(q); q += ps.back().size() + 1; }
   HostTrie trie;
   float min_score = 0;
-  int rc = build_estep_trie(ps, sc, &trie, &min_score, &g_err);
+  std::vector<int32_t> hot_ids;
+  int rc = build_estep_trie(ps, sc, &trie, &min_score, &g_err, &hot_ids);
   if (rc) return rc;
   std::unique_ptr<spm_cuda_estep> E(new spm_cuda_estep);
   E->device = device;
@@ -2724,8 +2779,14 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
   if ((rc = upload(&E->d_leaf, trie.leaf.data(), trie.leaf.size() * 8))) return rc;
   E->ev.units = (const uint32_t *)E->d_units.p;
   E->ev.leaf = (const uint2 *)E->d_leaf.p;
+  hot_ids.resize(kEstepHot, -1);
+  if ((rc = upload(&E->d_hot, hot_ids.data(), hot_ids.size() * 4))) return rc;
   E->ev.unk_score = min_score - 10.0f;   // kUnkPenalty, src/unigram_model.cc:550-551
+  E->ev.id_mask = V <= (1 << 20) ? 0xFFFFFu : 0x0FFFFFFFu;
   E->ev.unk_id = 0;                      // TrainerModel never calls InitializePieces
+  for (int k = 1; k < kEstepHot && V <= (1 << 20); ++k)
+    if (hot_ids[k] == 0) E->ev.unk_id = (uint32_t)k << 20;
+  CUDA_TRY(cudaFuncSetAttribute(k_estep, cudaFuncAttributeMaxDynamicSharedMemorySize, kEstepSmem));
   *out = E.release();
   return kOk;
 }
@@ -2733,8 +2794,8 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
 void spm_cuda_estep_free(spm_cuda_estep *E) {
   if (!E) return;
   DeviceGuard guard(E->device);
-  for (DevBuf *b : {&E->d_units, &E->d_leaf, &E->w_words, &E->w_off, &E->w_freq, &E->w_scratch, &E->w_expected,
-                    &E->w_out, &E->w_logz})
+  for (DevBuf *b : {&E->d_units, &E->d_leaf, &E->d_hot, &E->w_words, &E->w_off, &E->w_freq, &E->w_scratch,
+                    &E->w_expected, &E->w_out, &E->w_logz, &E->w_perm, &E->w_hist})
     b->release();
   delete E;
 }
@@ -2769,7 +2830,6 @@ int spm_cuda_estep_run(const spm_cuda_estep *E, const char *words, const int64_t
     if (hi < lo) { g_err = "word_offsets must be non-decreasing"; return kInvalidArgument; }
   }
   if ((rc = E->w_out.ensure(32))) return rc;
-  uint32_t *d_bad = (uint32_t *)((double *)E->w_out.p + 2);
   if (host) {
     if ((rc = E->w_words.ensure((size_t)(hi - lo) + 16))) return rc;
     if ((rc = E->w_off.ensure((size_t)(n + 1) * 8))) return rc;
@@ -2788,21 +2848,29 @@ int spm_cuda_estep_run(const spm_cuda_estep *E, const char *words, const int64_t
     d_logz = logz ? (float *)E->w_logz.p : nullptr;
     CUDA_TRY(cudaMemcpyAsync(d_out, obj_ntokens, 16, cudaMemcpyHostToDevice, st));
   }
-  CUDA_TRY(cudaMemsetAsync(d_bad, 0, 4, st));
   if (n > 0) {
     if ((rc = E->w_scratch.ensure((size_t)(4 * ((hi - lo) + n) + 16) * 4))) return rc;
-    k_estep<<<(unsigned)((n + kEstepThreads - 1) / kEstepThreads), kEstepThreads, 0, st>>>(
-        E->ev, d_words, d_off, d_freq, n, 1.0 / all_freq, (float *)E->w_scratch.p, d_exp, d_out, d_logz, d_bad);
+    if ((rc = E->w_perm.ensure((size_t)n * 4))) return rc;
+    if ((rc = E->w_hist.ensure(2 * kEstepBins * 4))) return rc;
+    uint32_t *d_hist = (uint32_t *)E->w_hist.p, *d_cursor = d_hist + kEstepBins;
+    CUDA_TRY(cudaMemsetAsync(d_hist, 0, kEstepBins * 4, st));
+    const unsigned gs = (unsigned)std::min<int64_t>((n + 255) / 256, 1184);
+    k_estep_hist<<<gs, 256, 0, st>>>(d_off, n, d_hist);
+    k_estep_binscan<<<1, 32, 0, st>>>(d_hist, d_cursor);
+    k_estep_scatter<<<gs, 256, 0, st>>>(d_off, n, d_cursor, (uint32_t *)E->w_perm.p);
+    k_estep<<<(unsigned)((n + kEstepThreads - 1) / kEstepThreads), kEstepThreads, kEstepSmem, st>>>(
+        E->ev, (const int32_t *)E->d_hot.p, d_words, d_off, d_freq, n, (const uint32_t *)E->w_perm.p, 1.0 / all_freq,
+        (float *)E->w_scratch.p, d_exp, d_out, d_logz);
     CUDA_TRY(cudaGetLastError());
   }
-  uint32_t bad = 0;
-  CUDA_TRY(cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, st));
-  if (host) {
-    CUDA_TRY(cudaMemcpyAsync(expected, d_exp, (size_t)E->V * 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaMemcpyAsync(obj_ntokens, d_out, 16, cudaMemcpyDeviceToHost, st));
-    if (logz && n > 0) CUDA_TRY(cudaMemcpyAsync(logz, d_logz, n * 4, cudaMemcpyDeviceToHost, st));
-  }
+  // Device-resident calls return with the work enqueued (no host sync between this kernel and a
+  // collective the caller puts on the same stream); a word of 1 MiB or more makes obj NaN there.
+  if (!host) return kOk;
+  CUDA_TRY(cudaMemcpyAsync(expected, d_exp, (size_t)E->V * 8, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(obj_ntokens, d_out, 16, cudaMemcpyDeviceToHost, st));
+  if (logz && n > 0) CUDA_TRY(cudaMemcpyAsync(logz, d_logz, n * 4, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
+  const bool bad = obj_ntokens[0] != obj_ntokens[0];
   if (bad) { g_err = "word longer than 1 MiB"; return kOutOfRange; }
   return kOk;
 }

@@ -80,11 +80,22 @@ SPM_HD void memo_store_slot(uint32_t *p, uint32_t v) {
 #endif
 }
 
+#ifndef SPM_MEMO_HASH32        // 32-bit multiply-add hash instead of three 64-bit multiplies (A/B builds)
+#define SPM_MEMO_HASH32 0
+#endif
 SPM_HD uint32_t memo_hash(uint64_t k0, uint64_t k1) {
+#if SPM_MEMO_HASH32
+  uint32_t h = (uint32_t)k0 * 0x9E3779B1u + (uint32_t)(k0 >> 32) * 0x85EBCA77u + (uint32_t)k1 * 0xC2B2AE3Du +
+               (uint32_t)(k1 >> 32) * 0x27D4EB2Fu;
+  h ^= h >> 15; h *= 0x2C1B3C6Du;
+  h ^= h >> 12; h *= 0x297A2D39u;
+  return h ^ (h >> 15);
+#else
   uint64_t h = k0 * 0x9E3779B97F4A7C15ull ^ (k1 + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full;
   h ^= h >> 29;
   h *= 0xBF58476D1CE4E5B9ull;
   return (uint32_t)(h >> 32);
+#endif
 }
 
 // compare-and-swap of the 16-byte key against "empty"; returns the previous key

@@ -1,4 +1,5 @@
 #include "spm_model.h"
+#include "spm_estep.cuh"
 
 #include <float.h>
 #include <math.h>
@@ -301,17 +302,32 @@ void scan_charsmap(HostModel *m) {
 }  // namespace
 
 int build_estep_trie(const std::vector<std::string> &pieces, const std::vector<float> &scores, HostTrie *out,
-                     float *min_score, std::string *err) {
+                     float *min_score, std::string *err, std::vector<int32_t> *hot_ids) {
   if (pieces.empty() || pieces.size() != scores.size()) { *err = "no pieces are loaded."; return kInternal; }
   if (pieces.size() >= (1u << 28)) { *err = "vocabulary too large"; return kUnimplemented; }
   std::vector<Key> keys;
   std::map<std::string, int> seen;
   float mn = FLT_MAX;
+  // hot slots (spm_estep.cuh): the kEstepHot - 1 pieces with the highest scores, when ids fit 20 bits
+  std::vector<uint32_t> hot(pieces.size(), 0);
+  if (hot_ids) {
+    hot_ids->assign(1, -1);                                  // slot 0 = "not hot"
+    if (pieces.size() <= (1u << 20)) {
+      std::vector<int32_t> order(pieces.size());
+      for (size_t i = 0; i < order.size(); ++i) order[i] = (int32_t)i;
+      const size_t k = std::min<size_t>(order.size(), kEstepHot - 1);
+      std::partial_sort(order.begin(), order.begin() + k, order.end(), [&](int32_t a, int32_t b) {
+        return scores[a] > scores[b] || (scores[a] == scores[b] && a < b);
+      });
+      for (size_t j = 0; j < k; ++j) { hot[order[j]] = (uint32_t)(j + 1); hot_ids->push_back(order[j]); }
+    }
+  }
   for (size_t i = 0; i < pieces.size(); ++i) {
     if (pieces[i].empty()) { *err = "piece must not be empty."; return kInternal; }
     if (!seen.emplace(pieces[i], (int)i).second) { *err = pieces[i] + " is already defined."; return kInternal; }
     mn = std::min(mn, scores[i]);
-    keys.push_back(Key{pieces[i], (uint32_t)i | ((uint32_t)T_NORMAL << 28), f2u(scores[i]), exp((double)scores[i])});
+    const uint32_t x = hot_ids ? ((uint32_t)i | (hot[i] << 20)) : ((uint32_t)i | ((uint32_t)T_NORMAL << 28));
+    keys.push_back(Key{pieces[i], x, f2u(scores[i]), exp((double)scores[i])});
   }
   *min_score = mn;
   if (!build_xda(keys, out, err)) return kUnimplemented;

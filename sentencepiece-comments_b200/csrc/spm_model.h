@@ -80,8 +80,9 @@ void refresh_leaf_types(HostModel *m);
 // Piece trie of a TrainerModel for the E-step (src/unigram_model_trainer.cc:97-119: every
 // piece NORMAL, ids = positions, trie over all of them).  leaf = (id, score bits).
 // *min_score = min over the scores.  Returns a StatusCode and fills *err.
+// hot_ids (may be null): slot -> piece id of the hot pieces packed into the leaf words (slot 0: -1).
 int build_estep_trie(const std::vector<std::string> &pieces, const std::vector<float> &scores, HostTrie *out,
-                     float *min_score, std::string *err);
+                     float *min_score, std::string *err, std::vector<int32_t> *hot_ids = nullptr);
 
 // id of a piece by string as ModelInterface::PieceToId (model_interface.cc:87-97)
 int piece_to_id(const HostModel &m, const std::string &piece);

@@ -467,7 +467,7 @@ int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *word
   if (rc) return rc;
   EstepView ev;
   ev.units = trie.units.data(); ev.leaf = trie.leaf.data();
-  ev.unk_score = min_score - 10.0f; ev.unk_id = 0;
+  ev.unk_score = min_score - 10.0f; ev.unk_id = 0; ev.id_mask = 0x0FFFFFFFu;
   for (int64_t i = 0; i < n; ++i) {
     const int len = (int)(off[i + 1] - off[i]);
     if (len == 0) { if (logz) logz[i] = 0; continue; }
@@ -475,8 +475,8 @@ int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *word
     std::vector<int32_t> C(len + 1);
     int32_t nt = 0;
     const float f = (float)freq[i];
-    const float z = estep_word(ev, words + off[i], len, f, A.data(), B.data(), Vt.data(), C.data(),
-                               [&](int32_t id, double v) { expected[id] += v; }, &nt);
+    const float z = estep_word(ev, words + off[i], len, f, A.data(), B.data(), Vt.data(), C.data(), 1,
+                               [&](uint32_t x, double v) { expected[x & ev.id_mask] += v; }, &nt);
     obj_ntok[0] -= (double)(f * z) / all_freq;
     obj_ntok[1] += nt;
     if (logz) logz[i] = z;
