@@ -14,6 +14,13 @@
  *
  * There is no CPU fallback: all calls fail with UNAVAILABLE-style INTERNAL
  * errors when no CUDA device is usable.
+ *
+ * Threading: a handle owns ONE device workspace, so calls on the same handle are
+ * serialised by a mutex inside the library (they are safe from any thread, they
+ * do not overlap).  Concurrency = one handle per stream / thread: handles are
+ * independent (tools/config5.py streams two blocks at a time through two handles
+ * on one GPU).  Every call runs on the handle's device and restores the caller's
+ * current CUDA device before it returns.
  */
 #ifndef SPM_CUDA_H_
 #define SPM_CUDA_H_

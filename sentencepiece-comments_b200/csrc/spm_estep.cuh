@@ -28,7 +28,7 @@ namespace spmb {
 // pieces, bits 20..31 carry the piece's slot in the per-CTA table of HOT pieces (1..kEstepHot-1; 0:
 // not hot) -- the pieces with the highest scores collect most of the expected counts, and one
 // global atomicAdd per node on a handful of addresses is what bounded the first kernel.
-constexpr int kEstepHot = 2048;
+constexpr int kEstepHot = 1024;
 struct EstepView {
   const uint32_t *units;   // XDA of all pieces (spm_model.cc build_xda)
   const uint2 *leaf;       // node -> (piece id | hot slot << 20, score bits)
@@ -68,25 +68,27 @@ SPM_HD void estep_nodes_from(const EstepView &ev, const uint8_t *w, int n, int b
   if (!single) f(b + cl, ev.unk_id, ev.unk_score);
 }
 
-// One word.  A, B, V: float tables of n + 1 entries each, C: Viterbi token counts (n + 1 entries of
-// type CT); entry k of a table lives at [k * stride] (stride 1: private arrays; stride = block
-// size: [position][thread] layout in shared memory).  expected[] receives freq * marginal through
-// add(x, value) with x = the leaf word (id | hot slot << 20).  Returns Z (log-likelihood of the word,
-// float as in the reference); *ntokens = length of the Viterbi path.
+// One word.  A, BV: float tables of n + 1 entries each (BV holds the Viterbi scores during the
+// forward pass and beta during the backward pass: the two are never alive together), C: Viterbi
+// token counts (n + 1 entries of type CT); entry k of a table lives at [k * stride] (stride 1:
+// private arrays; stride = block size: [position][thread] layout in shared memory).  expected[]
+// receives freq * marginal through add(x, value) with x = the leaf word (id | hot slot << 20).
+// Returns Z (log-likelihood of the word, float as in the reference); *ntokens = length of the
+// Viterbi path.
 template <class CT, class Add>
-SPM_HDN float estep_word(const EstepView &ev, const uint8_t *w, int n, float freq, float *A, float *B, float *V,
-                         CT *C, int stride, Add add, int32_t *ntokens) {
+SPM_HDN float estep_word(const EstepView &ev, const uint8_t *w, int n, float freq, float *A, float *BV, CT *C,
+                         int stride, Add add, int32_t *ntokens) {
   const float NINF = -INFINITY;
-  for (int k = 0; k <= n; ++k) { A[k * stride] = NINF; B[k * stride] = NINF; V[k * stride] = NINF; C[k * stride] = 0; }
-  A[0] = 0.0f; V[0] = 0.0f;
+  for (int k = 0; k <= n; ++k) { A[k * stride] = NINF; BV[k * stride] = NINF; C[k * stride] = 0; }
+  A[0] = 0.0f; BV[0] = 0.0f;
   // forward: alpha and the Viterbi count (first strictly greater wins, src/unigram_model.cc:229-246)
   for (int b = 0; b < n;) {
-    const float ab = A[b * stride], vb = V[b * stride];
+    const float ab = A[b * stride], vb = BV[b * stride];
     const int32_t cb = (int32_t)C[b * stride];
     estep_nodes_from(ev, w, n, b, [&](int e, uint32_t, float sc) {
       A[e * stride] = estep_lse(A[e * stride], sc + ab);
       const float cand = vb + sc;
-      if (cand > V[e * stride]) { V[e * stride] = cand; C[e * stride] = (CT)(cb + 1); }
+      if (cand > BV[e * stride]) { BV[e * stride] = cand; C[e * stride] = (CT)(cb + 1); }
     });
     int cl = one_char_len(w[b]);
     b += cl > n - b ? n - b : cl;
@@ -94,17 +96,17 @@ SPM_HDN float estep_word(const EstepView &ev, const uint8_t *w, int n, float fre
   const float Z = A[n * stride];
   *ntokens = (int32_t)C[n * stride];
   // backward: beta, and the expected counts of the nodes that begin at b
-  B[n * stride] = 0.0f;
+  BV[n * stride] = 0.0f;
   for (int b = n - 1; b >= 0; --b) {
     if (b > 0 && (w[b] & 0xC0u) == 0x80u) continue;   // not a character boundary
     float acc = NINF;
     const float ab = A[b * stride];
     estep_nodes_from(ev, w, n, b, [&](int e, uint32_t x, float sc) {
-      const float be = B[e * stride];
+      const float be = BV[e * stride];
       acc = estep_lse(acc, sc + be);
       add(x, (double)freq * exp((double)(ab + sc + be - Z)));
     });
-    B[b * stride] = acc;
+    BV[b * stride] = acc;
   }
   return Z;
 }

@@ -779,6 +779,9 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
 #ifndef SPM_SW_DEFER
 #define SPM_SW_DEFER 1
 #endif
+#ifndef SPM_SW_PIPE           // probe of word k + 32 issued before the probe of word k is waited for (A/B builds)
+#define SPM_SW_PIPE 1
+#endif
 // 32 sentences of the bench corpus: 3.2 KB of text and 512 words on average; 7.3 KB of shared
 // memory per warp -> 7 CTAs = 28 warps per SM
 constexpr int kSwWarps = 4, kSwBytes = SPM_SW_BYTES, kSwCap = 640, kSwLong = 64, kSwMapWords = kSwBytes / 32 + 4;
@@ -900,6 +903,45 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       // A word of more than 14 bytes takes two dependent probes (head key, tail key): one such word
       // among 32 would hold the whole warp for two more round trips, so these wait in a list.
       int nlong = 0;
+#if SPM_SW_PIPE
+      // Software pipeline over the words: the key of word k + 32 is built and the first load of its probe
+      // issued BEFORE the probe of word k is waited for, so the key arithmetic (~80 instructions, shared
+      // loads) runs under the L2 / DRAM round trip of the probe instead of after it.
+      MemoProbe pc;
+      int s_c = 0;
+      bool have_c = false, later_c = false;
+      auto prep = [&](int k, MemoProbe *p, int *s_out, bool *have, bool *later) {
+        *have = false; *later = false;
+        if (k < total) {
+          const uint32_t e = sh.wpos[k];
+          const int s = (int)(e & 0x7FFFu), n = (int)sh.wend[k] - s + 1;
+          *s_out = s;
+          if (n <= kMemoKeyBytes) {
+            uint64_t k0w, k1w;
+            sw_short_key(&sh.stage[s], n, (e >> 15) ? prefix0 : 1ull, &k0w, &k1w);
+            memo_probe_issue(tb, k0w, k1w, p);
+            *have = true;
+          } else if (n <= kMemoMaxBytes) {
+            *later = true;
+          } else {
+            atomicOr(&sh.flags[sw_owner(sh.sstart, s)], 1u);      // longer than a key pair holds
+          }
+        }
+      };
+      prep(lane, &pc, &s_c, &have_c, &later_c);
+      for (int k0 = 0; k0 < total; k0 += 32) {
+        const int k = k0 + lane;
+        MemoProbe pn;
+        int s_n = 0;
+        bool have_n, later_n;
+        prep(k + 32, &pn, &s_n, &have_n, &later_n);
+        if (have_c) {
+          const uint32_t slot = memo_probe_finish(tb, pc);
+          if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[sw_owner(sh.sstart, s_c)], 1u);   // rare: the owner is only looked up here
+          else memo_store_slot(wl + k, slot);
+        }
+        const bool later = later_c;
+#else
       for (int k0 = 0; k0 < total; k0 += 32) {
         const int k = k0 + lane;
         bool later = false;
@@ -913,6 +955,7 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
             else memo_store_slot(wl + k, slot);
           }
         }
+#endif
         const uint32_t bl = __ballot_sync(0xFFFFFFFFu, later);
         if (bl) {
           const int at = nlong + __popc(bl & ((1u << lane) - 1u));
@@ -929,6 +972,9 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
             nlong = kSwLong;
           }
         }
+#if SPM_SW_PIPE
+        pc = pn; s_c = s_n; have_c = have_n; later_c = later_n;
+#endif
       }
       __syncwarp();
       for (int j = lane; j < nlong; j += 32) {
@@ -1437,14 +1483,15 @@ k_nl_scatter(const uint8_t *buf, int64_t len, const int64_t *tile_base, uint8_t 
 
 // ---------------------------------------------------------------- unigram trainer E-step (spm_estep.cuh)
 // One thread per word, words taken in order of descending length (counting sort, so the 32 words
-// of a warp run equally long).  Words of up to kEstepSmemBytes bytes keep their forward / backward
+// of a warp run equally long).  Words of up to 31 bytes keep their forward / backward
 // / Viterbi tables in shared memory ([position][thread]: no local-memory traffic); longer ones
 // (text without spaces) use a slice of a global scratch buffer.  expected[] is accumulated in
 // double: pieces with a hot slot (the kEstepHot - 1 highest scores, which collect most of the mass)
 // in a per-CTA shared table flushed once at the end, the rest with one global atomicAdd per node;
 // the log-likelihood and the token count are reduced per warp first.
-constexpr int kEstepSmemBytes = 31, kEstepThreads = 128, kEstepBins = 64;
-constexpr int kEstepSmem = kEstepHot * 8 + (kEstepSmemBytes + 1) * kEstepThreads * 13;   // 69,632 bytes
+constexpr int kEstepThreads = 128, kEstepBins = 64;
+constexpr int kEstepPos = 32;      // words of up to 31 bytes keep their tables in shared memory
+constexpr int estep_smem_bytes(int pos) { return kEstepHot * 8 + pos * kEstepThreads * 9; }   // 45,056 bytes: 5 CTAs per SM
 __global__ void __launch_bounds__(256)
 k_estep_hist(const int64_t *off, int64_t n, uint32_t *hist) {
   __shared__ uint32_t sh[kEstepBins];
@@ -1478,17 +1525,25 @@ k_estep_scatter(const int64_t *off, int64_t n, uint32_t *cursor, uint32_t *perm)
   }
 }
 
+// POS = table entries per thread in shared memory (9 bytes each): what bounds the resident warps.
+// One launch over the whole sorted list [*range_lo or 0, *range_hi).  (Tried: three launches, one
+// per length class with 12 / 20 / 32 entries -- more resident warps for the short words, but the
+// tails of the classes no longer overlap: 1.25 ms against 1.16 ms.)
+template <int POS>
 __global__ void __launch_bounds__(kEstepThreads)
-k_estep(EstepView ev, const int32_t *hot_ids, const uint8_t *words, const int64_t *off, const int64_t *freq, int64_t n,
-        const uint32_t *perm, double inv_all_freq, float *scratch, double *expected, double *obj_ntok, float *logz) {
-  extern __shared__ __align__(16) uint8_t estep_smem[];     // kEstepSmem bytes: hot table | A | B | V | C
-  constexpr int kTab = (kEstepSmemBytes + 1) * kEstepThreads;
+k_estep(EstepView ev, const int32_t *hot_ids, const uint8_t *words, const int64_t *off, const int64_t *freq,
+        const uint32_t *range_lo, const uint32_t *range_hi, const uint32_t *perm, double inv_all_freq, float *scratch,
+        double *expected, double *obj_ntok, float *logz) {
+  extern __shared__ __align__(16) uint8_t estep_smem[];     // hot table | A | beta / Viterbi | C
+  constexpr int kTab = POS * kEstepThreads;
+  const int64_t lo = range_lo ? (int64_t)*range_lo : 0, n = (int64_t)*range_hi;
+  const int64_t idx = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (lo + (int64_t)blockIdx.x * blockDim.x >= n) return;   // the grid covers the whole list; most blocks of a class are empty
   double *s_hot = reinterpret_cast<double *>(estep_smem);
-  float *sA = reinterpret_cast<float *>(s_hot + kEstepHot), *sB = sA + kTab, *sV = sB + kTab;
-  uint8_t *sC = reinterpret_cast<uint8_t *>(sV + kTab);
+  float *sA = reinterpret_cast<float *>(s_hot + kEstepHot), *sB = sA + kTab;
+  uint8_t *sC = reinterpret_cast<uint8_t *>(sB + kTab);
   for (int k = threadIdx.x; k < kEstepHot; k += kEstepThreads) s_hot[k] = 0.0;
   __syncthreads();
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   double obj = 0.0, ntok = 0.0;
   if (idx < n) {
     const int64_t i = perm[idx];
@@ -1502,13 +1557,13 @@ k_estep(EstepView ev, const int32_t *hot_ids, const uint8_t *words, const int64_
         if (slot) atomicAdd(&s_hot[slot], v);
         else atomicAdd(&expected[x & ev.id_mask], v);
       };
-      if (len <= kEstepSmemBytes) {
-        z = estep_word(ev, words + o, (int)len, f, sA + threadIdx.x, sB + threadIdx.x, sV + threadIdx.x,
-                       sC + threadIdx.x, kEstepThreads, add, &nt);
+      if (len < POS) {
+        z = estep_word(ev, words + o, (int)len, f, sA + threadIdx.x, sB + threadIdx.x, sC + threadIdx.x,
+                       kEstepThreads, add, &nt);
       } else {
         float *base = scratch + 4 * ((o - off[0]) + i);
-        z = estep_word(ev, words + o, (int)len, f, base, base + (len + 1), base + 2 * (len + 1),
-                       (int32_t *)(base + 3 * (len + 1)), 1, add, &nt);
+        z = estep_word(ev, words + o, (int)len, f, base, base + (len + 1), (int32_t *)(base + 2 * (len + 1)), 1,
+                       add, &nt);
       }
       // objs[n] -= Z / all_sentence_freq with Z = freq * log-likelihood (:262-266)
       obj = -(double)(f * z) * inv_all_freq;
@@ -2786,7 +2841,8 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
   E->ev.unk_id = 0;                      // TrainerModel never calls InitializePieces
   for (int k = 1; k < kEstepHot && V <= (1 << 20); ++k)
     if (hot_ids[k] == 0) E->ev.unk_id = (uint32_t)k << 20;
-  CUDA_TRY(cudaFuncSetAttribute(k_estep, cudaFuncAttributeMaxDynamicSharedMemorySize, kEstepSmem));
+  CUDA_TRY(cudaFuncSetAttribute(k_estep<kEstepPos>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                estep_smem_bytes(kEstepPos)));
   *out = E.release();
   return kOk;
 }
@@ -2858,9 +2914,11 @@ int spm_cuda_estep_run(const spm_cuda_estep *E, const char *words, const int64_t
     k_estep_hist<<<gs, 256, 0, st>>>(d_off, n, d_hist);
     k_estep_binscan<<<1, 32, 0, st>>>(d_hist, d_cursor);
     k_estep_scatter<<<gs, 256, 0, st>>>(d_off, n, d_cursor, (uint32_t *)E->w_perm.p);
-    k_estep<<<(unsigned)((n + kEstepThreads - 1) / kEstepThreads), kEstepThreads, kEstepSmem, st>>>(
-        E->ev, (const int32_t *)E->d_hot.p, d_words, d_off, d_freq, n, (const uint32_t *)E->w_perm.p, 1.0 / all_freq,
-        (float *)E->w_scratch.p, d_exp, d_out, d_logz);
+    // (after the scatter cursor[kEstepBins - 1] = n: the end of the shortest bin)
+    const unsigned ge = (unsigned)((n + kEstepThreads - 1) / kEstepThreads);
+    k_estep<kEstepPos><<<ge, kEstepThreads, estep_smem_bytes(kEstepPos), st>>>(
+        E->ev, (const int32_t *)E->d_hot.p, d_words, d_off, d_freq, nullptr, d_cursor + (kEstepBins - 1),
+        (const uint32_t *)E->w_perm.p, 1.0 / all_freq, (float *)E->w_scratch.p, d_exp, d_out, d_logz);
     CUDA_TRY(cudaGetLastError());
   }
   // Device-resident calls return with the work enqueued (no host sync between this kernel and a

@@ -120,19 +120,20 @@ SPM_HD void memo_claim(MemoKey *e, uint64_t k0, uint64_t k1, uint64_t *o0, uint6
 // common case: both key halves carry the non-zero meta byte, so a half-written key can
 // never compare equal, and keys are immutable once written; "looks empty" is settled
 // by the CAS itself.
-SPM_HD uint32_t memo_find_or_insert(const MemoTable &tb, uint64_t k0, uint64_t k1) {
-  uint32_t slot = memo_hash(k0, k1) & tb.mask;
-  for (int probe = 0; probe < kMemoProbes; ++probe, slot = (slot + 1) & tb.mask) {
-    MemoKey *e = tb.keys + slot;
+SPM_HD void memo_load_key(const MemoKey *e, uint64_t *e0, uint64_t *e1) {
 #if defined(__CUDA_ARCH__)
-    uint64_t e0, e1;
-    asm volatile("ld.global.v2.u64 {%0, %1}, [%2];" : "=l"(e0), "=l"(e1) : "l"(e) : "memory");
+  asm volatile("ld.global.v2.u64 {%0, %1}, [%2];" : "=l"(*e0), "=l"(*e1) : "l"(e) : "memory");
 #else
-    uint64_t e0 = e->k0, e1 = e->k1;
+  *e0 = e->k0; *e1 = e->k1;
 #endif
+}
+// The probe sequence from `slot`, whose entry (e0, e1) has been loaded already.
+SPM_HD uint32_t memo_find_or_insert_from(const MemoTable &tb, uint64_t k0, uint64_t k1, uint32_t slot, uint64_t e0,
+                                         uint64_t e1) {
+  for (int probe = 0;;) {
     if (e0 == k0 && e1 == k1) return slot;
     if (e0 == 0 && e1 == 0) {
-      memo_claim(e, k0, k1, &e0, &e1);
+      memo_claim(tb.keys + slot, k0, k1, &e0, &e1);
       if (e0 == 0 && e1 == 0) {
 #if defined(__CUDA_ARCH__)
         const uint32_t idx = atomicAdd(tb.n_new, 1u);
@@ -144,8 +145,30 @@ SPM_HD uint32_t memo_find_or_insert(const MemoTable &tb, uint64_t k0, uint64_t k
       }
       if (e0 == k0 && e1 == k1) return slot;
     }
+    if (++probe == kMemoProbes) return 0xFFFFFFFFu;
+    slot = (slot + 1) & tb.mask;
+    memo_load_key(tb.keys + slot, &e0, &e1);
   }
-  return 0xFFFFFFFFu;
+}
+SPM_HD uint32_t memo_find_or_insert(const MemoTable &tb, uint64_t k0, uint64_t k1) {
+  const uint32_t slot = memo_hash(k0, k1) & tb.mask;
+  uint64_t e0, e1;
+  memo_load_key(tb.keys + slot, &e0, &e1);
+  return memo_find_or_insert_from(tb, k0, k1, slot, e0, e1);
+}
+// The same in two halves, so that a caller can key and issue the first load of its NEXT word before it
+// waits for the load of the current one (k_memo_scan_words: the probe is an L2 / DRAM round trip).
+struct MemoProbe {
+  uint64_t k0, k1, e0, e1;
+  uint32_t slot;
+};
+SPM_HD void memo_probe_issue(const MemoTable &tb, uint64_t k0, uint64_t k1, MemoProbe *p) {
+  p->k0 = k0; p->k1 = k1;
+  p->slot = memo_hash(k0, k1) & tb.mask;
+  memo_load_key(tb.keys + p->slot, &p->e0, &p->e1);
+}
+SPM_HD uint32_t memo_probe_finish(const MemoTable &tb, const MemoProbe &p) {
+  return memo_find_or_insert_from(tb, p.k0, p.k1, p.slot, p.e0, p.e1);
 }
 
 // Output sink of fast_normalize_scan(): the normalized characters of a sentence go
@@ -363,6 +386,18 @@ SPM_HD SwMasks sw_chunk_masks(uint64_t w, uint32_t pb, uint32_t nb, uint32_t b9,
 // Slot of the word s[0..n) (n >= 1 bytes of 0x21..0x7E, s readable in aligned 8-byte words up to
 // 32 + 7 bytes past its start): exactly the keys memo_scan_plain() builds -- one head key up to
 // 14 bytes, head + tail key up to 24.  0xFFFFFFFF: the word cannot be keyed (too long, table full).
+// Key of a word of 1..14 bytes (the one-key case of sw_word_slot below).
+SPM_HD void sw_short_key(const uint8_t *s, int n, uint64_t prefix, uint64_t *k0, uint64_t *k1) {
+  const uint8_t *q = (const uint8_t *)((uintptr_t)s & ~(uintptr_t)7);
+  const int r = (int)(s - q);
+  const uint64_t a0 = fast_load8(q), a1 = fast_load8(q + 8), a2 = fast_load8(q + 16);
+  uint64_t w0 = fast_window(a0, a1, r), w1 = fast_window(a1, a2, r);
+  if (n < 8) { w0 &= ~0ull >> (8 * (8 - n)); w1 = 0; }
+  else w1 &= n == 8 ? 0ull : ~0ull >> (8 * (16 - n));
+  const uint64_t mb = ((uint64_t)n << 1) | prefix;
+  *k0 = mb | (w0 << 8);
+  *k1 = (w0 >> 56) | (w1 << 8) | (mb << 56);
+}
 SPM_HD uint32_t sw_word_slot(const MemoTable &tb, const uint8_t *s, int n, uint64_t prefix) {
   if (n > kMemoMaxBytes) return 0xFFFFFFFFu;
   const uint8_t *q = (const uint8_t *)((uintptr_t)s & ~(uintptr_t)7);

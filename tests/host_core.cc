@@ -471,11 +471,11 @@ int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *word
   for (int64_t i = 0; i < n; ++i) {
     const int len = (int)(off[i + 1] - off[i]);
     if (len == 0) { if (logz) logz[i] = 0; continue; }
-    std::vector<float> A(len + 1), B(len + 1), Vt(len + 1);
+    std::vector<float> A(len + 1), B(len + 1);
     std::vector<int32_t> C(len + 1);
     int32_t nt = 0;
     const float f = (float)freq[i];
-    const float z = estep_word(ev, words + off[i], len, f, A.data(), B.data(), Vt.data(), C.data(), 1,
+    const float z = estep_word(ev, words + off[i], len, f, A.data(), B.data(), C.data(), 1,
                                [&](uint32_t x, double v) { expected[x & ev.id_mask] += v; }, &nt);
     obj_ntok[0] -= (double)(f * z) / all_freq;
     obj_ntok[1] += nt;
