@@ -776,12 +776,6 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
 #ifndef SPM_SW_BYTES          // build-time knobs of the measurements in profiles/r1_v21_summary.md
 #define SPM_SW_BYTES 4096
 #endif
-#ifndef SPM_SW_DEFER
-#define SPM_SW_DEFER 1
-#endif
-#ifndef SPM_SW_PIPE           // probe of word k + 32 issued before the probe of word k is waited for (A/B builds)
-#define SPM_SW_PIPE 1
-#endif
 // 32 sentences of the bench corpus: 3.2 KB of text and 512 words on average; 7.3 KB of shared
 // memory per warp -> 7 CTAs = 28 warps per SM
 constexpr int kSwWarps = 4, kSwBytes = SPM_SW_BYTES, kSwCap = 640, kSwLong = 64, kSwMapWords = kSwBytes / 32 + 4;
@@ -903,7 +897,6 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       // A word of more than 14 bytes takes two dependent probes (head key, tail key): one such word
       // among 32 would hold the whole warp for two more round trips, so these wait in a list.
       int nlong = 0;
-#if SPM_SW_PIPE
       // Software pipeline over the words: the key of word k + 32 is built and the first load of its probe
       // issued BEFORE the probe of word k is waited for, so the key arithmetic (~80 instructions, shared
       // loads) runs under the L2 / DRAM round trip of the probe instead of after it.
@@ -941,21 +934,6 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
           else memo_store_slot(wl + k, slot);
         }
         const bool later = later_c;
-#else
-      for (int k0 = 0; k0 < total; k0 += 32) {
-        const int k = k0 + lane;
-        bool later = false;
-        if (k < total) {
-          const uint32_t e = sh.wpos[k];
-          const int s = (int)(e & 0x7FFFu), n = (int)sh.wend[k] - s + 1;
-          later = SPM_SW_DEFER && n > kMemoKeyBytes && n <= kMemoMaxBytes;
-          if (!later) {
-            const uint32_t slot = sw_word_slot(tb, &sh.stage[s], n, (e >> 15) ? prefix0 : 1ull);
-            if (slot == 0xFFFFFFFFu) atomicOr(&sh.flags[sw_owner(sh.sstart, s)], 1u);   // rare: the owner is only looked up here
-            else memo_store_slot(wl + k, slot);
-          }
-        }
-#endif
         const uint32_t bl = __ballot_sync(0xFFFFFFFFu, later);
         if (bl) {
           const int at = nlong + __popc(bl & ((1u << lane) - 1u));
@@ -972,9 +950,7 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
             nlong = kSwLong;
           }
         }
-#if SPM_SW_PIPE
         pc = pn; s_c = s_n; have_c = have_n; later_c = later_n;
-#endif
       }
       __syncwarp();
       for (int j = lane; j < nlong; j += 32) {

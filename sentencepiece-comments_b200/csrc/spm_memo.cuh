@@ -80,8 +80,8 @@ SPM_HD void memo_store_slot(uint32_t *p, uint32_t v) {
 #endif
 }
 
-#ifndef SPM_MEMO_HASH32        // 32-bit multiply-add hash instead of three 64-bit multiplies (A/B builds)
-#define SPM_MEMO_HASH32 0
+#ifndef SPM_MEMO_HASH32        // 32-bit multiply-add hash (default) or three 64-bit multiplies (A/B builds: 2.60 -> 2.55 ms)
+#define SPM_MEMO_HASH32 1
 #endif
 SPM_HD uint32_t memo_hash(uint64_t k0, uint64_t k1) {
 #if SPM_MEMO_HASH32
