@@ -603,11 +603,12 @@ k_sort_long(const int64_t *off, int64_t c0, const int32_t *list, int count_idx, 
 // Long lines (kFastMaxRaw <= bytes < kLongMaxRaw) of unigram models: one WARP per line, exact
 // candidate lists in shared memory (spm_warp.cuh).  Persistent warps pull lines from the list.
 constexpr int kWarpWarps = 4;
+template <int HITS>
 __global__ void __launch_bounds__(kWarpWarps * 32)
 k_encode_warp(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
               const int32_t *list, int count_idx, int work_idx, uint32_t *back, int64_t stride, int32_t *stage,
               int32_t *cnt, int32_t *gen_list, uint32_t *counters) {
-  __shared__ WarpScratch ws[kWarpWarps];
+  __shared__ WarpScratch<HITS> ws[kWarpWarps];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   FastView fv;
   fv.units = fp.units; fv.score = fp.score; fv.leaf_id = fp.leaf_id;
@@ -2469,18 +2470,25 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
             warp_ok ? C_NLONG : C_NGEN, d_counters, warp_ok ? warp_route : 0u);
         if (warp_ok) {
           // one warp per line, exact candidate lists (spm_warp.cuh); back records: kWarpCapc rows of
-          // `wstride` per resident warp, at most 4 GiB in all; longest lines first
+          // `wstride` per resident warp, at most 8 GiB in all (the kernel is a chain of dependent shared-memory steps per
+          // character: what it needs is resident warps, and a 33 KB line costs each 1.6 MB of records); longest lines first
           const int64_t wstride = 3 * max_long + 136;
           int64_t wblocks = std::max<int64_t>(
-              1, std::min<int64_t>(5 * (int64_t)M->sm_count, (4096ll << 20) / (wstride * 4 * kWarpCapc * kWarpWarps)));
+              1, std::min<int64_t>(8 * (int64_t)M->sm_count, (8192ll << 20) / (wstride * 4 * kWarpCapc * kWarpWarps)));
           wblocks = std::min<int64_t>(wblocks, (cn + kWarpWarps - 1) / kWarpWarps);   // a warp per listed line at most
           if ((rc = M->w_wback.ensure((size_t)(wblocks * kWarpWarps * kWarpCapc * wstride * 4)))) return rc;
           k_sort_long<<<1, 1024, 0, st>>>(d_off, c0, (const int32_t *)M->w_longlist.p, C_NLONG,
                                           (int32_t *)M->w_vitl.p, d_counters);
-          k_encode_warp<<<(unsigned)wblocks, kWarpWarps * 32, 0, st>>>(
-              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
-              (const int32_t *)M->w_vitl.p, cnt_b, work_b, (uint32_t *)M->w_wback.p, wstride, d_vstage,
-              (int32_t *)M->w_cnt.p, (int32_t *)M->w_genlist.p, d_counters);
+          if (M->hm.max_piece_chars + 1 <= kWarpHitsSmall)
+            k_encode_warp<kWarpHitsSmall><<<(unsigned)wblocks, kWarpWarps * 32, 0, st>>>(
+                M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+                (const int32_t *)M->w_vitl.p, cnt_b, work_b, (uint32_t *)M->w_wback.p, wstride, d_vstage,
+                (int32_t *)M->w_cnt.p, (int32_t *)M->w_genlist.p, d_counters);
+          else
+            k_encode_warp<kWarpHits><<<(unsigned)wblocks, kWarpWarps * 32, 0, st>>>(
+                M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+                (const int32_t *)M->w_vitl.p, cnt_b, work_b, (uint32_t *)M->w_wback.p, wstride, d_vstage,
+                (int32_t *)M->w_cnt.p, (int32_t *)M->w_genlist.p, d_counters);
           launches += 2;
         } else if (has_long) {
           k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(

@@ -24,16 +24,19 @@ namespace spmb {
 
 constexpr int kWarpCapc = 4;      // candidates kept per end position
 constexpr int kWarpRing = 64;     // byte positions in flight (>= max piece bytes + 5)
-constexpr int kWarpHits = 20;     // hits per start position (>= max piece chars + 1)
+constexpr int kWarpHits = 20;     // hits per start position (>= max piece chars + 1) ...
+constexpr int kWarpHitsSmall = 12;  // ... or 12 for models whose pieces have at most 11 characters: 6.4 KB of shared
+                                    // memory per warp instead of 9 KB -> 8 instead of 6 resident CTAs per SM
 
+template <int HITS>
 struct WarpScratch {              // shared memory of one warp
   uint32_t cnt[kWarpRing];
   float maxbt[kWarpRing];
   float bt[kWarpRing * kWarpCapc];
   uint32_t rec[kWarpRing * kWarpCapc];
-  uint32_t hit_id[32 * kWarpHits];
-  float hit_sc[32 * kWarpHits];
-  uint16_t hit_end[32 * kWarpHits];   // end offset relative to the round base
+  uint32_t hit_id[32 * HITS];
+  float hit_sc[32 * HITS];
+  uint16_t hit_end[32 * HITS];   // end offset relative to the round base
 };
 
 #if defined(__CUDACC__)
@@ -45,7 +48,8 @@ SPM_HD uint32_t warp_pack_rec(uint32_t id, uint32_t len, uint32_t prevslot) {
 // s: normalized valid UTF-8 text, n bytes (zero padded).  back: kWarpCapc rows of `stride`
 // records.  out: ids in REVERSE order (unknown runs merged); returns the count, or -1 when
 // more than kWarpCapc near-tied candidates met at one position (caller: general tier).
-__device__ inline int32_t warp_unigram(const FastView &fv, WarpScratch &ws, const uint8_t *s, int32_t n,
+template <int HITS>
+__device__ inline int32_t warp_unigram(const FastView &fv, WarpScratch<HITS> &ws, const uint8_t *s, int32_t n,
                                        uint32_t *back, int64_t stride, int32_t *out) {
   const int lane = threadIdx.x & 31;
   const uint32_t mask = kWarpRing - 1;
@@ -76,18 +80,18 @@ __device__ inline int32_t warp_unigram(const FastView &fv, WarpScratch &ws, cons
           if ((v & 0xFFu) != c || (v & 0x300u) == 0) break;
           u = v;
           if ((c & 0xC0u) != 0x80u) ++nchars;
-          if ((v & 0x100u) && nh < kWarpHits) {
-            ws.hit_id[lane * kWarpHits + nh] = __ldg(fv.leaf_id + child);
-            ws.hit_sc[lane * kWarpHits + nh] = __ldg(fv.score + child);
-            ws.hit_end[lane * kWarpHits + nh] = (uint16_t)(i + 1 - P);
+          if ((v & 0x100u) && nh < HITS) {
+            ws.hit_id[lane * HITS + nh] = __ldg(fv.leaf_id + child);
+            ws.hit_sc[lane * HITS + nh] = __ldg(fv.score + child);
+            ws.hit_end[lane * HITS + nh] = (uint16_t)(i + 1 - P);
             ++nh;
             if (nchars == 1) single = true;
           }
         }
-        if (!single && nh < kWarpHits) {   // UNK node of one character (src/unigram_model.cc:598-602)
-          ws.hit_id[lane * kWarpHits + nh] = (uint32_t)fv.unk_id;
-          ws.hit_sc[lane * kWarpHits + nh] = fv.unk_score;
-          ws.hit_end[lane * kWarpHits + nh] = (uint16_t)(p + cl - P);
+        if (!single && nh < HITS) {   // UNK node of one character (src/unigram_model.cc:598-602)
+          ws.hit_id[lane * HITS + nh] = (uint32_t)fv.unk_id;
+          ws.hit_sc[lane * HITS + nh] = fv.unk_score;
+          ws.hit_end[lane * HITS + nh] = (uint16_t)(p + cl - P);
           ++nh;
         }
       }
@@ -104,9 +108,9 @@ __device__ inline int32_t warp_unigram(const FastView &fv, WarpScratch &ws, cons
       const int nhj = __shfl_sync(0xFFFFFFFFu, nh, j);
       if ((uint32_t)lane < cnt) back[(int64_t)lane * stride + pj] = ws.rec[r * kWarpCapc + lane];
       if (lane < nhj) {
-        const float sr = ws.hit_sc[j * kWarpHits + lane];
-        const uint32_t id = ws.hit_id[j * kWarpHits + lane];
-        const int32_t e = P + (int32_t)ws.hit_end[j * kWarpHits + lane];
+        const float sr = ws.hit_sc[j * HITS + lane];
+        const uint32_t id = ws.hit_id[j * HITS + lane];
+        const int32_t e = P + (int32_t)ws.hit_end[j * HITS + lane];
         // best predecessor (src/unigram_model.cc:229-246): first strictly greater, in begin order
         float best = ws.bt[r * kWarpCapc] + sr;
         uint32_t bs = 0;
@@ -145,7 +149,7 @@ __device__ inline int32_t warp_unigram(const FastView &fv, WarpScratch &ws, cons
       if (lane == 0) ws.cnt[r] = 0;
       __syncwarp();
     }
-    if (__any_sync(0xFFFFFFFFu, (start && nh >= kWarpHits) || overflow)) return -1;
+    if (__any_sync(0xFFFFFFFFu, (start && nh >= HITS) || overflow)) return -1;
   }
   __syncwarp();
   // ---- EOS (score 0) picks among the candidates ending at n; backtrace by lane 0
