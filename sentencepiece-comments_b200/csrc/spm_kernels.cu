@@ -2215,9 +2215,10 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     if ((rc = M->w_memo.ensure(entries * sizeof(MemoKey)))) return rc;
     if ((rc = M->w_mres.ensure(entries * sizeof(MemoRes)))) return rc;
     if ((rc = M->w_newlist.ensure(entries / 2 * 4))) return rc;
-    // keys: empty; results: meta 0 = "not encoded" (claimed beyond max_new, never served)
+    // keys: empty.  The result records are not zeroed (256 MB per call): a slot is only ever read after it
+    // was claimed in this call, and every claimed slot gets its meta word from the words kernel or -- beyond
+    // max_new -- from the claimer itself (meta 0 = "not encoded", never served).
     CUDA_TRY(cudaMemsetAsync(M->w_memo.p, 0, entries * sizeof(MemoKey), st));
-    CUDA_TRY(cudaMemsetAsync(M->w_mres.p, 0, entries * sizeof(MemoRes), st));
     memo_tb.keys = (MemoKey *)M->w_memo.p;
     memo_tb.res = (MemoRes *)M->w_mres.p;
     memo_tb.mask = (uint32_t)(entries - 1);

@@ -141,6 +141,8 @@ SPM_HD uint32_t memo_find_or_insert_from(const MemoTable &tb, uint64_t k0, uint6
         const uint32_t idx = (*tb.n_new)++;
 #endif
         if (idx < tb.max_new) tb.new_list[idx] = slot;
+        else tb.res[slot].meta = 0;      // beyond the list: never encoded, never served (res is NOT zeroed per call:
+                                         // every claimed slot gets its meta here or from the words kernel)
         return slot;
       }
       if (e0 == k0 && e1 == k1) return slot;

@@ -493,7 +493,7 @@ int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *word
 int64_t hc_scan_words_check(const uint8_t *text, const int64_t *off, int64_t n, int prefix0, int64_t *n_plain) {
   const size_t slots_n = 1 << 18;
   std::vector<MemoKey> mkeys(slots_n);
-  std::vector<MemoRes> mres(1);
+  std::vector<MemoRes> mres(slots_n);      // (a slot claimed beyond max_new gets its meta word written)
   std::vector<uint32_t> mnew(slots_n / 2);
   memset((void *)mkeys.data(), 0, slots_n * sizeof(MemoKey));
   uint32_t n_new = 0;
