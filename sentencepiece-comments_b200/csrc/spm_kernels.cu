@@ -2254,7 +2254,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
     int64_t want = kMaxChunk;
     if (host && n >= std::max<int64_t>(1, M->opt.host_chunk_min)) {
       const int64_t parts = std::max<int64_t>(
-          1, std::min<int64_t>(64, M->opt.host_chunks > 0 ? M->opt.host_chunks : (M->fast_kind == 2 ? 5 : 12)));
+          1, std::min<int64_t>(64, M->opt.host_chunks > 0 ? M->opt.host_chunks : (M->fast_kind == 2 ? 8 : 12)));
       want = std::max<int64_t>(1, std::min(kMaxChunk, (n + parts - 1) / parts));
     }
     int64_t c0 = 0, off_c0 = text_lo;
