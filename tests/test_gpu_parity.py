@@ -218,6 +218,9 @@ def test_word_scan_shapes(spm_b200, corpora, model):
     rng = np.random.default_rng(11)
     text, off = corpora["syn_en"]
     words = bytes(text[: off[400]]).split()
+    # (runs of 26 .. 1000 word bytes: the scan keeps 8-bit word ends and must flag them by its chunk rule)
+    words += [b"v" * n for n in (26, 31, 32, 33, 39, 40, 41, 47, 48, 49, 255, 256, 257, 258, 264, 270, 280, 300, 511,
+                                 512, 513, 520, 768, 1000)]
     words += [b"a", b"I", b"x" * 14, b"y" * 15, b"internationalisations", b"z" * 24, b"w" * 25, b"q" * 60,
               b"counter-revolutionary.", b"Mr.", b"(sic)", b"~", b"caf\xc3\xa9", b"na\xc3\xafve", b"\xef\xbd\x81"]
     lines = []
