@@ -341,9 +341,12 @@ SPM_HD uint64_t pack_rec(uint32_t id, uint32_t len, uint32_t prevslot) {
 // of the full end list we keep, per pending end position, only candidates that
 // can still be chosen by SOME right node:
 //   - a candidate whose bt is below the running max M by more than
-//     eps = 2^-20 (max(|M|,|bt|) + smax) loses to M for every right score s,
-//     because fl(x1+s) < fl(x2+s) whenever x2-x1 exceeds two float spacings at
-//     magnitude |x|+|s|;
+//     eps = 2^-22 (max(|M|,|bt|) + smax) loses to M for every right score s:
+//     rounding is monotonic, so fl(x1+s) <= fl(x2+s) for x1 < x2, and the two sums
+//     can only round to the SAME float y when x2 - x1 <= ulp(y) <= 2^-23 |y| with
+//     |y| <= (max(|x1|,|x2|) + |s|)(1 + 2^-24) -- eps is twice that bound (round 1
+//     used 2^-20, which flagged four times as many sentences in the one-candidate
+//     kernel for nothing: 91 % of the 4 KB Japanese lines);
 //   - a candidate whose bt equals an earlier kept candidate's bt yields the
 //     same sum and loses the first-wins tie.
 // Kept candidates stay in begin order, so the scan over them returns the
@@ -375,7 +378,7 @@ SPM_HD int32_t unigram_encode_impl(const ModelView &m, const uint8_t *s, int32_t
     }
     const float M = sc.ringM[r];
     const float am = fabsf(M), ab = fabsf(bt);
-    const float eps = ((am > ab ? am : ab) + m.smax) * 9.5367431640625e-07f;
+    const float eps = ((am > ab ? am : ab) + m.smax) * 2.384185791015625e-07f;
     if (bt - M > eps) {
       sc.ringM[r] = bt; sc.candBt[r * CAPC] = bt; sc.candRec[r * CAPC] = rec; sc.ringCnt[r] = 1;
     } else if (M - bt > eps) {

@@ -127,7 +127,7 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
   if (n <= 0) return 0;
   const int R = fv.ring;
   const float NEG = -3.0e38f;     // "no node ends here yet" (finite, so the tie tolerance stays finite)
-  const float TOL = 9.5367431640625e-07f;  // 2^-20, see unigram_encode() in spm_core.cuh
+  const float TOL = 2.384185791015625e-07f;  // 2^-22, see unigram_encode() in spm_core.cuh
   for (int k = 0; k < R; ++k) ring_bt[k * rstride] = NEG;
   const uint32_t root = fv.units_hot[0];
   const uint32_t *sw = reinterpret_cast<const uint32_t *>(s);
@@ -146,9 +146,9 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
   fast_prefetch_word(txt, txt_saddr, sw + 5);
   float bt_p = 0.0f;              // BOS
   // Near-tie tolerance of the walk that starts at the current character.  A push is flagged
-  // when |bt - M| <= 2^-20 (max(|M|,|bt|) + smax) and bt != M (see unigram_encode()); since
+  // when |bt - M| <= 2^-22 (max(|M|,|bt|) + smax) and bt != M (see unigram_encode()); since
   // |bt| <= |bt_p| + smax and a near-tied M is within the tolerance of bt, the per-character
-  // bound 2^-20 (|bt_p| + 2 smax + 1) flags a superset -- cheaper, still exact after the
+  // bound 2^-22 (|bt_p| + 2 smax + 1) flags a superset -- cheaper, still exact after the
   // exact tier re-runs the flagged sentences.
   float tol_p = (2.0f * fv.smax + 1.0f) * TOL;
   uint32_t cur = w0;

@@ -127,7 +127,7 @@ __device__ inline int32_t warp_unigram(const FastView &fv, WarpScratch<HITS> &ws
         } else {
           const float M = ws.maxbt[re];
           const float am = fabsf(M), ab = fabsf(best);
-          const float eps = ((am > ab ? am : ab) + fv.smax) * 9.5367431640625e-07f;
+          const float eps = ((am > ab ? am : ab) + fv.smax) * 2.384185791015625e-07f;
           if (best - M > eps) {
             ws.maxbt[re] = best; ws.bt[re * kWarpCapc] = best; ws.rec[re * kWarpCapc] = rec; ws.cnt[re] = 1;
           } else if (!(M - best > eps)) {
