@@ -369,12 +369,14 @@ k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t 
   nlen[t] = nl;
 }
 
-// Long lines: one BLOCK per line, one thread per piece of ~kNormChunk raw bytes.  Pieces start
+// Long lines: one BLOCK per line, its threads share the pieces of ~kNormChunk raw bytes.  Pieces start
 // at positions norm_find_cut() proves safe, are normalized independently into a temporary
 // slot each (fast_normalize_scan with mid = true), then the block concatenates them into the
 // line's slot of `norm` and finishes the line as fast_normalize() does (trailing whitespace,
-// suffix, zero padding).  A 33 KB line takes the time of one 512-byte piece instead of 20 ms.
-constexpr int kNormLongThreads = kLongMaxRaw / kNormChunk;   // 128
+// suffix, zero padding).  A 33 KB line takes the time of three 128-byte pieces instead of 20 ms.
+// (Pieces of 512 bytes, one per thread: a 4..8 KB line -- most long lines -- kept 8..16 of the block's
+// 128 threads busy; 14.6 ms for the 350 MB of long lines in 2.2 M lines of Japanese text.)
+constexpr int kNormLongThreads = 128, kNormMaxChunks = kLongMaxRaw / kNormChunk;   // 512 pieces at most
 __device__ __forceinline__ int64_t norm_tmp_base(const int64_t *off, int64_t c0, int64_t t) {
   const int64_t o = off[c0 + t] - off[c0];
   return ((3 * o + 7) & ~(int64_t)7) + 88 * (o / kNormChunk) + 96 * t;
@@ -384,8 +386,8 @@ k_normalize_long(ModelView mv, const uint8_t *text, const int64_t *off, int64_t 
                  const uint8_t *hi, const int32_t *list, int count_idx, uint8_t *tmp, uint8_t *norm, int32_t *nlen,
                  int32_t *gen_list, uint32_t *counters) {
   __shared__ uint32_t first2[2048];
-  __shared__ int64_t cuts[kNormLongThreads + 1];
-  __shared__ int32_t olen[kNormLongThreads], obase[kNormLongThreads + 1], onch[kNormLongThreads];
+  __shared__ int64_t cuts[kNormMaxChunks + 1];
+  __shared__ int32_t olen[kNormMaxChunks], obase[kNormMaxChunks + 1], onch[kNormMaxChunks];
   __shared__ int bad, started, total_len, total_nch;
   if (blockIdx.x >= counters[count_idx]) return;
   if (mv.cm_first2 != nullptr)
@@ -395,41 +397,58 @@ k_normalize_long(ModelView mv, const uint8_t *text, const int64_t *off, int64_t 
   const uint8_t *in = text + o0;
   uint8_t *line_tmp = tmp + norm_tmp_base(off, c0, t);
   const int i = threadIdx.x;
-  const int nchunks = (int)((len + kNormChunk - 1) / kNormChunk);
-  if (i == 0) { bad = 0; started = 0; }
+  const int nchunks = (int)((len + kNormChunk - 1) / kNormChunk);   // <= kNormMaxChunks: len < kLongMaxRaw
+  if (i == 0) { bad = 0; started = 0; cuts[0] = 0; cuts[nchunks] = len; }
   __syncthreads();
-  // (nchunks can equal the thread count -- lines of 65,025..65,535 bytes -- so the end cut is
-  // thread 0's job, not thread nchunks')
-  if (i == 0) { cuts[0] = 0; cuts[nchunks] = len; }
-  else if (i < nchunks) cuts[i] = norm_find_cut(mv, first2, in, (int64_t)i * kNormChunk, len);
+  for (int k = i; k < nchunks; k += kNormLongThreads)
+    if (k > 0) cuts[k] = norm_find_cut(mv, first2, in, (int64_t)k * kNormChunk, len);
   __syncthreads();
-  olen[i] = 0; onch[i] = 0;
-  if (i < nchunks) {
-    const int64_t a = cuts[i], b = cuts[i + 1];
+  for (int k = i; k < nchunks; k += kNormLongThreads) {
+    olen[k] = 0; onch[k] = 0;
+    const int64_t a = cuts[k], b = cuts[k + 1];
     if (b > a) {
       bool content = false;
-      const bool ok = norm_piece(mv, first2, in, a, b, lo, hi, line_tmp + norm_piece_slot(a, i), i, &olen[i], &onch[i],
+      const bool ok = norm_piece(mv, first2, in, a, b, lo, hi, line_tmp + norm_piece_slot(a, k), k, &olen[k], &onch[k],
                                  &content);
-      if (i == 0 && content) started = 1;
+      if (k == 0 && content) started = 1;
       // pieces after the first assume that the line's content has started
-      if (!ok || (i == 0 && !content && nchunks > 1)) bad = 1;
+      if (!ok || (k == 0 && !content && nchunks > 1)) bad = 1;
     }
   }
   __syncthreads();
-  if (i == 0) {
+  if (i < 32) {   // exclusive scan of the piece lengths by one warp
     int32_t run = 0, nc = 0;
-    for (int k = 0; k < nchunks; ++k) { obase[k] = run; run += olen[k]; nc += onch[k]; }
-    total_len = run; total_nch = nc;
-    if (run + 3 > 3 * len + 72) bad = 1;
+    for (int k0 = 0; k0 < nchunks; k0 += 32) {
+      const int k = k0 + i;
+      const int32_t v = k < nchunks ? olen[k] : 0;
+      int32_t inc = v, c = k < nchunks ? onch[k] : 0;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (i >= d) inc += y;
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, d);
+      if (k < nchunks) obase[k] = run + inc - v;
+      run += __shfl_sync(0xFFFFFFFFu, inc, 31);
+      nc += c;
+    }
+    if (i == 0) {
+      total_len = run; total_nch = nc;
+      if (run + 3 > 3 * len + 72) bad = 1;
+    }
   }
   __syncthreads();
   uint8_t *out = norm + fast_norm_base(off, c0, t);
   if (!bad) {
-    for (int k = 0; k < nchunks; ++k) {
+    // a warp per piece: 32 consecutive bytes per pass
+    const int lane = i & 31, wid = i >> 5;
+    for (int k = wid; k < nchunks; k += kNormLongThreads / 32) {
       const int32_t n_k = olen[k];
       if (n_k == 0) continue;
       const uint8_t *src = line_tmp + norm_piece_slot(cuts[k], k);
-      for (int32_t j = i; j < n_k; j += kNormLongThreads) out[obase[k] + j] = src[j];
+      uint8_t *dst = out + obase[k];
+      for (int32_t j = lane; j < n_k; j += 32) dst[j] = src[j];
     }
   }
   __syncthreads();
