@@ -1479,15 +1479,19 @@ k_nl_scatter(const uint8_t *buf, int64_t len, const int64_t *tile_base, uint8_t 
 
 // ---------------------------------------------------------------- unigram trainer E-step (spm_estep.cuh)
 // One thread per word, words taken in order of descending length (counting sort, so the 32 words
-// of a warp run equally long).  Words of up to 31 bytes keep their forward / backward
+// of a warp run equally long).  Words of up to 23 bytes keep their forward / backward
 // / Viterbi tables in shared memory ([position][thread]: no local-memory traffic); longer ones
 // (text without spaces) use a slice of a global scratch buffer.  expected[] is accumulated in
 // double: pieces with a hot slot (the kEstepHot - 1 highest scores, which collect most of the mass)
 // in a per-CTA shared table flushed once at the end, the rest with one global atomicAdd per node;
 // the log-likelihood and the token count are reduced per warp first.
-constexpr int kEstepThreads = 128, kEstepBins = 64;
-constexpr int kEstepPos = 32;      // words of up to 31 bytes keep their tables in shared memory
-constexpr int estep_smem_bytes(int pos) { return kEstepHot * 8 + pos * kEstepThreads * 9; }   // 45,056 bytes: 5 CTAs per SM
+constexpr int kEstepThreads = 640, kEstepBins = 64;   // ONE persistent CTA per SM (20 warps)
+constexpr int kEstepPos = 24;      // words of up to 23 bytes keep their tables (and their bytes) in shared memory
+constexpr int kEstepHotUnits = 14336;   // units of the top of the trie kept in shared memory (56 KB)
+// hot table | LogSumExp polynomials | hot units | A, BV (float), C, word (u8): 223,232 bytes
+constexpr int estep_smem_bytes(int pos) {
+  return kEstepHot * 8 + kLseN * kLseCoef * 8 + kEstepHotUnits * 4 + pos * kEstepThreads * 10;
+}
 __global__ void __launch_bounds__(256)
 k_estep_hist(const int64_t *off, int64_t n, uint32_t *hist) {
   __shared__ uint32_t sh[kEstepBins];
@@ -1526,22 +1530,30 @@ k_estep_scatter(const int64_t *off, int64_t n, uint32_t *cursor, uint32_t *perm)
 // per length class with 12 / 20 / 32 entries -- more resident warps for the short words, but the
 // tails of the classes no longer overlap: 1.25 ms against 1.16 ms.)
 template <int POS>
-__global__ void __launch_bounds__(kEstepThreads)
+__global__ void __launch_bounds__(kEstepThreads, 1)
 k_estep(EstepView ev, const int32_t *hot_ids, const uint8_t *words, const int64_t *off, const int64_t *freq,
         const uint32_t *range_lo, const uint32_t *range_hi, const uint32_t *perm, double inv_all_freq, float *scratch,
         double *expected, double *obj_ntok, float *logz) {
   extern __shared__ __align__(16) uint8_t estep_smem[];     // hot table | A | beta / Viterbi | C
   constexpr int kTab = POS * kEstepThreads;
   const int64_t lo = range_lo ? (int64_t)*range_lo : 0, n = (int64_t)*range_hi;
-  const int64_t idx = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (lo + (int64_t)blockIdx.x * blockDim.x >= n) return;   // the grid covers the whole list; most blocks of a class are empty
+  if (lo + (int64_t)blockIdx.x * blockDim.x >= n) return;
   double *s_hot = reinterpret_cast<double *>(estep_smem);
-  float *sA = reinterpret_cast<float *>(s_hot + kEstepHot), *sB = sA + kTab;
-  uint8_t *sC = reinterpret_cast<uint8_t *>(sB + kTab);
+  double *s_lse = s_hot + kEstepHot;
+  uint32_t *s_units = reinterpret_cast<uint32_t *>(s_lse + kLseN * kLseCoef);
+  float *sA = reinterpret_cast<float *>(s_units + kEstepHotUnits), *sB = sA + kTab;
+  uint8_t *sC = reinterpret_cast<uint8_t *>(sB + kTab), *sW = sC + kTab;
   for (int k = threadIdx.x; k < kEstepHot; k += kEstepThreads) s_hot[k] = 0.0;
+  // (with most of the SM's memory carved out as shared, L1 is ~30 KB: whatever every word touches sits here)
+  for (int k = threadIdx.x; k < kLseN * kLseCoef; k += kEstepThreads) s_lse[k] = ev.lse[k];
+  for (uint32_t k = threadIdx.x; k < ev.k_units; k += kEstepThreads) s_units[k] = ev.units[k];
+  ev.lse = s_lse;
+  ev.units_hot = s_units;
   __syncthreads();
   double obj = 0.0, ntok = 0.0;
-  if (idx < n) {
+  // persistent CTAs: tile k of the sorted list goes to CTA k mod gridDim (every CTA gets long and short
+  // words alike), so the hot table is zeroed and flushed once per CTA, not once per 128 words
+  for (int64_t idx = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (int64_t)gridDim.x * blockDim.x) {
     const int64_t i = perm[idx];
     const int64_t o = off[i], len = off[i + 1] - o;
     float z = 0.0f;
@@ -1553,17 +1565,20 @@ k_estep(EstepView ev, const int32_t *hot_ids, const uint8_t *words, const int64_
         if (slot) atomicAdd(&s_hot[slot], v);
         else atomicAdd(&expected[x & ev.id_mask], v);
       };
+      const uint8_t *w = words + o;
       if (len < POS) {
-        z = estep_word(ev, words + o, (int)len, f, sA + threadIdx.x, sB + threadIdx.x, sC + threadIdx.x,
-                       kEstepThreads, add, &nt);
+        uint8_t *myw = sW + threadIdx.x;
+        for (int j = 0; j < (int)len; ++j) myw[j * kEstepThreads] = w[j];
+        z = estep_word(ev, [myw](int j) -> uint32_t { return myw[j * kEstepThreads]; }, (int)len, f, sA + threadIdx.x,
+                       sB + threadIdx.x, sC + threadIdx.x, kEstepThreads, add, &nt);
       } else {
         float *base = scratch + 4 * ((o - off[0]) + i);
-        z = estep_word(ev, words + o, (int)len, f, base, base + (len + 1), (int32_t *)(base + 2 * (len + 1)), 1,
-                       add, &nt);
+        z = estep_word(ev, [w](int j) -> uint32_t { return w[j]; }, (int)len, f, base, base + (len + 1),
+                       (int32_t *)(base + 2 * (len + 1)), 1, add, &nt);
       }
       // objs[n] -= Z / all_sentence_freq with Z = freq * log-likelihood (:262-266)
-      obj = -(double)(f * z) * inv_all_freq;
-      ntok = (double)nt;
+      obj -= (double)(f * z) * inv_all_freq;
+      ntok += (double)nt;
     } else if (len != 0) {
       obj = __longlong_as_double(0x7FF8000000000000ll);   // a word of 1 MiB or more: the objective comes back NaN
     }
@@ -2805,8 +2820,9 @@ int spm_cuda_split_lines_noalloc(const spm_cuda_model *M, const char *buf, int64
 struct spm_cuda_estep {
   int device = 0;
   int V = 0;
+  int max_ctas = 1;        // resident CTAs of k_estep on the device (the grid of the persistent kernel)
   EstepView ev;
-  DevBuf d_units, d_leaf, d_hot;
+  DevBuf d_units, d_leaf, d_hot, d_lse;
   mutable std::mutex mu;
   mutable DevBuf w_words, w_off, w_freq, w_scratch, w_expected, w_out, w_logz, w_perm, w_hist;
 };
@@ -2836,8 +2852,16 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
   DEVICE_GUARD(device);
   if ((rc = upload(&E->d_units, trie.units.data(), trie.units.size() * 4))) return rc;
   if ((rc = upload(&E->d_leaf, trie.leaf.data(), trie.leaf.size() * 8))) return rc;
+  {
+    std::vector<double> lse;
+    build_lse_table(&lse);
+    if ((rc = upload(&E->d_lse, lse.data(), lse.size() * 8))) return rc;
+    E->ev.lse = (const double *)E->d_lse.p;
+  }
   E->ev.units = (const uint32_t *)E->d_units.p;
   E->ev.leaf = (const uint2 *)E->d_leaf.p;
+  E->ev.units_hot = nullptr;   // (the kernel points it at its shared-memory copy)
+  E->ev.k_units = (uint32_t)std::min<size_t>(trie.units.size(), kEstepHotUnits);
   hot_ids.resize(kEstepHot, -1);
   if ((rc = upload(&E->d_hot, hot_ids.data(), hot_ids.size() * 4))) return rc;
   E->ev.unk_score = min_score - 10.0f;   // kUnkPenalty, src/unigram_model.cc:550-551
@@ -2847,6 +2871,13 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
     if (hot_ids[k] == 0) E->ev.unk_id = (uint32_t)k << 20;
   CUDA_TRY(cudaFuncSetAttribute(k_estep<kEstepPos>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 estep_smem_bytes(kEstepPos)));
+  {
+    int occ = 0, sms = 1;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_estep<kEstepPos>, kEstepThreads,
+                                                           estep_smem_bytes(kEstepPos)));
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    E->max_ctas = std::max(1, occ) * std::max(1, sms);
+  }
   *out = E.release();
   return kOk;
 }
@@ -2854,7 +2885,7 @@ int spm_cuda_estep_create(const char *pieces, const float *scores, int V, int de
 void spm_cuda_estep_free(spm_cuda_estep *E) {
   if (!E) return;
   DeviceGuard guard(E->device);
-  for (DevBuf *b : {&E->d_units, &E->d_leaf, &E->d_hot, &E->w_words, &E->w_off, &E->w_freq, &E->w_scratch,
+  for (DevBuf *b : {&E->d_units, &E->d_leaf, &E->d_hot, &E->d_lse, &E->w_words, &E->w_off, &E->w_freq, &E->w_scratch,
                     &E->w_expected, &E->w_out, &E->w_logz, &E->w_perm, &E->w_hist})
     b->release();
   delete E;
@@ -2919,7 +2950,7 @@ int spm_cuda_estep_run(const spm_cuda_estep *E, const char *words, const int64_t
     k_estep_binscan<<<1, 32, 0, st>>>(d_hist, d_cursor);
     k_estep_scatter<<<gs, 256, 0, st>>>(d_off, n, d_cursor, (uint32_t *)E->w_perm.p);
     // (after the scatter cursor[kEstepBins - 1] = n: the end of the shortest bin)
-    const unsigned ge = (unsigned)((n + kEstepThreads - 1) / kEstepThreads);
+    const unsigned ge = (unsigned)std::min<int64_t>((n + kEstepThreads - 1) / kEstepThreads, E->max_ctas);
     k_estep<kEstepPos><<<ge, kEstepThreads, estep_smem_bytes(kEstepPos), st>>>(
         E->ev, (const int32_t *)E->d_hot.p, d_words, d_off, d_freq, nullptr, d_cursor + (kEstepBins - 1),
         (const uint32_t *)E->w_perm.p, 1.0 / all_freq, (float *)E->w_scratch.p, d_exp, d_out, d_logz);

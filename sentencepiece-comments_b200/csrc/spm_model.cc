@@ -301,6 +301,39 @@ void scan_charsmap(HostModel *m) {
 
 }  // namespace
 
+// log(exp(d) + 1) on [-kLseLo, 0]: per interval the polynomial of degree kLseCoef - 1 through the function's
+// values (long double) at the Chebyshev nodes, in powers of t = d - centre.
+void build_lse_table(std::vector<double> *tab) {
+  constexpr int N = kLseN, C = kLseCoef;
+  tab->assign((size_t)N * C, 0.0);
+  const long double h = (long double)kLseLo / N, pi = 3.14159265358979323846264338327950288L;
+  for (int k = 0; k < N; ++k) {
+    const long double centre = -((long double)k + 0.5L) * h;
+    long double a[C][C + 1];
+    for (int j = 0; j < C; ++j) {
+      const long double u = cosl((2 * j + 1) * pi / (2 * C));   // node in [-1, 1]; t = u h / 2
+      long double pw = 1.0L;
+      for (int q = 0; q < C; ++q) { a[j][q] = pw; pw *= u; }
+      a[j][C] = log1pl(expl(centre + u * h / 2));
+    }
+    for (int col = 0; col < C; ++col) {   // Gauss-Jordan with partial pivoting
+      int piv = col;
+      for (int r = col + 1; r < C; ++r) if (fabsl(a[r][col]) > fabsl(a[piv][col])) piv = r;
+      for (int q = 0; q <= C; ++q) std::swap(a[col][q], a[piv][q]);
+      for (int r = 0; r < C; ++r) {
+        if (r == col) continue;
+        const long double f = a[r][col] / a[col][col];
+        for (int q = col; q <= C; ++q) a[r][q] -= f * a[col][q];
+      }
+    }
+    long double scale = 1.0L;   // coefficient of u^q -> of t^q: / (h/2)^q
+    for (int q = 0; q < C; ++q) {
+      (*tab)[(size_t)k * C + q] = (double)(a[q][C] / a[q][q] / scale);
+      scale *= h / 2;
+    }
+  }
+}
+
 int build_estep_trie(const std::vector<std::string> &pieces, const std::vector<float> &scores, HostTrie *out,
                      float *min_score, std::string *err, std::vector<int32_t> *hot_ids) {
   if (pieces.empty() || pieces.size() != scores.size()) { *err = "no pieces are loaded."; return kInternal; }

@@ -81,6 +81,8 @@ void refresh_leaf_types(HostModel *m);
 // piece NORMAL, ids = positions, trie over all of them).  leaf = (id, score bits).
 // *min_score = min over the scores.  Returns a StatusCode and fills *err.
 // hot_ids (may be null): slot -> piece id of the hot pieces packed into the leaf words (slot 0: -1).
+// estep_softplus()'s table (spm_estep.cuh): kLseN x kLseCoef doubles.
+void build_lse_table(std::vector<double> *tab);
 int build_estep_trie(const std::vector<std::string> &pieces, const std::vector<float> &scores, HostTrie *out,
                      float *min_score, std::string *err, std::vector<int32_t> *hot_ids = nullptr);
 

@@ -105,6 +105,8 @@ def hostcore():
     L.hc_encode_batch.argtypes = [ctypes.c_void_p] * 3 + [ctypes.c_int64, ctypes.c_uint32, ctypes.c_int,
                                                          ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p,
                                                          ctypes.c_void_p]
+    L.hc_lse_table_error.restype = ctypes.c_double
+    L.hc_lse_table_error.argtypes = [ctypes.c_int64]
     L.hc_estep.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                            ctypes.c_void_p, ctypes.c_int64, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p,
                            ctypes.c_void_p]

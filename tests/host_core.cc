@@ -453,6 +453,19 @@ int hc_encode_pieces_batch(void *p, const uint8_t *text, const int64_t *off, int
   return 0;
 }
 
+// estep_softplus() against libm on m points of [-50, 0]: the largest absolute difference.
+double hc_lse_table_error(int64_t m) {
+  std::vector<double> lse;
+  build_lse_table(&lse);
+  double worst = 0;
+  for (int64_t i = 0; i <= m; ++i) {
+    const double d = -50.0 * (double)i / (double)m;
+    const double e = fabs(estep_softplus(lse.data(), d) - (double)log1pl(expl((long double)d)));
+    if (e > worst) worst = e;
+  }
+  return worst;
+}
+
 // E-step of the unigram trainer: the kernel's per-word function (spm_estep.cuh) on the CPU.
 int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *words, const int64_t *off,
              const int64_t *freq, int64_t n, double all_freq, double *expected, double *obj_ntok, float *logz) {
@@ -466,6 +479,10 @@ int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *word
   const int rc = build_estep_trie(ps, sc, &trie, &min_score, &err);
   if (rc) return rc;
   EstepView ev;
+  std::vector<double> lse;
+  build_lse_table(&lse);
+  ev.lse = lse.data();
+  ev.units_hot = nullptr; ev.k_units = 0;
   ev.units = trie.units.data(); ev.leaf = trie.leaf.data();
   ev.unk_score = min_score - 10.0f; ev.unk_id = 0; ev.id_mask = 0x0FFFFFFFu;
   for (int64_t i = 0; i < n; ++i) {
@@ -475,7 +492,8 @@ int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *word
     std::vector<int32_t> C(len + 1);
     int32_t nt = 0;
     const float f = (float)freq[i];
-    const float z = estep_word(ev, words + off[i], len, f, A.data(), B.data(), C.data(), 1,
+    const uint8_t *w = words + off[i];
+    const float z = estep_word(ev, [w](int j) -> uint32_t { return w[j]; }, len, f, A.data(), B.data(), C.data(), 1,
                                [&](uint32_t x, double v) { expected[x & ev.id_mask] += v; }, &nt);
     obj_ntok[0] -= (double)(f * z) / all_freq;
     obj_ntok[1] += nt;

@@ -79,6 +79,12 @@ def check_against_reference(exp, logz, obj, nt, freq, rexp, rlogz, robj, rnt, re
     assert np.allclose(exp, rexp, rtol=1e-3, atol=1e-5)
 
 
+def test_lse_table_accuracy(hostcore):
+    """estep_softplus() (polynomial table) against log1pl(expl(d)) on a fine grid of [-50, 0]: the float that
+    vmax + softplus rounds to then differs from the libm formula about once in 10^7 LogSumExp calls."""
+    assert hostcore.hc_lse_table_error(2_000_003) < 1e-14
+
+
 def test_closed_form_of_the_reference_test(hostcore):
     """src/unigram_model_test.cc:271-313 (LatticeTest.PopulateMarginalTest), tolerance 1e-3 there."""
     pieces = [b"A", b"B", b"C", b"AB", b"BC", b"ABC"]
