@@ -345,28 +345,43 @@ k_scatter(const int64_t *off, int64_t c0, int64_t cn, const int32_t *list, int l
 }
 
 // One thread per sentence, in sorted order (lanes of a warp: equal raw lengths).
-constexpr int kNormThreads = 256;
+// Block shape of k_normalize_fast, measured on 2.2 M Japanese lines (the kernel's time inside the normalize
+// stage): 256 threads 9.4 ms, 512 or 1024 threads 5.7 ms, 128 threads 16 ms; persistent blocks (SPM_NORM_BLOCKS
+// per SM, tiles dealt round-robin) 5 x 256: 12.9, 2 x 512: 7.6, 3 x 512: 6.6 ms -- the grid over the whole
+// chunk with 512 threads is what ships.
+#ifndef SPM_NORM_THREADS
+#define SPM_NORM_THREADS 512
+#endif
+constexpr int kNormThreads = SPM_NORM_THREADS;
+#ifndef SPM_NORM_BLOCKS
+#define SPM_NORM_BLOCKS (1 << 20)      // blocks of k_normalize_fast per SM at most (no cap)
+#endif
 __global__ void __launch_bounds__(kNormThreads)
 k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t c0, const uint8_t *lo,
                  const uint8_t *hi, const int32_t *perm, int count_idx, uint8_t *norm, int32_t *nlen,
                  int32_t *gen_list, uint32_t *counters) {
   __shared__ uint32_t first2[2048];
+  // (the grid covers the chunk at most; the list is usually far shorter -- what the word memo left over -- and
+  // a block without work must not pay for the 8 KB table)
+  const int64_t count = (int64_t)counters[count_idx];
+  if ((int64_t)blockIdx.x * blockDim.x >= count) return;
   if (mv.cm_first2 != nullptr)
     for (int k = threadIdx.x; k < 2048; k += kNormThreads) first2[k] = mv.cm_first2[k];
   __syncthreads();
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)counters[count_idx]) return;
-  const int32_t t = perm[idx];
-  const int64_t i = c0 + t;
-  const int64_t len = off[i + 1] - off[i];
-  int32_t nc = 0;
-  int32_t nl = fast_normalize(mv, first2, text + off[i], len, lo, hi, norm + fast_norm_base(off, c0, t),
-                              (int32_t)(3 * len + 72), &nc);
-  if (nl < 0 || nc > len + kFastExtraChars) {
-    gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
-    nl = -1;
+  // persistent blocks: tile k of the sorted list goes to block k mod gridDim, the table is staged once
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < count; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t t = perm[idx];
+    const int64_t i = c0 + t;
+    const int64_t len = off[i + 1] - off[i];
+    int32_t nc = 0;
+    int32_t nl = fast_normalize(mv, first2, text + off[i], len, lo, hi, norm + fast_norm_base(off, c0, t),
+                                (int32_t)(3 * len + 72), &nc);
+    if (nl < 0 || nc > len + kFastExtraChars) {
+      gen_list[atomicAdd(&counters[C_NGEN], 1u)] = t;
+      nl = -1;
+    }
+    nlen[t] = nl;
   }
-  nlen[t] = nl;
 }
 
 // Long lines: one BLOCK per line, its threads share the pieces of ~kNormChunk raw bytes.  Pieces start
@@ -1046,13 +1061,18 @@ k_ls_scatter(const int64_t *off, int64_t c0, const int32_t *list, const uint32_t
 
 // k_memo_scan: the general scan (fast_normalize_scan + MemoSink: every normalizer rule,
 // user symbols, whitespace policy, long words) over the sentences k_memo_scan_plain listed.
-__global__ void __launch_bounds__(kMemoThreads)
+#ifndef SPM_MEMO_SCAN_THREADS
+#define SPM_MEMO_SCAN_THREADS 256
+#endif
+constexpr int kMemoScanThreads = SPM_MEMO_SCAN_THREADS;
+__global__ void __launch_bounds__(kMemoScanThreads)
 k_memo_scan(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t *off, int64_t c0, const uint8_t *lo,
             const uint8_t *hi, const int32_t *slow_list, uint32_t *wslots, int32_t *nwords,
             const uint32_t *counters) {
   __shared__ uint32_t first2[2048];
+  if ((int64_t)blockIdx.x * blockDim.x >= (int64_t)counters[C_NSLOW]) return;   // (see k_normalize_fast)
   if (mv.cm_first2 != nullptr)
-    for (int k = threadIdx.x; k < 2048; k += kMemoThreads) first2[k] = mv.cm_first2[k];
+    for (int k = threadIdx.x; k < 2048; k += kMemoScanThreads) first2[k] = mv.cm_first2[k];
   __syncthreads();
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)counters[C_NSLOW]) return;
@@ -2401,7 +2421,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       const int64_t max_n_long = has_long ? std::min<int64_t>(cn, raw / kFastMaxRaw + 1) : 0;
       const unsigned gsort = (unsigned)((cn + kSortTile - 1) / kSortTile);
       const unsigned gsent = (unsigned)((cn + 255) / 256), glong = (unsigned)((max_n_long + 255) / 256);
-      static_assert(kNormThreads == 256 && kMemoThreads == 256 && kScanWarps * 32 == 256, "grids assume 256 threads");
+      static_assert(kMemoThreads == 256 && kScanWarps * 32 == 256, "grids assume 256 threads");
       // Word memo first (spm_memo.cuh): what it cannot serve is listed in w_vit and takes the
       // sort -> normalize -> Viterbi / merge path below, like every sentence does without the memo.
       const int32_t *todo = nullptr;     // nullptr: all sentences of the chunk
@@ -2436,7 +2456,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
         k_ls_scatter<<<gls, kLsThreads, 0, st>>>(d_off, c0, (const int32_t *)M->w_vit.p, d_counters, C_NSLOW,
                                                 (uint32_t *)M->w_lshist.p + kLsBins, (int32_t *)M->w_perm.p);
         launches += 3;
-        k_memo_scan<<<gsent, kMemoThreads, 0, st>>>(
+        k_memo_scan<<<(unsigned)((cn + kMemoScanThreads - 1) / kMemoScanThreads), kMemoScanThreads, 0, st>>>(
             M->mv, tb, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p,
             (uint32_t *)M->w_wslots.p + wslot_half, (int32_t *)M->w_nwords.p, d_counters);
         launches += 1;
@@ -2480,7 +2500,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       k_scatter<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, todo, C_NVIT, d_bincur, (int32_t *)M->w_perm.p,
                                       d_counters);
       if ((rc = kev_record(M, st, 0, T_NORMALIZE))) return rc;
-      k_normalize_fast<<<gsent, kNormThreads, 0, st>>>(
+      k_normalize_fast<<<(unsigned)std::min<int64_t>((cn + kNormThreads - 1) / kNormThreads, (int64_t)M->sm_count * SPM_NORM_BLOCKS), kNormThreads, 0, st>>>(
           M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_perm.p, C_NFAST,
           (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p, d_counters);
       if (has_long) {   // one block per long line; the grid covers the most long lines the chunk's bytes can hold
