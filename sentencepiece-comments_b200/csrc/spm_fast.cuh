@@ -651,7 +651,10 @@ SPM_HD int64_t norm_find_cut(const ModelView &m, const uint32_t *first2, const u
 
 // Piece `idx` = in[a..b) of a line cut by norm_find_cut: normalized into `slot` (8-byte
 // aligned, 3 * (b - a) + 72 + 8 bytes).  *content is only meaningful for piece 0.
-constexpr int kNormChunk = 128;   // raw bytes per piece (before the cut is moved to a safe position)
+#ifndef SPM_NORM_CHUNK
+#define SPM_NORM_CHUNK 128
+#endif
+constexpr int kNormChunk = SPM_NORM_CHUNK;   // raw bytes per piece (before the cut is moved to a safe position)
 SPM_HD int64_t norm_piece_slot(int64_t a, int idx) { return (3 * a + 88 * (int64_t)idx + 7) & ~(int64_t)7; }
 SPM_HDN bool norm_piece(const ModelView &m, const uint32_t *first2, const uint8_t *in, int64_t a, int64_t b,
                         const uint8_t *lo, const uint8_t *hi, uint8_t *slot, int idx, int32_t *out_len,

@@ -391,7 +391,10 @@ k_normalize_fast(ModelView mv, const uint8_t *text, const int64_t *off, int64_t 
 // suffix, zero padding).  A 33 KB line takes the time of three 128-byte pieces instead of 20 ms.
 // (Pieces of 512 bytes, one per thread: a 4..8 KB line -- most long lines -- kept 8..16 of the block's
 // 128 threads busy; 14.6 ms for the 350 MB of long lines in 2.2 M lines of Japanese text.)
-constexpr int kNormLongThreads = 128, kNormMaxChunks = kLongMaxRaw / kNormChunk;   // 512 pieces at most
+#ifndef SPM_NORM_LONG_THREADS
+#define SPM_NORM_LONG_THREADS 128
+#endif
+constexpr int kNormLongThreads = SPM_NORM_LONG_THREADS, kNormMaxChunks = kLongMaxRaw / kNormChunk;   // 512 pieces at most
 __device__ __forceinline__ int64_t norm_tmp_base(const int64_t *off, int64_t c0, int64_t t) {
   const int64_t o = off[c0 + t] - off[c0];
   return ((3 * o + 7) & ~(int64_t)7) + 88 * (o / kNormChunk) + 96 * t;
