@@ -73,6 +73,8 @@ int spm_cuda_model_set_piece_types(spm_cuda_model *model, const uint8_t *types, 
  *   "emit_blocks"       0   CTAs of the memo emit kernel per SM (0: occupancy query)
  *   "pieces_exact"      0   encode_batch_pieces: every sentence through the exact tier
  *   "bpe_route"         8192  BPE: leftover lists up to this size go to the general tier as a whole (0: never)
+ *   "fast_side"         1   thread-per-sentence Viterbi kernel keeps near-tied candidates itself (0: hands the sentence on)
+ *   "mid_lines"         0   lines of 4..8 KiB take the thread-per-sentence kernel instead of the warp kernel
  * NOT_FOUND for an unknown name.  Must not run concurrently with calls on the same model. */
 int spm_cuda_model_set_option(spm_cuda_model *model, const char *name, int64_t value);
 int spm_cuda_model_get_option(const spm_cuda_model *model, const char *name, int64_t *value);

@@ -83,8 +83,10 @@ struct ModelView {
 
 #if defined(__CUDA_ARCH__)
 SPM_HD float __uint_as_float_hd(uint32_t x) { return __uint_as_float(x); }
+SPM_HD uint32_t __float_as_uint_hd(float x) { return __float_as_uint(x); }
 #else
 SPM_HD float __uint_as_float_hd(uint32_t x) { union { uint32_t u; float f; } v; v.u = x; return v.f; }
+SPM_HD uint32_t __float_as_uint_hd(float x) { union { uint32_t u; float f; } v; v.f = x; return v.u; }
 #endif
 
 // ------------------------------------------------------------------ UTF-8

@@ -32,6 +32,7 @@ namespace spmb {
 
 constexpr uint32_t kFastUnk = 0x00FFFFFFu;   // node field of an UNK back record
 constexpr int kFastMaxRaw = 4096;            // fast tier: raw sentence length < this (bytes); also the sort key range
+constexpr int kMidMaxRaw = 8192;             // lines of kFastMaxRaw <= bytes < this: normalized in pieces, then the fast tier
 constexpr int kFastExtraChars = 16;          // fast tier: characters <= raw bytes + this
 constexpr int kLongMaxRaw = 65536;           // long lines (kFastMaxRaw <= bytes < this): same kernels, few threads
 constexpr int kNormPad = 40;                 // zero bytes guaranteed after a normalized sentence
@@ -111,9 +112,26 @@ SPM_HD void fast_prefetch_wait() {
 #endif
 }
 
+// Near ties, in line.  A position whose best candidates are within the tolerance of each other keeps up to
+// kFastCapc of them (unigram_encode()'s rule: within eps of the running maximum, exact duplicates dropped, in
+// begin order), the first in the ring as always, the others in a per-thread SIDE area in global memory -- a
+// near tie is met a few times per 10^4 characters, so the area is touched rarely and costs the common path one
+// register (`multi`: bit k = ring slot k holds more than one candidate; bit 31 = the current position does)
+// and two tests per trie hit.  Round 1 flagged such a sentence and had another kernel run it again: with the
+// tolerance growing with the running score, that was nearly every line beyond 2 KB of Japanese text.
+// Side area (32-bit words): [0, R) candidate count of the slot, [R, 2R) its running maximum, [2R, 5R) scores and
+// [5R, 8R) records of candidates 1..3; [8R, 8R + 4) the current position's count and scores 1..3; then the
+// back records of candidates 1..3 of the positions that had them: [8R + 4] = entries, pairs (character index
+// << 2 | candidate, record).  Needs R <= 31 and pieces of at most 63 characters (record: trie node, 24 bits |
+// characters, 6 bits | the predecessor's candidate, 2 bits); else, or with side == nullptr, the sentence is
+// flagged at the first near tie as before.
+constexpr int kFastCapc = 4;
+constexpr int kFastSideEntries = 56;
+constexpr int kFastSideWords = 8 * 31 + 4 + 1 + 2 * kFastSideEntries + 3;   // 368
+
 // One sentence.  s: normalized VALID UTF-8 text (8-byte aligned, followed by >= kNormPad
 // zero bytes), n bytes.  ring_bt / ring_bk: R slots, element k at [k * rstride].
-// back: this thread's own back-record array (nchars + 2 entries).
+// back: this thread's own back-record array (nchars + 2 entries).  side: kFastSideWords words, or nullptr.
 // out: ids in REVERSE order (at most nchars); returns their count.
 //
 // The loop is flattened: every iteration is either one trie step of the walk that
@@ -123,15 +141,18 @@ SPM_HD void fast_prefetch_wait() {
 // txt: two words of per-thread staging for the text prefetch, element j at [j * rstride].
 SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, float *ring_bt,
                              uint32_t *ring_bk, uint32_t *txt, int rstride, uint32_t *back, int32_t *out,
-                             uint32_t *status) {
+                             uint32_t *status, uint32_t *side = nullptr) {
   if (n <= 0) return 0;
   const int R = fv.ring;
+  if (R > 31) side = nullptr;
   const float NEG = -3.0e38f;     // "no node ends here yet" (finite, so the tie tolerance stays finite)
   const float TOL = 2.384185791015625e-07f;  // 2^-22, see unigram_encode() in spm_core.cuh
   for (int k = 0; k < R; ++k) ring_bt[k * rstride] = NEG;
   const uint32_t root = fv.units_hot[0];
   const uint32_t *sw = reinterpret_cast<const uint32_t *>(s);
   uint32_t flag = 0;
+  uint32_t multi = 0;             // see above
+  if (side) side[8 * R + 4] = 0;
   int32_t p = 0, ci = 0, ridx = 0;
   // text window: words w0..w3 = bytes [4*qw, 4*qw + 16), w4 prefetched; r = p - 4*qw in [0, 4)
   int32_t qw = 0;
@@ -145,11 +166,11 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
   uint32_t tslot = 0;             // staging slot that holds word qw + 5
   fast_prefetch_word(txt, txt_saddr, sw + 5);
   float bt_p = 0.0f;              // BOS
-  // Near-tie tolerance of the walk that starts at the current character.  A push is flagged
+  // Near-tie tolerance of the walk that starts at the current character.  A push is a near tie
   // when |bt - M| <= 2^-22 (max(|M|,|bt|) + smax) and bt != M (see unigram_encode()); since
   // |bt| <= |bt_p| + smax and a near-tied M is within the tolerance of bt, the per-character
-  // bound 2^-22 (|bt_p| + 2 smax + 1) flags a superset -- cheaper, still exact after the
-  // exact tier re-runs the flagged sentences.
+  // bound 2^-22 (|bt_p| + 2 smax + 1) catches a superset -- cheaper; the side path then applies the
+  // rule itself.
   float tol_p = (2.0f * fv.smax + 1.0f) * TOL;
   uint32_t cur = w0;
   int cl = one_char_len((uint8_t)cur);
@@ -157,6 +178,57 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
   int d = 0, k = 0;
   bool single = false;
   uint32_t *bp = back;            // back record of character ci goes to bp[0]
+  // One node (current character -> slot, score sc, record body rec = node | chars << 24).
+  auto push = [&](int slot, float sc, uint32_t rec) {
+    float bt = bt_p + sc;
+    if (multi >> 31) {            // several candidates end at the current character: first strictly greater, in order
+      const uint32_t nc = side[8 * R];
+      for (uint32_t c = 1; c < nc; ++c) {
+        const float v = __uint_as_float_hd(side[8 * R + c]) + sc;
+        if (v > bt) { bt = v; rec = (rec & 0x3FFFFFFFu) | (c << 30); }
+      }
+    }
+    const float M = ring_bt[slot * rstride];
+    const float diff = bt - M;
+    const bool near = fabsf(diff) <= tol_p && diff != 0.0f;
+    if (near || ((multi >> slot) & 1u)) {
+      if (side == nullptr) {
+        flag = ST_CAND_OVERFLOW;
+        if (diff > 0.0f) { ring_bt[slot * rstride] = bt; ring_bk[slot * rstride] = rec; }
+        return;
+      }
+      // unigram_encode()'s push on the slot's candidate list
+      const bool many = ((multi >> slot) & 1u) != 0;
+      const uint32_t cnt = many ? side[slot] : 1u;
+      const float Mrun = many ? __uint_as_float_hd(side[R + slot]) : M;
+      const float am = fabsf(Mrun), ab = fabsf(bt);
+      const float eps = ((am > ab ? am : ab) + fv.smax) * TOL;
+      if (bt - Mrun > eps) {
+        ring_bt[slot * rstride] = bt; ring_bk[slot * rstride] = rec;
+        multi &= ~(1u << slot);
+      } else if (!(Mrun - bt > eps)) {
+        bool dup = M == bt;       // an equal score loses the first-wins tie for every right score
+        for (uint32_t c = 1; c < cnt; ++c)
+          if (__uint_as_float_hd(side[2 * R + 3 * slot + (c - 1)]) == bt) dup = true;
+        if (!dup) {
+          if (cnt == (uint32_t)kFastCapc) {
+            flag = ST_CAND_OVERFLOW;
+          } else {
+            side[2 * R + 3 * slot + (cnt - 1)] = __float_as_uint_hd(bt);
+            side[5 * R + 3 * slot + (cnt - 1)] = rec;
+            side[slot] = cnt + 1;
+            side[R + slot] = __float_as_uint_hd(bt > Mrun ? bt : Mrun);
+            multi |= 1u << slot;
+          }
+        }
+      }
+      return;
+    }
+    if (diff > 0.0f) {            // strict '>' keeps the first (longest) of equals
+      ring_bt[slot * rstride] = bt;
+      ring_bk[slot * rstride] = rec;
+    }
+  };
   for (;;) {
     const uint32_t c = cur & 0xFFu;
     bool ok = (u & 0x200u) && c != 0;
@@ -174,16 +246,10 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
       cur >>= 8;
       if (v & 0x100u) {                    // a piece ends here: node (ci -> ci + k)
         const float sc = fast_ld_tiered(fv.score_hot, fv.score_hot_saddr, fv.score, child, fv.k_scores);
-        const float bt = bt_p + sc;
         int slot = ridx + k;
         if (slot >= R) slot -= R;
-        const float M = ring_bt[slot * rstride];
-        const float diff = bt - M;
-        if (fabsf(diff) <= tol_p && diff != 0.0f) flag = ST_CAND_OVERFLOW;
-        if (diff > 0.0f) {                 // strict '>' keeps the first (longest) of equals
-          ring_bt[slot * rstride] = bt;
-          ring_bk[slot * rstride] = child | ((uint32_t)k << 24);
-        }
+        if (k > 63) flag = ST_CAND_OVERFLOW;   // (does not fit the record; such models stay with the exact tier)
+        push(slot, sc, child | ((uint32_t)k << 24));
         if (k == 1) single = true;
       }
       if ((d & 3) == 0) {                  // crossed into the next 4 bytes of text
@@ -198,16 +264,9 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
     } else {
       // ---- the walk from character ci is over: move to character ci + 1
       if (!single) {  // UNK node of one character (unigram_model.cc:598-602)
-        const float bt = bt_p + fv.unk_score;
         int slot = ridx + 1;
         if (slot >= R) slot -= R;
-        const float M = ring_bt[slot * rstride];
-        const float diff = bt - M;
-        if (fabsf(diff) <= tol_p && diff != 0.0f) flag = ST_CAND_OVERFLOW;
-        if (diff > 0.0f) {
-          ring_bt[slot * rstride] = bt;
-          ring_bk[slot * rstride] = kFastUnk | (1u << 24);
-        }
+        push(slot, fv.unk_score, kFastUnk | (1u << 24));
       }
       p += cl;
       r += cl;
@@ -217,6 +276,24 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
       bt_p = ring_bt[ridx * rstride];
       *bp = ring_bk[ridx * rstride];
       ring_bt[ridx * rstride] = NEG;
+      multi &= 0x7FFFFFFFu;
+      if ((multi >> ridx) & 1u) {          // the candidates of the new position: scores for its pushes, records to the side list
+        multi = (multi & ~(1u << ridx)) | 0x80000000u;
+        const uint32_t nc = side[ridx];
+        side[8 * R] = nc;
+        uint32_t ne = side[8 * R + 4];
+        for (uint32_t c2 = 1; c2 < nc; ++c2) {
+          side[8 * R + c2] = side[2 * R + 3 * ridx + (c2 - 1)];
+          if (ne < (uint32_t)kFastSideEntries) {
+            side[8 * R + 5 + 2 * ne] = ((uint32_t)ci << 2) | c2;
+            side[8 * R + 6 + 2 * ne] = side[5 * R + 3 * ridx + (c2 - 1)];
+            ++ne;
+          } else {
+            flag = ST_CAND_OVERFLOW;
+          }
+        }
+        side[8 * R + 4] = ne;
+      }
       if (p >= n) break;
       tol_p = (fabsf(bt_p) + 2.0f * fv.smax + 1.0f) * TOL;
       if (r >= 4) {                        // slide the window by one word; word qw + 5 was requested one slide ago
@@ -233,16 +310,33 @@ SPM_HDN int32_t fast_unigram(const FastView &fv, const uint8_t *s, int32_t n, fl
       u = root; d = 0; k = 0; single = false;
     }
   }
+  // EOS (score 0) picks among the candidates that end at the last character (first strictly greater)
+  uint32_t pick = 0;
+  if (multi >> 31) {
+    float best = bt_p + 0.0f;
+    const uint32_t nc = side[8 * R];
+    for (uint32_t c2 = 1; c2 < nc; ++c2) {
+      const float v2 = __uint_as_float_hd(side[8 * R + c2]) + 0.0f;
+      if (v2 > best) { best = v2; pick = c2; }
+    }
+  }
   // backtrace; runs of unknown pieces collapse to one id (sentencepiece_processor.cc:525-529)
   int32_t cnt = 0;
   bool prev_unk = false;
+  int32_t se = side ? (int32_t)side[8 * R + 4] : 0;   // side entries are in ascending character order: search from the end
   while (ci > 0) {
-    const uint32_t rec = back[ci];
+    uint32_t rec = back[ci];
+    if (pick != 0) {
+      const uint32_t key = ((uint32_t)ci << 2) | pick;
+      while (se > 0 && side[8 * R + 5 + 2 * (se - 1)] > key) --se;
+      rec = (se > 0 && side[8 * R + 5 + 2 * (se - 1)] == key) ? side[8 * R + 6 + 2 * (se - 1)] : rec;
+    }
     const uint32_t node = rec & 0x00FFFFFFu;
     const bool is_unk = node == kFastUnk;
     if (!(is_unk && prev_unk)) out[cnt++] = is_unk ? fv.unk_id : (int32_t)SPM_LDG(fv.leaf_id + node);
     prev_unk = is_unk;
-    ci -= (int32_t)(rec >> 24);
+    ci -= (int32_t)((rec >> 24) & 0x3Fu);
+    pick = rec >> 30;
   }
   *status |= flag;
   return cnt;

@@ -98,7 +98,8 @@ constexpr uint32_t ST_PACKED = 1u << 18;  // word memo: ids forward, packed with
 
 // device-side counters of one chunk
 enum { C_WORK = 0, C_NFAST = 1, C_NGEN = 2, C_STATUS_OR = 3, C_WORK_LONG = 4, C_NLONG = 5,
-       C_NVIT = 6, C_WORK_VIT = 7, C_NVITL = 8, C_WORK_VITL = 9, C_NNEW = 10, C_NSLOW = 11, C_NRETRY = 12, C_COUNT = 16 };
+       C_NVIT = 6, C_WORK_VIT = 7, C_NVITL = 8, C_WORK_VITL = 9, C_NNEW = 10, C_NSLOW = 11, C_NRETRY = 12,
+       C_NMID = 13, C_WORK_MID = 14, C_COUNT = 16 };
 // k_publish snapshot (int64 slots): counters | scalars | running id total of chunk k
 constexpr int kPubScal = C_COUNT, kPubTot = C_COUNT + 8;
 
@@ -244,7 +245,9 @@ __device__ __forceinline__ int64_t fast_stage_base(const int64_t *off, int64_t c
 constexpr int kSortThreads = 1024, kSortItems = 8, kSortTile = kSortThreads * kSortItems;
 __global__ void __launch_bounds__(kSortThreads)
 k_hist(const int64_t *off, int64_t c0, int64_t cn, const int32_t *list, int list_cnt, int32_t *cnt,
-       uint32_t *status, uint32_t *hist, int32_t *gen_list, int32_t *long_list, uint32_t *counters) {
+       uint32_t *status, uint32_t *hist, int32_t *gen_list, int32_t *long_list, int32_t *mid_list, uint32_t *counters) {
+  // mid_list (may be null): lines of kFastMaxRaw <= bytes < kMidMaxRaw get a list of their own -- normalized in
+  // pieces like the long ones, encoded by k_encode_fast like the short ones
   // list == nullptr: all cn sentences of the chunk; else the counters[list_cnt] listed ones
   // (what the word memo left over; their cnt / status are initialised already)
   __shared__ uint32_t sh[kFastMaxRaw];
@@ -263,6 +266,7 @@ k_hist(const int64_t *off, int64_t c0, int64_t cn, const int32_t *list, int list
         status[t] = 0;
       }
       if (len >= kLongMaxRaw) gen_list[atomicAdd(&counters[C_NGEN], 1u)] = (int32_t)t;
+      else if (len >= kFastMaxRaw && len < kMidMaxRaw && mid_list) mid_list[atomicAdd(&counters[C_NMID], 1u)] = (int32_t)t;
       else if (len >= kFastMaxRaw) long_list[atomicAdd(&counters[C_NLONG], 1u)] = (int32_t)t;
       else if (len > 0) atomicAdd(&sh[len], 1u);
     }
@@ -552,14 +556,17 @@ __global__ void __launch_bounds__(kFastThreads, 1)
 k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm, const int32_t *nlen,
               const int32_t *perm, int count_idx, int work_idx, int max_warps, uint32_t *back, int64_t back_rows,
               int32_t *stage, int32_t *cnt, uint32_t *status, int32_t *flag_list, int flag_idx, uint32_t *counters,
-              uint32_t warp_route) {
+              uint32_t warp_route, int route_idx, int side_words) {
+  // side_words: kFastSideWords at the end of every thread's back_rows hold the near-tied candidates
+  // (fast_unigram), or 0: a sentence with a near tie is flagged.  route_idx: the list whose size decides the
+  // routing below (the mid-length pass follows the main list's decision)
   // flag_list / flag_idx: where sentences with near-tied candidates go -- the list of k_encode_warp
   // (keeps kWarpCapc candidates per position) when that kernel follows, else the general tier's
   extern __shared__ __align__(16) uint32_t smem[];
   // A short list (what the word memo leaves over: a few thousand sentences with rare words) is
   // latency-bound here -- one thread walks a whole sentence through cold trie paths -- so it is
   // handed to k_encode_warp as a whole: 32 lanes per sentence, 6 x shorter on 6 k sentences.
-  if (warp_route != 0 && counters[count_idx] <= warp_route) {
+  if (warp_route != 0 && counters[route_idx] <= warp_route) {
     const uint32_t nf = counters[count_idx];
     for (uint32_t i = blockIdx.x * kFastThreads + threadIdx.x; i < nf; i += gridDim.x * kFastThreads)
       flag_list[atomicAdd(&counters[flag_idx], 1u)] = perm[i];
@@ -599,7 +606,8 @@ k_encode_fast(FastParams fp, const int64_t *off, int64_t c0, const uint8_t *norm
       const int32_t c = nl <= 0 ? 0 :
                         fast_unigram(fv, norm + fast_norm_base(off, c0, t), nl, ring_bt + threadIdx.x,
                                      ring_bk + threadIdx.x, txt + threadIdx.x, kFastThreads, myback,
-                                     stage + fast_stage_base(off, c0, t), &st);
+                                     stage + fast_stage_base(off, c0, t), &st,
+                                     side_words ? myback + (back_rows - side_words) : nullptr);
       if (st) {
         flag_list[atomicAdd(&counters[flag_idx], 1u)] = t;
         if (flag_idx != C_NGEN) atomicAdd(&counters[C_NRETRY], 1u);
@@ -1656,6 +1664,8 @@ struct Options {
   int64_t warp_route = 262144;    // leftover lists up to this size go to k_encode_warp as a whole (0: never)
   int64_t emit_blocks = 0;        // CTAs of k_memo_emit per SM (0: occupancy query)
   int64_t pieces_exact = 0;       // pieces path: every sentence through the exact tier
+  int64_t fast_side = 1;          // k_encode_fast keeps near-tied candidates itself (0: flags the sentence, round 1)
+  int64_t mid_lines = 0;          // lines of 4..8 KiB: second pass of k_encode_fast instead of the warp kernel (measured: a loss, see below)
   int64_t bpe_route = 8192;       // BPE leftover lists up to this size go to the general tier as a whole (0: never)
 };
 
@@ -1674,7 +1684,7 @@ struct spm_cuda_model {
   mutable std::mutex mu;
   mutable bool lshist_zeroed = false;
   mutable DevBuf w_lshist, w_text, w_off, w_ids, w_idoff, w_norm, w_stage, w_vstage, w_spos, w_nlen, w_nchars, w_cnt, w_status, w_srcoff,
-      w_perm, w_genlist, w_longlist, w_wslots, w_wbase, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
+      w_perm, w_genlist, w_longlist, w_midlist, w_wslots, w_wbase, w_nwords, w_vit, w_vitl, w_memo, w_mres, w_movf, w_wback, w_ntmp, w_newlist, w_wtext, w_wlen, w_hist, w_counters, w_back, w_partial, w_scalars, g_need, g_noff, g_norm, g_stage,
       g_nlen, g_words, g_woff, g_scratch, g_status, g_rbase, g_rscratch;
   mutable DevBuf px[20];   // workspace of the pieces / decode / dense calls (spm_pieces.inc)
   mutable int emit_blocks = 0;      // resident CTAs of k_memo_emit per SM (occupancy query, first use)
@@ -1705,7 +1715,7 @@ struct spm_cuda_model {
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2, &m->d_cont2,
             &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
             &m->w_stage, &m->w_vstage, &m->w_spos, &m->w_lshist, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
-            &m->w_genlist, &m->w_longlist, &m->w_wslots, &m->w_wbase, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
+            &m->w_genlist, &m->w_longlist, &m->w_midlist, &m->w_wslots, &m->w_wbase, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
             &m->g_noff, &m->g_norm, &m->g_stage, &m->g_nlen, &m->g_words, &m->g_woff, &m->g_scratch, &m->g_status, &m->g_rbase, &m->g_rscratch,
             &m->px[0], &m->px[1], &m->px[2], &m->px[3], &m->px[4], &m->px[5], &m->px[6], &m->px[7], &m->px[8], &m->px[9],
@@ -2054,7 +2064,7 @@ static int64_t *option_slot(Options *o, const char *name) {
   const struct { const char *name; int64_t *p; } table[] = {
       {"memo", &o->memo}, {"memo_bits", &o->memo_bits}, {"host_chunks", &o->host_chunks},
       {"host_chunk_min", &o->host_chunk_min}, {"max_chunk", &o->max_chunk}, {"warp", &o->warp},
-      {"scan_per_sentence", &o->scan_per_sentence}, {"warp_route", &o->warp_route},
+      {"scan_per_sentence", &o->scan_per_sentence}, {"warp_route", &o->warp_route}, {"fast_side", &o->fast_side}, {"mid_lines", &o->mid_lines},
       {"emit_blocks", &o->emit_blocks}, {"pieces_exact", &o->pieces_exact}, {"bpe_route", &o->bpe_route}};
   for (const auto &e : table)
     if (strcmp(e.name, name) == 0) return e.p;
@@ -2398,7 +2408,9 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       if ((rc = M->w_perm.ensure(cn * 4))) return rc;
       if ((rc = M->w_genlist.ensure(cn * 4))) return rc;
       // back-pointer rows: one per character (<= raw + kFastExtraChars) + BOS/EOS rows
-      const int64_t back_rows = (max_raw + kFastExtraChars + 8 + 3) & ~(int64_t)3;
+      // (+ the side area of fast_unigram's near-tied candidates, when the model's ring fits its bit mask)
+      const int side_words = (M->fast_kind == 1 && M->hm.max_piece_chars + 1 <= 31 && M->opt.fast_side != 0) ? kFastSideWords : 0;
+      const int64_t back_rows = ((max_raw + kFastExtraChars + 8 + 3) & ~(int64_t)3) + side_words;
       // long lines (kFastMaxRaw <= bytes < kLongMaxRaw): same kernels over long_list, on as
       // many warps per SM as a 2 GiB back-pointer budget allows
       const bool has_long = max_len >= kFastMaxRaw && max_long >= kFastMaxRaw;
@@ -2414,6 +2426,18 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       const uint32_t warp_route = (uint32_t)std::max<int64_t>(0, std::min<int64_t>(M->opt.warp_route, 0x7FFFFFFF));
       const bool fast_may_run = !(warp_ok && warp_route != 0 && (uint64_t)cn <= warp_route);
       size_t back_bytes = fast_may_run ? (size_t)back_rows * M->sm_count * kFastThreads * 4 : 0;
+      // Option "mid_lines": lines of 4..8 KiB normalized in pieces like the long ones, then a second pass of
+      // k_encode_fast (one thread per line is ~6 x cheaper per byte than the warp kernel; needs the side area: a
+      // fifth of these lines meets a near tie).  OFF: 2.2 M Japanese lines hold 58 k such lines -- 12 warps per SM,
+      // every one a chain of 8 KB of dependent trie steps and scattered back-record stores: 33.8 ms for the
+      // Viterbi stage against 28.2 ms with these lines in the warp kernel.
+      const bool use_mid = warp_ok && side_words != 0 && fast_may_run && has_long && M->opt.mid_lines != 0;
+      const int64_t back_rows_mid =
+          ((std::min<int64_t>(max_long, kMidMaxRaw - 1) + kFastExtraChars + 8 + 3) & ~(int64_t)3) + side_words;
+      if (use_mid) {
+        back_bytes = std::max(back_bytes, (size_t)back_rows_mid * M->sm_count * kFastThreads * 4);
+        if ((rc = M->w_midlist.ensure((size_t)std::min<int64_t>(cn, raw / kFastMaxRaw + 1) * 4))) return rc;
+      }
       if (has_long && !warp_ok)
         back_bytes = std::max(back_bytes, (size_t)back_rows_long * M->sm_count * long_warps * 32 * 4);
       if (M->fast_kind == 1 && back_bytes > 0 && (rc = M->w_back.ensure(back_bytes))) return rc;
@@ -2498,7 +2522,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       }
       k_hist<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, todo, C_NVIT, (int32_t *)M->w_cnt.p,
                                    (uint32_t *)M->w_status.p, d_hist, (int32_t *)M->w_genlist.p,
-                                   (int32_t *)M->w_longlist.p, d_counters);
+                                   (int32_t *)M->w_longlist.p, use_mid ? (int32_t *)M->w_midlist.p : nullptr, d_counters);
       k_binscan<<<1, 1024, 0, st>>>(d_hist, d_bincur, d_counters);
       k_scatter<<<gsort, kSortThreads, 0, st>>>(d_off, c0, cn, todo, C_NVIT, d_bincur, (int32_t *)M->w_perm.p,
                                       d_counters);
@@ -2512,6 +2536,13 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
             M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_longlist.p, C_NLONG,
             (uint8_t *)M->w_ntmp.p, (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p,
             d_counters);
+        if (use_mid) {
+          k_normalize_long<<<(unsigned)max_n_long, kNormLongThreads, 0, st>>>(
+              M->mv, d_text, d_off, c0, d_text + text_lo, d_text + text_hi, (const int32_t *)M->w_midlist.p, C_NMID,
+              (uint8_t *)M->w_ntmp.p, (uint8_t *)M->w_norm.p, (int32_t *)M->w_nlen.p, (int32_t *)M->w_genlist.p,
+              d_counters);
+          launches += 1;
+        }
       }
       if ((rc = kev_record(M, st, 1))) return rc;
       launches += has_long ? 5 : 4;
@@ -2525,7 +2556,15 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
             M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_a, cnt_a, work_a,
             kFastThreads / 32, (uint32_t *)M->w_back.p, back_rows, d_vstage, (int32_t *)M->w_cnt.p,
             (uint32_t *)M->w_status.p, (int32_t *)(warp_ok ? M->w_longlist.p : M->w_genlist.p),
-            warp_ok ? C_NLONG : C_NGEN, d_counters, warp_ok ? warp_route : 0u);
+            warp_ok ? C_NLONG : C_NGEN, d_counters, warp_ok ? warp_route : 0u, C_NFAST, side_words);
+        if (use_mid) {
+          k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
+              M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p,
+              (const int32_t *)M->w_midlist.p, C_NMID, C_WORK_MID, kFastThreads / 32, (uint32_t *)M->w_back.p,
+              back_rows_mid, d_vstage, (int32_t *)M->w_cnt.p, (uint32_t *)M->w_status.p, (int32_t *)M->w_longlist.p,
+              C_NLONG, d_counters, warp_route, C_NFAST, side_words);
+          launches += 1;
+        }
         if (warp_ok) {
           // one warp per line, exact candidate lists (spm_warp.cuh); back records: kWarpCapc rows of
           // `wstride` per resident warp, at most 8 GiB in all (the kernel is a chain of dependent shared-memory steps per
@@ -2552,7 +2591,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
           k_encode_fast<<<M->sm_count, kFastThreads, M->fast_smem, st>>>(
               M->fp, d_off, c0, (const uint8_t *)M->w_norm.p, (const int32_t *)M->w_nlen.p, list_b, cnt_b, work_b,
               long_warps, (uint32_t *)M->w_back.p, back_rows_long, d_vstage, (int32_t *)M->w_cnt.p,
-              (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, C_NGEN, d_counters, 0u);
+              (uint32_t *)M->w_status.p, (int32_t *)M->w_genlist.p, C_NGEN, d_counters, 0u, cnt_b, 0);
           launches += 1;
         }
       } else {
@@ -2591,7 +2630,7 @@ static int encode_batch_locked(const spm_cuda_model *M, const char *text, const 
       tr("fast kernel done, chunk", (long)kc);
       if (host && (rc = flush_outputs(kc))) return rc;   // earlier chunks are complete by now
       n_general += hc[C_NGEN];
-      n_viterbi += hc[C_NFAST] + hc[C_NLONG] - hc[C_NRETRY];
+      n_viterbi += hc[C_NFAST] + hc[C_NMID] + hc[C_NLONG] - hc[C_NRETRY];
       n_memo_words += hc[C_NNEW];
       if ((rc = run_general(M, st, d_text, d_off, c0, (const int32_t *)M->w_genlist.p, hc[C_NGEN], false,
                             &launches)))

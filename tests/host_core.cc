@@ -148,6 +148,7 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
   const ModelView &mv = h->mv;
   const bool use_memo = capc_arg == -1 && h->hm.memo_ok;
   const int capc = capc_arg == -1 ? 0 : capc_arg;
+  const bool fast_side = getenv("HC_FAST_NO_SIDE") == nullptr;   // near ties of the fast tier in line (default) or flagged
   // word memo state of this call (small table: probe-exhaustion paths get exercised too)
   std::vector<MemoKey> mkeys;
   std::vector<MemoRes> mres;
@@ -272,7 +273,10 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
       std::vector<float> rbt(fv.ring);
       std::vector<uint32_t> rbk(fv.ring), back(nl + 12), txt(2);
       std::vector<int32_t> rev(nl + 1);
-      cnt = fast_unigram(fv, (const uint8_t *)tbuf.data(), nl, rbt.data(), rbk.data(), txt.data(), 1, (uint32_t *)(((uintptr_t)back.data() + 15) & ~(uintptr_t)15), rev.data(), &st);
+      std::vector<uint32_t> side(kFastSideWords, 0xDEADBEEFu);   // (the function initialises what it reads)
+      cnt = fast_unigram(fv, (const uint8_t *)tbuf.data(), nl, rbt.data(), rbk.data(), txt.data(), 1, (uint32_t *)(((uintptr_t)back.data() + 15) & ~(uintptr_t)15), rev.data(), &st,
+                         fast_side ? side.data() : nullptr);
+      if (!(st & ST_CAND_OVERFLOW) && fast_side) st |= 1u << 24;   // (served with the side area in use)
       if (st & ST_CAND_OVERFLOW) {
         // reported; the result comes from the exact tier as in the library: 8 candidates per
         // position, then the retry with room for every candidate

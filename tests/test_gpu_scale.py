@@ -192,7 +192,8 @@ def test_memo_overflow_rows(spm_b200):
                                           ("ref_ja_8k", "wagahai"), ("botchan_uni2k_ud", "botchan"),
                                           ("botchan_bpe2k_ud", "botchan")])
 @pytest.mark.parametrize("opts", [{"memo": 0}, {"warp": 0}, {"scan_per_sentence": 1}, {"memo": 0, "warp": 0},
-                                  {"emit_blocks": 1}, {"max_chunk": 777}])
+                                  {"emit_blocks": 1}, {"max_chunk": 777}, {"fast_side": 0, "warp_route": 0},
+                                  {"mid_lines": 1, "warp_route": 0}])
 def test_option_paths(spm_b200, corpora, model, corpus, opts):
     mb = model_bytes(model)
     sp = load(spm_b200, mb, **opts)

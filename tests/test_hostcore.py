@@ -63,6 +63,38 @@ def test_core_near_tie_retry(make_hostcore):
         assert np.array_equal(go, wo) and np.array_equal(gi, wi), capc
 
 
+@pytest.mark.parametrize("model", ["ref_ja_8k", "wagahai_uni"])
+def test_fast_tier_near_ties_in_line(make_hostcore, model, monkeypatch):
+    """fast_unigram keeps near-tied candidates itself (side area) instead of flagging the sentence: on long
+    Japanese lines -- where the tolerance, which grows with the running score, meets a near tie almost surely --
+    nearly every line is served by the fast tier itself (status bit 24), with the reference's ids; with the side
+    area off (round 1's behaviour) most of these lines are flagged (status bit 2) and re-run by the exact tier."""
+    from tools import synth
+    lines = [l for l in synth.read_gz_lines("corpus_ja_wagahai.txt.gz") if len(l) >= 1500]
+    # longer ones still: pairs of lines glued together (up to ~40 KB)
+    lines += [a + b for a, b in zip(lines[::2], lines[1::2])][:40]
+    text, off = synth.pack_lines(lines)
+    mb = model_bytes(model)
+    chk, _ = checker(mb)
+    wi, wo = chk.encode_batch(text, off)
+    hc = make_hostcore(mb)
+    gi, go, st = hc.encode_batch(text, off, capc=0)
+    assert np.array_equal(go, wo) and np.array_equal(gi, wi)
+    served = int(((st >> 24) & 1).sum())
+    monkeypatch.setenv("HC_FAST_NO_SIDE", "1")
+    gi, go, st0 = hc.encode_batch(text, off, capc=0)
+    assert np.array_equal(go, wo) and np.array_equal(gi, wi)
+    flagged0 = int(((st0 >> 2) & 1).sum())
+    print("%s: %d lines, served in line %d, flagged without the side area %d" % (model, len(lines), served, flagged0))
+    n = np.diff(off)
+    for lo, hi in ((1500, 4096), (4096, 8192), (8192, 16384), (16384, 1 << 20)):
+        m = (n >= lo) & (n < hi)
+        print("   %6d..%7d bytes: %3d lines, %3d flagged without the side area, %3d not served in line" % (
+            lo, hi, m.sum(), ((st0 >> 2) & 1)[m].sum(), m.sum() - ((st >> 24) & 1)[m].sum()))
+    assert flagged0 >= 10, "these lines were expected to meet near ties"
+    assert served >= len(lines) - max(2, len(lines) // 20)
+
+
 @pytest.mark.parametrize("model", mf.EDGE_MODELS)
 def test_core_edge_sentences(make_hostcore, corpora, ref_ids, model):
     text, off = corpora["edge"]
