@@ -799,7 +799,7 @@ k_memo_scan_plain(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
   else if (len > 0 && !staged) nw = -2;
   else if (len > 0)
     nw = memo_scan_plain(tb, &stage[wid][0] + ((text + o0) - src), (int32_t)len, mv.add_dummy_prefix ? 1 : 0,
-                         wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4);
+                         wslots + memo_wslot_base(off, c0, t), (int32_t)(len >> 1) + 4, memo_relax_of(mv));
   if (nw == -2) slow_list[atomicAdd(&counters[C_NSLOW], 1u)] = (int32_t)t;
   wbase[t] = (uint32_t)memo_wslot_base(off, c0, t) + (nw == -2 ? half : 0u);
   nwords[t] = nw;
@@ -886,6 +886,7 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
     if (lane == 31) atomicOr(&sh.bmap[b_rel >> 5], 1u << (b_rel & 31));
     __syncwarp();
     // ---- sweep
+    const int relax = memo_relax_of(mv);   // leading / trailing / repeated spaces (and tabs) only separate words
     const uint8_t *bm8 = reinterpret_cast<const uint8_t *>(sh.bmap);
     int total = 0, total_e = 0;
     bool over = false;
@@ -897,7 +898,7 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
         const uint64_t w = *reinterpret_cast<const uint64_t *>(&sh.stage[g]);
         const uint32_t pb = g > 0 ? sh.stage[g - 1] : 0u, nb = sh.stage[g + 8];
         const uint32_t b9 = (uint32_t)bm8[g >> 3] | ((uint32_t)bm8[(g >> 3) + 1] << 8);
-        m = sw_chunk_masks(w, pb, nb, b9, a_rel - g, b_rel - g);
+        m = sw_chunk_masks(w, pb, nb, b9, a_rel - g, b_rel - g, relax);
       }
       const uint32_t mine = (uint32_t)__popc(m.ws) | ((uint32_t)__popc(m.we) << 16);
       uint32_t inc = mine;
@@ -909,11 +910,8 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       const uint32_t all = __shfl_sync(0xFFFFFFFFu, inc, 31);
       if (total + (int)(all & 0xFFFFu) > kSwCap) { over = true; break; }
       int ks = total + (int)((inc - mine) & 0xFFFFu), ke = total_e + (int)((inc - mine) >> 16);
-      // bit 15: the word begins its sentence (the dummy prefix decides its first key bit)
-      for (uint32_t x = m.ws; x; x &= x - 1) {
-        const int at = __ffs(x) - 1;
-        sh.wpos[ks++] = (uint16_t)((g + at) | (((m.b >> at) & 1u) << 15));
-      }
+      // (bit 15 -- the word begins its sentence: the dummy prefix decides its first key bit -- is set below)
+      for (uint32_t x = m.ws; x; x &= x - 1) sh.wpos[ks++] = (uint16_t)(g + __ffs(x) - 1);
       for (uint32_t x = m.we; x; x &= x - 1) sh.wend[ke++] = (uint16_t)(g + __ffs(x) - 1);
       for (uint32_t x = m.bad; x; x &= x - 1) atomicOr(&sh.flags[sw_owner(sh.sstart, g + __ffs(x) - 1)], 2u);
       total += (int)(all & 0xFFFFu);
@@ -923,7 +921,7 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
     if (over) {
       if (len > 0)
         nw = memo_scan_plain(tb, &sh.stage[s_rel], (int32_t)len, mv.add_dummy_prefix ? 1 : 0, wslots + wb,
-                             (int32_t)(len >> 1) + 4);
+                             (int32_t)(len >> 1) + 4, relax);
     } else {
       // words before my sentence = starts listed below my first byte
       int first = 0;
@@ -935,6 +933,8 @@ k_memo_scan_words(ModelView mv, MemoTable tb, const uint8_t *text, const int64_t
       sh.fw[lane] = (uint16_t)first;
       const int next = __shfl_down_sync(0xFFFFFFFFu, first, 1);
       nw = (lane == 31 ? total : next) - first;
+      // the first word of a sentence (not necessarily at its first byte: leading spaces) carries bit 15
+      if (nw > 0) sh.wpos[first] |= 0x8000u;
       __syncwarp();
       // ---- words
       const uint32_t wbw = (uint32_t)memo_wslot_base(off, c0, tw);   // the warp's words: wl[0 .. total)
@@ -1806,7 +1806,7 @@ int upload_model(spm_cuda_model *M) {
   v.max_score = hm.max_score; v.smax = hm.smax; v.ring = hm.ring;
   v.add_dummy_prefix = hm.add_dummy_prefix; v.remove_extra_ws = hm.remove_extra_ws;
   v.escape_ws = hm.escape_ws; v.ws_suffix = hm.ws_suffix; v.has_unused = hm.has_unused;
-  v.ascii_plain = hm.ascii_plain;
+  v.ascii_plain = hm.ascii_plain; v.ws_tab = hm.ws_tab;
 
   CUDA_TRY(cudaDeviceGetAttribute(&M->sm_count, cudaDevAttrMultiProcessorCount, M->device));
   return configure_fast(M);

@@ -288,8 +288,13 @@ struct MemoSink {
 // s[0..n) must be readable in aligned 8-byte words up to 16 bytes past the end.
 // Returns the word count, -1 when the memo cannot serve the sentence, or -2 when the
 // sentence is not of this shape (the general scan, fast_normalize_scan + MemoSink, decides).
+// relax (memo_relax_of): 1 = the model removes extra whitespace (leading, trailing and repeated spaces vanish
+// before the dummy prefix is added, src/normalizer.cc:88-211), so such spaces only separate words here; 2 = and a
+// TAB normalizes to exactly one space (ModelView::ws_tab), so it is such a separator too; 0 = they make the
+// sentence unfit (-2).
+SPM_HD int memo_relax_of(const ModelView &m) { return m.remove_extra_ws ? (m.ws_tab ? 2 : 1) : 0; }
 SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n, int prefix0, uint32_t *slots,
-                                int32_t cap) {
+                                int32_t cap, int relax = 0) {
   const uint8_t *q = (const uint8_t *)((uintptr_t)s & ~(uintptr_t)7);
   int r = (int)(s - q);
   uint64_t a0 = fast_load8(q), a1 = fast_load8(q + 8);
@@ -303,6 +308,12 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
   for (;;) {
     const uint64_t w = fast_window(a0, a1, r);
     const int32_t rem = n - p;
+    if (relax && pos == 0 && !tail && ((w & 0xFFu) == 0x20u || (relax == 2 && (w & 0xFFu) == 0x09u))) {   // a separator where a word would begin: skip it
+      p += 1; r += 1;
+      if (p >= n) break;
+      if (r >= 8) { r -= 8; a0 = a1; q += 8; a1 = fast_load8(q + 8); }
+      continue;
+    }
     // 0x80 marks bytes < 0x21 or > 0x7E (borrows / carries only disturb bytes above the first mark)
     const uint64_t np = (((w - 0x2121212121212121ull) & ~w) | ((w + 0x0101010101010101ull) | w)) & 0x8080808080808080ull;
     int run = np ? (ffs64(np) - 1) >> 3 : 8;
@@ -314,9 +325,9 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
       run = 7;                                   // keep the successor in sight
     } else {
       const uint32_t b = (uint32_t)(w >> (8 * run)) & 0xFFu;
-      if (b != 0x20u) return -2;                 // control / non-ASCII: rules may apply
+      if (b != 0x20u && !(relax == 2 && b == 0x09u)) return -2;   // control / non-ASCII: rules may apply
       endw = true; skip = 1;
-      if (run + 1 >= rem) return -2;             // trailing space
+      if (run + 1 >= rem && !relax) return -2;   // trailing space
     }
     if (run == 0) return -2;                     // leading / repeated space
     uint64_t wm = w & (0xFFFFFFFFFFFFFFFFull >> (8 * (8 - run)));
@@ -372,19 +383,23 @@ struct SwMasks {
 SPM_HD uint32_t sw_gather(uint64_t f) {   // bit 7 of byte j -> bit j
   return (uint32_t)(((f >> 7) * 0x0102040810204080ull) >> 56);
 }
-SPM_HD SwMasks sw_chunk_masks(uint64_t w, uint32_t pb, uint32_t nb, uint32_t b9, int lo, int hi) {
+SPM_HD SwMasks sw_chunk_masks(uint64_t w, uint32_t pb, uint32_t nb, uint32_t b9, int lo, int hi, int relax = 0) {
   const uint64_t H = 0x8080808080808080ull, L7 = 0x7F7F7F7F7F7F7F7Full;
   const uint64_t lw = w & L7;
   const uint64_t ge21 = (lw | H) - 0x2121212121212121ull;   // bit 7: low seven bits >= 0x21 (no borrow leaves a byte)
   const uint64_t le7e = ~(lw + 0x0101010101010101ull);      // bit 7: low seven bits <= 0x7E (no carry leaves a byte)
   const uint64_t x = w ^ 0x2020202020202020ull;
-  const uint64_t spf = ~(((x & L7) + L7) | x) & H;          // byte == 0x20
+  uint64_t spf = ~(((x & L7) + L7) | x) & H;                // byte == 0x20
+  if (relax == 2) {                                         // ... or a TAB
+    const uint64_t x9 = w ^ 0x0909090909090909ull;
+    spf |= ~(((x9 & L7) + L7) | x9) & H;
+  }
   lo = lo < 0 ? 0 : (lo > 8 ? 8 : lo);
   hi = hi < 0 ? 0 : (hi > 8 ? 8 : hi);
   const uint32_t valid = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
   const uint32_t good = sw_gather(ge21 & le7e & ~w & H) & valid;
   const uint32_t sp = sw_gather(spf);
-  const uint32_t pgood = (pb >= 0x21u && pb <= 0x7Eu) ? 1u : 0u, psp = pb == 0x20u ? 1u : 0u;
+  const uint32_t pgood = (pb >= 0x21u && pb <= 0x7Eu) ? 1u : 0u, psp = (pb == 0x20u || (relax == 2 && pb == 0x09u)) ? 1u : 0u;
   const uint32_t ngood = (nb >= 0x21u && nb <= 0x7Eu) ? 0x80u : 0u;
   const uint32_t bcur = b9 & 0xFFu, bnext = (b9 >> 1) & 0xFFu;
   const uint32_t gprev = (good << 1) | pgood, gnext = (good >> 1) | ngood;
@@ -392,7 +407,8 @@ SPM_HD SwMasks sw_chunk_masks(uint64_t w, uint32_t pb, uint32_t nb, uint32_t b9,
   m.b = bcur;
   m.ws = good & (bcur | ~gprev) & 0xFFu;
   m.we = good & (bnext | ~gnext) & 0xFFu;
-  m.bad = ((valid & ~good & ~sp) | (sp & valid & (bcur | bnext | (sp << 1) | psp))) & 0xFFu;
+  // (relax, see memo_scan_plain: leading, trailing and repeated spaces are no reason to leave the sentence out)
+  m.bad = ((valid & ~good & ~sp) | (relax ? 0u : (sp & valid & (bcur | bnext | (sp << 1) | psp)))) & 0xFFu;
   return m;
 }
 

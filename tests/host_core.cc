@@ -40,7 +40,7 @@ void make_view(Handle *h) {
   v.unk_score = m.min_score - 10.0f; v.max_score = m.max_score; v.smax = m.smax; v.ring = m.ring;
   v.add_dummy_prefix = m.add_dummy_prefix; v.remove_extra_ws = m.remove_extra_ws;
   v.escape_ws = m.escape_ws; v.ws_suffix = m.ws_suffix; v.has_unused = m.has_unused;
-  v.ascii_plain = m.ascii_plain;
+  v.ascii_plain = m.ascii_plain; v.ws_tab = m.ws_tab;
   h->pt.plen = m.plen.data(); h->pt.poff = m.poff.data(); h->pt.pool = (const uint8_t *)m.ppool.data();
 }
 }  // namespace
@@ -207,7 +207,8 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
         std::vector<uint64_t> pbuf(len / 8 + 5, 0x2020202020202020ull);   // what follows must not matter
         uint8_t *ps = (uint8_t *)pbuf.data() + (i % 8);                    // any alignment
         memcpy(ps, text + off[i], len);
-        nw = memo_scan_plain(tb, ps, (int32_t)len, mv.add_dummy_prefix ? 1 : 0, slots.data(), (int32_t)(len / 2 + 4));
+        nw = memo_scan_plain(tb, ps, (int32_t)len, mv.add_dummy_prefix ? 1 : 0, slots.data(), (int32_t)(len / 2 + 4),
+                             memo_relax_of(mv));
         if (nw != -2) st |= 1u << 23;
       }
       if (nw == -2) {                                                  // k_memo_scan
@@ -512,7 +513,7 @@ int hc_estep(const char *pieces, const float *scores, int V, const uint8_t *word
 // slots, no key that the per-sentence scan did not make.  text/off: n sentences; groups of 32
 // are laid out like a warp's staging buffer at every alignment.  Returns 0, or 100000000 * kind +
 // sentence index of the first difference.
-int64_t hc_scan_words_check(const uint8_t *text, const int64_t *off, int64_t n, int prefix0, int64_t *n_plain) {
+int64_t hc_scan_words_check(const uint8_t *text, const int64_t *off, int64_t n, int prefix0, int relax, int64_t *n_plain) {
   const size_t slots_n = 1 << 18;
   std::vector<MemoKey> mkeys(slots_n);
   std::vector<MemoRes> mres(slots_n);      // (a slot claimed beyond max_new gets its meta word written)
@@ -541,7 +542,7 @@ int64_t hc_scan_words_check(const uint8_t *text, const int64_t *off, int64_t n, 
       const int64_t len = off[t + 1] - off[t];
       want[t - tw].assign(len / 2 + 4, 0);
       want_nw[t - tw] = len > 0 ? memo_scan_plain(tb, stage + a_rel + (off[t] - a), (int32_t)len, prefix0,
-                                                  want[t - tw].data(), (int32_t)(len / 2 + 4)) : 0;
+                                                  want[t - tw].data(), (int32_t)(len / 2 + 4), relax) : 0;
       if (want_nw[t - tw] < 0) all_ok = false; else ++*n_plain;
     }
     const uint32_t new_before = n_new;
@@ -564,7 +565,7 @@ int64_t hc_scan_words_check(const uint8_t *text, const int64_t *off, int64_t n, 
         memcpy(&w, stage + g, 8);
         const uint32_t pb = g > 0 ? stage[g - 1] : 0u, nb = stage[g + 8];
         const uint32_t b9 = (uint32_t)bmap[g >> 3] | ((uint32_t)bmap[(g >> 3) + 1] << 8);
-        const SwMasks m = sw_chunk_masks(w, pb, nb, b9, a_rel - g, b_rel - g);
+        const SwMasks m = sw_chunk_masks(w, pb, nb, b9, a_rel - g, b_rel - g, relax);
         for (uint32_t x = m.ws; x; x &= x - 1) wpos.push_back(g + __builtin_ctz(x));
         for (uint32_t x = m.we; x; x &= x - 1) wend.push_back(g + __builtin_ctz(x));
         for (uint32_t x = m.bad; x; x &= x - 1) flags[owner(g + __builtin_ctz(x))] |= 2u;
@@ -578,7 +579,7 @@ int64_t hc_scan_words_check(const uint8_t *text, const int64_t *off, int64_t n, 
       const int s = wpos[k], len = wend[k] - s + 1;
       if (len < 1) return 200000000ll + tw;
       const int u = owner(s);
-      const uint32_t slot = sw_word_slot(tb, stage + s, len, s == sstart[u] ? (uint64_t)prefix0 : 1ull);
+      const uint32_t slot = sw_word_slot(tb, stage + s, len, (int)k == first[u] ? (uint64_t)prefix0 : 1ull);   // the first word of its sentence
       if (slot == 0xFFFFFFFFu) flags[u] |= 1u;
       if ((int)got[u].size() != (int)k - first[u]) return 300000000ll + tw + u;
       got[u].push_back(slot);

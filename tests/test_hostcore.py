@@ -226,7 +226,7 @@ def test_word_scan_matches_sentence_scan(hostcore, corpora):
             b"", b"", b"z", b"ab cd ef gh ij kl mn op qr st uv wx yz" * 3, b"q" * 60 + b" r"]
     for _ in range(300):    # random shapes around the 8-byte chunk borders
         k = int(rng.integers(0, 40))
-        edge.append(bytes(rng.choice(np.frombuffer(b"ab  c.Z~", dtype=np.uint8), size=k).tolist()))
+        edge.append(bytes(rng.choice(np.frombuffer(b"ab  c.Z~\t", dtype=np.uint8), size=k).tolist()))
     etext = np.frombuffer(b"".join(edge), dtype=np.uint8)
     eoff = np.concatenate([[0], np.cumsum([len(e) for e in edge])]).astype(np.int64)
     cases = [(etext, eoff)]
@@ -235,15 +235,21 @@ def test_word_scan_matches_sentence_scan(hostcore, corpora):
         m = min(4000, len(off) - 1)
         cases.append((np.ascontiguousarray(text[: off[m]]), np.ascontiguousarray(off[: m + 1])))
     hostcore.hc_scan_words_check.restype = ctypes.c_int64
-    hostcore.hc_scan_words_check.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p]
-    plain = []
-    for text, off in cases:
-        for prefix in (1, 0):
-            n_plain = ctypes.c_int64(0)
-            rc = hostcore.hc_scan_words_check(text.ctypes.data, off.ctypes.data, len(off) - 1, prefix, ctypes.byref(n_plain))
-            assert rc == 0, rc
-        plain.append(n_plain.value)
-    assert plain[1] >= 3900 and 2000 < plain[2] < 3900, plain   # clean text: all plain; "dirty": most (botchan lines end in \r: none)
+    hostcore.hc_scan_words_check.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_void_p]
+    plain = {0: [], 1: [], 2: []}
+    for relax in (0, 1, 2):  # 1: a model that removes extra whitespace -- leading / trailing / repeated spaces only separate words; 2: tabs too
+        for text, off in cases:
+            for prefix in (1, 0):
+                n_plain = ctypes.c_int64(0)
+                rc = hostcore.hc_scan_words_check(text.ctypes.data, off.ctypes.data, len(off) - 1, prefix, relax,
+                                                  ctypes.byref(n_plain))
+                assert rc == 0, (rc, relax)
+            plain[relax].append(n_plain.value)
+    # clean text: all plain; "dirty": most (botchan lines end in \r: none); more of the dirty and of the edge shapes when relaxed
+    assert plain[0][1] >= 3900 and 2000 < plain[0][2] < 3900, plain
+    assert plain[1][1] == plain[0][1] and plain[1][2] > plain[0][2] + 50 and plain[1][0] > plain[0][0] + 20, plain
+    assert plain[2][1] == plain[0][1] and plain[2][2] > plain[1][2] + 30 and plain[2][0] > plain[1][0] + 50, plain
 
 
 def test_loader_rejects_bad_models(hostcore):
