@@ -376,7 +376,8 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
 // j of the chunk (bit 8: at the first byte after it; the end of the warp's text counts as a
 // start), `lo`/`hi` clip the chunk to the warp's text ([lo, hi) of 0..8), `pb`/`nb` are the
 // bytes before and after the chunk.  A sentence is unfit (memo_scan_plain's -2) when it holds
-// a byte outside 0x20..0x7E, or a space that is leading, trailing or follows a space.
+// a byte outside 0x20..0x7E, or -- with relax == 0 -- a space that is leading, trailing or follows a space
+// (relax: see memo_scan_plain; a TAB counts as a space with relax == 2).
 struct SwMasks {
   uint32_t ws, we, bad, b;   // b: the sentence starts among the chunk's 8 bytes
 };
