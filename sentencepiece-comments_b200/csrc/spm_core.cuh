@@ -78,7 +78,7 @@ struct ModelView {
   uint8_t add_dummy_prefix, remove_extra_ws, escape_ws, ws_suffix;
   uint8_t has_unused;        // any UNUSED piece (BPE resegmentation needed)
   uint8_t ascii_plain;       // bytes 0x21..0x7E followed by an ASCII byte never start a rule / user symbol
-  uint8_t ws_tab;            // a TAB normalizes to exactly one space whatever follows it (word scan: a separator)
+  uint8_t ws_ctl;            // TAB, LF, FF and CR each normalize to exactly one space whatever follows (word scan: separators)
   uint8_t pad_[1];
 };
 

@@ -1806,7 +1806,7 @@ int upload_model(spm_cuda_model *M) {
   v.max_score = hm.max_score; v.smax = hm.smax; v.ring = hm.ring;
   v.add_dummy_prefix = hm.add_dummy_prefix; v.remove_extra_ws = hm.remove_extra_ws;
   v.escape_ws = hm.escape_ws; v.ws_suffix = hm.ws_suffix; v.has_unused = hm.has_unused;
-  v.ascii_plain = hm.ascii_plain; v.ws_tab = hm.ws_tab;
+  v.ascii_plain = hm.ascii_plain; v.ws_ctl = hm.ws_ctl;
 
   CUDA_TRY(cudaDeviceGetAttribute(&M->sm_count, cudaDevAttrMultiProcessorCount, M->device));
   return configure_fast(M);

@@ -290,9 +290,10 @@ struct MemoSink {
 // sentence is not of this shape (the general scan, fast_normalize_scan + MemoSink, decides).
 // relax (memo_relax_of): 1 = the model removes extra whitespace (leading, trailing and repeated spaces vanish
 // before the dummy prefix is added, src/normalizer.cc:88-211), so such spaces only separate words here; 2 = and a
-// TAB normalizes to exactly one space (ModelView::ws_tab), so it is such a separator too; 0 = they make the
+// TAB, LF, FF and CR each normalize to exactly one space (ModelView::ws_ctl), so they are such separators too; 0 = they make the
 // sentence unfit (-2).
-SPM_HD int memo_relax_of(const ModelView &m) { return m.remove_extra_ws ? (m.ws_tab ? 2 : 1) : 0; }
+SPM_HD int memo_relax_of(const ModelView &m) { return m.remove_extra_ws ? (m.ws_ctl ? 2 : 1) : 0; }
+SPM_HD bool memo_is_ctl_space(uint32_t b) { return b >= 0x09u && b <= 0x0Du && b != 0x0Bu; }
 SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n, int prefix0, uint32_t *slots,
                                 int32_t cap, int relax = 0) {
   const uint8_t *q = (const uint8_t *)((uintptr_t)s & ~(uintptr_t)7);
@@ -308,7 +309,7 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
   for (;;) {
     const uint64_t w = fast_window(a0, a1, r);
     const int32_t rem = n - p;
-    if (relax && pos == 0 && !tail && ((w & 0xFFu) == 0x20u || (relax == 2 && (w & 0xFFu) == 0x09u))) {   // a separator where a word would begin: skip it
+    if (relax && pos == 0 && !tail && ((w & 0xFFu) == 0x20u || (relax == 2 && memo_is_ctl_space((uint32_t)w & 0xFFu)))) {   // a separator where a word would begin: skip it
       p += 1; r += 1;
       if (p >= n) break;
       if (r >= 8) { r -= 8; a0 = a1; q += 8; a1 = fast_load8(q + 8); }
@@ -325,7 +326,7 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
       run = 7;                                   // keep the successor in sight
     } else {
       const uint32_t b = (uint32_t)(w >> (8 * run)) & 0xFFu;
-      if (b != 0x20u && !(relax == 2 && b == 0x09u)) return -2;   // control / non-ASCII: rules may apply
+      if (b != 0x20u && !(relax == 2 && memo_is_ctl_space(b))) return -2;   // control / non-ASCII: rules may apply
       endw = true; skip = 1;
       if (run + 1 >= rem && !relax) return -2;   // trailing space
     }
@@ -377,7 +378,7 @@ SPM_HDN int32_t memo_scan_plain(const MemoTable &tb, const uint8_t *s, int32_t n
 // start), `lo`/`hi` clip the chunk to the warp's text ([lo, hi) of 0..8), `pb`/`nb` are the
 // bytes before and after the chunk.  A sentence is unfit (memo_scan_plain's -2) when it holds
 // a byte outside 0x20..0x7E, or -- with relax == 0 -- a space that is leading, trailing or follows a space
-// (relax: see memo_scan_plain; a TAB counts as a space with relax == 2).
+// (relax: see memo_scan_plain; TAB, LF, FF and CR count as spaces with relax == 2).
 struct SwMasks {
   uint32_t ws, we, bad, b;   // b: the sentence starts among the chunk's 8 bytes
 };
@@ -390,17 +391,23 @@ SPM_HD SwMasks sw_chunk_masks(uint64_t w, uint32_t pb, uint32_t nb, uint32_t b9,
   const uint64_t ge21 = (lw | H) - 0x2121212121212121ull;   // bit 7: low seven bits >= 0x21 (no borrow leaves a byte)
   const uint64_t le7e = ~(lw + 0x0101010101010101ull);      // bit 7: low seven bits <= 0x7E (no carry leaves a byte)
   const uint64_t x = w ^ 0x2020202020202020ull;
-  uint64_t spf = ~(((x & L7) + L7) | x) & H;                // byte == 0x20
-  if (relax == 2) {                                         // ... or a TAB
-    const uint64_t x9 = w ^ 0x0909090909090909ull;
-    spf |= ~(((x9 & L7) + L7) | x9) & H;
-  }
+  const uint64_t spf = ~(((x & L7) + L7) | x) & H;          // byte == 0x20
   lo = lo < 0 ? 0 : (lo > 8 ? 8 : lo);
   hi = hi < 0 ? 0 : (hi > 8 ? 8 : hi);
   const uint32_t valid = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
   const uint32_t good = sw_gather(ge21 & le7e & ~w & H) & valid;
-  const uint32_t sp = sw_gather(spf);
-  const uint32_t pgood = (pb >= 0x21u && pb <= 0x7Eu) ? 1u : 0u, psp = (pb == 0x20u || (relax == 2 && pb == 0x09u)) ? 1u : 0u;
+  uint32_t sp = sw_gather(spf);
+  uint32_t other = valid & ~good & ~sp;                     // neither a word byte nor a space
+  if (relax == 2 && other != 0) {                           // ... unless TAB, LF, FF, CR: 0x09..0x0D without 0x0B.
+    // (Only looked at when there is such a byte at all: clean text never pays for it.)
+    const uint64_t ge09 = (lw | H) - 0x0909090909090909ull;   // bit 7: low seven bits >= 0x09
+    const uint64_t le0d = ~(lw + 0x7272727272727272ull);      // bit 7: low seven bits <= 0x0D
+    const uint64_t xb = w ^ 0x0B0B0B0B0B0B0B0Bull;
+    const uint64_t eq0b = ~(((xb & L7) + L7) | xb);           // bit 7: byte == 0x0B
+    sp |= sw_gather(ge09 & le0d & ~w & ~eq0b & H);
+    other = valid & ~good & ~sp;
+  }
+  const uint32_t pgood = (pb >= 0x21u && pb <= 0x7Eu) ? 1u : 0u, psp = pb == 0x20u ? 1u : 0u;   // (psp: relax == 0 only)
   const uint32_t ngood = (nb >= 0x21u && nb <= 0x7Eu) ? 0x80u : 0u;
   const uint32_t bcur = b9 & 0xFFu, bnext = (b9 >> 1) & 0xFFu;
   const uint32_t gprev = (good << 1) | pgood, gnext = (good >> 1) | ngood;
@@ -409,7 +416,7 @@ SPM_HD SwMasks sw_chunk_masks(uint64_t w, uint32_t pb, uint32_t nb, uint32_t b9,
   m.ws = good & (bcur | ~gprev) & 0xFFu;
   m.we = good & (bnext | ~gnext) & 0xFFu;
   // (relax, see memo_scan_plain: leading, trailing and repeated spaces are no reason to leave the sentence out)
-  m.bad = ((valid & ~good & ~sp) | (relax ? 0u : (sp & valid & (bcur | bnext | (sp << 1) | psp)))) & 0xFFu;
+  m.bad = (other | (relax ? 0u : (sp & valid & (bcur | bnext | (sp << 1) | psp)))) & 0xFFu;
   return m;
 }
 

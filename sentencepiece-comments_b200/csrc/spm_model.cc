@@ -522,8 +522,9 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
       for (uint32_t x = 0; x < 0x80; ++x)
         if ((m->cm_first2[((b << 8) | x) >> 5] >> (((b << 8) | x) & 31)) & 1) m->ascii_plain = false;
   }
-  // A TAB is a word separator for the byte-parallel word scan when the normalizer turns it into exactly one
-  // space whatever follows it (nmt_nfkc does): normalize_prefix() itself is asked, on host copies of the tables.
+  // TAB, LF, FF and CR are word separators for the byte-parallel word scan when the normalizer turns each of them
+  // into exactly one space whatever follows (nmt_nfkc does; text with CRLF line ends otherwise takes the general
+  // scan sentence by sentence): normalize_prefix() itself is asked, on host copies of the tables.
   {
     ModelView v;
     memset(&v, 0, sizeof(v));
@@ -531,13 +532,14 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
     v.cm_units = m->cm_units; v.cm_pool = m->cm_pool; v.cm_n = m->cm_n;
     v.cm_first2 = m->cm_first2.empty() ? nullptr : m->cm_first2.data();
     memcpy(v.user_first, m->user_first, sizeof(v.user_first));
-    m->ws_tab = m->cm_n != 0;
-    for (int x = -1; x < 256 && m->ws_tab; ++x) {     // -1: the tab is the last byte
-      uint8_t in[8] = {0x09, (uint8_t)(x < 0 ? 0 : x), 0, 0, 0, 0, 0, 0};
+    m->ws_ctl = m->cm_n != 0;
+    for (int ctl : {0x09, 0x0A, 0x0C, 0x0D})
+    for (int x = -1; x < 256 && m->ws_ctl; ++x) {     // -1: the byte is the last one
+      uint8_t in[8] = {(uint8_t)ctl, (uint8_t)(x < 0 ? 0 : x), 0, 0, 0, 0, 0, 0};
       const uint8_t *rep = nullptr;
       int rl = 0;
       const int c = normalize_prefix(v, in, x < 0 ? 1 : 2, &rep, &rl);
-      if (!(c == 1 && rl == 1 && rep != nullptr && rep[0] == ' ')) m->ws_tab = false;
+      if (!(c == 1 && rl == 1 && rep != nullptr && rep[0] == ' ')) m->ws_ctl = false;
     }
   }
   m->ring = 8;

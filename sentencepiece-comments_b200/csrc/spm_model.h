@@ -61,7 +61,7 @@ struct HostModel {
   bool text_valid = true;         // normalized text is always valid UTF-8
   bool bpe_fast_ok = false;       // BPE model whose merges never cross a word boundary (fast_bpe)
   bool ascii_plain = false;       // see build_host_model
-  bool ws_tab = false;            // see build_host_model
+  bool ws_ctl = false;            // see build_host_model
   bool memo_ok = false;           // no lattice node / merge crosses a U+2581: words can be memoised (spm_memo.cuh)
   bool neg_only = false;          // every node score of the fast view (and the UNK score) is <= 0
   // ---- piece strings by id (pieces path)

@@ -40,7 +40,7 @@ void make_view(Handle *h) {
   v.unk_score = m.min_score - 10.0f; v.max_score = m.max_score; v.smax = m.smax; v.ring = m.ring;
   v.add_dummy_prefix = m.add_dummy_prefix; v.remove_extra_ws = m.remove_extra_ws;
   v.escape_ws = m.escape_ws; v.ws_suffix = m.ws_suffix; v.has_unused = m.has_unused;
-  v.ascii_plain = m.ascii_plain; v.ws_tab = m.ws_tab;
+  v.ascii_plain = m.ascii_plain; v.ws_ctl = m.ws_ctl;
   h->pt.plen = m.plen.data(); h->pt.poff = m.poff.data(); h->pt.pool = (const uint8_t *)m.ppool.data();
 }
 }  // namespace

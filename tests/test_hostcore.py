@@ -226,7 +226,7 @@ def test_word_scan_matches_sentence_scan(hostcore, corpora):
             b"", b"", b"z", b"ab cd ef gh ij kl mn op qr st uv wx yz" * 3, b"q" * 60 + b" r"]
     for _ in range(300):    # random shapes around the 8-byte chunk borders
         k = int(rng.integers(0, 40))
-        edge.append(bytes(rng.choice(np.frombuffer(b"ab  c.Z~\t", dtype=np.uint8), size=k).tolist()))
+        edge.append(bytes(rng.choice(np.frombuffer(b"ab  c.Z~\t\r\n\x0b", dtype=np.uint8), size=k).tolist()))
     etext = np.frombuffer(b"".join(edge), dtype=np.uint8)
     eoff = np.concatenate([[0], np.cumsum([len(e) for e in edge])]).astype(np.int64)
     cases = [(etext, eoff)]
@@ -248,8 +248,9 @@ def test_word_scan_matches_sentence_scan(hostcore, corpora):
             plain[relax].append(n_plain.value)
     # clean text: all plain; "dirty": most (botchan lines end in \r: none); more of the dirty and of the edge shapes when relaxed
     assert plain[0][1] >= 3900 and 2000 < plain[0][2] < 3900, plain
-    assert plain[1][1] == plain[0][1] and plain[1][2] > plain[0][2] + 50 and plain[1][0] > plain[0][0] + 20, plain
-    assert plain[2][1] == plain[0][1] and plain[2][2] > plain[1][2] + 30 and plain[2][0] > plain[1][0] + 50, plain
+    assert plain[1][1] == plain[0][1] and plain[1][2] > plain[0][2] + 50 and plain[1][0] > plain[0][0] + 5, plain
+    assert plain[2][1] == plain[0][1] and plain[2][2] > plain[1][2] + 30 and plain[2][0] > plain[1][0] + 30, plain
+    assert plain[0][3] == 0 and plain[2][3] >= 3900, plain      # botchan: CR at every line end
 
 
 def test_loader_rejects_bad_models(hostcore):
