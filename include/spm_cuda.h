@@ -72,6 +72,7 @@ int spm_cuda_model_set_piece_types(spm_cuda_model *model, const uint8_t *types, 
  *   "scan_per_sentence" 0   thread-per-sentence word scan instead of the byte-parallel one
  *   "emit_blocks"       0   CTAs of the memo emit kernel per SM (0: occupancy query)
  *   "pieces_exact"      0   encode_batch_pieces: every sentence through the exact tier
+ *   "pieces_plain"      1   encode_batch_pieces: plain sentences (printable ASCII, single spaces) skip the normalizer
  *   "bpe_route"         8192  BPE: leftover lists up to this size go to the general tier as a whole (0: never)
  *   "fast_side"         1   thread-per-sentence Viterbi kernel keeps near-tied candidates itself (0: hands the sentence on)
  *   "mid_lines"         0   lines of 4..8 KiB take the thread-per-sentence kernel instead of the warp kernel

@@ -710,6 +710,7 @@ SPM_HD PieceSpan final_piece_at(const ExtraPlan &p, const int32_t *core_ids, con
 // the sentence is redone by the exact tier, which records the piece ends.
 struct PieceTable {
   const int32_t *plen;    // bytes of piece id
+  const int32_t *olen;    // bytes of its surface in a plain sentence (every U+2581 = one space): plen - 2 * count(U+2581)
   const uint32_t *poff;   // offset of its string in pool
   const uint8_t *pool;
 };
@@ -806,6 +807,77 @@ SPM_HDN bool spans_from_ids(const ModelView &m, const PieceTable &pt, const Extr
     ++k;
   }
   return pos == nl;
+}
+
+// ---- the plain sentence: the pieces path without the normalizer ------------------------
+// Most sentences of most corpora are printable ASCII words separated by single spaces.  When the
+// model leaves such bytes alone (ascii_plain) and escapes whitespace, the normalized text is the
+// input with U+2581 for every space (and in front, with add_dummy_prefix), and norm_to_orig is
+// affine between spaces: orig(dummy U+2581) = 0 for all its bytes, a space's U+2581 maps to the
+// space, every other byte to itself.  So neither the normalized text nor norm_to_orig has to be
+// made to place the pieces: a piece of plen normalized bytes with w U+2581 covers plen - 2 w input
+// bytes (olen), one less when its first U+2581 is the dummy prefix.
+SPM_HD bool pc_plain_model(const ModelView &m) {
+  return m.ascii_plain && m.escape_ws && !m.ws_suffix && m.user.n == 0;
+}
+// Normalized length of the plain sentence s[0..n), or -1 when it is not one (a byte outside
+// 0x20..0x7E, a leading / trailing / repeated space, or empty).  s is read in aligned 8-byte
+// words within [lo, hi) (fast_load8_guard's contract is not needed: bytes outside [0, n) are masked).
+SPM_HDN int32_t pc_plain_length(const ModelView &m, const uint8_t *s, int64_t n) {
+  if (n <= 0 || n > (1 << 24)) return -1;
+  if (s[0] == 0x20u || s[n - 1] == 0x20u) return -1;
+  int32_t spaces = 0;
+  uint32_t prev = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const uint32_t c = s[i];
+    if (c < 0x20u || c > 0x7Eu) return -1;
+    if (c == 0x20u) { if (prev == 0x20u) return -1; ++spaces; }
+    prev = c;
+  }
+  return (int32_t)n + 2 * spaces + (m.add_dummy_prefix ? 3 : 0);
+}
+// The normalized text of a plain sentence: out[0 .. pc_plain_length).
+SPM_HD void pc_plain_expand(const ModelView &m, const uint8_t *s, int64_t n, uint8_t *out) {
+  int64_t o = 0;
+  if (m.add_dummy_prefix) { out[0] = 0xE2; out[1] = 0x96; out[2] = 0x81; o = 3; }
+  for (int64_t i = 0; i < n; ++i) {
+    if (s[i] == 0x20u) { out[o] = 0xE2; out[o + 1] = 0x96; out[o + 2] = 0x81; o += 3; }
+    else out[o++] = s[i];
+  }
+}
+// spans_from_ids for a plain sentence of n input bytes and nl normalized bytes.  False (the exact
+// tier redoes the sentence) when an unknown piece is among the ids or the lengths do not add up.
+SPM_HDN bool spans_plain_from_ids(const ModelView &m, const PieceTable &pt, const ExtraPlan &plan, int32_t n, int32_t nl,
+                                  const int32_t *fids, int32_t fc, int32_t *begin, int32_t *end, int32_t *nbegin,
+                                  int32_t *nend, int64_t room) {
+  if (fc == 0) return nl == 0;
+  const int32_t core = fc - plan.npre - plan.nsuf;
+  if (core < 0) return false;
+  for (int32_t j = 0; j < fc; ++j) {
+    if (j >= plan.npre && j < plan.npre + core) continue;
+    if (j < room) { begin[j] = 0; end[j] = 0; nbegin[j] = -1; nend[j] = -1; }
+  }
+  int32_t pos = 0, opos = 0;
+  for (int32_t k = 0; k < core;) {
+    constexpr int G = 8;   // independent loads, as in spans_from_ids
+    const int32_t g = core - k < G ? core - k : G;
+    int32_t idv[G], pl[G], ol[G];
+    bool has_unk = false;
+    for (int u = 0; u < G; ++u)
+      if (u < g) { idv[u] = fids[plan.npre + (plan.flip ? core - 1 - (k + u) : k + u)]; has_unk |= idv[u] == m.unk_id; }
+    if (has_unk) return false;
+    for (int u = 0; u < G; ++u) if (u < g) { pl[u] = SPM_LDG(pt.plen + idv[u]); ol[u] = SPM_LDG(pt.olen + idv[u]); }
+    if (k == 0 && m.add_dummy_prefix) ol[0] -= 1;      // the dummy prefix stands for no input byte
+    for (int u = 0; u < G; ++u) {
+      if (u >= g) break;
+      const int32_t j = plan.npre + (plan.flip ? core - 1 - (k + u) : k + u);
+      if (j < room) { nbegin[j] = pos; nend[j] = pos + pl[u]; begin[j] = opos; end[j] = opos + ol[u]; }
+      pos += pl[u];
+      opos += ol[u];
+    }
+    k += g;
+  }
+  return pos == nl && opos == n;
 }
 
 }  // namespace spmb

@@ -722,6 +722,37 @@ SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, con
   return !overflow;
 }
 
+// pc_plain_length() (spm_core.cuh) eight bytes at a time: aligned words of the batch's text [lo, hi), bytes
+// outside the sentence replaced by 'a'.  A byte outside 0x20..0x7E marks its bit 7 (or one further up: only
+// "any" is asked); spaces are counted with a popcount, a repeated space is two neighbouring marks.
+SPM_HDN int32_t pc_plain_length_swar(const ModelView &m, const uint8_t *s, int64_t n, const uint8_t *lo, const uint8_t *hi) {
+  if (n <= 0 || n > (1 << 24)) return -1;
+  if (s[0] == 0x20u || s[n - 1] == 0x20u) return -1;
+  const uint64_t H = 0x8080808080808080ull, L7 = 0x7F7F7F7F7F7F7F7Full, A = 0x6161616161616161ull;
+  const uint8_t *q = (const uint8_t *)((uintptr_t)s & ~(uintptr_t)7);
+  const uint8_t *e = s + n;
+  int32_t spaces = 0;
+  uint64_t prev_sp = 0;   // bit 63: the byte before this word was a space
+  for (; q < e; q += 8) {
+    uint64_t w = fast_load8_guard(q, lo, hi);
+    if (q < s) { const int k = (int)(s - q); w = (w & (~0ull << (8 * k))) | (A & ~(~0ull << (8 * k))); }
+    if (q + 8 > e) { const int k = (int)(e - q); w = (w & ~(~0ull << (8 * k))) | (A & (~0ull << (8 * k))); }
+    const uint64_t bad = (((w - 0x2020202020202020ull) & ~w) | ((w + 0x0101010101010101ull) | w)) & H;
+    if (bad) return -1;
+    const uint64_t x = w ^ 0x2020202020202020ull;
+    const uint64_t sp = ~(((x & L7) + L7) | x) & H;          // bit 7 of every space
+    if (sp & ((sp << 8) | (prev_sp >> 56))) return -1;       // a space after a space
+    prev_sp = sp;
+    spaces += (int32_t)
+#if defined(__CUDA_ARCH__)
+        __popcll(sp);
+#else
+        __builtin_popcountll(sp);
+#endif
+  }
+  return (int32_t)n + 2 * spaces + (m.add_dummy_prefix ? 3 : 0);
+}
+
 // Long lines are normalized in pieces (k_normalize_long).  A piece may start at `p` when the
 // scan is guaranteed to arrive there with a fresh match and a state that does not matter:
 //   * in[p] starts a character that never sits inside a rule key / user symbol (cm_cont2),

@@ -1664,6 +1664,7 @@ struct Options {
   int64_t warp_route = 262144;    // leftover lists up to this size go to k_encode_warp as a whole (0: never)
   int64_t emit_blocks = 0;        // CTAs of k_memo_emit per SM (0: occupancy query)
   int64_t pieces_exact = 0;       // pieces path: every sentence through the exact tier
+  int64_t pieces_plain = 1;       // pieces path: plain sentences (printable ASCII, single spaces) skip the normalizer
   int64_t fast_side = 1;          // k_encode_fast keeps near-tied candidates itself (0: flags the sentence, round 1)
   int64_t mid_lines = 0;          // lines of 4..8 KiB: second pass of k_encode_fast instead of the warp kernel (measured: a loss, see below)
   int64_t bpe_route = 8192;       // BPE leftover lists up to this size go to the general tier as a whole (0: never)
@@ -2065,7 +2066,7 @@ static int64_t *option_slot(Options *o, const char *name) {
       {"memo", &o->memo}, {"memo_bits", &o->memo_bits}, {"host_chunks", &o->host_chunks},
       {"host_chunk_min", &o->host_chunk_min}, {"max_chunk", &o->max_chunk}, {"warp", &o->warp},
       {"scan_per_sentence", &o->scan_per_sentence}, {"warp_route", &o->warp_route}, {"fast_side", &o->fast_side}, {"mid_lines", &o->mid_lines},
-      {"emit_blocks", &o->emit_blocks}, {"pieces_exact", &o->pieces_exact}, {"bpe_route", &o->bpe_route}};
+      {"emit_blocks", &o->emit_blocks}, {"pieces_exact", &o->pieces_exact}, {"pieces_plain", &o->pieces_plain}, {"bpe_route", &o->bpe_route}};
   for (const auto &e : table)
     if (strcmp(e.name, name) == 0) return e.p;
   return nullptr;

@@ -573,11 +573,17 @@ int build_host_model(const void *data, size_t len, HostModel *m) {
                m->max_piece_chars < 200;
   refresh_leaf_types(m);  // (re)derives bpe_fast_ok as well
   // piece strings by id (spans_from_ids of the pieces path, spm_core.cuh)
-  m->plen.resize(V);
+  // (plen[V + i]: bytes of the piece's surface in a plain-ASCII sentence, where every U+2581 stands for one
+  // space -- PieceTable::olen, spans_fit_from_ids)
+  m->plen.resize(2 * V);
   m->poff.resize(V);
   m->ppool.clear();
   for (size_t i = 0; i < V; ++i) {
     m->plen[i] = (int32_t)m->piece[i].size();
+    int32_t nws = 0;
+    for (size_t b = 0; b + 2 < m->piece[i].size(); ++b)
+      if ((uint8_t)m->piece[i][b] == 0xE2 && (uint8_t)m->piece[i][b + 1] == 0x96 && (uint8_t)m->piece[i][b + 2] == 0x81) ++nws;
+    m->plen[V + i] = m->plen[i] - 2 * nws;
     m->poff[i] = (uint32_t)m->ppool.size();
     m->ppool += m->piece[i];
   }

@@ -181,15 +181,16 @@ class HostCore:
         norm = np.empty(ncap, dtype=np.uint8)
         no = np.zeros(n + 1, dtype=np.int64)
         flagged = ctypes.c_int64(0)     # sentences spans_from_ids hands back to the exact tier
+        plain = ctypes.c_int64(0)       # sentences the plain-sentence path settles (checked against the exact spans)
         rc = self.L.hc_encode_pieces_batch(
             ctypes.c_void_p(self.h), ctypes.c_void_p(text.ctypes.data), ctypes.c_void_p(off.ctypes.data),
             ctypes.c_int64(n), ctypes.c_uint32(opts), *[ctypes.c_void_p(a[k].ctypes.data) for k in
                                                         ("ids", "begin", "end", "nbegin", "nend")],
             ctypes.c_int64(cap), ctypes.c_void_p(io.ctypes.data), ctypes.c_void_p(norm.ctypes.data),
-            ctypes.c_int64(ncap), ctypes.c_void_p(no.ctypes.data), ctypes.byref(flagged))
+            ctypes.c_int64(ncap), ctypes.c_void_p(no.ctypes.data), ctypes.byref(flagged), ctypes.byref(plain))
         assert rc == 0, rc
         out = {k: v[: io[n]].copy() for k, v in a.items()}
-        out.update(id_off=io, norm=norm[: no[n]].copy(), norm_off=no, flagged=flagged.value)
+        out.update(id_off=io, norm=norm[: no[n]].copy(), norm_off=no, flagged=flagged.value, plain=plain.value)
         return out
 
 

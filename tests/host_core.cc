@@ -41,7 +41,7 @@ void make_view(Handle *h) {
   v.add_dummy_prefix = m.add_dummy_prefix; v.remove_extra_ws = m.remove_extra_ws;
   v.escape_ws = m.escape_ws; v.ws_suffix = m.ws_suffix; v.has_unused = m.has_unused;
   v.ascii_plain = m.ascii_plain; v.ws_ctl = m.ws_ctl;
-  h->pt.plen = m.plen.data(); h->pt.poff = m.poff.data(); h->pt.pool = (const uint8_t *)m.ppool.data();
+  h->pt.plen = m.plen.data(); h->pt.olen = m.plen.data() + m.plen.size() / 2; h->pt.poff = m.poff.data(); h->pt.pool = (const uint8_t *)m.ppool.data();
 }
 }  // namespace
 
@@ -378,7 +378,7 @@ int hc_encode_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n,
 // as spm_cuda_encode_batch_pieces.
 int hc_encode_pieces_batch(void *p, const uint8_t *text, const int64_t *off, int64_t n, uint32_t opts, int32_t *ids,
                            int32_t *begin, int32_t *end, int32_t *nbegin, int32_t *nend, int64_t cap, int64_t *id_off,
-                           uint8_t *norm_out, int64_t norm_cap, int64_t *norm_off, int64_t *n_flagged) {
+                           uint8_t *norm_out, int64_t norm_cap, int64_t *norm_off, int64_t *n_flagged, int64_t *n_plain) {
   Handle *h = (Handle *)p;
   const ModelView &mv = h->mv;
   const ExtraPlan plan = make_extra_plan(opts, piece_to_id(h->hm, h->hm.bos_piece), piece_to_id(h->hm, h->hm.eos_piece));
@@ -448,6 +448,32 @@ int hc_encode_pieces_batch(void *p, const uint8_t *text, const int64_t *off, int
         for (int32_t j = 0; j < fc; ++j) {
           const int64_t q = id_off[i] + j;
           if (fb[j] != begin[q] || fe[j] != end[q] || fnb[j] != nbegin[q] || fne[j] != nend[q]) return 95;
+        }
+      }
+    }
+    // the plain-sentence path (k_pc_prepare / k_pc_spans / k_pc_copy_norm): same length, same text, and --
+    // where it claims success -- the exact tier's spans
+    if (pc_plain_model(mv)) {
+      const int32_t pl = pc_plain_length(mv, text + off[i], len);
+      {   // the kernel's eight-bytes-at-a-time version, at every alignment and with foreign bytes around the sentence
+        std::vector<uint64_t> pbuf((len + 40) / 8 + 2, 0x2020202020802020ull);
+        uint8_t *src = (uint8_t *)pbuf.data() + 8 + (i % 8);
+        memcpy(src, text + off[i], len);
+        if (pc_plain_length_swar(mv, src, len, (const uint8_t *)pbuf.data(), (const uint8_t *)(pbuf.data() + pbuf.size())) != pl) return 93;
+      }
+      if (pl >= 0) {
+        if (pl != nl) return 98;
+        std::vector<uint8_t> ex(pl + 8, 0);
+        pc_plain_expand(mv, text + off[i], len, ex.data());
+        if (memcmp(ex.data(), norm.data(), nl) != 0) return 99;
+        std::vector<int32_t> fb(fc + 1), fe(fc + 1), fnb(fc + 1), fne(fc + 1);
+        if (spans_plain_from_ids(mv, h->pt, plan, (int32_t)len, nl, ids + id_off[i], fc, fb.data(), fe.data(), fnb.data(),
+                                 fne.data(), fc)) {
+          for (int32_t j = 0; j < fc; ++j) {
+            const int64_t q = id_off[i] + j;
+            if (fb[j] != begin[q] || fe[j] != end[q] || fnb[j] != nbegin[q] || fne[j] != nend[q]) return 94;
+          }
+          if (n_plain != nullptr) ++*n_plain;
         }
       }
     }

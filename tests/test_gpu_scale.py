@@ -221,11 +221,32 @@ def test_pieces_exact_tier(spm_b200, corpora, model, corpus):
     m = min(3000, len(off) - 1)
     text, off = text[: off[m]], off[: m + 1]
     want = port.OracleProcessor(mb).encode_pieces_batch(text, off)
-    for exact in (0, 1):
-        sp = load(spm_b200, mb, pieces_exact=exact)
+    for opts in ({"pieces_exact": 0}, {"pieces_exact": 1}, {"pieces_plain": 0}):
+        sp = load(spm_b200, mb, **opts)
         got = sp.encode_pieces_packed(text, off)
         for k in ("id_off", "norm_off", "ids", "begin", "end", "nbegin", "nend", "norm"):
-            assert np.array_equal(got[k], want[k]), (k, exact)
+            assert np.array_equal(got[k], want[k]), (k, opts)
+
+
+@pytest.mark.parametrize("model,opts", [("syn_uni32k", 0), ("syn_bpe32k", 0), ("syn_uni32k", 1), ("botchan_uni8k", 0)])
+def test_pieces_plain_sentences(spm_b200, model, opts):
+    """The plain-sentence half of encode_batch_pieces (no normalizer, no norm_to_orig) on 200 k clean and noisy
+    synthetic sentences, with and without extra options, against the path that normalizes every sentence."""
+    from tools import synth
+    n = 200_000
+    ct, co = synth.EnglishCorpus().generate(n // 2, first=3_000_000)
+    dt, do = synth.EnglishCorpus(dirty=True).generate(n // 2, first=11)
+    text = np.concatenate([ct, dt])
+    off = np.concatenate([co, do[1:] + co[-1]])
+    mb = model_bytes(model)
+    extra = ["", "bos:eos:reverse"][opts]
+    res = []
+    for plain in (1, 0):
+        sp = load(spm_b200, mb, pieces_plain=plain)
+        sp.SetEncodeExtraOptions(extra)
+        res.append(sp.encode_pieces_packed(text, off))
+    for k in ("id_off", "norm_off", "ids", "begin", "end", "nbegin", "nend", "norm"):
+        assert np.array_equal(res[0][k], res[1][k]), k
 
 
 # ---------------------------------------------------------------- multi-chunk HOST pipeline on small batches

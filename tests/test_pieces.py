@@ -84,7 +84,10 @@ def test_core_pieces_match_reference(make_hostcore, ref_pieces, small_corpora, s
     # (inside: spans_from_ids, the fast half, must agree with the exact tier wherever it claims success)
     n_unknown_runs = 0 if corpus == "edge" or "wagahai" in (corpus, model.split("_")[0]) or model == "ref_ja_8k" else 1
     assert res["flagged"] <= (len(off) - 1) * (0.02 if n_unknown_runs else 1.0), res["flagged"]
-    print(model, corpus, "flagged", res["flagged"], "of", len(off) - 1)
+    print(model, corpus, "flagged", res["flagged"], "plain", res["plain"], "of", len(off) - 1)
+    # (inside too: the plain-sentence path -- length, text, spans -- against the exact tier on every sentence it takes)
+    if corpus == "syn_en" and model.startswith("syn_"):
+        assert res["plain"] >= 0.9 * (len(off) - 1), res["plain"]
     assert_protos(protos_of(spt_mod, text, off, res, model_pieces(mb)), ref_pieces, mpf.case_name(model, corpus, opts),
                   text, off)
 
