@@ -57,7 +57,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=0, help="sentences of the parity / cpu_baseline sample (0: auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the reference leg (no parity counters either)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--configs", default="config3,config4,config2_dirty,estep",
+    ap.add_argument("--configs", default="config3,config4,config2_dirty,estep,pieces",
                     help="extra records measured after the headline run ('' or --no-configs: none)")
     ap.add_argument("--no-configs", action="store_true")
     ap.add_argument("--option", action="append", default=[], help="name=value for spm_cuda_model_set_option (A/B runs)")
@@ -513,6 +513,11 @@ def run_b200(args):
             if name == "estep":
                 from tools import estep_bench
                 extras[name] = estep_bench.record(ctx, steps=max(3, min(steps, 5)), with_reference=parity_n > 0)
+            elif name == "pieces":
+                from tools import pieces_bench
+                pn = 10_000_000 if args.sentences >= 10_000_000 else max(1000, args.sentences)
+                extras[name] = pieces_bench.record(ctx, n=pn, steps=3, parity_n=50_000 if (parity_n > 0 and world == 1) else
+                                                   (12_500 if parity_n > 0 else 0))
             elif name in EXTRA_CONFIGS:
                 model, corpus, n, pn = EXTRA_CONFIGS[name]
                 if args.sentences < 10_000_000:           # a scaled-down run scales the extras with it

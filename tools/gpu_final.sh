@@ -13,6 +13,8 @@ d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
 print("config2", round(d["value"]/1e6,1), "M/s", round(d["ms_per_step"],3), "ms; e2e", round(d["e2e"]["ms_per_step"],2), d["stage_ms_per_step"], d["parity"]["sentences_mismatching"], "frac", round(d["roofline"]["frac"],4), "traffic", d["roofline"]["traffic"], "launches", d["gpu_launches"])
 for k,v in d.get("configs",{}).items():
     if "error" in v: print(k, v); continue
+    if k=="pieces":
+        print(k, round(v["value"]/1e6,1), "M/s", round(v["ms_per_step"],3), "ms", v.get("stage_ms_per_step"), (v.get("parity") or {}).get("sentences_mismatching"), "wall", v.get("wall_s")); continue
     if k=="estep":
         for n in ("final","seed"): print(k,n, round(v[n]["value"]/1e6,1),"Mwords/s", round(v[n]["ms_per_step"],3), v[n]["parity"]["ok"])
     else: print(k, round(v["value"]/1e6,1), "M/s", round(v["ms_per_step"],3), "ms; e2e", round(v["e2e"]["ms_per_step"],2), v["parity"]["sentences_mismatching"], v["general_tier_sentences_per_step"], v["viterbi_tier_sentences_per_step"], "wall", v.get("wall_s"))

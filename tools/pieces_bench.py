@@ -24,6 +24,71 @@ sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 
 
+def record(ctx, n=10_000_000, steps=3, parity_n=50_000, model="syn_uni32k", corpus="syn_en"):
+    """Compact record for bench.py's `configs.pieces`: spm_cuda_encode_batch_pieces (Encode(input,
+    SentencePieceText*), src/sentencepiece_processor.cc:488-573) device-resident on this rank's share of the
+    config-2 corpus, timed with CUDA events; parity = serialized SentencePieceText of the first parity_n
+    sentences against the unmodified reference's EncodeAsSerializedProto (rank 0)."""
+    torch = ctx.torch
+    pkg = ctx.pkg
+    mb = bench.model_bytes(model)
+    sp = pkg.SentencePieceProcessor(device=ctx.local)
+    sp.LoadFromSerializedProto(mb)
+    text, off = bench.make_corpus(corpus, n, ctx.rank * n)
+    in_bytes = int(off[-1])
+    dev = ctx.dev
+    stream = torch.cuda.current_stream(dev)
+    d_text, d_off = torch.from_numpy(text).to(dev), torch.from_numpy(off).to(dev)
+    cap = in_bytes // 3 + 64
+    arrs = [torch.empty(cap, dtype=torch.int32, device=dev) for _ in range(5)]
+    d_idoff = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    d_norm = torch.empty(2 * in_bytes + 8 * n, dtype=torch.uint8, device=dev)
+    d_normoff = torch.empty(n + 1, dtype=torch.int64, device=dev)
+
+    def step():
+        sp.encode_pieces_device(d_text, d_off, *arrs, d_idoff, d_norm, d_normoff, stream=stream.cuda_stream)
+    for _ in range(3):
+        step()
+    stage_ms, launches = {}, 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx.barrier()
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    for _ in range(steps):
+        step()
+        st = sp.last_stats()
+        launches += st["launches"]
+        for k, v in st["stage_ms"].items():
+            stage_ms[k] = stage_ms.get(k, 0.0) + v
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    ms = ctx.reduce([ev0.elapsed_time(ev1)], "MAX")[0]
+    n_ids = int(d_idoff[-1].item())
+    rec = {"metric": "batch EncodeAsPieces / SentencePieceText sentences/s", "value": ctx.world * n * steps / (ms * 1e-3),
+           "unit": "sentences/s", "ms_per_step": ms / steps, "steps": steps,
+           "workload": "%s, %d %s sentences per GPU: ids + input / normalized spans + normalized text, device-resident"
+                       % (model, n, corpus),
+           "pieces_per_gpu": n_ids, "stage_ms_per_step": {k: round(v / steps, 4) for k, v in stage_ms.items()},
+           "gpu_launches": launches}
+    if ctx.rank == 0 and parity_n > 0:
+        chk, kind = bench.ref_processor(mb)
+        if kind == "reference":
+            m = min(n, parity_n)
+            t0 = time.perf_counter()
+            want, woff = chk.encode_proto_batch(text[: off[m]], off[: m + 1], threads=bench.host_threads())
+            dt = time.perf_counter() - t0
+            got = sp.encode_as_serialized_protos(text[: off[m]], off[: m + 1])
+            bad = sum(1 for i in range(m) if got[i] != want[woff[i]: woff[i + 1]].tobytes())
+            rec["parity"] = {"sentences_compared": m, "sentences_mismatching": bad, "checker": kind,
+                             "what": "serialized SentencePieceText (pieces, ids, surfaces, begin / end)",
+                             "reference_sentences_per_s": m / dt, "reference_threads": bench.host_threads()}
+            if bad:
+                raise bench.ParityError("pieces: %d of %d serialized protos differ from the reference" % (bad, m))
+    del d_text, d_off, arrs, d_norm
+    torch.cuda.empty_cache()
+    return rec
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--op", default="pieces", choices=["pieces", "decode", "dense"])
