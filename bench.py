@@ -12,8 +12,9 @@ collective, weak scaling):
   `parity` ids of the timed call compared with the unmodified reference
            (oracle/_ref) on a prefix of the benched batch -- a mismatch is a non-zero exit;
   `configs` the same record for config 3 (BPE-32k), config 4 (CJK lines, >= 1 GB),
-           config 2 with dirty text, and the unigram E-step (with its all-reduce at N > 1),
-           measured in the same process after the headline run.
+           config 2 with dirty text, the unigram E-step (with its all-reduce at N > 1) and the
+           pieces call (EncodeAsPieces / SentencePieceText, serialized protos compared with the
+           reference's), measured in the same process after the headline run.
 `--impl reference` times the unmodified reference compiled into oracle/_ref (all host
 threads) on a bounded sample of the same workload.
 """
