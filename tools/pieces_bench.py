@@ -70,6 +70,7 @@ def record(ctx, n=10_000_000, steps=3, parity_n=50_000, model="syn_uni32k", corp
                        % (model, n, corpus),
            "pieces_per_gpu": n_ids, "stage_ms_per_step": {k: round(v / steps, 4) for k, v in stage_ms.items()},
            "gpu_launches": launches}
+    bad = 0
     if ctx.rank == 0 and parity_n > 0:
         chk, kind = bench.ref_processor(mb)
         if kind == "reference":
@@ -82,10 +83,11 @@ def record(ctx, n=10_000_000, steps=3, parity_n=50_000, model="syn_uni32k", corp
             rec["parity"] = {"sentences_compared": m, "sentences_mismatching": bad, "checker": kind,
                              "what": "serialized SentencePieceText (pieces, ids, surfaces, begin / end)",
                              "reference_sentences_per_s": m / dt, "reference_threads": bench.host_threads()}
-            if bad:
-                raise bench.ParityError("pieces: %d of %d serialized protos differ from the reference" % (bad, m))
     del d_text, d_off, arrs, d_norm
     torch.cuda.empty_cache()
+    bad_all = ctx.reduce([float(bad)], "SUM")[0]      # (every rank leaves the same way)
+    if bad_all > 0:
+        raise bench.ParityError("pieces: %d serialized protos of the compared prefix differ from the reference" % int(bad_all))
     return rec
 
 
