@@ -8,6 +8,8 @@ d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
 print("config2", d["n_gpus"], "GPUs", round(d["value"]/1e6,1), "M/s", round(d["ms_per_step"],3), "ms; e2e", round(d["e2e"]["value"]/1e6,1), "M/s", round(d["e2e"]["ms_per_step"],2), d.get("parity"))
 for k,v in d.get("configs",{}).items():
     if "error" in v: print(k, v); continue
+    if k=="pieces":
+        print(k, round(v["value"]/1e6,1), "M/s", round(v["ms_per_step"],3), "ms", (v.get("parity") or {}).get("sentences_mismatching")); continue
     if k=="estep":
         for n in ("final","seed"): print(k,n, round(v[n]["value"]/1e6,1),"Mwords/s", round(v[n]["ms_per_step"],3), "kernel", round(v[n]["kernel_ms"],3), "allreduce", round(v[n]["allreduce_ms"],3), (v[n].get("parity") or {}).get("ok"))
     else: print(k, round(v["value"]/1e6,1), "M/s", round(v["ms_per_step"],3), "ms; e2e", round(v["e2e"]["value"]/1e6,1), round(v["e2e"]["ms_per_step"],2), (v.get("parity") or {}).get("sentences_mismatching"))
