@@ -67,6 +67,7 @@ struct ModelView {
   const uint8_t *cm_pool;    // NUL-delimited replacement strings
   const uint32_t *cm_first2; // 65536-bit filter: can a rule start with (b0,b1)?
   const uint32_t *cm_cont2;  // 65536-bit filter: can a character starting (b0,b1) sit INSIDE a rule key / user symbol?
+  const uint32_t *cm_first3; // 65536-bit filter by code point U+0800..U+FFFF: does a rule key start with this 3-byte character? (may be null)
   uint32_t cm_n;             // 0: identity normalization
   uint32_t user_first[8];    // 256-bit filter on the first byte of user symbols
   int32_t model_type;

@@ -549,6 +549,7 @@ struct FastOut {
   SPM_HD bool room(int64_t more) const { return (int64_t)len + more <= cap; }   // can `more` bytes still follow?
   SPM_HD bool done() const { return false; }
   static constexpr bool kRuns = false;           // no bulk path for runs of plain bytes
+  static constexpr bool kFirst3 = true;          // consult the per-character rule filter (text sinks: CJK lines)
   SPM_HD int take(uint64_t, int) { return 0; }
   SPM_HD void at(int32_t) {}                     // (input position of the step: only AlignedOut records it)
   SPM_HD void put(uint32_t v, int k) {  // k in 1..4 bytes, little-endian in v
@@ -571,6 +572,7 @@ struct AlignedOut : FastOut {
   int32_t *n2o;
   int32_t cur;
   static constexpr bool kRuns = true;   // runs of plain bytes are taken from the window in one piece
+  static constexpr bool kFirst3 = true;
   SPM_HD void at(int32_t p) { cur = p; }
   SPM_HD void put(uint32_t v, int k) {
     for (int j = 0; j < k; ++j) n2o[len + j] = cur;
@@ -652,6 +654,12 @@ SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, con
     if (!slow && m.cm_n != 0) {
       const uint32_t key = (b0 << 8) | b1;
       slow = n - p < 2 || ((first2[key >> 5] >> (key & 31)) & 1);  // first2 may live in shared memory
+      // a 3-byte character (kana, CJK, ...): first2 passes its whole block of 64 code points; first3 knows the character
+      if (Sink::kFirst3 && slow && m.cm_first3 != nullptr && n - p >= 3 && (b0 & 0xF0u) == 0xE0u && (b1 & 0xC0u) == 0x80u &&
+          ((uint32_t)(w >> 16) & 0xC0u) == 0x80u) {
+        const uint32_t cp = ((b0 & 15u) << 12) | ((b1 & 63u) << 6) | ((uint32_t)(w >> 16) & 63u);
+        slow = (SPM_LDG(m.cm_first3 + (cp >> 5)) >> (cp & 31)) & 1;
+      }
     }
     if (!slow) {
       // one character straight from the window (src/normalizer.cc:271-291)

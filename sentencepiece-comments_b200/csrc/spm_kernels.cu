@@ -1680,7 +1680,7 @@ struct spm_cuda_model {
   int fast_kind = 0;       // 1: unigram (k_encode_fast), 2: BPE (k_encode_bpe_fast)
   int sm_count = 1;
   size_t fast_smem = 0;
-  DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2, d_cont2, d_funits, d_fscore, d_fleaf;
+  DevBuf d_units, d_leaf, d_uunits, d_uleaf, d_cm_units, d_cm_pool, d_first2, d_cont2, d_funits, d_fscore, d_fleaf, d_first3;
   // workspace of encode calls (guarded by mu)
   mutable std::mutex mu;
   mutable bool lshist_zeroed = false;
@@ -1708,13 +1708,13 @@ struct spm_cuda_model {
   int bos_id = 0, eos_id = 0, pad_id = 0;
   std::vector<DevBuf *> workspace_bufs() const {   // all_bufs() without the model tables (d_*)
     std::vector<DevBuf *> v = all_bufs();
-    v.erase(v.begin(), v.begin() + 11);
+    v.erase(v.begin(), v.begin() + 12);
     return v;
   }
   std::vector<DevBuf *> all_bufs() const {
     spm_cuda_model *m = const_cast<spm_cuda_model *>(this);
     return {&m->d_units, &m->d_leaf, &m->d_uunits, &m->d_uleaf, &m->d_cm_units, &m->d_cm_pool, &m->d_first2, &m->d_cont2,
-            &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
+            &m->d_funits, &m->d_fscore, &m->d_fleaf, &m->d_first3, &m->w_text, &m->w_off, &m->w_ids, &m->w_idoff, &m->w_norm,
             &m->w_stage, &m->w_vstage, &m->w_spos, &m->w_lshist, &m->w_nlen, &m->w_nchars, &m->w_cnt, &m->w_status, &m->w_srcoff, &m->w_perm,
             &m->w_genlist, &m->w_longlist, &m->w_midlist, &m->w_wslots, &m->w_wbase, &m->w_nwords, &m->w_vit, &m->w_vitl, &m->w_memo, &m->w_mres, &m->w_movf, &m->w_wback, &m->w_ntmp,
             &m->w_newlist, &m->w_wtext, &m->w_wlen, &m->w_hist, &m->w_counters, &m->w_back, &m->w_partial, &m->w_scalars, &m->g_need,
@@ -1791,6 +1791,7 @@ int upload_model(spm_cuda_model *M) {
   if ((rc = upload(&M->d_cm_pool, hm.cm_pool, hm.cm_pool_size))) return rc;
   if ((rc = upload(&M->d_first2, hm.cm_first2.data(), hm.cm_first2.size() * 4))) return rc;
   if ((rc = upload(&M->d_cont2, hm.cm_cont2.data(), hm.cm_cont2.size() * 4))) return rc;
+  if ((rc = upload(&M->d_first3, hm.cm_first3.data(), hm.cm_first3.size() * 4))) return rc;
   ModelView &v = M->mv;
   memset(&v, 0, sizeof(v));
   v.pieces.units = (const uint32_t *)M->d_units.p; v.pieces.leaf = (const uint2 *)M->d_leaf.p;
@@ -1800,6 +1801,7 @@ int upload_model(spm_cuda_model *M) {
   v.cm_units = (const uint32_t *)M->d_cm_units.p; v.cm_pool = (const uint8_t *)M->d_cm_pool.p;
   v.cm_first2 = hm.cm_first2.empty() ? nullptr : (const uint32_t *)M->d_first2.p;
   v.cm_cont2 = hm.cm_cont2.empty() ? nullptr : (const uint32_t *)M->d_cont2.p;
+  v.cm_first3 = hm.cm_first3.empty() ? nullptr : (const uint32_t *)M->d_first3.p;
   v.cm_n = hm.cm_n;
   memcpy(v.user_first, hm.user_first, sizeof(v.user_first));
   v.model_type = hm.model_type; v.unk_id = hm.unk_id;

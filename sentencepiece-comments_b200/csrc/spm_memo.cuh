@@ -199,6 +199,7 @@ struct MemoSink {
   bool fail;                // a word cannot be keyed (too long, table full, too many words)
   int32_t pending;          // bare U+2581 words not yet written to slots[]
   static constexpr bool kRuns = true;
+  static constexpr bool kFirst3 = false;   // (the word memo's scan sees mostly ASCII: the extra test only costs it, 9.2 -> 9.7 ms on noisy text)
   SPM_HD void init(const MemoTable &t, uint32_t *s, int32_t c) {
     tb = t; slots = s; cap = c; nw = 0; c0 = 0; c1 = 0; len = 0; prefix = 0;
     tail = false; started = false; fail = false; pending = 0;

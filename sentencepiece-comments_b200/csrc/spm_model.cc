@@ -240,6 +240,7 @@ bool is_trie_type(uint32_t t) { return t == T_NORMAL || t == T_USER_DEFINED || t
 // charsmap statistics: first-two-bytes filter and worst-case expansion.
 void scan_charsmap(HostModel *m) {
   m->cm_first2.assign(65536 / 32, 0);
+  m->cm_first3.assign(65536 / 32, 0);
   m->cm_cont2.assign(65536 / 32, 0);
   // user-defined symbols are matched before the charsmap (src/normalizer.cc:240-249)
   for (size_t i = 0; i < m->piece.size(); ++i) {
@@ -252,7 +253,7 @@ void scan_charsmap(HostModel *m) {
     }
   }
   m->expansion = 3;  // ' ' -> U+2581 and a malformed byte -> U+FFFD are both 1 -> 3
-  if (m->cm_n == 0) { m->cm_first2.clear(); return; }   // (cm_cont2 keeps the user-symbol marks)
+  if (m->cm_n == 0) { m->cm_first2.clear(); m->cm_first3.clear(); return; }   // (cm_cont2 keeps the user-symbol marks)
   const uint32_t *a = m->cm_units;
   const uint32_t n = m->cm_n;
   // cm_cont2: first two bytes of every character that sits at a NON-initial position of some
@@ -280,6 +281,18 @@ void scan_charsmap(HostModel *m) {
         else if (it.lead >= 0) mark_cont((uint32_t)it.lead, c);
       }
       if (depth == 2) m->cm_first2[((b0 << 8) | b1) >> 5] |= 1u << (((b0 << 8) | b1) & 31);
+      // cm_first3: the first2 filter passes a whole block of 64 code points when one of them starts a rule (kana,
+      // CJK: nearly every block); keyed by the code point itself it passes the one character.  (b0, b1, b2) ->
+      // (b0 & 15) << 12 | (b1 & 63) << 6 | (b2 & 63); a key that ends inside its first character marks the block.
+      if ((b0 & 0xF0u) == 0xE0u) {
+        auto mark3 = [&](uint32_t x1, uint32_t x2) {
+          const uint32_t cp = ((b0 & 15u) << 12) | ((x1 & 63u) << 6) | (x2 & 63u);
+          m->cm_first3[cp >> 5] |= 1u << (cp & 31);
+        };
+        if (depth == 3) mark3(it.b1, c);
+        if (((u >> 8) & 1) && depth == 2) for (uint32_t x = 0; x < 64; ++x) mark3(b1, x);
+        if (((u >> 8) & 1) && depth == 1) for (uint32_t x = 0; x < 4096; ++x) mark3(x >> 6, x & 63);
+      }
       if ((u >> 8) & 1) {
         if (depth == 1)
           for (uint32_t x = 0; x < 256; ++x) m->cm_first2[((b0 << 8) | x) >> 5] |= 1u << (((b0 << 8) | x) & 31);

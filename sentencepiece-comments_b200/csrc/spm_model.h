@@ -62,6 +62,7 @@ struct HostModel {
   bool bpe_fast_ok = false;       // BPE model whose merges never cross a word boundary (fast_bpe)
   bool ascii_plain = false;       // see build_host_model
   bool ws_ctl = false;            // see build_host_model
+  std::vector<uint32_t> cm_first3;   // 65536-bit filter: does a rule key start with this 3-byte character (U+0800..U+FFFF)?
   bool memo_ok = false;           // no lattice node / merge crosses a U+2581: words can be memoised (spm_memo.cuh)
   bool neg_only = false;          // every node score of the fast view (and the UNK score) is <= 0
   // ---- piece strings by id (pieces path)

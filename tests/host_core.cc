@@ -35,6 +35,7 @@ void make_view(Handle *h) {
   v.cm_units = m.cm_units; v.cm_pool = m.cm_pool; v.cm_n = m.cm_n;
   v.cm_first2 = m.cm_first2.empty() ? nullptr : m.cm_first2.data();
   v.cm_cont2 = m.cm_cont2.empty() ? nullptr : m.cm_cont2.data();
+  v.cm_first3 = m.cm_first3.empty() ? nullptr : m.cm_first3.data();
   memcpy(v.user_first, m.user_first, sizeof(v.user_first));
   v.model_type = m.model_type; v.unk_id = m.unk_id;
   v.unk_score = m.min_score - 10.0f; v.max_score = m.max_score; v.smax = m.smax; v.ring = m.ring;
