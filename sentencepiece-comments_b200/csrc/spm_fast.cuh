@@ -548,9 +548,22 @@ struct FastOut {
   int32_t cap;       // capacity of the slot
   SPM_HD bool room(int64_t more) const { return (int64_t)len + more <= cap; }   // can `more` bytes still follow?
   SPM_HD bool done() const { return false; }
-  static constexpr bool kRuns = false;           // no bulk path for runs of plain bytes
+  static constexpr bool kRuns = true;            // runs of plain bytes are taken from the window in one piece
   static constexpr bool kFirst3 = true;          // consult the per-character rule filter (text sinks: CJK lines)
-  SPM_HD int take(uint64_t, int) { return 0; }
+  // `run` (1..8) printable-ASCII bytes from the low end of w, appended as they are (until run v77 this sink took
+  // them one by one through the general step: ~40 instructions per byte on a lone thread, 0.17 ms for the 6 k
+  // sentences the word memo leaves over per 10 M)
+  SPM_HD int take(uint64_t w, int run) {
+    const int f = len & 7;
+    const uint64_t v = run == 8 ? w : (w & ((1ull << (8 * run)) - 1));
+    acc |= v << (8 * f);
+    if (f + run >= 8) {
+      *reinterpret_cast<uint64_t *>(base + (len & ~7)) = acc;
+      acc = f ? v >> (8 * (8 - f)) : 0;
+    }
+    len += run;
+    return run;
+  }
   SPM_HD void at(int32_t) {}                     // (input position of the step: only AlignedOut records it)
   SPM_HD void put(uint32_t v, int k) {  // k in 1..4 bytes, little-endian in v
     const int f = len & 7;
@@ -582,15 +595,7 @@ struct AlignedOut : FastOut {
   // its own (one byte in, the same byte out), so byte j maps to input offset cur + j.
   SPM_HD int take(uint64_t w, int run) {
     for (int j = 0; j < run; ++j) n2o[len + j] = cur + j;
-    const int f = len & 7;
-    const uint64_t v = run == 8 ? w : (w & ((1ull << (8 * run)) - 1));
-    acc |= v << (8 * f);
-    if (f + run >= 8) {
-      *reinterpret_cast<uint64_t *>(base + (len & ~7)) = acc;
-      acc = f ? v >> (8 * (8 - f)) : 0;
-    }
-    len += run;
-    return run;
+    return FastOut::take(w, run);
   }
 };
 
@@ -625,7 +630,7 @@ SPM_HDN bool fast_normalize_scan(const ModelView &m, const uint32_t *first2, con
   int64_t p = 0;
   while (p < n) {
     uint64_t w = fast_window(a0, a1, r);
-    if (Sink::kRuns && m.ascii_plain && started) {
+    if (Sink::kRuns && m.ascii_plain && started && !(w & 0x80u)) {   // (a non-ASCII byte first: no run to look for)
       // A run of printable ASCII (0x21..0x7E) inside a word: no rule, user symbol or whitespace
       // handling applies to a byte whose successor is ASCII as well (HostModel::ascii_plain),
       // so the run goes to the sink in one piece.  SWAR: 0x80 marks bytes < 0x21 or > 0x7E
