@@ -485,6 +485,51 @@ int hc_encode_pieces_batch(void *p, const uint8_t *text, const int64_t *off, int
   return 0;
 }
 
+// Loader verdicts of a model: bit 0 ascii_plain, bit 1 ws_ctl, bit 2 memo_ok, bit 3 remove_extra_ws,
+// bit 4 a rule filter for 3-byte characters exists.
+int hc_model_flags(void *p) {
+  Handle *h = (Handle *)p;
+  return (h->hm.ascii_plain ? 1 : 0) | (h->hm.ws_ctl ? 2 : 0) | (h->hm.memo_ok ? 4 : 0) |
+         (h->hm.remove_extra_ws ? 8 : 0) | (h->hm.cm_first3.empty() ? 0 : 16);
+}
+
+// cm_first3 must not hide a rule: for every 3-byte character U+0800..U+FFFF (surrogates left out) whose bit
+// is clear, NormalizePrefix -- whatever follows the character -- returns the character itself.  Also what the
+// loader claims with ws_ctl: TAB, LF, FF, CR -> one space.  Returns the number of violations.
+int64_t hc_check_filters(void *p) {
+  Handle *h = (Handle *)p;
+  const ModelView &mv = h->mv;
+  int64_t bad = 0;
+  if (mv.cm_first3 != nullptr) {
+    const uint8_t follow[5] = {0x00, 0x20, 0x61, 0xCC, 0xE3};   // end / space / letter / a combining mark's lead / another CJK lead
+    for (uint32_t cp = 0x800; cp < 0x10000; ++cp) {
+      if (cp >= 0xD800 && cp < 0xE000) continue;
+      if ((mv.cm_first3[cp >> 5] >> (cp & 31)) & 1) continue;
+      for (int f = 0; f < 5; ++f) {
+        uint8_t in[8] = {(uint8_t)(0xE0 | (cp >> 12)), (uint8_t)(0x80 | ((cp >> 6) & 63)), (uint8_t)(0x80 | (cp & 63)),
+                         follow[f], 0x81, 0x82, 0, 0};
+        const int n = f == 0 ? 3 : 6;
+        const uint8_t *rep = nullptr;
+        int rl = 0;
+        const int c = normalize_prefix(mv, in, n, &rep, &rl);
+        if (!(c == 3 && rl == 3 && rep != nullptr && rep[0] == in[0] && rep[1] == in[1] && rep[2] == in[2])) ++bad;
+      }
+    }
+  }
+  if (h->hm.ws_ctl) {
+    const uint8_t ctl[4] = {0x09, 0x0A, 0x0C, 0x0D};
+    for (int k = 0; k < 4; ++k)
+      for (int x = 0; x < 256; ++x) {
+        uint8_t in[4] = {ctl[k], (uint8_t)x, 0, 0};
+        const uint8_t *rep = nullptr;
+        int rl = 0;
+        const int c = normalize_prefix(mv, in, 2, &rep, &rl);
+        if (!(c == 1 && rl == 1 && rep != nullptr && rep[0] == ' ')) ++bad;
+      }
+  }
+  return bad;
+}
+
 // estep_softplus() against libm on m points of [-50, 0]: the largest absolute difference.
 double hc_lse_table_error(int64_t m) {
   std::vector<double> lse;

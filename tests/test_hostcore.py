@@ -253,6 +253,24 @@ def test_word_scan_matches_sentence_scan(hostcore, corpora):
     assert plain[0][3] == 0 and plain[2][3] >= 3900, plain      # botchan: CR at every line end
 
 
+@pytest.mark.parametrize("model,want", [("syn_uni32k", 0b11111), ("botchan_uni8k", 0b11111), ("botchan_bpe4k", 0b11111),
+                                        ("ref_ja_8k", None), ("wagahai_uni", None), ("ref_en_1k", None)])
+def test_loader_filters(hostcore, make_hostcore, model, want):
+    """What the loader derives from the charsmap for the byte-parallel paths: printable ASCII passes untouched
+    (ascii_plain), TAB / LF / FF / CR normalize to one space (ws_ctl, nmt_nfkc models), and the per-character rule
+    filter for 3-byte characters (cm_first3) never hides a rule -- every character it clears comes back from
+    NormalizePrefix as itself, whatever follows it."""
+    hc = make_hostcore(model_bytes(model))
+    hostcore.hc_model_flags.argtypes = [ctypes.c_void_p]
+    hostcore.hc_check_filters.argtypes = [ctypes.c_void_p]
+    hostcore.hc_check_filters.restype = ctypes.c_int64
+    flags = hostcore.hc_model_flags(hc.h)
+    if want is not None:
+        assert flags == want, bin(flags)
+    assert hostcore.hc_check_filters(hc.h) == 0
+    print(model, "flags", bin(flags))
+
+
 def test_loader_rejects_bad_models(hostcore):
     import ctypes
     for blob in (b"", b"garbage\xff\xff", b"\x0a\x03abc"):
